@@ -1,0 +1,104 @@
+"""Generate `tests/golden/*.npz` by running the reference's own code (see `ref_harness.py`).
+
+    python tests/golden/make_golden.py            # all cases
+    python tests/golden/make_golden.py c1_full    # selected cases
+
+Runs only in the authoring container (needs `/root/reference`).  Also writes
+`logged_detections.json`: the two detections the reference logged in `err.txt:5`, a known-answer
+vector for `get_cuboid_verts_faces` (corners = R . local + centre).
+"""
+from __future__ import annotations
+
+import json
+import os
+import re
+import sys
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+
+from tests.golden import cases as gc  # noqa: E402
+from tests.golden import ref_harness as rh  # noqa: E402
+
+
+def run_case(case: gc.Case) -> dict:
+    inp, weights, priors = gc.build_case(case)
+    cfg = gc.make_cfg(case)
+    head = rh.build_reference_head(cfg, case.in_features, list(case.strides), case.channels)
+    missing = head.cube_head.load_state_dict(weights, strict=True)
+    assert not missing.missing_keys and not missing.unexpected_keys
+    if priors is not None:
+        dims, z_scales, z_stats = priors
+        head.priors_dims_per_cat.data = dims.clone()
+        head.priors_z_scales.data = z_scales.clone()
+        if hasattr(head, "priors_z_stats"):
+            head.priors_z_stats.data = z_stats.clone()
+
+    captured = {}
+    head.cube_pooler.register_forward_hook(lambda m, a, o: captured.__setitem__("pooled", o.detach().clone()))
+    head.cube_head.register_forward_hook(lambda m, a, o: captured.__setitem__("head", o))
+    out = rh.run_reference_forward_cube(head, inp, with_scores=case.with_scores)
+
+    n_total = sum(len(b) for b in inp.boxes)
+    rec = {"checksum": gc.input_checksum(inp, weights), "n": np.int64(n_total)}
+    pooled = captured["pooled"]
+    rec["pooled_shape"] = np.array(pooled.shape, dtype=np.int64)
+    rec["pooled"] = pooled.flatten()[:: case.pooled_stride].numpy()
+    if n_total:
+        # level assignment: re-derive from the pooler the reference built (d2 semantics, thirdparty.py)
+        scaled = head.scale_proposals([rh_boxes(b) for b in inp.boxes])
+        if len(case.strides) > 1:
+            rec["levels"] = head.cube_pooler.impl.levels([b.tensor for b in scaled]).numpy()
+        else:
+            rec["levels"] = np.zeros(n_total, dtype=np.int64)
+        deltas, z, dims, pose, uncert = captured["head"]
+        rec["raw_deltas"] = deltas.detach().numpy()
+        rec["raw_z"] = z.detach().numpy()
+        rec["raw_dims"] = dims.detach().numpy()
+        rec["raw_pose"] = pose.detach().numpy()
+        if uncert is not None:
+            rec["raw_uncert"] = uncert.detach().numpy()
+        for i, inst in enumerate(out):
+            if len(inp.boxes[i]) == 0 and not inst.has("pred_bbox3D"):
+                continue
+            for f in ("scores", "pred_bbox3D", "pred_center_cam", "pred_center_2D", "pred_dimensions", "pred_pose"):
+                rec["im%d_%s" % (i, f)] = inst.get(f).detach().numpy()
+    return rec
+
+
+def rh_boxes(t: torch.Tensor):
+    from ovmono3d_b200.compat import Boxes
+    return Boxes(t.clone())
+
+
+def logged_detections() -> None:
+    """err.txt:5 -> tests/golden/logged_detections.json (numbers only)."""
+    with open(os.path.join(rh.REFERENCE_ROOT, "err.txt")) as f:
+        line = [ln for ln in f if "Sample instances" in ln][0]
+    dets = []
+    for m in re.finditer(r"\{'image_id'.*?'depth': [-0-9.e]+\}", line):
+        d = eval(m.group(0), {"__builtins__": {}})  # plain literal dict printed by the reference
+        dets.append({k: d[k] for k in ("bbox3D", "center_cam", "dimensions", "pose", "depth")})
+    assert dets, "no complete detection found in err.txt:5"
+    with open(os.path.join(HERE, "logged_detections.json"), "w") as f:
+        json.dump({"source": "reference err.txt line 5 (Sample instances)", "detections": dets}, f, indent=1)
+    print("logged_detections.json:", len(dets), "detections")
+
+
+def main() -> None:
+    names = sys.argv[1:] or [c.name for c in gc.CASES]
+    torch.set_num_threads(max(1, os.cpu_count() or 1))
+    for name in names:
+        case = gc.CASE_BY_NAME[name]
+        rec = run_case(case)
+        np.savez_compressed(gc.golden_path(case), **rec)
+        print("%-32s n=%-4d %6.1f KB" % (name, int(rec["n"]), os.path.getsize(gc.golden_path(case)) / 1024))
+    if not sys.argv[1:]:
+        logged_detections()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,60 @@
+"""Shared test helpers: run the oracle on a golden case, tolerance metrics."""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from oracle import lift_oracle as lo
+from tests.golden import cases as gc
+
+
+def lift_config(case: gc.Case) -> lo.LiftConfig:
+    cube = case.cube
+    return lo.LiftConfig(
+        scales=tuple(1.0 / s for s in case.strides),
+        pooler_resolution=7,
+        sampling_ratio=cube.get("POOLER_SAMPLING_RATIO", 0),
+        num_classes=case.num_classes,
+        z_type=cube.get("Z_TYPE", "direct"),
+        pose_type=cube.get("POSE_TYPE", "6d"),
+        cluster_bins=cube.get("CLUSTER_BINS", 1),
+        shared_fc=cube.get("SHARED_FC", True),
+        dims_priors_enabled=cube.get("DIMS_PRIORS_ENABLED", True),
+        dims_priors_func=cube.get("DIMS_PRIORS_FUNC", "exp"),
+        use_confidence=cube.get("USE_CONFIDENCE", 1.0),
+        virtual_depth=cube.get("VIRTUAL_DEPTH", True),
+        virtual_focal=cube.get("VIRTUAL_FOCAL", 512.0),
+        allocentric_pose=cube.get("ALLOCENTRIC_POSE", True),
+        scale_roi_boxes=cube.get("SCALE_ROI_BOXES", 0.0),
+    )
+
+
+def run_oracle(case: gc.Case):
+    inp, weights, priors = gc.build_case(case)
+    cfg = lift_config(case)
+    kw = {}
+    if priors is not None:
+        kw = dict(priors_dims_per_cat=priors[0], priors_z_scales=priors[1], priors_z_stats=priors[2])
+    with torch.no_grad():
+        out = lo.forward_cube(inp.features, inp.boxes, inp.classes, inp.scores if case.with_scores else None,
+                              inp.Ks, inp.im_dims, inp.im_scales_ratio, weights, cfg, **kw)
+    return inp, weights, priors, cfg, out
+
+
+def rel_err(a, b, floor: float = 1e-6) -> float:
+    """max |a-b| / (|b| + floor*max|b|): element-wise relative error with a scale-aware floor."""
+    a = np.asarray(a, dtype=np.float64)
+    b = np.asarray(b, dtype=np.float64)
+    if b.size == 0:
+        return 0.0
+    scale = max(float(np.abs(b).max()), 1e-30)
+    return float((np.abs(a - b) / (np.abs(b) + floor * scale)).max())
+
+
+def norm_err(a, b) -> float:
+    """max |a-b| / max |b|."""
+    a = np.asarray(a, dtype=np.float64)
+    b = np.asarray(b, dtype=np.float64)
+    if b.size == 0:
+        return 0.0
+    return float(np.abs(a - b).max() / max(float(np.abs(b).max()), 1e-30))
