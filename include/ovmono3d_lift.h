@@ -1,0 +1,169 @@
+/* ovmono3d_lift.h -- C ABI of the B200-native 2D->3D lift (libovmono3d_lift.so).
+ *
+ * Every entry point takes raw device pointers, sizes and a cudaStream_t (passed as void*),
+ * returns 0 on success or a negative OVM_E* code (text through ovm_last_error()), never throws,
+ * never allocates or frees device memory, and never synchronises the stream.  The caller
+ * (ovmono3d_b200/ops.py through ctypes) owns every buffer.
+ *
+ * What each call replaces in the reference (paths relative to the reference checkout):
+ *   ovm_roi_align    detectron2 ROIPooler.forward + assign_boxes_to_levels + torchvision roi_align,
+ *                    constructed at cubercnn/modeling/roi_heads/roi_heads.py:166-171, called at :366;
+ *                    optional zoom = ROIHeads3D.scale_proposals, roi_heads.py:310-327.
+ *   ovm_gemm_bf16    one nn.Linear(+ReLU) of CubeHead's FC stack, cube_head.py:64-74,157
+ *                    (cuBLAS SGEMM in the reference; tcgen05 bf16 x bf16 -> fp32 here).
+ *   ovm_bias_act     the bias + ReLU that follows a split-K ovm_gemm_bf16 (same lines).
+ *   ovm_head_decode  the five linear heads, cube_head.py:158-164,176-204, the class/bin selection
+ *                    roi_heads.py:433-477 and the whole decode roi_heads.py:378-419,480-549,795-843
+ *                    with math_util.py:116-219,581-592,651-679,969-978.
+ *   ovm_lift_forward the inference slice of ROIHeads3D._forward_cube, roi_heads.py:329-848:
+ *                    the three kernels above on one stream.
+ */
+#ifndef OVMONO3D_LIFT_H_
+#define OVMONO3D_LIFT_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define OVM_ABI_VERSION 1
+#define OVM_MAX_LEVELS 8
+#define OVM_RECORD_WIDTH 48   /* floats per detection record, see ovm_head_decode */
+
+enum {
+  OVM_OK = 0,
+  OVM_EINVAL = -1,      /* bad argument (shape, alignment, enum value) */
+  OVM_ECUDA = -2,       /* a CUDA runtime / driver call failed */
+  OVM_EUNSUPPORTED = -3 /* valid in the reference, not implemented here (message says what) */
+};
+
+enum { OVM_LAYOUT_NCHW = 0, OVM_LAYOUT_NHWC = 1 };
+enum { OVM_F32 = 0, OVM_BF16 = 1 };
+enum { OVM_Z_DIRECT = 0, OVM_Z_SIGMOID = 1, OVM_Z_LOG = 2, OVM_Z_CLUSTERS = 3 };
+enum { OVM_POSE_6D = 0, OVM_POSE_QUATERNION = 1, OVM_POSE_EULER = 2 };
+enum { OVM_DIMS_EXP = 0, OVM_DIMS_SIGMOID = 1 };
+enum { OVM_GEMM_AUTO = 0, OVM_GEMM_DIRECT = 1, OVM_GEMM_STREAMK = 2 };
+
+/* One pyramid level: fp32 feature map of N images, C channels, contiguous in `layout`. */
+typedef struct {
+  const float* data;      /* device */
+  int32_t height, width;
+  double spatial_scale;   /* 1 / stride, as d2 ROIPooler receives it (roi_heads.py:161) */
+  int32_t layout;         /* OVM_LAYOUT_* */
+  int32_t _pad;
+} ovm_level_t;
+
+typedef struct {
+  int32_t num_levels;
+  ovm_level_t levels[OVM_MAX_LEVELS];
+  int32_t num_images, channels;
+  int32_t pooler_resolution;     /* MODEL.ROI_CUBE_HEAD.POOLER_RESOLUTION (7) */
+  int32_t sampling_ratio;        /* POOLER_SAMPLING_RATIO (0 = adaptive) */
+  int32_t canonical_box_size;    /* d2 default 224 */
+  int32_t canonical_level;       /* d2 default 4 */
+  float scale_roi_boxes;         /* SCALE_ROI_BOXES; <= 0 disables (roi_heads.py:310-327) */
+  int32_t _pad;
+} ovm_pooler_t;
+
+/* Multi-level ROIAlignV2.  boxes [n,4] xyxy fp32, batch_idx [n] int32 (image of each box), both
+ * device.  out: [n, out_ld] of out_dtype, row = box, columns (c, ph, pw)-major exactly like
+ * `cube_pooler(...).flatten(1)` (roi_heads.py:366); out_ld >= C*P*P, columns past C*P*P untouched.
+ * level_out (optional, device [n] int32): 0-based level per box, -1 where the reference's float->int
+ * conversion of a NaN size is undefined (such boxes pool to zeros in both).                       */
+int ovm_roi_align(const ovm_pooler_t* pooler, const float* boxes, const int32_t* batch_idx, int32_t n,
+                  void* out, int32_t out_dtype, int64_t out_ld, int32_t* level_out, void* stream);
+
+/* D[M,N] = act(A[M,K] . B[N,K]^T + bias), A and B bf16 row-major with leading dimensions lda, ldb
+ * (elements, multiples of 8; base pointers 16-byte aligned), fp32 accumulation in TMEM.
+ * mode DIRECT: one CTA per 128 x BN tile, epilogue applies bias (may be NULL) and ReLU (relu != 0)
+ *   and stores out_dtype.
+ * mode STREAMK: K is cut so that every SM gets the same number of 64-wide K blocks; partial tiles
+ *   are added into `out` (fp32, MUST be zeroed by the caller, out_dtype must be OVM_F32) with
+ *   red.global.add; bias/relu are NOT applied -- follow with ovm_bias_act.
+ * mode AUTO picks STREAMK when the tile count cannot fill the SMs and K is long.  The chosen mode
+ * is returned through mode_used (optional).                                                     */
+int ovm_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t ldb, int32_t M, int32_t N, int32_t K,
+                  const float* bias, int32_t relu, void* out, int32_t out_dtype, int64_t ldo,
+                  int32_t mode, int32_t* mode_used, void* stream);
+
+/* out[m, j] = act(in[m, j] + bias[j]) for j < N; in fp32 [M, ldi], out out_dtype [M, ldo]. */
+int ovm_bias_act(const float* in, int64_t ldi, const float* bias, int32_t relu, int32_t M, int32_t N,
+                 void* out, int32_t out_dtype, int64_t ldo, void* stream);
+
+/* x (fp32 [rows, ld_in]) -> bf16 [rows, ld_out], columns >= cols zero-filled up to ld_out. */
+int ovm_cast_bf16(const float* in, int64_t ld_in, int32_t rows, int32_t cols, void* out, int64_t ld_out,
+                  void* stream);
+
+typedef struct {
+  int32_t z_type, pose_type, dims_priors_func;  /* OVM_Z_*, OVM_POSE_*, OVM_DIMS_* */
+  int32_t cluster_bins, num_classes;
+  int32_t dims_priors_enabled, use_confidence, virtual_depth, allocentric_pose;
+  float virtual_focal;
+  int32_t fc_dim;          /* width of one FC feature vector (MODEL.ROI_CUBE_HEAD.FC_DIM) */
+  int32_t feat_offset[5];  /* column of `feats` where the features feeding deltas, dims, pose, z,
+                              uncertainty start: all 0 with SHARED_FC, g*fc_dim otherwise */
+} ovm_decode_cfg_t;
+
+typedef struct {
+  /* Linear heads, fp32, reference layout [out, fc_dim] (cube_head.py:109-143); uncertainty may be
+   * NULL when use_confidence == 0. */
+  const float *w_deltas, *b_deltas, *w_dims, *b_dims, *w_pose, *b_pose, *w_z, *b_z, *w_uncert, *b_uncert;
+  const float* priors_dims_per_cat; /* [num_classes, 2, 3] (roi_heads.py:117-120) or NULL */
+  const float* priors_z_scales;     /* [num_classes, cluster_bins] (roi_heads.py:123-130) or NULL */
+  const float* priors_z_stats;      /* [num_classes, cluster_bins, 2] (roi_heads.py:133-143) or NULL */
+} ovm_head_weights_t;
+
+/* Heads + decode, one warp per box.
+ * feats [n, ld_feats] fp32: output of the last FC layer(s).  boxes [n,4] (unscaled 2-D boxes),
+ * classes [n] int64, scores [n] fp32 or NULL, batch_idx [n] int32.
+ * cams [num_images, 12] fp32: K row-major (9), im_scales_ratio, H of the padded network input, 0
+ * (roi_heads.py:378-400).
+ * records [n, 48] fp32: bbox3D 8x3 (0..23) | center_cam (24..26) | center_2D (27..28) |
+ *   dimensions W,H,L (29..31) | pose 3x3 (32..40) | 2-D box (41..44) | score (45) | class (46) | 0.
+ * raw (optional) [n,16] fp32: the selected head outputs before decode: deltas(2) z(1) dims(3)
+ *   uncertainty(1) pose(<=9, row-major rotation is NOT here; these are the raw 6/4/3 numbers).  */
+int ovm_head_decode(const ovm_decode_cfg_t* cfg, const ovm_head_weights_t* w, const float* feats,
+                    int64_t ld_feats, const float* boxes, const int64_t* classes, const float* scores,
+                    const int32_t* batch_idx, const float* cams, int32_t num_images, int32_t n,
+                    float* records, float* raw, void* stream);
+
+/* One FC layer of the stack as the lift runs it. */
+typedef struct {
+  const void* weight;   /* bf16 [N, ldw], K-major (nn.Linear layout), device */
+  const float* bias;    /* fp32 [N] */
+  int32_t N, K;
+  int64_t ldw;
+} ovm_fc_layer_t;
+
+typedef struct {
+  int32_t num_groups;          /* 1 with SHARED_FC, 5 (dims, XY, pose, Z, conf) or 4 otherwise */
+  int32_t num_fc;              /* layers per group (MODEL.ROI_CUBE_HEAD.NUM_FC) */
+  const ovm_fc_layer_t* layers; /* host array [num_groups * num_fc], group-major */
+} ovm_fc_stack_t;
+
+typedef struct {
+  void* pooled;        /* bf16 [n, ld_pooled], ld_pooled = roundup(C*P*P, 8) */
+  int64_t ld_pooled;
+  float* acc;          /* fp32 [n, fc_dim] split-K accumulator */
+  void* act_a;         /* bf16 [n, fc_dim] ping */
+  void* act_b;         /* bf16 [n, fc_dim] pong */
+  float* feats;        /* fp32 [n, num_groups * fc_dim] */
+  int32_t* levels;     /* int32 [n] */
+} ovm_workspace_t;
+
+/* ROIAlign (bf16 out) -> FC stack -> heads + decode on `stream`. */
+int ovm_lift_forward(const ovm_pooler_t* pooler, const ovm_fc_stack_t* fc, const ovm_decode_cfg_t* cfg,
+                     const ovm_head_weights_t* heads, const float* boxes, const int64_t* classes,
+                     const float* scores, const int32_t* batch_idx, const float* cams, int32_t n,
+                     const ovm_workspace_t* ws, float* records, float* raw, void* stream);
+
+int ovm_abi_version(void);
+const char* ovm_last_error(void);
+/* Number of kernel launches (incl. memsets) the library has issued in this process. */
+int64_t ovm_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OVMONO3D_LIFT_H_ */

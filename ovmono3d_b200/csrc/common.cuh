@@ -1,0 +1,66 @@
+// Shared helpers for the lift kernels (sm_100a only).
+#pragma once
+
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <atomic>
+#include <cstdio>
+
+#include "../../include/ovmono3d_lift.h"
+
+namespace ovm {
+
+void set_error(const char* fmt, ...);
+extern std::atomic<int64_t> g_launches;
+
+inline int check_cuda(cudaError_t e, const char* what) {
+  if (e == cudaSuccess) return OVM_OK;
+  set_error("%s: %s", what, cudaGetErrorString(e));
+  return OVM_ECUDA;
+}
+
+#define OVM_CUDA(call)                                         \
+  do {                                                         \
+    int _rc = ::ovm::check_cuda((call), #call);                \
+    if (_rc != OVM_OK) return _rc;                             \
+  } while (0)
+
+#define OVM_LAUNCHED(name)                                     \
+  do {                                                         \
+    ::ovm::g_launches.fetch_add(1, std::memory_order_relaxed); \
+    int _rc = ::ovm::check_cuda(cudaGetLastError(), name);     \
+    if (_rc != OVM_OK) return _rc;                             \
+  } while (0)
+
+#define OVM_REQUIRE(cond, ...)       \
+  do {                               \
+    if (!(cond)) {                   \
+      ::ovm::set_error(__VA_ARGS__); \
+      return OVM_EINVAL;             \
+    }                                \
+  } while (0)
+
+constexpr int kNumSMs = 148;  // B200
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+
+// Entry points implemented per translation unit (host side, called from lift_api.cu).
+int roi_align_launch(const ovm_pooler_t* pooler, const float* boxes, const int32_t* batch_idx, int32_t n,
+                     void* out, int32_t out_dtype, int64_t out_ld, int32_t* level_out, cudaStream_t stream);
+int gemm_bf16_launch(const void* A, int64_t lda, const void* B, int64_t ldb, int32_t M, int32_t N, int32_t K,
+                     const float* bias, int32_t relu, void* out, int32_t out_dtype, int64_t ldo, int32_t mode,
+                     int32_t* mode_used, cudaStream_t stream);
+int bias_act_launch(const float* in, int64_t ldi, const float* bias, int32_t relu, int32_t M, int32_t N,
+                    void* out, int32_t out_dtype, int64_t ldo, cudaStream_t stream);
+int cast_bf16_launch(const float* in, int64_t ld_in, int32_t rows, int32_t cols, void* out, int64_t ld_out,
+                     cudaStream_t stream);
+int head_decode_launch(const ovm_decode_cfg_t* cfg, const ovm_head_weights_t* w, const float* feats,
+                       int64_t ld_feats, const float* boxes, const int64_t* classes, const float* scores,
+                       const int32_t* batch_idx, const float* cams, int32_t num_images, int32_t n,
+                       float* records, float* raw, cudaStream_t stream);
+
+}  // namespace ovm
