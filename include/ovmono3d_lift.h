@@ -159,6 +159,10 @@ int ovm_lift_forward(const ovm_pooler_t* pooler, const ovm_fc_stack_t* fc, const
                      const ovm_workspace_t* ws, float* records, float* raw, void* stream);
 
 int ovm_abi_version(void);
+/* sizeof() of the ABI structs as this library was compiled, for binding self-checks:
+ * 0 ovm_level_t, 1 ovm_pooler_t, 2 ovm_decode_cfg_t, 3 ovm_head_weights_t, 4 ovm_fc_layer_t,
+ * 5 ovm_fc_stack_t, 6 ovm_workspace_t; -1 for any other index. */
+int ovm_struct_size(int which);
 const char* ovm_last_error(void);
 /* Number of kernel launches (incl. memsets) the library has issued in this process. */
 int64_t ovm_launch_count(void);

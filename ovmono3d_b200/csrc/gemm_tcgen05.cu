@@ -31,7 +31,6 @@ constexpr int BM = 128;
 constexpr int BK = 64;            // 64 bf16 = 128 bytes = one swizzle row
 constexpr int UMMA_K = 16;
 constexpr int kGemmThreads = 192;
-constexpr int kEpiWarp0 = 2;      // warps 2..5 are the epilogue
 
 template <int BN>
 struct GemmShape {

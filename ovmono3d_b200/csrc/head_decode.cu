@@ -1,0 +1,361 @@
+// Kernel 3: the five linear heads of CubeHead and the whole cube decode, one warp per box.
+//
+// Replaces (reference paths relative to the checkout):
+//   * the 5 nn.Linear heads + uncertainty clip      cubercnn/modeling/roi_heads/cube_head.py:158-164 (shared FC)
+//                                                    and :167-173 (one FC stack per head)
+//   * pose -> rotation matrix                        cube_head.py:176-186 with pytorch3d rotation_6d_to_matrix /
+//                                                    quaternion_to_matrix / euler_angles_to_matrix("XYZ")
+//   * per-box camera / scale prep                    roi_heads.py:378-408, math_util.py:581-592
+//   * class / depth-bin selection                    roi_heads.py:433-477
+//   * xy, dims, allocentric->egocentric, z           roi_heads.py:414-419,480-549, math_util.py:651-679,969-978
+//   * back-projection, confidence, score merge       roi_heads.py:798-829
+//   * the 8 corners                                  math_util.py:116-193 (get_cuboid_verts_faces)
+//
+// Only the rows of the head matrices that the reference's advanced indexing keeps ([fg, box_classes] and the
+// nearest depth bin) are evaluated: at most 2+3+6+1+1 = 13 dot products of length FC_DIM per box whatever
+// NUM_CLASSES is.  The warp splits each dot product across lanes (float4 loads, coalesced over the feature row),
+// reduces with shuffles, and every lane then runs the ~300 scalar FLOP of the decode redundantly in registers;
+// lane 0 writes the 48-float detection record with 128-bit stores.  No fast-math: acosf/sinf/cosf/expf are the
+// accurate versions, and NaNs propagate exactly where the reference lets them.
+#include <cmath>
+
+#include "common.cuh"
+
+namespace ovm {
+
+namespace {
+
+constexpr int kWarpsPerBlock = 8;
+
+struct DecodeArgs {
+  ovm_decode_cfg_t cfg;
+  ovm_head_weights_t w;
+  const float* feats;
+  long long ld_feats;
+  const float* boxes;
+  const long long* classes;
+  const float* scores;
+  const int* batch_idx;
+  const float* cams;
+  int num_images, n;
+  float* records;
+  float* raw;
+};
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// <w_row, feat> + bias over K elements; every lane returns the full sum.
+__device__ __forceinline__ float head_dot(const float* __restrict__ w_row, const float* __restrict__ feat, int K,
+                                          float bias, int lane, bool vec4) {
+  float acc = 0.f;
+  if (vec4) {
+    const float4* w4 = reinterpret_cast<const float4*>(w_row);
+    const float4* f4 = reinterpret_cast<const float4*>(feat);
+    for (int i = lane; i < (K >> 2); i += 32) {
+      const float4 a = __ldg(w4 + i);
+      const float4 b = f4[i];
+      acc = fmaf(a.x, b.x, acc);
+      acc = fmaf(a.y, b.y, acc);
+      acc = fmaf(a.z, b.z, acc);
+      acc = fmaf(a.w, b.w, acc);
+    }
+  } else {
+    for (int i = lane; i < K; i += 32) acc = fmaf(__ldg(w_row + i), feat[i], acc);
+  }
+  return warp_sum(acc) + bias;
+}
+
+__device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + expf(-x)); }
+// torch .clip(min): NaN-transparent, unlike fmaxf
+__device__ __forceinline__ float clip_min(float x, float lo) { return x < lo ? lo : x; }
+
+// pytorch3d quaternion_to_matrix (real part first), row-major 3x3.
+__device__ __forceinline__ void quat_to_matrix(float r, float i, float j, float k, float* R) {
+  const float two_s = 2.f / (r * r + i * i + j * j + k * k);
+  R[0] = 1.f - two_s * (j * j + k * k);
+  R[1] = two_s * (i * j - k * r);
+  R[2] = two_s * (i * k + j * r);
+  R[3] = two_s * (i * j + k * r);
+  R[4] = 1.f - two_s * (i * i + k * k);
+  R[5] = two_s * (j * k - i * r);
+  R[6] = two_s * (i * k - j * r);
+  R[7] = two_s * (j * k + i * r);
+  R[8] = 1.f - two_s * (i * i + j * j);
+}
+
+__device__ __forceinline__ void matmul3(const float* A, const float* B, float* C) {
+#pragma unroll
+  for (int r = 0; r < 3; ++r)
+#pragma unroll
+    for (int c = 0; c < 3; ++c) C[3 * r + c] = A[3 * r] * B[c] + A[3 * r + 1] * B[3 + c] + A[3 * r + 2] * B[6 + c];
+}
+
+__global__ void __launch_bounds__(kWarpsPerBlock * 32) head_decode_kernel(const DecodeArgs a) {
+  const int lane = threadIdx.x & 31;
+  const int box = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
+  if (box >= a.n) return;  // warp-uniform
+  const ovm_decode_cfg_t& cfg = a.cfg;
+  const int K = cfg.fc_dim;
+  const int NC = cfg.num_classes;
+  const bool per_class = cfg.dims_priors_enabled != 0;
+  const int cls = (int)a.classes[box];
+  const int csel = per_class ? cls : 0;
+
+  const float x1 = a.boxes[4 * box + 0], y1 = a.boxes[4 * box + 1];
+  const float x2 = a.boxes[4 * box + 2], y2 = a.boxes[4 * box + 3];
+  // roi_heads.py:414-419
+  const float src_w = x2 - x1, src_h = y2 - y1;
+  const float src_scale = sqrtf(src_h * src_h + src_w * src_w);
+  const float ctr_x = x1 + 0.5f * src_w, ctr_y = y1 + 0.5f * src_h;
+
+  // roi_heads.py:378-408: K / ratio with [2,2] forced to 1; focal is the un-scaled K[1,1]
+  const float* cam = a.cams + 12 * a.batch_idx[box];
+  const float ratio = cam[9], h_cur = cam[10];
+  const float fx = cam[0] / ratio, fy = cam[4] / ratio, px = cam[2] / ratio, py = cam[5] / ratio;
+  const float focal = cam[4];
+  const float h_orig = h_cur * ratio;
+  const float virtual_to_real = cfg.virtual_depth ? (h_cur * focal) / (cfg.virtual_focal * h_orig) : 1.f;
+
+  const float* frow = a.feats + (long long)box * a.ld_feats;
+  const bool vec4 = (K & 3) == 0 && (a.ld_feats & 3) == 0 && ((reinterpret_cast<uintptr_t>(a.feats) & 15) == 0);
+  const float* f_deltas = frow + cfg.feat_offset[0];
+  const float* f_dims = frow + cfg.feat_offset[1];
+  const float* f_pose = frow + cfg.feat_offset[2];
+  const float* f_z = frow + cfg.feat_offset[3];
+  const float* f_unc = frow + cfg.feat_offset[4];
+  // a feature vector that does not start on a 16-byte boundary falls back to scalar loads
+  const bool v_deltas = vec4 && !(cfg.feat_offset[0] & 3), v_dims = vec4 && !(cfg.feat_offset[1] & 3);
+  const bool v_pose = vec4 && !(cfg.feat_offset[2] & 3), v_z = vec4 && !(cfg.feat_offset[3] & 3);
+  const bool v_unc = vec4 && !(cfg.feat_offset[4] & 3);
+
+  // ---- heads: only the rows [fg, box_classes] keeps (roi_heads.py:452-477)
+  float deltas[2], dims_raw[3], pose_raw[6];
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const int row = csel * 2 + j;
+    deltas[j] = head_dot(a.w.w_deltas + (long long)row * K, f_deltas, K, a.w.b_deltas[row], lane, v_deltas);
+  }
+#pragma unroll
+  for (int j = 0; j < 3; ++j) {
+    const int row = csel * 3 + j;
+    dims_raw[j] = head_dot(a.w.w_dims + (long long)row * K, f_dims, K, a.w.b_dims[row], lane, v_dims);
+  }
+  const int pose_n = cfg.pose_type == OVM_POSE_6D ? 6 : (cfg.pose_type == OVM_POSE_QUATERNION ? 4 : 3);
+#pragma unroll
+  for (int j = 0; j < 6; ++j) {
+    pose_raw[j] = 0.f;
+    if (j < pose_n) {
+      const int row = csel * pose_n + j;
+      pose_raw[j] = head_dot(a.w.w_pose + (long long)row * K, f_pose, K, a.w.b_pose[row], lane, v_pose);
+    }
+  }
+  // depth bin: nearest priors_z_scales[class, bin] to the 2-D diagonal, first minimum wins (roi_heads.py:436-444)
+  int bin = 0;
+  if (cfg.cluster_bins > 1) {
+    // torch.argmin: first minimum wins, and a NaN counts as smaller than everything
+    float best = fabsf(a.w.priors_z_scales[(long long)cls * cfg.cluster_bins] - src_scale);
+    for (int b = 1; b < cfg.cluster_bins; ++b) {
+      const float d = fabsf(a.w.priors_z_scales[(long long)cls * cfg.cluster_bins + b] - src_scale);
+      if (best == best && (d < best || d != d)) {
+        best = d;
+        bin = b;
+      }
+    }
+  }
+  // box_z.view(n, bins, C, -1)[i, bin, class] / view(n, C, -1)[i, class] (cube_head.py:192-201)
+  const int z_row = cfg.cluster_bins > 1 ? bin * NC + cls : csel;
+  const float z_raw = head_dot(a.w.w_z + (long long)z_row * K, f_z, K, a.w.b_z[z_row], lane, v_z);
+  float uncert = 0.f;
+  if (cfg.use_confidence) {
+    uncert = head_dot(a.w.w_uncert + (long long)csel * K, f_unc, K, a.w.b_uncert[csel], lane, v_unc);
+    uncert = clip_min(uncert, 0.01f);  // .clip(0.01), cube_head.py:164
+  }
+
+  // ---- pose -> R (rows), cube_head.py:176-186
+  float R[9];
+  if (cfg.pose_type == OVM_POSE_6D) {
+    const float a1x = pose_raw[0], a1y = pose_raw[1], a1z = pose_raw[2];
+    const float a2x = pose_raw[3], a2y = pose_raw[4], a2z = pose_raw[5];
+    const float n1 = fmaxf(sqrtf(a1x * a1x + a1y * a1y + a1z * a1z), 1e-12f);
+    const float b1x = a1x / n1, b1y = a1y / n1, b1z = a1z / n1;
+    const float d = b1x * a2x + b1y * a2y + b1z * a2z;
+    float b2x = a2x - d * b1x, b2y = a2y - d * b1y, b2z = a2z - d * b1z;
+    const float n2 = fmaxf(sqrtf(b2x * b2x + b2y * b2y + b2z * b2z), 1e-12f);
+    b2x /= n2; b2y /= n2; b2z /= n2;
+    R[0] = b1x; R[1] = b1y; R[2] = b1z;
+    R[3] = b2x; R[4] = b2y; R[5] = b2z;
+    R[6] = b1y * b2z - b1z * b2y;
+    R[7] = b1z * b2x - b1x * b2z;
+    R[8] = b1x * b2y - b1y * b2x;
+  } else if (cfg.pose_type == OVM_POSE_QUATERNION) {
+    // quats / _copysign(sqrt(sum q^2), q0): flips the sign of the norm when q0 < 0
+    const float q0 = pose_raw[0], q1 = pose_raw[1], q2 = pose_raw[2], q3 = pose_raw[3];
+    float nq = sqrtf(q0 * q0 + q1 * q1 + q2 * q2 + q3 * q3);
+    if ((nq < 0.f) != (q0 < 0.f)) nq = -nq;
+    quat_to_matrix(q0 / nq, q1 / nq, q2 / nq, q3 / nq, R);
+  } else {
+    // euler_angles_to_matrix(., "XYZ") = Rx(a0) @ Ry(a1) @ Rz(a2)
+    const float cx = cosf(pose_raw[0]), sx = sinf(pose_raw[0]);
+    const float cy = cosf(pose_raw[1]), sy = sinf(pose_raw[1]);
+    const float cz = cosf(pose_raw[2]), sz = sinf(pose_raw[2]);
+    const float Rx[9] = {1.f, 0.f, 0.f, 0.f, cx, -sx, 0.f, sx, cx};
+    const float Ry[9] = {cy, 0.f, sy, 0.f, 1.f, 0.f, -sy, 0.f, cy};
+    const float Rz[9] = {cz, -sz, 0.f, sz, cz, 0.f, 0.f, 0.f, 1.f};
+    float T[9];
+    matmul3(Rx, Ry, T);
+    matmul3(T, Rz, R);
+  }
+
+  // ---- xy and dims (roi_heads.py:480-507)
+  const float u = ctr_x + src_w * deltas[0];
+  const float v = ctr_y + src_h * deltas[1];
+  float dims[3];
+#pragma unroll
+  for (int j = 0; j < 3; ++j) {
+    if (per_class) {
+      const float mean = a.w.priors_dims_per_cat[(long long)cls * 6 + j];
+      const float sd = a.w.priors_dims_per_cat[(long long)cls * 6 + 3 + j];
+      if (cfg.dims_priors_func == OVM_DIMS_SIGMOID) {
+        const float lo = clip_min(mean - 3.f * sd, 0.f), hi = mean + 3.f * sd;
+        dims[j] = lo + (hi - lo) * sigmoidf_(dims_raw[j]);
+      } else {
+        dims[j] = expf(dims_raw[j] > 5.f ? 5.f : dims_raw[j]) * mean;
+      }
+    } else {
+      dims[j] = expf(dims_raw[j] > 5.f ? 5.f : dims_raw[j]);
+    }
+  }
+
+  // ---- allocentric -> egocentric (math_util.py:657-679)
+  if (cfg.allocentric_pose) {
+    float rx = (u - px) / fx, ry = (v - py) / fy, rz = 1.f;
+    const float rn = sqrtf(rx * rx + ry * ry + rz * rz);
+    rx /= rn; ry /= rn; rz /= rn;
+    const float angle = acosf(rz);
+    if (angle > 0.f) {  // false for 0 and NaN: R_view is kept (boolean-mask assignment :678-679)
+      const float ax = 0.f - ry, ay = 0.f + rx;
+      const float an = sqrtf(ax * ax + ay * ay + 0.f);
+      const float vx = angle * ax / an, vy = angle * ay / an, vz = angle * 0.f / an;
+      // pytorch3d axis_angle_to_quaternion -> quaternion_to_matrix
+      const float angles = sqrtf(vx * vx + vy * vy + vz * vz);
+      const float half = angles * 0.5f;
+      const float s = fabsf(angles) < 1e-6f ? 0.5f - (angles * angles) / 48.f : sinf(half) / angles;
+      float M[9], T[9];
+      quat_to_matrix(cosf(half), vx * s, vy * s, vz * s, M);
+      matmul3(M, R, T);
+#pragma unroll
+      for (int i = 0; i < 9; ++i) R[i] = T[i];
+    }
+  }
+
+  // ---- z (roi_heads.py:515-549)
+  float z = z_raw;
+  if (cfg.z_type == OVM_Z_SIGMOID) {
+    z = sigmoidf_(z) * 100.f;
+  } else if (cfg.z_type == OVM_Z_LOG) {
+    z = expf(z);
+  } else if (cfg.z_type == OVM_Z_CLUSTERS) {
+    const float* st = a.w.priors_z_stats + ((long long)cls * cfg.cluster_bins + bin) * 2;
+    const float zlo = clip_min(st[0] - 3.f * st[1], 0.f), zhi = st[0] + 3.f * st[1];
+    z = zlo + (zhi - zlo) * sigmoidf_(z);
+  }
+  if (cfg.virtual_depth) z = z * virtual_to_real;
+
+  // ---- back-projection, confidence, score (roi_heads.py:802-829)
+  const float X = z * (u - px) / fx;
+  const float Y = z * (v - py) / fy;
+  const float u_out = u * ratio, v_out = v * ratio;
+  const float last = cfg.use_confidence ? expf(-uncert) : v_out;  // cube_3D[:, -1]
+  const float score = a.scores ? sqrtf(a.scores[box] * last) : last;
+
+  if (lane != 0) return;
+  // ---- corners (math_util.py:172-193): x <-> L, y <-> H, z <-> W; box order is X,Y,Z,W,H,L
+  const float hw = dims[0] / 2.f, hh = dims[1] / 2.f, hl = dims[2] / 2.f;
+  float rec[OVM_RECORD_WIDTH];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const float lx = (k == 0 || k == 3 || k == 4 || k == 7) ? -hl : hl;
+    const float ly = (k == 0 || k == 1 || k == 4 || k == 5) ? -hh : hh;
+    const float lz = (k < 4) ? -hw : hw;
+    rec[3 * k + 0] = (R[0] * lx + R[1] * ly + R[2] * lz) + X;
+    rec[3 * k + 1] = (R[3] * lx + R[4] * ly + R[5] * lz) + Y;
+    rec[3 * k + 2] = (R[6] * lx + R[7] * ly + R[8] * lz) + z;
+  }
+  rec[24] = X; rec[25] = Y; rec[26] = z;
+  rec[27] = u_out; rec[28] = v_out;
+  rec[29] = dims[0]; rec[30] = dims[1]; rec[31] = dims[2];
+#pragma unroll
+  for (int i = 0; i < 9; ++i) rec[32 + i] = R[i];
+  rec[41] = x1; rec[42] = y1; rec[43] = x2; rec[44] = y2;
+  rec[45] = score;
+  rec[46] = (float)cls;
+  rec[47] = 0.f;
+  float4* out = reinterpret_cast<float4*>(a.records + (long long)box * OVM_RECORD_WIDTH);
+#pragma unroll
+  for (int i = 0; i < OVM_RECORD_WIDTH / 4; ++i) out[i] = make_float4(rec[4 * i], rec[4 * i + 1], rec[4 * i + 2], rec[4 * i + 3]);
+  if (a.raw) {
+    float4* ro = reinterpret_cast<float4*>(a.raw + (long long)box * 16);
+    ro[0] = make_float4(deltas[0], deltas[1], z_raw, dims_raw[0]);
+    ro[1] = make_float4(dims_raw[1], dims_raw[2], uncert, pose_raw[0]);
+    ro[2] = make_float4(pose_raw[1], pose_raw[2], pose_raw[3], pose_raw[4]);
+    ro[3] = make_float4(pose_raw[5], 0.f, 0.f, 0.f);
+  }
+}
+
+}  // namespace
+
+int head_decode_launch(const ovm_decode_cfg_t* cfg, const ovm_head_weights_t* w, const float* feats, int64_t ld_feats,
+                       const float* boxes, const int64_t* classes, const float* scores, const int32_t* batch_idx,
+                       const float* cams, int32_t num_images, int32_t n, float* records, float* raw,
+                       cudaStream_t stream) {
+  OVM_REQUIRE(cfg && w, "ovm_head_decode: cfg / weights are NULL");
+  OVM_REQUIRE(cfg->z_type >= OVM_Z_DIRECT && cfg->z_type <= OVM_Z_CLUSTERS, "ovm_head_decode: z_type %d", cfg->z_type);
+  OVM_REQUIRE(cfg->pose_type >= OVM_POSE_6D && cfg->pose_type <= OVM_POSE_EULER,
+              "Cuboid pose type %d is not recognized", cfg->pose_type);
+  OVM_REQUIRE(cfg->dims_priors_func == OVM_DIMS_EXP || cfg->dims_priors_func == OVM_DIMS_SIGMOID,
+              "ovm_head_decode: dims_priors_func %d", cfg->dims_priors_func);
+  OVM_REQUIRE(cfg->fc_dim > 0 && cfg->num_classes > 0 && cfg->cluster_bins >= 1, "ovm_head_decode: bad sizes");
+  if (cfg->cluster_bins > 1 && !cfg->dims_priors_enabled) {
+    // the reference itself fails here: assignments is [n, num_classes] and indexes a [n, bins, 1] tensor
+    // (roi_heads.py:449)
+    set_error("ovm_head_decode: CLUSTER_BINS > 1 needs DIMS_PRIORS_ENABLED (the reference raises at roi_heads.py:449)");
+    return OVM_EUNSUPPORTED;
+  }
+  OVM_REQUIRE(cfg->cluster_bins == 1 || w->priors_z_scales, "ovm_head_decode: priors_z_scales needed for CLUSTER_BINS > 1");
+  OVM_REQUIRE(cfg->z_type != OVM_Z_CLUSTERS || w->priors_z_stats, "ovm_head_decode: priors_z_stats needed for Z_TYPE clusters");
+  OVM_REQUIRE(!cfg->dims_priors_enabled || w->priors_dims_per_cat, "ovm_head_decode: priors_dims_per_cat needed");
+  OVM_REQUIRE(w->w_deltas && w->b_deltas && w->w_dims && w->b_dims && w->w_pose && w->b_pose && w->w_z && w->b_z,
+              "ovm_head_decode: a head weight is NULL");
+  OVM_REQUIRE(!cfg->use_confidence || (w->w_uncert && w->b_uncert), "ovm_head_decode: uncertainty head is NULL");
+  for (int i = 0; i < 5; ++i)
+    OVM_REQUIRE(cfg->feat_offset[i] >= 0 && cfg->feat_offset[i] + cfg->fc_dim <= ld_feats,
+                "ovm_head_decode: feat_offset[%d]=%d + fc_dim exceeds ld_feats", i, cfg->feat_offset[i]);
+  if (n == 0) return OVM_OK;
+  OVM_REQUIRE(n > 0 && feats && boxes && classes && batch_idx && cams && records && num_images > 0,
+              "ovm_head_decode: NULL input with n=%d", n);
+  OVM_REQUIRE(!(reinterpret_cast<uintptr_t>(records) & 15) && (!raw || !(reinterpret_cast<uintptr_t>(raw) & 15)),
+              "ovm_head_decode: records / raw must be 16-byte aligned");
+  DecodeArgs a{};
+  a.cfg = *cfg;
+  a.w = *w;
+  a.feats = feats;
+  a.ld_feats = ld_feats;
+  a.boxes = boxes;
+  a.classes = reinterpret_cast<const long long*>(classes);
+  a.scores = scores;
+  a.batch_idx = batch_idx;
+  a.cams = cams;
+  a.num_images = num_images;
+  a.n = n;
+  a.records = records;
+  a.raw = raw;
+  head_decode_kernel<<<(n + kWarpsPerBlock - 1) / kWarpsPerBlock, kWarpsPerBlock * 32, 0, stream>>>(a);
+  OVM_LAUNCHED("head_decode_kernel");
+  return OVM_OK;
+}
+
+}  // namespace ovm

@@ -1,0 +1,161 @@
+// C ABI of libovmono3d_lift.so (declared in include/ovmono3d_lift.h) and the three-kernel lift sequence.
+//
+// ovm_lift_forward is the inference slice of ROIHeads3D._forward_cube (reference
+// cubercnn/modeling/roi_heads/roi_heads.py:329-848): cube_pooler (:366) -> cube_head (:430) -> decode (:378-549,
+// 798-843), issued back to back on the caller's stream with no host synchronisation in between.
+#include <cstdarg>
+#include <cstring>
+
+#include "common.cuh"
+
+namespace ovm {
+
+std::atomic<int64_t> g_launches{0};
+
+namespace {
+thread_local char g_error[512] = "";
+}
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_error, sizeof(g_error), fmt, ap);
+  va_end(ap);
+}
+
+namespace {
+
+// One FC stack (cube_head.py:64-74): every layer is Linear + ReLU.  The last layer's output is the fp32
+// feature block `feats[:, col0 : col0 + N]`; earlier layers ping-pong through bf16 activations.
+int run_fc_group(const ovm_fc_layer_t* layers, int num_fc, const void* x, int64_t ldx, int32_t n,
+                 const ovm_workspace_t* ws, float* feats, int64_t ld_feats, cudaStream_t stream) {
+  const void* in = x;
+  int64_t ld_in = ldx;
+  for (int k = 0; k < num_fc; ++k) {
+    const ovm_fc_layer_t& L = layers[k];
+    const bool last = k == num_fc - 1;
+    OVM_REQUIRE(L.weight && L.bias && L.N > 0 && L.K > 0, "ovm_lift_forward: FC layer %d is incomplete", k);
+    OVM_REQUIRE(L.N % 8 == 0, "ovm_lift_forward: FC_DIM must be a multiple of 8 (got %d)", L.N);
+    void* out = last ? static_cast<void*>(feats) : (k % 2 == 0 ? ws->act_a : ws->act_b);
+    const int64_t ldo = last ? ld_feats : L.N;
+    const int out_dtype = last ? OVM_F32 : OVM_BF16;
+    // Ask the GEMM which mode it would pick for a raw fp32 accumulation; a long-K layer whose tiles cannot fill
+    // the SMs runs split-K into ws->acc and gets bias+ReLU from the small follow-up kernel.
+    int mode = OVM_GEMM_DIRECT;
+    {
+      const int BN = L.N >= 256 ? 256 : (L.N >= 128 ? 128 : 64);
+      const int tiles = ((n + 127) / 128) * ((L.N + BN - 1) / BN);
+      const int kb = (L.K + 63) / 64;
+      const bool ragged = tiles < kNumSMs || (tiles % kNumSMs) * 2 < kNumSMs;
+      if (kb >= 32 && tiles < 2 * kNumSMs && ragged && ws->acc) mode = OVM_GEMM_STREAMK;
+    }
+    if (mode == OVM_GEMM_STREAMK) {
+      OVM_CUDA(cudaMemsetAsync(ws->acc, 0, (size_t)n * L.N * sizeof(float), stream));
+      g_launches.fetch_add(1, std::memory_order_relaxed);
+      int rc = gemm_bf16_launch(in, ld_in, L.weight, L.ldw, n, L.N, L.K, nullptr, 0, ws->acc, OVM_F32, L.N,
+                                OVM_GEMM_STREAMK, nullptr, stream);
+      if (rc != OVM_OK) return rc;
+      rc = bias_act_launch(ws->acc, L.N, L.bias, 1, n, L.N, out, out_dtype, ldo, stream);
+      if (rc != OVM_OK) return rc;
+    } else {
+      int rc = gemm_bf16_launch(in, ld_in, L.weight, L.ldw, n, L.N, L.K, L.bias, 1, out, out_dtype, ldo,
+                                OVM_GEMM_DIRECT, nullptr, stream);
+      if (rc != OVM_OK) return rc;
+    }
+    in = out;
+    ld_in = ldo;
+  }
+  return OVM_OK;
+}
+
+}  // namespace
+}  // namespace ovm
+
+using namespace ovm;
+
+#pragma GCC visibility push(default)
+extern "C" {
+
+int ovm_abi_version(void) { return OVM_ABI_VERSION; }
+
+const char* ovm_last_error(void) { return g_error; }
+
+int ovm_struct_size(int which) {
+  switch (which) {
+    case 0: return (int)sizeof(ovm_level_t);
+    case 1: return (int)sizeof(ovm_pooler_t);
+    case 2: return (int)sizeof(ovm_decode_cfg_t);
+    case 3: return (int)sizeof(ovm_head_weights_t);
+    case 4: return (int)sizeof(ovm_fc_layer_t);
+    case 5: return (int)sizeof(ovm_fc_stack_t);
+    case 6: return (int)sizeof(ovm_workspace_t);
+    default: return -1;
+  }
+}
+
+int64_t ovm_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+int ovm_roi_align(const ovm_pooler_t* pooler, const float* boxes, const int32_t* batch_idx, int32_t n, void* out,
+                  int32_t out_dtype, int64_t out_ld, int32_t* level_out, void* stream) {
+  return roi_align_launch(pooler, boxes, batch_idx, n, out, out_dtype, out_ld, level_out,
+                          static_cast<cudaStream_t>(stream));
+}
+
+int ovm_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t ldb, int32_t M, int32_t N, int32_t K,
+                  const float* bias, int32_t relu, void* out, int32_t out_dtype, int64_t ldo, int32_t mode,
+                  int32_t* mode_used, void* stream) {
+  return gemm_bf16_launch(A, lda, B, ldb, M, N, K, bias, relu, out, out_dtype, ldo, mode, mode_used,
+                          static_cast<cudaStream_t>(stream));
+}
+
+int ovm_bias_act(const float* in, int64_t ldi, const float* bias, int32_t relu, int32_t M, int32_t N, void* out,
+                 int32_t out_dtype, int64_t ldo, void* stream) {
+  return bias_act_launch(in, ldi, bias, relu, M, N, out, out_dtype, ldo, static_cast<cudaStream_t>(stream));
+}
+
+int ovm_cast_bf16(const float* in, int64_t ld_in, int32_t rows, int32_t cols, void* out, int64_t ld_out,
+                  void* stream) {
+  return cast_bf16_launch(in, ld_in, rows, cols, out, ld_out, static_cast<cudaStream_t>(stream));
+}
+
+int ovm_head_decode(const ovm_decode_cfg_t* cfg, const ovm_head_weights_t* w, const float* feats, int64_t ld_feats,
+                    const float* boxes, const int64_t* classes, const float* scores, const int32_t* batch_idx,
+                    const float* cams, int32_t num_images, int32_t n, float* records, float* raw, void* stream) {
+  return head_decode_launch(cfg, w, feats, ld_feats, boxes, classes, scores, batch_idx, cams, num_images, n, records,
+                            raw, static_cast<cudaStream_t>(stream));
+}
+
+int ovm_lift_forward(const ovm_pooler_t* pooler, const ovm_fc_stack_t* fc, const ovm_decode_cfg_t* cfg,
+                     const ovm_head_weights_t* heads, const float* boxes, const int64_t* classes, const float* scores,
+                     const int32_t* batch_idx, const float* cams, int32_t n, const ovm_workspace_t* ws,
+                     float* records, float* raw, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  OVM_REQUIRE(pooler && fc && cfg && heads && ws, "ovm_lift_forward: NULL descriptor");
+  OVM_REQUIRE(fc->num_groups >= 1 && fc->num_groups <= 5 && fc->num_fc >= 1 && fc->layers,
+              "ovm_lift_forward: bad FC stack (%d groups x %d layers)", fc->num_groups, fc->num_fc);
+  if (n == 0) return OVM_OK;  // roi_heads.py:368-372
+  OVM_REQUIRE(n > 0, "ovm_lift_forward: n=%d", n);
+  const int PP = pooler->pooler_resolution * pooler->pooler_resolution;
+  const int64_t k_in = (int64_t)pooler->channels * PP;
+  OVM_REQUIRE(ws->pooled && ws->feats && ws->ld_pooled >= k_in && ws->ld_pooled % 8 == 0,
+              "ovm_lift_forward: workspace.pooled must be [n, ld_pooled >= C*P*P], ld_pooled %% 8 == 0");
+  OVM_REQUIRE(fc->num_fc == 1 || (ws->act_a && ws->act_b), "ovm_lift_forward: workspace.act_a/act_b missing");
+  int rc = roi_align_launch(pooler, boxes, batch_idx, n, ws->pooled, OVM_BF16, ws->ld_pooled, ws->levels, stream);
+  if (rc != OVM_OK) return rc;
+  // fc1 reads only the first C*P*P columns of each pooled row (its TMA map is K wide), so the pad is never touched
+  const int64_t ld_feats = (int64_t)fc->num_groups * cfg->fc_dim;
+  for (int g = 0; g < fc->num_groups; ++g) {
+    const ovm_fc_layer_t* layers = fc->layers + (size_t)g * fc->num_fc;
+    OVM_REQUIRE(layers[0].K == k_in, "ovm_lift_forward: fc1 expects K=%d but the pooler produces %lld",
+                layers[0].K, (long long)k_in);
+    OVM_REQUIRE(layers[fc->num_fc - 1].N == cfg->fc_dim, "ovm_lift_forward: last FC width != cfg.fc_dim");
+    rc = run_fc_group(layers, fc->num_fc, ws->pooled, ws->ld_pooled, n, ws, ws->feats + (size_t)g * cfg->fc_dim,
+                      ld_feats, stream);
+    if (rc != OVM_OK) return rc;
+  }
+  return head_decode_launch(cfg, heads, ws->feats, ld_feats, boxes, classes, scores, batch_idx, cams,
+                            pooler->num_images, n, records, raw, stream);
+}
+
+}  // extern "C"
+#pragma GCC visibility pop

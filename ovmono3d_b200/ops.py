@@ -1,0 +1,261 @@
+"""ctypes binding of `libovmono3d_lift.so` (include/ovmono3d_lift.h) for torch CUDA tensors.
+
+Every function here takes CUDA tensors, passes raw device pointers + the current CUDA stream through the C ABI
+and raises `LiftError` on a non-zero status.  There is no CPU path: a missing library or a CPU tensor is an error.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import List, Optional, Sequence, Tuple
+
+import torch
+
+OVM_ABI_VERSION = 1
+OVM_MAX_LEVELS = 8
+RECORD_WIDTH = 48
+LAYOUT_NCHW, LAYOUT_NHWC = 0, 1
+F32, BF16 = 0, 1
+Z_TYPES = {"direct": 0, "sigmoid": 1, "log": 2, "clusters": 3}
+POSE_TYPES = {"6d": 0, "quaternion": 1, "euler": 2}
+DIMS_FUNCS = {"exp": 0, "sigmoid": 1}
+GEMM_AUTO, GEMM_DIRECT, GEMM_STREAMK = 0, 1, 2
+
+# record columns (include/ovmono3d_lift.h, ovm_head_decode)
+REC_BBOX3D = slice(0, 24)
+REC_CENTER_CAM = slice(24, 27)
+REC_CENTER_2D = slice(27, 29)
+REC_DIMENSIONS = slice(29, 32)
+REC_POSE = slice(32, 41)
+REC_BOX2D = slice(41, 45)
+REC_SCORE = 45
+REC_CLASS = 46
+
+EXPORTS = ("ovm_abi_version", "ovm_last_error", "ovm_launch_count", "ovm_struct_size", "ovm_roi_align", "ovm_gemm_bf16",
+           "ovm_bias_act", "ovm_cast_bf16", "ovm_head_decode", "ovm_lift_forward")
+
+
+class LiftError(RuntimeError):
+    pass
+
+
+class ovm_level_t(C.Structure):
+    _fields_ = [("data", C.c_void_p), ("height", C.c_int32), ("width", C.c_int32), ("spatial_scale", C.c_double),
+                ("layout", C.c_int32), ("_pad", C.c_int32)]
+
+
+class ovm_pooler_t(C.Structure):
+    _fields_ = [("num_levels", C.c_int32), ("levels", ovm_level_t * OVM_MAX_LEVELS), ("num_images", C.c_int32),
+                ("channels", C.c_int32), ("pooler_resolution", C.c_int32), ("sampling_ratio", C.c_int32),
+                ("canonical_box_size", C.c_int32), ("canonical_level", C.c_int32), ("scale_roi_boxes", C.c_float),
+                ("_pad", C.c_int32)]
+
+
+class ovm_decode_cfg_t(C.Structure):
+    _fields_ = [("z_type", C.c_int32), ("pose_type", C.c_int32), ("dims_priors_func", C.c_int32),
+                ("cluster_bins", C.c_int32), ("num_classes", C.c_int32), ("dims_priors_enabled", C.c_int32),
+                ("use_confidence", C.c_int32), ("virtual_depth", C.c_int32), ("allocentric_pose", C.c_int32),
+                ("virtual_focal", C.c_float), ("fc_dim", C.c_int32), ("feat_offset", C.c_int32 * 5)]
+
+
+class ovm_head_weights_t(C.Structure):
+    _fields_ = [(k, C.c_void_p) for k in (
+        "w_deltas", "b_deltas", "w_dims", "b_dims", "w_pose", "b_pose", "w_z", "b_z", "w_uncert", "b_uncert",
+        "priors_dims_per_cat", "priors_z_scales", "priors_z_stats")]
+
+
+class ovm_fc_layer_t(C.Structure):
+    _fields_ = [("weight", C.c_void_p), ("bias", C.c_void_p), ("N", C.c_int32), ("K", C.c_int32), ("ldw", C.c_int64)]
+
+
+class ovm_fc_stack_t(C.Structure):
+    _fields_ = [("num_groups", C.c_int32), ("num_fc", C.c_int32), ("layers", C.POINTER(ovm_fc_layer_t))]
+
+
+class ovm_workspace_t(C.Structure):
+    _fields_ = [("pooled", C.c_void_p), ("ld_pooled", C.c_int64), ("acc", C.c_void_p), ("act_a", C.c_void_p),
+                ("act_b", C.c_void_p), ("feats", C.c_void_p), ("levels", C.c_void_p)]
+
+
+ABI_STRUCTS = (ovm_level_t, ovm_pooler_t, ovm_decode_cfg_t, ovm_head_weights_t, ovm_fc_layer_t, ovm_fc_stack_t,
+               ovm_workspace_t)
+_LIB: Optional[C.CDLL] = None
+LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libovmono3d_lift.so")
+
+
+def load_library() -> C.CDLL:
+    """Load the in-tree C-ABI library.  Fails loudly: the lift has no other implementation."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    if not os.path.exists(LIB_PATH):
+        raise LiftError(
+            "%s is missing: build it with `python -m ovmono3d_b200.build` (needs nvcc, sm_100a). "
+            "The lift path has no CPU or PyTorch fallback." % LIB_PATH)
+    lib = C.CDLL(LIB_PATH)
+    for name in EXPORTS:
+        if not hasattr(lib, name):
+            raise LiftError("%s does not export %s" % (LIB_PATH, name))
+    lib.ovm_abi_version.restype = C.c_int
+    lib.ovm_last_error.restype = C.c_char_p
+    lib.ovm_launch_count.restype = C.c_int64
+    if lib.ovm_abi_version() != OVM_ABI_VERSION:
+        raise LiftError("ABI version mismatch: library %d, binding %d" % (lib.ovm_abi_version(), OVM_ABI_VERSION))
+    vp, i32, i64 = C.c_void_p, C.c_int32, C.c_int64
+    lib.ovm_roi_align.argtypes = [C.POINTER(ovm_pooler_t), vp, vp, i32, vp, i32, i64, vp, vp]
+    lib.ovm_gemm_bf16.argtypes = [vp, i64, vp, i64, i32, i32, i32, vp, i32, vp, i32, i64, i32, C.POINTER(i32), vp]
+    lib.ovm_bias_act.argtypes = [vp, i64, vp, i32, i32, i32, vp, i32, i64, vp]
+    lib.ovm_cast_bf16.argtypes = [vp, i64, i32, i32, vp, i64, vp]
+    lib.ovm_head_decode.argtypes = [C.POINTER(ovm_decode_cfg_t), C.POINTER(ovm_head_weights_t), vp, i64, vp, vp, vp,
+                                    vp, vp, i32, i32, vp, vp, vp]
+    lib.ovm_lift_forward.argtypes = [C.POINTER(ovm_pooler_t), C.POINTER(ovm_fc_stack_t), C.POINTER(ovm_decode_cfg_t),
+                                     C.POINTER(ovm_head_weights_t), vp, vp, vp, vp, vp, i32,
+                                     C.POINTER(ovm_workspace_t), vp, vp, vp]
+    for name in EXPORTS[3:]:
+        getattr(lib, name).restype = C.c_int
+    lib.ovm_struct_size.argtypes = [C.c_int]
+    for i, st in enumerate(ABI_STRUCTS):
+        if lib.ovm_struct_size(i) != C.sizeof(st):
+            raise LiftError("ABI struct %s: library says %d bytes, binding %d" % (
+                st.__name__, lib.ovm_struct_size(i), C.sizeof(st)))
+    _LIB = lib
+    return lib
+
+
+def launch_count() -> int:
+    return int(load_library().ovm_launch_count())
+
+
+def _check(rc: int, what: str) -> None:
+    if rc != 0:
+        msg = load_library().ovm_last_error().decode("utf-8", "replace")
+        raise LiftError("%s failed (%d): %s" % (what, rc, msg))
+
+
+def _stream() -> C.c_void_p:
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _need_cuda(t: torch.Tensor, name: str, dtype: torch.dtype) -> torch.Tensor:
+    if not t.is_cuda:
+        raise LiftError("%s must be a CUDA tensor (the lift has no CPU path)" % name)
+    if t.dtype != dtype:
+        raise LiftError("%s must be %s, got %s" % (name, dtype, t.dtype))
+    return t
+
+
+def dtype_code(dt: torch.dtype) -> int:
+    if dt == torch.float32:
+        return F32
+    if dt == torch.bfloat16:
+        return BF16
+    raise LiftError("unsupported output dtype %s" % dt)
+
+
+def make_pooler(features: Sequence[torch.Tensor], scales: Sequence[float], output_size: int, sampling_ratio: int,
+                canonical_box_size: int = 224, canonical_level: int = 4, scale_roi_boxes: float = 0.0
+                ) -> Tuple[ovm_pooler_t, List[torch.Tensor]]:
+    """Describe a pyramid for `ovm_roi_align`.  Returns the struct and the tensors it points into (keep alive).
+
+    NCHW-contiguous maps are used as they are; `torch.channels_last` maps are passed as NHWC without a copy."""
+    if not 1 <= len(features) <= OVM_MAX_LEVELS or len(features) != len(scales):
+        raise LiftError("need 1..%d feature maps with one scale each" % OVM_MAX_LEVELS)
+    p = ovm_pooler_t()
+    p.num_levels = len(features)
+    keep = []
+    N, Cc = features[0].shape[0], features[0].shape[1]
+    for l, (f, s) in enumerate(zip(features, scales)):
+        _need_cuda(f, "features[%d]" % l, torch.float32)
+        if f.dim() != 4 or f.shape[0] != N or f.shape[1] != Cc:
+            raise LiftError("features[%d] has shape %s, expected [%d, %d, H, W]" % (l, tuple(f.shape), N, Cc))
+        if f.is_contiguous():
+            layout = LAYOUT_NCHW
+        elif f.is_contiguous(memory_format=torch.channels_last):
+            layout = LAYOUT_NHWC
+        else:
+            f = f.contiguous()
+            layout = LAYOUT_NCHW
+        keep.append(f)
+        p.levels[l] = ovm_level_t(f.data_ptr(), f.shape[2], f.shape[3], float(s), layout, 0)
+    p.num_images, p.channels = N, Cc
+    p.pooler_resolution, p.sampling_ratio = int(output_size), int(sampling_ratio)
+    p.canonical_box_size, p.canonical_level = int(canonical_box_size), int(canonical_level)
+    p.scale_roi_boxes = float(scale_roi_boxes)
+    return p, keep
+
+
+def roi_align(features: Sequence[torch.Tensor], scales: Sequence[float], boxes: torch.Tensor,
+              batch_idx: torch.Tensor, output_size: int = 7, sampling_ratio: int = 0,
+              out_dtype: torch.dtype = torch.float32, scale_roi_boxes: float = 0.0,
+              canonical_box_size: int = 224, canonical_level: int = 4) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Multi-level ROIAlignV2 -> (pooled [n, C, P, P], 0-based level per box [n] int32)."""
+    lib = load_library()
+    pooler, keep = make_pooler(features, scales, output_size, sampling_ratio, canonical_box_size, canonical_level,
+                               scale_roi_boxes)
+    boxes = _need_cuda(boxes, "boxes", torch.float32).contiguous()
+    batch_idx = _need_cuda(batch_idx, "batch_idx", torch.int32).contiguous()
+    n = boxes.shape[0]
+    Cc, P = pooler.channels, output_size
+    out = torch.empty((n, Cc, P, P), device=boxes.device, dtype=out_dtype)
+    levels = torch.empty((n,), device=boxes.device, dtype=torch.int32)
+    if n:
+        _check(lib.ovm_roi_align(C.byref(pooler), boxes.data_ptr(), batch_idx.data_ptr(), n, out.data_ptr(),
+                                 dtype_code(out_dtype), Cc * P * P, levels.data_ptr(), _stream()), "ovm_roi_align")
+    del keep
+    return out, levels
+
+
+def gemm_bf16(A: torch.Tensor, B: torch.Tensor, bias: Optional[torch.Tensor] = None, relu: bool = False,
+              out_dtype: torch.dtype = torch.float32, mode: int = GEMM_AUTO,
+              out: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, int]:
+    """act(A[M,K] @ B[N,K]^T + bias) with bf16 operands and fp32 accumulation.  Returns (out, mode used).
+
+    In STREAMK mode (chosen by AUTO for long-K, few-tile shapes when no bias/relu is requested) `out` is the raw
+    fp32 accumulation and must start at zero (it is zeroed here when allocated here)."""
+    lib = load_library()
+    _need_cuda(A, "A", torch.bfloat16)
+    _need_cuda(B, "B", torch.bfloat16)
+    if A.stride(-1) != 1 or B.stride(-1) != 1 or A.dim() != 2 or B.dim() != 2 or A.shape[1] != B.shape[1]:
+        raise LiftError("gemm_bf16: A [M,K] and B [N,K] must be row-major with the same K")
+    M, K = A.shape
+    N = B.shape[0]
+    ldo = (N + 7) // 8 * 8
+    if out is None:
+        store = torch.zeros((M, ldo), device=A.device, dtype=out_dtype)
+        out = store[:, :N]
+    else:
+        ldo = out.stride(0)
+    used = C.c_int32(0)
+    if bias is not None:
+        _need_cuda(bias, "bias", torch.float32)
+    _check(lib.ovm_gemm_bf16(A.data_ptr(), A.stride(0), B.data_ptr(), B.stride(0), M, N, K, _ptr(bias), int(relu),
+                             out.data_ptr(), dtype_code(out.dtype), ldo, mode, C.byref(used), _stream()),
+           "ovm_gemm_bf16")
+    return out, used.value
+
+
+def bias_act(x: torch.Tensor, bias: Optional[torch.Tensor], relu: bool, out_dtype: torch.dtype) -> torch.Tensor:
+    lib = load_library()
+    _need_cuda(x, "x", torch.float32)
+    M, N = x.shape
+    out = torch.empty((M, N), device=x.device, dtype=out_dtype)
+    _check(lib.ovm_bias_act(x.data_ptr(), x.stride(0), _ptr(bias), int(relu), M, N, out.data_ptr(),
+                            dtype_code(out_dtype), N, _stream()), "ovm_bias_act")
+    return out
+
+
+def cast_bf16(x: torch.Tensor, ld_out: Optional[int] = None) -> torch.Tensor:
+    """fp32 [rows, cols] -> bf16 [rows, ld_out] (zero-padded), returned as the [rows, cols] view."""
+    lib = load_library()
+    _need_cuda(x, "x", torch.float32)
+    rows, cols = x.shape
+    ld_out = ld_out or (cols + 7) // 8 * 8
+    out = torch.empty((rows, ld_out), device=x.device, dtype=torch.bfloat16)
+    if rows:
+        _check(lib.ovm_cast_bf16(x.data_ptr(), x.stride(0), rows, cols, out.data_ptr(), ld_out, _stream()),
+               "ovm_cast_bf16")
+    return out[:, :cols]

@@ -1,0 +1,421 @@
+"""Drop-in ROI heads for the 2D->3D lift: `ROIHeads3DB200` / `ROIHeads3DGDINOB200`.
+
+They register into `ROI_HEADS_REGISTRY` under their own names and are selected with
+`MODEL.ROI_HEADS.NAME`, exactly as the reference's `ROIHeads3D` / `ROIHeads3DGDINO` are
+(reference cubercnn/modeling/roi_heads/roi_heads.py:31-40, roi_heads_gdino.py:26-27, README.md:59).
+Constructor (`from_config(cfg, input_shape, priors=None)`), `forward` signature, `_forward_cube`
+signature, the `Instances` fields written and the state-dict keys are the reference's
+(roi_heads.py:42-204,207-249,329,811-848; cube_head.py:64-145); the arithmetic runs in the sm_100a
+library behind `ovmono3d_b200.ops` and nowhere else -- there is no PyTorch or CPU fallback.
+
+Out of scope here: training losses / proposal sampling, the 2-D box head, and
+GroundingDINO itself -- the open-vocabulary 2-D detector is injected as a callable.
+"""
+from __future__ import annotations
+
+from typing import Any, Callable, Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+from torch import nn
+
+from . import ops
+from .compat import ROI_CUBE_HEAD_REGISTRY, ROI_HEADS_REGISTRY, Boxes, Instances, ShapeSpec, configurable
+from .engine import DecodeSettings, LiftEngine
+
+
+def build_roi_heads(cfg, input_shape, priors=None):
+    """`cfg.MODEL.ROI_HEADS.NAME` -> head (reference roi_heads.py:31-36)."""
+    name = cfg.MODEL.ROI_HEADS.NAME
+    return ROI_HEADS_REGISTRY.get(name)(cfg, input_shape, priors=priors)
+
+
+def build_cube_head(cfg, input_shape):
+    """`cfg.MODEL.ROI_CUBE_HEAD.NAME` -> cube head (reference cube_head.py:207-209)."""
+    name = cfg.MODEL.ROI_CUBE_HEAD.NAME
+    return ROI_CUBE_HEAD_REGISTRY.get(name)(cfg, input_shape)
+
+
+def _xavier_fc(fan_in: int, fan_out: int) -> nn.Linear:
+    fc = nn.Linear(fan_in, fan_out)
+    nn.init.kaiming_uniform_(fc.weight, a=1)     # fvcore c2_xavier_fill (cube_head.py:72)
+    nn.init.constant_(fc.bias, 0)
+    return fc
+
+
+def _head_fc(fan_in: int, fan_out: int, bias: float = 0.0) -> nn.Linear:
+    fc = nn.Linear(fan_in, fan_out)
+    nn.init.normal_(fc.weight, std=0.001)        # cube_head.py:110-145
+    nn.init.constant_(fc.bias, bias)
+    return fc
+
+
+@ROI_CUBE_HEAD_REGISTRY.register()
+class CubeHead(nn.Module):
+    """Parameter container with the reference CubeHead's module tree and state-dict keys
+    (`feature_generator[_XY|_dims|_pose|_Z|_conf].fc{k}`, `bbox_3D_{dims,center_deltas,pose,center_depth,
+    uncertainty}`; cube_head.py:20-145).  It has no `forward` of its own: the FC stack and the heads run
+    inside `ovm_lift_forward` (tcgen05 GEMMs + the fused head/decode kernel)."""
+
+    def __init__(self, cfg, input_shape: ShapeSpec):
+        super().__init__()
+        cube = cfg.MODEL.ROI_CUBE_HEAD
+        self.num_classes = cfg.MODEL.ROI_HEADS.NUM_CLASSES
+        self.use_conf = cube.USE_CONFIDENCE
+        self.z_type = cube.Z_TYPE
+        self.pose_type = cube.POSE_TYPE
+        self.cluster_bins = cube.CLUSTER_BINS
+        self.shared_fc = cube.SHARED_FC
+        self.use_prior = cube.DIMS_PRIORS_ENABLED
+        num_fc, fc_dim = cube.NUM_FC, cube.FC_DIM
+        if cube.NUM_CONV != 0:
+            raise NotImplementedError("ROI_CUBE_HEAD.NUM_CONV > 0 is read by the reference config but never built "
+                                      "by its CubeHead (cube_head.py:41-48)")
+        assert num_fc > 0
+        names = ["feature_generator"] if self.shared_fc else (
+            ["feature_generator_XY", "feature_generator_dims", "feature_generator_pose", "feature_generator_Z"]
+            + (["feature_generator_conf"] if self.use_conf else []))
+        in_dim = int(input_shape.channels * input_shape.height * input_shape.width)
+        for name in names:
+            seq, d = nn.Sequential(), in_dim
+            for k in range(num_fc):
+                seq.add_module("fc{}".format(k + 1), _xavier_fc(d, fc_dim))
+                seq.add_module("fc_relu{}".format(k + 1), nn.ReLU())
+                d = fc_dim
+            setattr(self, name, seq)
+        self._output_size = fc_dim
+        mult = self.num_classes if self.use_prior else 1
+        bins = self.cluster_bins if self.cluster_bins > 1 else 1
+        self.bbox_3D_dims = _head_fc(fc_dim, mult * 3)
+        self.bbox_3D_center_deltas = _head_fc(fc_dim, mult * 2)
+        if self.pose_type not in ops.POSE_TYPES:
+            raise ValueError("Cuboid pose type {} is not recognized".format(self.pose_type))
+        self.bbox_3D_pose = _head_fc(fc_dim, mult * {"6d": 6, "quaternion": 4, "euler": 3}[self.pose_type])
+        self.bbox_3D_center_depth = _head_fc(fc_dim, mult * bins)
+        if self.use_conf:
+            self.bbox_3D_uncertainty = _head_fc(fc_dim, mult * 1, bias=5.0)
+
+    def forward(self, x, num_boxes_per_image=None):
+        raise ops.LiftError("CubeHead (B200) holds parameters only; the head runs inside ovm_lift_forward. "
+                            "Call ROIHeads3DB200._forward_cube instead.")
+
+
+class ROIPooler(nn.Module):
+    """d2 `ROIPooler(output_size, scales, sampling_ratio, pooler_type)` on the sm_100a ROIAlign kernel
+    (reference construction roi_heads.py:166-171, call :366)."""
+
+    def __init__(self, output_size, scales, sampling_ratio, pooler_type, canonical_box_size=224, canonical_level=4):
+        super().__init__()
+        if isinstance(output_size, (tuple, list)):
+            assert len(output_size) == 2 and output_size[0] == output_size[1], "square output only"
+            output_size = output_size[0]
+        if pooler_type != "ROIAlignV2":
+            raise ValueError("Unknown / unsupported pooler type: {} (the lift ships ROIAlignV2 only, "
+                             "config.py:122)".format(pooler_type))
+        self.output_size = int(output_size)
+        self.scales = tuple(float(s) for s in scales)
+        self.sampling_ratio = int(sampling_ratio)
+        min_level, max_level = -np.log2(self.scales[0]), -np.log2(self.scales[-1])
+        self.min_level, self.max_level = int(min_level), int(max_level)
+        assert len(self.scales) == self.max_level - self.min_level + 1, \
+            "[ROIPooler] Sizes of input featuremaps do not form a pyramid!"
+        assert 0 <= self.min_level <= self.max_level
+        assert canonical_box_size > 0
+        self.canonical_box_size, self.canonical_level = canonical_box_size, canonical_level
+        self.last_levels: Optional[torch.Tensor] = None
+
+    def forward(self, x: List[torch.Tensor], box_lists: List[Boxes]) -> torch.Tensor:
+        assert isinstance(x, list) and isinstance(box_lists, list), "Arguments to pooler must be lists"
+        assert len(x) == len(self.scales), "unequal value, num_level_assignments={}, but x is list of {} Tensors".format(
+            len(self.scales), len(x))
+        assert len(box_lists) == x[0].size(0), "unequal value, x[0] batch dim 0 is {}, but box_list has length {}".format(
+            x[0].size(0), len(box_lists))
+        boxes, batch_idx = _cat_boxes([b.tensor for b in box_lists], x[0].device)
+        out, levels = ops.roi_align(x, self.scales, boxes, batch_idx, self.output_size, self.sampling_ratio,
+                                    torch.float32, 0.0, self.canonical_box_size, self.canonical_level)
+        self.last_levels = levels
+        return out
+
+
+def _cat_boxes(box_tensors: Sequence[torch.Tensor], device: torch.device) -> Tuple[torch.Tensor, torch.Tensor]:
+    counts = [int(b.shape[0]) for b in box_tensors]
+    boxes = torch.cat([b.to(device=device, dtype=torch.float32) for b in box_tensors], dim=0) if counts else \
+        torch.zeros((0, 4), device=device)
+    idx = np.repeat(np.arange(len(counts), dtype=np.int32), counts)
+    batch_idx = torch.from_numpy(idx).to(device, non_blocking=True)
+    return boxes.contiguous(), batch_idx
+
+
+@ROI_HEADS_REGISTRY.register()
+class ROIHeads3DB200(nn.Module):
+    """`ROIHeads3D` with the inference lift on sm_100a kernels (reference roi_heads.py:39-249,329-848)."""
+
+    @configurable
+    def __init__(
+        self,
+        *,
+        ignore_thresh: float = 0.5,
+        cube_head: nn.Module,
+        cube_pooler: nn.Module,
+        loss_w_3d: float = 1.0,
+        loss_w_xy: float = 1.0,
+        loss_w_z: float = 1.0,
+        loss_w_dims: float = 1.0,
+        loss_w_pose: float = 1.0,
+        loss_w_joint: float = 1.0,
+        use_confidence: float = 1.0,
+        inverse_z_weight: bool = False,
+        z_type: str = "direct",
+        pose_type: str = "6d",
+        cluster_bins: int = 1,
+        priors=None,
+        dims_priors_enabled=None,
+        dims_priors_func=None,
+        disentangled_loss=None,
+        virtual_depth=None,
+        virtual_focal=None,
+        test_scale=None,
+        allocentric_pose=None,
+        chamfer_pose=None,
+        scale_roi_boxes=None,
+        num_classes: int = 50,
+        box_in_features: Optional[List[str]] = None,
+        **kwargs: Any,
+    ):
+        super().__init__()
+        self.num_classes = num_classes
+        self.in_features = self.box_in_features = list(box_in_features or [])
+        self.scale_roi_boxes = scale_roi_boxes or 0.0
+        self.allocentric_pose, self.chamfer_pose = allocentric_pose, chamfer_pose
+        self.virtual_depth, self.virtual_focal = virtual_depth, virtual_focal
+        self.loss_w_3d, self.loss_w_xy, self.loss_w_z = loss_w_3d, loss_w_xy, loss_w_z
+        self.loss_w_dims, self.loss_w_pose, self.loss_w_joint = loss_w_dims, loss_w_pose, loss_w_joint
+        self.disentangled_loss, self.inverse_z_weight = disentangled_loss, inverse_z_weight
+        self.test_scale, self.ignore_thresh = test_scale, ignore_thresh
+        self.z_type, self.pose_type, self.use_confidence = z_type, pose_type, use_confidence
+        self.cluster_bins = cluster_bins
+        self.dims_priors_enabled, self.dims_priors_func = dims_priors_enabled, dims_priors_func
+        if pose_type not in ops.POSE_TYPES:
+            raise ValueError("Cuboid pose type {} is not recognized".format(pose_type))
+        self._engine: Optional[LiftEngine] = None
+        if loss_w_3d > 0:
+            self.cube_head = cube_head
+            self.cube_pooler = cube_pooler
+            # priors as parameters, same names / shapes as roi_heads.py:113-143
+            if self.dims_priors_enabled and priors is not None:
+                self.priors_dims_per_cat = nn.Parameter(torch.FloatTensor(priors["priors_dims_per_cat"]).unsqueeze(0))
+            else:
+                self.priors_dims_per_cat = nn.Parameter(torch.ones(1, self.num_classes, 2, 3))
+            if self.cluster_bins > 1 and priors is not None:
+                self.priors_z_scales = nn.Parameter(
+                    torch.stack([torch.FloatTensor(prior[1]) for prior in priors["priors_bins"]]))
+            else:
+                self.priors_z_scales = nn.Parameter(torch.ones(self.num_classes, self.cluster_bins))
+            if self.z_type == "clusters":
+                assert self.cluster_bins > 1, "To use z_type of priors, there must be more than 1 cluster bin"
+                if priors is None:
+                    self.priors_z_stats = nn.Parameter(torch.ones(self.num_classes, self.cluster_bins, 2).float())
+                else:
+                    self.priors_z_stats = nn.Parameter(
+                        torch.cat([torch.FloatTensor(prior[2]).unsqueeze(0) for prior in priors["priors_bins"]]))
+
+    # ------------------------------------------------------------------ construction from cfg
+    @classmethod
+    def from_config(cls, cfg, input_shape: Dict[str, ShapeSpec], priors=None):
+        ret = dict(num_classes=cfg.MODEL.ROI_HEADS.NUM_CLASSES, box_in_features=list(cfg.MODEL.ROI_HEADS.IN_FEATURES))
+        ret.update(cls._init_cube_head(cfg, input_shape))
+        ret["priors"] = priors
+        return ret
+
+    @classmethod
+    def _init_cube_head(cls, cfg, input_shape: Dict[str, ShapeSpec]):
+        cube = cfg.MODEL.ROI_CUBE_HEAD
+        in_features = cfg.MODEL.ROI_HEADS.IN_FEATURES
+        pooler_scales = tuple(1.0 / input_shape[k].stride for k in in_features)
+        res = cube.POOLER_RESOLUTION
+        cube_pooler = ROIPooler(output_size=res, scales=pooler_scales, sampling_ratio=cube.POOLER_SAMPLING_RATIO,
+                                pooler_type=cube.POOLER_TYPE)
+        in_channels = [input_shape[f].channels for f in in_features][0]
+        cube_head = build_cube_head(cfg, ShapeSpec(channels=in_channels, width=res, height=res))
+        return {
+            "cube_head": cube_head, "cube_pooler": cube_pooler,
+            "use_confidence": cube.USE_CONFIDENCE, "inverse_z_weight": cube.INVERSE_Z_WEIGHT,
+            "loss_w_3d": cube.LOSS_W_3D, "loss_w_xy": cube.LOSS_W_XY, "loss_w_z": cube.LOSS_W_Z,
+            "loss_w_dims": cube.LOSS_W_DIMS, "loss_w_pose": cube.LOSS_W_POSE, "loss_w_joint": cube.LOSS_W_JOINT,
+            "z_type": cube.Z_TYPE, "pose_type": cube.POSE_TYPE,
+            "dims_priors_enabled": cube.DIMS_PRIORS_ENABLED, "dims_priors_func": cube.DIMS_PRIORS_FUNC,
+            "disentangled_loss": cube.DISENTANGLED_LOSS, "virtual_depth": cube.VIRTUAL_DEPTH,
+            "virtual_focal": cube.VIRTUAL_FOCAL, "test_scale": cfg.INPUT.MIN_SIZE_TEST,
+            "chamfer_pose": cube.CHAMFER_POSE, "allocentric_pose": cube.ALLOCENTRIC_POSE,
+            "cluster_bins": cube.CLUSTER_BINS, "ignore_thresh": cfg.MODEL.RPN.IGNORE_THRESHOLD,
+            "scale_roi_boxes": cube.SCALE_ROI_BOXES,
+        }
+
+    # ------------------------------------------------------------------ forward
+    def forward(self, images, features, proposals, Ks, im_scales_ratio, targets=None):
+        """Inference branch of `ROIHeads3D.forward` (roi_heads.py:207-249).  `proposals` is either the list of
+        oracle dicts (`gt_bbox2D`, `gt_classes`[, `gt_scores`]) the reference accepts (:232-243) or a list of
+        `Instances` carrying `pred_boxes` / `pred_classes` / `scores` from a 2-D detector."""
+        if self.training:
+            raise NotImplementedError("training losses are outside the lift path (SURVEY.md section 8)")
+        im_dims = [tuple(image.shape[1:]) for image in images]
+        device = list(features.values())[0].device
+        if isinstance(proposals, list) and not any(isinstance(p, Instances) for p in proposals):
+            pred_instances = []
+            for proposal, im_dim, r in zip(proposals, im_dims, im_scales_ratio):
+                inst = Instances(im_dim)
+                inst.pred_boxes = Boxes(proposal["gt_bbox2D"] / r).to(device=device)
+                inst.pred_classes = proposal["gt_classes"].to(device=device)
+                if "gt_scores" in proposal:
+                    inst.scores = proposal["gt_scores"].to(device=device)
+                else:
+                    inst.scores = torch.ones_like(proposal["gt_classes"]).float().to(device=device)
+                pred_instances.append(inst)
+        else:
+            pred_instances = proposals
+        if self.loss_w_3d > 0:
+            pred_instances = self._forward_cube(features, pred_instances, Ks, im_dims, im_scales_ratio)
+        return pred_instances, {}
+
+    def scale_proposals(self, proposal_boxes: List[Boxes]) -> List[Boxes]:
+        """roi_heads.py:310-327 for callers that want the zoomed boxes; `_forward_cube` applies the same zoom
+        inside the ROIAlign kernel.  Heights use x2-x1, exactly as the reference does (:317)."""
+        if not self.scale_roi_boxes > 0:
+            return proposal_boxes
+        out = []
+        for b in proposal_boxes:
+            t = b.tensor
+            centers = b.get_centers()
+            widths = t[:, 2] - t[:, 0]
+            heights = t[:, 2] - t[:, 0]
+            x1 = centers[:, 0] - 0.5 * widths * self.scale_roi_boxes
+            x2 = centers[:, 0] + 0.5 * widths * self.scale_roi_boxes
+            y1 = centers[:, 1] - 0.5 * heights * self.scale_roi_boxes
+            y2 = centers[:, 1] + 0.5 * heights * self.scale_roi_boxes
+            out.append(Boxes(torch.stack([x1, y1, x2, y2], dim=1)))
+        return out
+
+    def _get_engine(self) -> LiftEngine:
+        if self._engine is None:
+            settings = DecodeSettings(
+                z_type=self.z_type, pose_type=self.pose_type, cluster_bins=self.cluster_bins,
+                num_classes=self.num_classes, dims_priors_enabled=bool(self.dims_priors_enabled),
+                dims_priors_func=self.dims_priors_func or "exp", use_confidence=self.use_confidence,
+                virtual_depth=bool(self.virtual_depth), virtual_focal=float(self.virtual_focal or 512.0),
+                allocentric_pose=bool(self.allocentric_pose), scale_roi_boxes=float(self.scale_roi_boxes))
+            p = self.cube_pooler
+            self._engine = LiftEngine(self.cube_head, p.scales, p.output_size, p.sampling_ratio, settings,
+                                      p.canonical_box_size, p.canonical_level)
+        return self._engine
+
+    @torch.no_grad()
+    def _forward_cube(self, features, instances, Ks, im_current_dims, im_scales_ratio, return_raw: bool = False):
+        """Inference slice of `ROIHeads3D._forward_cube` (roi_heads.py:329-848).  Mutates and returns the same
+        `Instances` (:817): scores merged, `pred_bbox3D`, `pred_center_cam`, `pred_center_2D`, `pred_dimensions`,
+        `pred_pose` added.  n == 0 returns the input untouched (:368-372)."""
+        if self.training:
+            raise NotImplementedError("training losses are outside the lift path (SURVEY.md section 8)")
+        feats = [features[f] for f in self.in_features]
+        device = feats[0].device
+        if device.type != "cuda":
+            raise ops.LiftError("the B200 lift runs on CUDA only (features are on %s); there is no CPU fallback"
+                                % device)
+        num_boxes_per_image = [len(i) for i in instances]
+        n = sum(num_boxes_per_image)
+        if n == 0:
+            return instances
+        N = len(instances)
+        assert N == feats[0].shape[0] == len(Ks) == len(im_scales_ratio) == len(im_current_dims)
+
+        # one pinned staging buffer -> one H2D copy: cams [N,12] fp32 (K, ratio, H_cur, 0) then batch_idx [n] int32
+        stage = torch.empty(N * 12 + n, dtype=torch.float32, pin_memory=True)
+        cams_h = stage[: N * 12].view(N, 12)
+        for i in range(N):
+            cams_h[i, :9] = torch.as_tensor(Ks[i], dtype=torch.float32).reshape(9)
+            cams_h[i, 9] = float(im_scales_ratio[i])
+            cams_h[i, 10] = float(im_current_dims[i][0])
+            cams_h[i, 11] = 0.0
+        stage[N * 12:].view(torch.int32).copy_(
+            torch.from_numpy(np.repeat(np.arange(N, dtype=np.int32), num_boxes_per_image)))
+        stage_d = stage.to(device, non_blocking=True)
+        cams = stage_d[: N * 12].view(N, 12)
+        batch_idx = stage_d[N * 12:].view(torch.int32)
+
+        boxes = torch.cat([x.pred_boxes.tensor for x in instances]).to(device=device, dtype=torch.float32).contiguous()
+        classes = torch.cat([x.pred_classes for x in instances]).to(device=device, dtype=torch.int64).contiguous()
+        have_scores = [x.has("scores") for x in instances]
+        if all(have_scores):
+            scores = torch.cat([x.scores for x in instances]).to(device=device, dtype=torch.float32).contiguous()
+        elif not any(have_scores):
+            scores = None
+        else:  # mixed: a NaN marks "no score" -- handled per image below
+            raise ops.LiftError("either every Instances or none must carry `scores`")
+
+        eng = self._get_engine()
+        eng.prepare(device, self.priors_dims_per_cat, self.priors_z_scales, getattr(self, "priors_z_stats", None))
+        records, raw = eng.forward(feats, boxes, classes, scores, batch_idx, cams, want_raw=return_raw)
+
+        start = 0
+        for inst, k in zip(instances, num_boxes_per_image):
+            rec = records[start:start + k]
+            start += k
+            inst.scores = rec[:, ops.REC_SCORE]
+            inst.pred_bbox3D = rec[:, ops.REC_BBOX3D].view(k, 8, 3)
+            inst.pred_center_cam = rec[:, ops.REC_CENTER_CAM]
+            inst.pred_center_2D = rec[:, ops.REC_CENTER_2D]
+            inst.pred_dimensions = rec[:, ops.REC_DIMENSIONS]
+            inst.pred_pose = rec[:, ops.REC_POSE].view(k, 3, 3)
+        self.last_records, self.last_raw = records, raw
+        return instances
+
+
+Detector2D = Callable[[torch.Tensor, List[List[str]]], Dict[str, Any]]
+
+
+@ROI_HEADS_REGISTRY.register()
+class ROIHeads3DGDINOB200(ROIHeads3DB200):
+    """`ROIHeads3DGDINO` (reference roi_heads_gdino.py:26-171) with the lift on sm_100a kernels.
+
+    The reference loads GroundingDINO from hard-coded paths in its constructor (:87-91) and calls it in
+    `forward` (:137-154).  GroundingDINO is a separate detector and out of scope; here it is an injected
+    callable `detector(image_bgr [3,H,W], text_prompt [[cat], ...]) -> {"labels", "bboxes", "scores"}` with the
+    same result dict as `grounding_dino_inference_detector` (:262-294).  Everything after it -- building the
+    `Instances` target (:157-167) and `_forward_cube` (:169-170) -- is the reference's flow."""
+
+    @configurable
+    def __init__(self, *, detector: Optional[Detector2D] = None, **kwargs: Any):
+        super().__init__(**kwargs)
+        self.groundingdino_model = detector
+
+    @classmethod
+    def from_config(cls, cfg, input_shape: Dict[str, ShapeSpec], priors=None, detector: Optional[Detector2D] = None):
+        ret = super().from_config(cfg, input_shape, priors=priors)
+        ret["detector"] = detector
+        return ret
+
+    def forward(self, images, features, proposals, Ks, im_scales_ratio, targets=None, category_list=None):
+        if self.training:
+            raise NotImplementedError("training losses are outside the lift path (SURVEY.md section 8)")
+        im_dims = [tuple(image.shape[1:]) for image in images]
+        device = list(features.values())[0].device
+        filtered_texts = [[cat] for cat in category_list] if category_list else []
+        target = Instances(im_dims[0])
+        if not filtered_texts:
+            # the reference means to return an empty Instances here (:130-136)
+            target.pred_classes = torch.zeros((0,), dtype=torch.int64, device=device)
+            target.pred_boxes = Boxes(torch.zeros((0, 4), dtype=torch.float32, device=device))
+            target.scores = torch.zeros((0,), dtype=torch.float32, device=device)
+        else:
+            if self.groundingdino_model is None:
+                raise ops.LiftError("ROIHeads3DGDINOB200 needs a 2-D detector callable (GroundingDINO is not part of "
+                                    "the lift path); pass detector=... or use ROIHeads3DB200 with given boxes")
+            ov = self.groundingdino_model(images[0][[2, 1, 0], :, :], filtered_texts)
+            target.pred_classes = torch.tensor([filtered_texts.index([name]) for name in ov["labels"]],
+                                               dtype=torch.int64)
+            target.pred_boxes = Boxes(ov["bboxes"])
+            target.scores = ov["scores"]
+            target = target.to(device=device)
+        pred_instances = [target]
+        if self.loss_w_3d > 0:
+            pred_instances = self._forward_cube(features, pred_instances, Ks, im_dims, im_scales_ratio)
+        return pred_instances, {}

@@ -1,0 +1,415 @@
+"""Parity of the CUDA path (through the C ABI) with the oracle and with the reference's golden vectors.
+
+Tolerances are BASELINE.json's: box-to-level assignment bit-exact; pooled features, 3-D centres, dimensions and
+corners within 1e-3 relative in fp32; within 1e-2 with the bf16 head.  "Relative" is measured against the scale
+of the field (max |reference| over the field), because corners and centres cross zero.
+"""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+from tests import helpers
+from tests.golden import cases as gc
+
+pytestmark = pytest.mark.gpu
+
+FP32_TOL = 1e-3
+BF16_TOL = 1e-2
+FIELDS = ("scores", "pred_bbox3D", "pred_center_cam", "pred_center_2D", "pred_dimensions", "pred_pose")
+SMALL_CASES = [c for c in gc.CASES]
+
+
+def _dev():
+    return torch.device("cuda:0")
+
+
+def _field_err(got: torch.Tensor, want: torch.Tensor) -> float:
+    got, want = got.detach().double().cpu(), want.detach().double().cpu()
+    if want.numel() == 0:
+        return 0.0
+    finite = torch.isfinite(want)
+    assert torch.equal(torch.isfinite(got), finite), "non-finite pattern differs"
+    if not finite.any():
+        return 0.0
+    scale = want[finite].abs().max().clamp_min(1e-30)
+    return float(((got - want)[finite].abs().max() / scale))
+
+
+def _cat_inputs(inp, device):
+    counts = [len(b) for b in inp.boxes]
+    boxes = torch.cat(inp.boxes).to(device)
+    batch_idx = torch.from_numpy(np.repeat(np.arange(len(counts), dtype=np.int32), counts)).to(device)
+    return boxes, batch_idx, counts
+
+
+# --------------------------------------------------------------------------- Kernel 1: ROIAlign
+@pytest.mark.parametrize("case", SMALL_CASES, ids=lambda c: c.name)
+def test_roi_align_matches_oracle(case):
+    from ovmono3d_b200 import ops
+
+    inp, weights, priors, cfg, out = helpers.run_oracle(case)
+    dev = _dev()
+    boxes, batch_idx, counts = _cat_inputs(inp, dev)
+    feats = [f.to(dev) for f in inp.features]
+    pooled, levels = ops.roi_align(feats, cfg.scales, boxes, batch_idx, cfg.pooler_resolution, cfg.sampling_ratio,
+                                   torch.float32, cfg.scale_roi_boxes)
+    assert pooled.shape == out.pooled.shape
+    if sum(counts) == 0:
+        return
+    assert torch.equal(levels.cpu().long(), out.levels), "box-to-level assignment must be bit-exact"
+    assert _field_err(pooled, out.pooled) <= FP32_TOL
+    # per-box check as well, so one small box cannot hide behind a large one
+    ref = out.pooled.flatten(1)
+    got = pooled.flatten(1).cpu()
+    scale = ref.abs().amax(dim=1).clamp_min(1e-6)
+    assert float(((got - ref).abs().amax(dim=1) / scale).max()) <= FP32_TOL
+    # the committed vectors written by the reference's own code
+    g = np.load(gc.golden_path(case))
+    np.testing.assert_allclose(pooled.flatten()[:: case.pooled_stride].cpu().numpy(), g["pooled"],
+                               rtol=0, atol=FP32_TOL * float(np.abs(g["pooled"]).max()))
+    np.testing.assert_array_equal(levels.cpu().numpy().astype(np.int64), g["levels"])
+
+
+def test_roi_align_bf16_out_and_channels_last():
+    from ovmono3d_b200 import ops
+
+    case = gc.CASE_BY_NAME["clip_4level"]
+    inp, weights, priors, cfg, out = helpers.run_oracle(case)
+    dev = _dev()
+    boxes, batch_idx, _ = _cat_inputs(inp, dev)
+    feats = [f.to(dev) for f in inp.features]
+    p16, _ = ops.roi_align(feats, cfg.scales, boxes, batch_idx, 7, 0, torch.bfloat16)
+    assert _field_err(p16.float(), out.pooled) <= 2 ** -8   # one bf16 rounding of an fp32-exact result
+    cl = [f.contiguous(memory_format=torch.channels_last) for f in feats]
+    pcl, lv = ops.roi_align(cl, cfg.scales, boxes, batch_idx, 7, 0, torch.float32)
+    assert torch.equal(lv.cpu().long(), out.levels)
+    assert _field_err(pcl, out.pooled) <= FP32_TOL
+
+
+def test_level_assignment_ulp_sweep():
+    """Every fp32 box size within +-64 ulp of each level break point, for power-of-two and 7/14/28 pyramids."""
+    from oracle import thirdparty as tp
+    from ovmono3d_b200 import ops
+
+    dev = _dev()
+    for strides in ((4, 8, 16, 32, 64), (7, 14, 28), (4, 8, 16, 32)):
+        scales = [1.0 / s for s in strides]
+        pool = tp.ROIPoolerOracle(7, scales, 0)
+        sides = []
+        for k in range(pool.min_level - 1, pool.max_level + 3):
+            base = np.float32(224.0 * 2.0 ** (k - 4))
+            s = base
+            for _ in range(64):
+                s = np.nextafter(s, np.float32(0), dtype=np.float32)
+            for _ in range(129):
+                sides.append(s)
+                s = np.nextafter(s, np.float32(np.inf), dtype=np.float32)
+        side = torch.tensor(np.array(sides, dtype=np.float32))
+        # squares at the origin (area = side^2) and 1 x side^2... keep sqrt(area) near the break: use w=side, h=side
+        boxes = torch.stack([torch.zeros_like(side), torch.zeros_like(side), side, side], dim=1)
+        # and thin boxes whose area is a non-square product
+        thin = torch.stack([torch.zeros_like(side), torch.zeros_like(side), side * 4, side / 4], dim=1)
+        boxes = torch.cat([boxes, thin])
+        want = pool.levels([boxes])
+        feats = [torch.zeros(1, 8, 16, 16, device=dev) for _ in strides]
+        _, got = ops.roi_align(feats, scales, boxes.to(dev), torch.zeros(len(boxes), dtype=torch.int32, device=dev))
+        assert torch.equal(got.cpu().long(), want), "strides %s" % (strides,)
+
+
+def test_roi_align_random_geometry_property():
+    """Size-independent property at a large shape: pooling a constant map returns the constant wherever the
+    sampling grid is inside the map, and pooling is linear in the features."""
+    from ovmono3d_b200 import ops
+    from ovmono3d_b200 import synth
+
+    dev = _dev()
+    inp = synth.make_inputs(99, 2, 500, strides=(4, 8, 16, 32), canvas=1024, channels=64)
+    boxes, batch_idx, _ = _cat_inputs(inp, dev)
+    scales = [1 / 4, 1 / 8, 1 / 16, 1 / 32]
+    f1 = [f.to(dev) for f in inp.features]
+    f2 = [torch.randn_like(f) for f in f1]
+    a, _ = ops.roi_align(f1, scales, boxes, batch_idx)
+    b, _ = ops.roi_align(f2, scales, boxes, batch_idx)
+    c, _ = ops.roi_align([2 * x - 3 * y for x, y in zip(f1, f2)], scales, boxes, batch_idx)
+    assert _field_err(c, 2 * a - 3 * b) <= 1e-4
+    ones, _ = ops.roi_align([torch.full_like(f, 2.5) for f in f1], scales, boxes, batch_idx)
+    inside = ((boxes[:, 0] > 40) & (boxes[:, 1] > 40) & (boxes[:, 2] < 980) & (boxes[:, 3] < 980))
+    assert inside.sum() > 50
+    assert torch.allclose(ones[inside], torch.full_like(ones[inside], 2.5), rtol=1e-5, atol=1e-5)
+
+
+# --------------------------------------------------------------------------- Kernel 2: tcgen05 GEMM
+@pytest.mark.parametrize("M,N,K", [(80, 1024, 12544), (1600, 1024, 12544), (1600, 1024, 1024), (1, 64, 784),
+                                   (129, 200, 392), (300, 1024, 72), (2000, 128, 6272), (37, 64, 64)])
+@pytest.mark.parametrize("mode", ["direct", "streamk"])
+def test_gemm_bf16_matches_fp32_reference(M, N, K, mode):
+    from ovmono3d_b200 import ops
+
+    dev = _dev()
+    g = torch.Generator().manual_seed(M * 7 + N * 3 + K)
+    A = (torch.randn(M, K, generator=g) / math.sqrt(K)).to(dev).bfloat16()
+    B = torch.randn(N, K, generator=g).to(dev).bfloat16()
+    bias = torch.randn(N, generator=g).to(dev)
+    ref = A.float() @ B.float().T     # plain fp32 reference of the same op on the same bf16 operands
+    if mode == "direct":
+        out, used = ops.gemm_bf16(A, B, bias, relu=True, out_dtype=torch.float32, mode=ops.GEMM_DIRECT)
+        assert used == ops.GEMM_DIRECT
+        want = torch.relu(ref + bias)
+        out16, _ = ops.gemm_bf16(A, B, bias, relu=False, out_dtype=torch.bfloat16, mode=ops.GEMM_DIRECT)
+        assert _field_err(out16.float(), ref + bias) <= 2 ** -7
+    else:
+        acc, used = ops.gemm_bf16(A, B, None, relu=False, out_dtype=torch.float32, mode=ops.GEMM_STREAMK)
+        assert used == ops.GEMM_STREAMK
+        if N % 4 == 0:
+            out = ops.bias_act(acc.contiguous(), bias, True, torch.float32)
+            want = torch.relu(ref + bias)
+        else:
+            out, want = acc, ref
+    assert _field_err(out, want) <= 1e-4   # fp32 accumulation: only summation order differs
+
+
+# --------------------------------------------------------------------------- Kernel 3: heads + decode (fp32)
+def _run_head_decode_fp32(case):
+    """Feed the oracle's own fp32 FC features to ovm_head_decode: isolates Kernel 3 at fp32 precision."""
+    import ctypes as C
+
+    from oracle import lift_oracle as lo
+    from ovmono3d_b200 import ops
+    from ovmono3d_b200.compat import ShapeSpec
+    from ovmono3d_b200.engine import DecodeSettings, LiftEngine
+    from ovmono3d_b200.roi_heads import CubeHead
+
+    inp, weights, priors, cfg, out = helpers.run_oracle(case)
+    dev = _dev()
+    n = sum(len(b) for b in inp.boxes)
+    x = out.pooled.flatten(1)
+    if cfg.shared_fc:
+        feats = lo._fc_stack(weights, "feature_generator", x)
+    else:
+        names = ["XY", "dims", "pose", "Z"] + (["conf"] if cfg.use_confidence else [])
+        feats = torch.cat([lo._fc_stack(weights, "feature_generator_" + g, x) for g in names], dim=1)
+    head = CubeHead(gc.make_cfg(case), ShapeSpec(channels=case.channels, height=7, width=7))
+    head.load_state_dict(weights, strict=True)
+    head = head.to(dev)
+    s = DecodeSettings(z_type=cfg.z_type, pose_type=cfg.pose_type, cluster_bins=cfg.cluster_bins,
+                       num_classes=cfg.num_classes, dims_priors_enabled=cfg.dims_priors_enabled,
+                       dims_priors_func=cfg.dims_priors_func, use_confidence=cfg.use_confidence,
+                       virtual_depth=cfg.virtual_depth, virtual_focal=cfg.virtual_focal,
+                       allocentric_pose=cfg.allocentric_pose, scale_roi_boxes=cfg.scale_roi_boxes)
+    eng = LiftEngine(head, cfg.scales, 7, cfg.sampling_ratio, s)
+    pr = [p.to(dev) for p in priors] if priors is not None else [None, None, None]
+    eng.prepare(dev, *pr)
+    boxes, batch_idx, counts = _cat_inputs(inp, dev)
+    cams = torch.zeros(len(counts), 12)
+    for i in range(len(counts)):
+        cams[i, :9] = inp.Ks[i].reshape(9)
+        cams[i, 9] = inp.im_scales_ratio[i]
+        cams[i, 10] = inp.im_dims[i][0]
+    cams = cams.to(dev)
+    classes = torch.cat(inp.classes).to(dev)
+    scores = torch.cat(inp.scores).to(dev) if case.with_scores else None
+    feats_d = feats.to(dev).contiguous()
+    rec = torch.empty(n, ops.RECORD_WIDTH, device=dev)
+    raw = torch.empty(n, 16, device=dev)
+    lib = ops.load_library()
+    rc = lib.ovm_head_decode(C.byref(eng._cfg), C.byref(eng._heads), feats_d.data_ptr(), feats_d.stride(0),
+                             boxes.data_ptr(), classes.data_ptr(), ops._ptr(scores), batch_idx.data_ptr(),
+                             cams.data_ptr(), len(counts), n, rec.data_ptr(), raw.data_ptr(), ops._stream())
+    ops._check(rc, "ovm_head_decode")
+    torch.cuda.synchronize()
+    return inp, out, counts, rec.cpu(), raw.cpu()
+
+
+def _compare_records(out, counts, rec, tol):
+    start = 0
+    j = 0
+    errs = {}
+    for k in counts:
+        r = rec[start:start + k]
+        start += k
+        if k == 0 and len(out.scores) <= j:
+            continue
+        got = dict(scores=r[:, 45], pred_bbox3D=r[:, 0:24].reshape(k, 8, 3), pred_center_cam=r[:, 24:27],
+                   pred_center_2D=r[:, 27:29], pred_dimensions=r[:, 29:32], pred_pose=r[:, 32:41].reshape(k, 3, 3))
+        for f in FIELDS:
+            want = getattr(out, f)[j]
+            e = _field_err(got[f], want)
+            errs[f] = max(errs.get(f, 0.0), e)
+            assert e <= tol, "%s: %.3g > %.3g" % (f, e, tol)
+        j += 1
+    return errs
+
+
+@pytest.mark.parametrize("case", [c for c in SMALL_CASES if sum(c.boxes_per_image) > 0], ids=lambda c: c.name)
+def test_head_decode_fp32_matches_oracle(case):
+    inp, out, counts, rec, raw = _run_head_decode_fp32(case)
+    _compare_records(out, counts, rec, FP32_TOL)
+
+
+# --------------------------------------------------------------------------- the plugin end to end (bf16 head)
+def _run_plugin(case, return_raw=False):
+    from ovmono3d_b200.compat import Boxes, Instances, ShapeSpec
+    from ovmono3d_b200.roi_heads import build_roi_heads
+
+    inp, weights, priors, cfg, out = helpers.run_oracle(case)
+    dev = _dev()
+    c = gc.make_cfg(case)
+    c.MODEL.ROI_HEADS.NAME = "ROIHeads3DB200"
+    shape = {f: ShapeSpec(channels=case.channels, stride=s) for f, s in zip(case.in_features, case.strides)}
+    head = build_roi_heads(c, shape, priors=None)
+    missing = head.cube_head.load_state_dict(weights, strict=True)
+    assert not missing.missing_keys and not missing.unexpected_keys
+    if priors is not None:
+        head.priors_dims_per_cat.data = priors[0].clone()
+        head.priors_z_scales.data = priors[1].clone()
+        if hasattr(head, "priors_z_stats"):
+            head.priors_z_stats.data = priors[2].clone()
+    head = head.to(dev).eval()
+    feats = {f: t.to(dev) for f, t in zip(case.in_features, inp.features)}
+    instances = []
+    for i in range(len(inp.boxes)):
+        inst = Instances(tuple(inp.im_dims[i]))
+        inst.pred_boxes = Boxes(inp.boxes[i].clone().to(dev))
+        inst.pred_classes = inp.classes[i].clone().to(dev)
+        if case.with_scores:
+            inst.scores = inp.scores[i].clone().to(dev)
+        instances.append(inst)
+    res = head._forward_cube(feats, instances, [k.clone() for k in inp.Ks], [tuple(d) for d in inp.im_dims],
+                             list(inp.im_scales_ratio), return_raw=return_raw)
+    torch.cuda.synchronize()
+    return inp, out, head, res
+
+
+@pytest.mark.parametrize("case", SMALL_CASES, ids=lambda c: c.name)
+def test_plugin_forward_cube_matches_oracle_and_golden(case):
+    inp, out, head, res = _run_plugin(case)
+    assert len(res) == len(inp.boxes)
+    g = np.load(gc.golden_path(case))
+    n = sum(len(b) for b in inp.boxes)
+    if n:
+        assert torch.equal(head._engine.last_levels[:n].cpu().long(), out.levels)
+    j = 0
+    for i, inst in enumerate(res):
+        k = len(inp.boxes[i])
+        if not inst.has("pred_bbox3D"):
+            assert n == 0 or k == 0
+            continue
+        assert inst.pred_bbox3D.shape == (k, 8, 3) and inst.pred_pose.shape == (k, 3, 3)
+        for f in FIELDS:
+            got = inst.get(f)
+            assert _field_err(got, getattr(out, f)[i]) <= BF16_TOL, f
+            if "im%d_%s" % (i, f) in g:   # the reference's own output
+                assert _field_err(got, torch.from_numpy(g["im%d_%s" % (i, f)])) <= BF16_TOL, "golden " + f
+        j += 1
+
+
+def test_plugin_n0_returns_input_untouched():
+    case = gc.Case("all_empty", 31, boxes_per_image=(0, 0), cube=dict(gc.SHIPPED))
+    from ovmono3d_b200.compat import Boxes, Instances, ShapeSpec
+    from ovmono3d_b200.roi_heads import build_roi_heads
+
+    dev = _dev()
+    c = gc.make_cfg(case)
+    c.MODEL.ROI_HEADS.NAME = "ROIHeads3DB200"
+    shape = {f: ShapeSpec(channels=16, stride=s) for f, s in zip(case.in_features, case.strides)}
+    head = build_roi_heads(c, shape).to(dev).eval()
+    feats = {f: torch.zeros(2, 16, 896 // s, 896 // s, device=dev) for f, s in zip(case.in_features, case.strides)}
+    insts = []
+    for _ in range(2):
+        inst = Instances((896, 896))
+        inst.pred_boxes = Boxes(torch.zeros(0, 4, device=dev))
+        inst.pred_classes = torch.zeros(0, dtype=torch.int64, device=dev)
+        insts.append(inst)
+    res = head._forward_cube(feats, insts, [torch.eye(3)] * 2, [(896, 896)] * 2, [1.0, 1.0])
+    assert res is insts and not res[0].has("pred_bbox3D")
+
+
+def test_gdino_head_with_injected_detector():
+    """ROIHeads3DGDINOB200.forward: detector dict -> Instances target -> lift (roi_heads_gdino.py:137-171)."""
+    from ovmono3d_b200.compat import ShapeSpec
+    from ovmono3d_b200.roi_heads import build_roi_heads
+
+    case = gc.CASE_BY_NAME["dinov2_agnostic"]
+    inp, weights, priors, cfg, _ = helpers.run_oracle(case)
+    dev = _dev()
+    c = gc.make_cfg(case)
+    c.MODEL.ROI_HEADS.NAME = "ROIHeads3DGDINOB200"
+    shape = {f: ShapeSpec(channels=case.channels, stride=s) for f, s in zip(case.in_features, case.strides)}
+    cats = ["chair", "table", "sofa"]
+    boxes0 = inp.boxes[0]
+
+    def detector(image_bgr, prompts):
+        assert image_bgr.shape[0] == 3 and prompts == [[c_] for c_ in cats]
+        return {"labels": [cats[i % 3] for i in range(len(boxes0))], "bboxes": boxes0.clone(),
+                "scores": inp.scores[0].clone()}
+
+    head = build_roi_heads(c, shape)
+    head.groundingdino_model = detector
+    head.cube_head.load_state_dict(weights)
+    head = head.to(dev).eval()
+    feats = {f: t[:1].to(dev) for f, t in zip(case.in_features, inp.features)}
+    images = [torch.zeros(3, 896, 896, device=dev)]
+    res, losses = head(images, feats, None, [inp.Ks[0]], [inp.im_scales_ratio[0]], category_list=cats)
+    assert losses == {} and len(res) == 1 and len(res[0]) == len(boxes0)
+    assert res[0].pred_classes.tolist() == [i % 3 for i in range(len(boxes0))]
+    # same boxes through the oracle
+    from oracle import lift_oracle as lo
+    want = lo.forward_cube([f[:1] for f in inp.features], [boxes0], [res[0].pred_classes.cpu()], [inp.scores[0]],
+                           [inp.Ks[0]], [inp.im_dims[0]], [inp.im_scales_ratio[0]], weights, cfg)
+    for f in FIELDS:
+        assert _field_err(res[0].get(f), getattr(want, f)[0]) <= BF16_TOL, f
+    empty, _ = head(images, feats, None, [inp.Ks[0]], [inp.im_scales_ratio[0]], category_list=[])
+    assert len(empty[0]) == 0
+
+
+def test_full_size_c2_properties():
+    """BASELINE config 2 (16 x 100 boxes, full-size head): size-independent properties of the records."""
+    from ovmono3d_b200.compat import Boxes, Instances, ShapeSpec
+    from ovmono3d_b200.config import get_cfg
+    from ovmono3d_b200.roi_heads import build_roi_heads
+    from ovmono3d_b200 import synth
+
+    dev = _dev()
+    inp = synth.make_inputs(1235, 16, 100)
+    c = get_cfg()
+    c.MODEL.ROI_HEADS.NAME = "ROIHeads3DB200"
+    c.MODEL.ROI_HEADS.IN_FEATURES = ["p2", "p3", "p4"]
+    c.MODEL.ROI_CUBE_HEAD.DIMS_PRIORS_ENABLED = False
+    shape = {f: ShapeSpec(channels=256, stride=s) for f, s in zip(["p2", "p3", "p4"], (7, 14, 28))}
+    head = build_roi_heads(c, shape)
+    head.cube_head.load_state_dict(synth.make_head_weights(77))
+    head = head.to(dev).eval()
+    feats = {f: t.to(dev) for f, t in zip(["p2", "p3", "p4"], inp.features)}
+    insts = []
+    for i in range(16):
+        inst = Instances((896, 896))
+        inst.pred_boxes = Boxes(inp.boxes[i].to(dev))
+        inst.pred_classes = inp.classes[i].to(dev)
+        inst.scores = inp.scores[i].to(dev)
+        insts.append(inst)
+    res = head._forward_cube(feats, insts, inp.Ks, inp.im_dims, inp.im_scales_ratio)
+    rec = head.last_records
+    assert rec.shape == (1600, 48) and torch.isfinite(rec).all()
+    R = rec[:, 32:41].view(-1, 3, 3)
+    eye = torch.eye(3, device=dev).expand_as(R)
+    assert torch.allclose(R @ R.transpose(1, 2), eye, atol=1e-4)           # rotations are orthonormal
+    assert torch.allclose(torch.linalg.det(R), torch.ones(1600, device=dev), atol=1e-4)
+    corners = rec[:, :24].view(-1, 8, 3)
+    assert torch.allclose(corners.mean(dim=1), rec[:, 24:27], rtol=1e-4, atol=1e-4)   # centroid of corners = centre
+    dims = rec[:, 29:32]                                                   # W, H, L
+    e_l = (corners[:, 1] - corners[:, 0]).norm(dim=1)                      # edge 0-1 runs along local x (L)
+    e_h = (corners[:, 3] - corners[:, 0]).norm(dim=1)                      # edge 0-3 along local y (H)
+    e_w = (corners[:, 4] - corners[:, 0]).norm(dim=1)                      # edge 0-4 along local z (W)
+    assert torch.allclose(torch.stack([e_w, e_h, e_l], 1), dims, rtol=1e-3, atol=1e-4)
+    # back-projection: centre re-projects to the predicted 2-D centre
+    for i in (0, 7, 15):
+        r = rec[100 * i:100 * (i + 1)]
+        K = inp.Ks[i].to(dev)
+        uv = (K @ r[:, 24:27].T).T
+        uv = uv[:, :2] / uv[:, 2:3]
+        assert torch.allclose(uv, r[:, 27:29], rtol=1e-3, atol=1e-2)
+    # running the same call again is bit-identical where no atomics are involved (decode) and close elsewhere
+    res2 = head._forward_cube(feats, insts, inp.Ks, inp.im_dims, inp.im_scales_ratio)
+    assert len(res2) == 16
