@@ -158,6 +158,13 @@ int ovm_lift_forward(const ovm_pooler_t* pooler, const ovm_fc_stack_t* fc, const
                      const float* scores, const int32_t* batch_idx, const float* cams, int32_t n,
                      const ovm_workspace_t* ws, float* records, float* raw, void* stream);
 
+/* Measurement hook (bench.py): while set, ovm_lift_forward records events[0] before its first launch and the
+ * next event after each stage -- ROIAlign, every FC layer in issue order (memset + split-K GEMM + bias/ReLU
+ * count as one layer), heads+decode -- on the stream it was given, up to `count` events.  Events are
+ * cudaEvent_t handles owned by the caller; count = 0 (or events = NULL) switches the hook off.  The hook is
+ * per host thread and adds no synchronisation.                                                           */
+int ovm_set_stage_events(void* const* events, int32_t count);
+
 int ovm_abi_version(void);
 /* sizeof() of the ABI structs as this library was compiled, for binding self-checks:
  * 0 ovm_level_t, 1 ovm_pooler_t, 2 ovm_decode_cfg_t, 3 ovm_head_weights_t, 4 ovm_fc_layer_t,

@@ -14,6 +14,16 @@ std::atomic<int64_t> g_launches{0};
 
 namespace {
 thread_local char g_error[512] = "";
+constexpr int kMaxStageEvents = 32;
+thread_local cudaEvent_t g_stage_events[kMaxStageEvents];
+thread_local int g_num_stage_events = 0;
+
+// bench.py's per-stage timing hook (ovm_set_stage_events): record the idx-th event if one was supplied
+int stage_mark(int& idx, cudaStream_t stream) {
+  if (idx < g_num_stage_events) OVM_CUDA(cudaEventRecord(g_stage_events[idx], stream));
+  ++idx;
+  return OVM_OK;
+}
 }
 
 void set_error(const char* fmt, ...) {
@@ -28,7 +38,7 @@ namespace {
 // One FC stack (cube_head.py:64-74): every layer is Linear + ReLU.  The last layer's output is the fp32
 // feature block `feats[:, col0 : col0 + N]`; earlier layers ping-pong through bf16 activations.
 int run_fc_group(const ovm_fc_layer_t* layers, int num_fc, const void* x, int64_t ldx, int32_t n,
-                 const ovm_workspace_t* ws, float* feats, int64_t ld_feats, cudaStream_t stream) {
+                 const ovm_workspace_t* ws, float* feats, int64_t ld_feats, cudaStream_t stream, int& stage) {
   const void* in = x;
   int64_t ld_in = ldx;
   for (int k = 0; k < num_fc; ++k) {
@@ -64,6 +74,8 @@ int run_fc_group(const ovm_fc_layer_t* layers, int num_fc, const void* x, int64_
     }
     in = out;
     ld_in = ldo;
+    int rc = stage_mark(stage, stream);
+    if (rc != OVM_OK) return rc;
   }
   return OVM_OK;
 }
@@ -94,6 +106,15 @@ int ovm_struct_size(int which) {
 }
 
 int64_t ovm_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+int ovm_set_stage_events(void* const* events, int32_t count) {
+  OVM_REQUIRE(count >= 0 && count <= kMaxStageEvents, "ovm_set_stage_events: count %d not in [0,%d]", count,
+              kMaxStageEvents);
+  OVM_REQUIRE(count == 0 || events, "ovm_set_stage_events: events is NULL");
+  for (int i = 0; i < count; ++i) g_stage_events[i] = static_cast<cudaEvent_t>(events[i]);
+  g_num_stage_events = events ? count : 0;
+  return OVM_OK;
+}
 
 int ovm_roi_align(const ovm_pooler_t* pooler, const float* boxes, const int32_t* batch_idx, int32_t n, void* out,
                   int32_t out_dtype, int64_t out_ld, int32_t* level_out, void* stream) {
@@ -140,7 +161,12 @@ int ovm_lift_forward(const ovm_pooler_t* pooler, const ovm_fc_stack_t* fc, const
   OVM_REQUIRE(ws->pooled && ws->feats && ws->ld_pooled >= k_in && ws->ld_pooled % 8 == 0,
               "ovm_lift_forward: workspace.pooled must be [n, ld_pooled >= C*P*P], ld_pooled %% 8 == 0");
   OVM_REQUIRE(fc->num_fc == 1 || (ws->act_a && ws->act_b), "ovm_lift_forward: workspace.act_a/act_b missing");
-  int rc = roi_align_launch(pooler, boxes, batch_idx, n, ws->pooled, OVM_BF16, ws->ld_pooled, ws->levels, stream);
+  int stage = 0;
+  int rc = stage_mark(stage, stream);
+  if (rc != OVM_OK) return rc;
+  rc = roi_align_launch(pooler, boxes, batch_idx, n, ws->pooled, OVM_BF16, ws->ld_pooled, ws->levels, stream);
+  if (rc != OVM_OK) return rc;
+  rc = stage_mark(stage, stream);
   if (rc != OVM_OK) return rc;
   // fc1 reads only the first C*P*P columns of each pooled row (its TMA map is K wide), so the pad is never touched
   const int64_t ld_feats = (int64_t)fc->num_groups * cfg->fc_dim;
@@ -150,11 +176,13 @@ int ovm_lift_forward(const ovm_pooler_t* pooler, const ovm_fc_stack_t* fc, const
                 layers[0].K, (long long)k_in);
     OVM_REQUIRE(layers[fc->num_fc - 1].N == cfg->fc_dim, "ovm_lift_forward: last FC width != cfg.fc_dim");
     rc = run_fc_group(layers, fc->num_fc, ws->pooled, ws->ld_pooled, n, ws, ws->feats + (size_t)g * cfg->fc_dim,
-                      ld_feats, stream);
+                      ld_feats, stream, stage);
     if (rc != OVM_OK) return rc;
   }
-  return head_decode_launch(cfg, heads, ws->feats, ld_feats, boxes, classes, scores, batch_idx, cams,
-                            pooler->num_images, n, records, raw, stream);
+  rc = head_decode_launch(cfg, heads, ws->feats, ld_feats, boxes, classes, scores, batch_idx, cams,
+                          pooler->num_images, n, records, raw, stream);
+  if (rc != OVM_OK) return rc;
+  return stage_mark(stage, stream);
 }
 
 }  // extern "C"

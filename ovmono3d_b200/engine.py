@@ -169,12 +169,19 @@ class LiftEngine:
     # ------------------------------------------------------------------ forward
     def forward(self, features: Sequence[torch.Tensor], boxes: torch.Tensor, classes: torch.Tensor,
                 scores: Optional[torch.Tensor], batch_idx: torch.Tensor, cams: torch.Tensor,
-                want_raw: bool = False) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
-        """-> (records [n, 48] fp32, raw [n, 16] or None).  `prepare` must have been called."""
+                want_raw: bool = False, out: Optional[torch.Tensor] = None
+                ) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+        """-> (records [n, 48] fp32, raw [n, 16] or None).  `prepare` must have been called.  `out` (optional,
+        contiguous fp32 [n, 48] on the same device) receives the records instead of a fresh tensor."""
         lib = ops.load_library()
         n = boxes.shape[0]
         device = boxes.device
-        records = torch.empty((n, ops.RECORD_WIDTH), device=device, dtype=torch.float32)
+        if out is not None:
+            if out.shape != (n, ops.RECORD_WIDTH) or not out.is_contiguous() or out.device != device:
+                raise ops.LiftError("out must be a contiguous [n, %d] tensor on %s" % (ops.RECORD_WIDTH, device))
+            records = ops._need_cuda(out, "out", torch.float32)
+        else:
+            records = torch.empty((n, ops.RECORD_WIDTH), device=device, dtype=torch.float32)
         raw = torch.empty((n, 16), device=device, dtype=torch.float32) if want_raw else None
         if n == 0:
             return records, raw

@@ -32,7 +32,7 @@ REC_SCORE = 45
 REC_CLASS = 46
 
 EXPORTS = ("ovm_abi_version", "ovm_last_error", "ovm_launch_count", "ovm_struct_size", "ovm_roi_align", "ovm_gemm_bf16",
-           "ovm_bias_act", "ovm_cast_bf16", "ovm_head_decode", "ovm_lift_forward")
+           "ovm_bias_act", "ovm_cast_bf16", "ovm_head_decode", "ovm_lift_forward", "ovm_set_stage_events")
 
 
 class LiftError(RuntimeError):
@@ -111,6 +111,7 @@ def load_library() -> C.CDLL:
     lib.ovm_lift_forward.argtypes = [C.POINTER(ovm_pooler_t), C.POINTER(ovm_fc_stack_t), C.POINTER(ovm_decode_cfg_t),
                                      C.POINTER(ovm_head_weights_t), vp, vp, vp, vp, vp, i32,
                                      C.POINTER(ovm_workspace_t), vp, vp, vp]
+    lib.ovm_set_stage_events.argtypes = [C.POINTER(C.c_void_p), i32]
     for name in EXPORTS[3:]:
         getattr(lib, name).restype = C.c_int
     lib.ovm_struct_size.argtypes = [C.c_int]
@@ -124,6 +125,17 @@ def load_library() -> C.CDLL:
 
 def launch_count() -> int:
     return int(load_library().ovm_launch_count())
+
+
+def set_stage_events(events: Optional[Sequence["torch.cuda.Event"]]) -> None:
+    """bench.py's per-stage timing hook: `ovm_lift_forward` records these events between its stages (see the
+    header).  The events must have been recorded once already so that their CUDA handles exist."""
+    lib = load_library()
+    if not events:
+        _check(lib.ovm_set_stage_events(None, 0), "ovm_set_stage_events")
+        return
+    arr = (C.c_void_p * len(events))(*[e.cuda_event for e in events])
+    _check(lib.ovm_set_stage_events(arr, len(events)), "ovm_set_stage_events")
 
 
 def _check(rc: int, what: str) -> None:

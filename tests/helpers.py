@@ -29,7 +29,29 @@ def lift_config(case: gc.Case) -> lo.LiftConfig:
     )
 
 
-def run_oracle(case: gc.Case):
+def _fc_stack_bf16_operands(w, prefix, x):
+    """`lift_oracle._fc_stack` with both operands of every Linear rounded to bf16 (round-to-nearest-even) and the
+    products summed exactly (fp64), which is what the tcgen05 GEMMs compute up to fp32 summation order: the
+    kernel-correctness oracle for the bf16 head, separate from the error of the number format itself."""
+    import torch.nn.functional as F
+
+    k = 1
+    while f"{prefix}.fc{k}.weight" in w:
+        a = x.bfloat16().double()
+        wt = w[f"{prefix}.fc{k}.weight"].bfloat16().double()
+        x = F.relu(F.linear(a, wt, w[f"{prefix}.fc{k}.bias"].double())).float()
+        k += 1
+    return x
+
+
+def run_oracle(case: gc.Case, bf16_operands: bool = False):
+    if bf16_operands:
+        saved = lo._fc_stack
+        lo._fc_stack = _fc_stack_bf16_operands
+        try:
+            return run_oracle(case)
+        finally:
+            lo._fc_stack = saved
     inp, weights, priors = gc.build_case(case)
     cfg = lift_config(case)
     kw = {}
