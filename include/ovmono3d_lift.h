@@ -87,6 +87,13 @@ int ovm_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t ldb, int32_
                   const float* bias, int32_t relu, void* out, int32_t out_dtype, int64_t ldo,
                   int32_t mode, int32_t* mode_used, void* stream);
 
+/* Tracing hook (tools/gemm_trace.py): while buf != NULL every ovm_gemm_bf16 launched from this host thread writes
+ * sixteen %globaltimer stamps (ns) per CTA into buf[cta*16 + k], buf sized for the largest grid (<= 4096 CTAs):
+ * 0 kernel entry, 1 set-up done (barriers, TMEM), 2 last TMA issued, 3 first operand tile landed, 4 last MMA
+ * issued, 5 last accumulator ready, 6 epilogue done, 7 before TMEM release, 8..15 the first eight 32-column
+ * chunks of the last accumulator read out of TMEM.  NULL switches it off.                                     */
+int ovm_gemm_set_trace(uint64_t* buf);
+
 /* out[m, j] = act(in[m, j] + bias[j]) for j < N; in fp32 [M, ldi], out out_dtype [M, ldo]. */
 int ovm_bias_act(const float* in, int64_t ldi, const float* bias, int32_t relu, int32_t M, int32_t N,
                  void* out, int32_t out_dtype, int64_t ldo, void* stream);

@@ -54,6 +54,7 @@ int roi_align_launch(const ovm_pooler_t* pooler, const float* boxes, const int32
 int gemm_bf16_launch(const void* A, int64_t lda, const void* B, int64_t ldb, int32_t M, int32_t N, int32_t K,
                      const float* bias, int32_t relu, void* out, int32_t out_dtype, int64_t ldo, int32_t mode,
                      int32_t* mode_used, cudaStream_t stream);
+void gemm_set_trace(unsigned long long* buf);
 int bias_act_launch(const float* in, int64_t ldi, const float* bias, int32_t relu, int32_t M, int32_t N,
                     void* out, int32_t out_dtype, int64_t ldo, cudaStream_t stream);
 int cast_bf16_launch(const float* in, int64_t ld_in, int32_t rows, int32_t cols, void* out, int64_t ld_out,

@@ -30,7 +30,11 @@ namespace {
 constexpr int BM = 128;
 constexpr int BK = 64;            // 64 bf16 = 128 bytes = one swizzle row
 constexpr int UMMA_K = 16;
-constexpr int kGemmThreads = 192;
+constexpr int kEpiWarps = 8;          // two per TMEM lane quadrant, each takes half of the tile's columns
+constexpr int kGemmThreads = (2 + kEpiWarps) * 32;
+constexpr int kChunk = 16;            // accumulator columns per tcgen05.ld
+constexpr int kStgFloats = 32 * kChunk;   // swizzled 32 x 16 fp32 transpose tile per epilogue warp
+enum { kModeF32 = 0, kModeBF16 = 1, kModeStreamK = 2 };
 
 template <int BN>
 struct GemmShape {
@@ -40,7 +44,8 @@ struct GemmShape {
   static constexpr int kStages = BN == 256 ? 4 : (BN == 128 ? 6 : 8);
   static constexpr int kTmemCols = BN * 2 < 32 ? 32 : BN * 2;   // two accumulator stages
   static constexpr int kBarrierBytes = (2 * kStages + 4) * 8 + 16;
-  static constexpr size_t kSmemBytes = 1024 + (size_t)kStages * kStageBytes + kBarrierBytes;
+  static constexpr int kStgBytes = kEpiWarps * kStgFloats * 4;    // epilogue transpose tiles, one per warp
+  static constexpr size_t kSmemBytes = 1024 + (size_t)kStages * kStageBytes + kBarrierBytes + kStgBytes;
 };
 
 struct GemmArgs {
@@ -53,7 +58,18 @@ struct GemmArgs {
   const float* bias;
   void* out;
   long long ldo;
+  unsigned long long* trace;   // optional [grid, 16] globaltimer stamps (ovm_gemm_set_trace), else NULL
 };
+
+thread_local unsigned long long* g_gemm_trace = nullptr;
+
+__device__ __forceinline__ void trace_stamp(const GemmArgs& g, int slot) {
+  if (g.trace) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    g.trace[(size_t)blockIdx.x * 16 + slot] = t;
+  }
+}
 
 // ------------------------------------------------------------------ PTX wrappers
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
@@ -113,6 +129,16 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* v) {
       : "memory");
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* v) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
 __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
@@ -162,7 +188,7 @@ struct WorkIter {
   }
 };
 
-template <int BN>
+template <int BN, int MODE>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmArgs g) {
   using Sh = GemmShape<BN>;
@@ -177,9 +203,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const uint32_t tfull_bar = bars + 16 * Sh::kStages;     // 2
   const uint32_t tempty_bar = tfull_bar + 16;             // 2
   const uint32_t tmem_slot = tempty_bar + 16;
+  const uint32_t stage_buf = tmem_slot + 16;
   uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - raw));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) trace_stamp(g, 0);
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
@@ -192,7 +220,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(tfull_bar + 8 * s, 1);
-      mbar_init(tempty_bar + 8 * s, 4);   // one arrive per epilogue warp
+      mbar_init(tempty_bar + 8 * s, kEpiWarps);   // one arrive per epilogue warp
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -205,6 +233,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
+  if (threadIdx.x == 0) trace_stamp(g, 1);
 
   if (warp == 0) {
     if (lane == 0) {
@@ -225,6 +254,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           }
         }
       }
+      trace_stamp(g, 2);   // last TMA issued
     }
   } else if (warp == 1) {
     if (lane == 0) {
@@ -236,6 +266,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
+      bool first = true;
       while (it.next(s)) {
         mbar_wait(tempty_bar + 8 * acc, acc_phase ^ 1);
         tcgen05_fence_after();
@@ -243,6 +274,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         for (int kb = s.k0; kb < s.k1; ++kb) {
           mbar_wait(full_bar + 8 * stage, phase);
           tcgen05_fence_after();
+          if (first) {
+            trace_stamp(g, 3);   // first operand tile landed
+            first = false;
+          }
           const uint64_t adesc = make_smem_desc(smem_a + stage * Sh::kABytes);
           const uint64_t bdesc = make_smem_desc(smem_b + stage * Sh::kBBytes);
 #pragma unroll
@@ -260,10 +295,23 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1;
       }
+      trace_stamp(g, 4);   // last MMA issued
     }
   } else {
-    // ===== epilogue warps: TMEM lane quadrant = warp % 4
+    // ===== epilogue warps: TMEM lane quadrant = warp % 4, column half = (warp - 2) / 4
+    // tcgen05.ld hands lane r the columns of accumulator row r.  Storing that directly scatters every warp store
+    // over 32 output rows (measured: 17 us for one 128 x 256 fp32 tile).  Each 32 x 16 chunk is transposed
+    // through a swizzled shared-memory tile instead (16-byte unit k of row r lives at unit k ^ ((r >> 1) & 3), so
+    // both the row-wise 128-bit writes and the 8-rows-by-4-units 128-bit reads are bank-conflict free); after the
+    // transpose lane (q, l4) owns columns 4*l4..4*l4+3 of rows q, q+8, q+16, q+24 and one warp instruction
+    // writes eight 64-byte row segments.  Bias / ReLU are applied there.  MODE is a template parameter and the
+    // full-chunk case has no per-element predicates: with one warp per scheduler the epilogue is bound by
+    // instruction latency, not by bytes.
     const int quad = warp & 3;
+    const int half = (warp - 2) >> 2;
+    float* stg = reinterpret_cast<float*>(smem_raw + (stage_buf - raw)) + (warp - 2) * kStgFloats;
+    const int q = lane >> 2, l4 = lane & 3;
+    constexpr int kChunksPerWarp = BN / kChunk / 2;
     WorkIter it(g);
     Segment s;
     int acc = 0;
@@ -271,67 +319,72 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     while (it.next(s)) {
       mbar_wait(tfull_bar + 8 * acc, acc_phase);
       tcgen05_fence_after();
-      const int row = s.m_tile * BM + quad * 32 + lane;
-      const bool row_ok = row < g.M;
+      if (threadIdx.x == 64) trace_stamp(g, 5);   // (last) accumulator ready
+      const int row0 = s.m_tile * BM + quad * 32;
+      const bool rows_full = row0 + 32 <= g.M;
 #pragma unroll 1
-      for (int ch = 0; ch < BN / 32; ++ch) {
-        uint32_t v[32];
-        __syncwarp();   // tcgen05.ld is .sync.aligned: reconverge after the predicated stores below
-        tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN + ch * 32), v);
-        const int col0 = s.n_tile * BN + ch * 32;
-        if (!row_ok || col0 >= g.N) continue;
-        const bool full = col0 + 32 <= g.N;
-        if (g.streamk) {
-          float* dst = reinterpret_cast<float*>(g.out) + (long long)row * g.ldo + col0;
+      for (int ci = 0; ci < kChunksPerWarp; ++ci) {
+        const int ch = half * kChunksPerWarp + ci;
+        uint32_t v[kChunk];
+        __syncwarp();   // tcgen05.ld is .sync.aligned; also: the previous chunk's readers are done with stg
+        tmem_ld16(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN + ch * kChunk), v);
+        const int col0 = s.n_tile * BN + ch * kChunk;
+        if (threadIdx.x == 64 && ci < 8) trace_stamp(g, 8 + ci);   // chunk left TMEM
+        if (row0 >= g.M || col0 >= g.N) continue;   // warp-uniform
+        {
+          float4* wr = reinterpret_cast<float4*>(stg + lane * kChunk);
+          const int sw = (lane >> 1) & 3;
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            wr[k ^ sw] = make_float4(__uint_as_float(v[4 * k]), __uint_as_float(v[4 * k + 1]),
+                                     __uint_as_float(v[4 * k + 2]), __uint_as_float(v[4 * k + 3]));
+        }
+        __syncwarp();
+        const int c = col0 + 4 * l4;
+        const bool full = rows_full && col0 + kChunk <= g.N;   // warp-uniform
+        float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (MODE != kModeStreamK && g.bias) {
+          if (c + 3 < g.N) bv = __ldg(reinterpret_cast<const float4*>(g.bias + c));
+          else {
+            if (c < g.N) bv.x = __ldg(g.bias + c);
+            if (c + 1 < g.N) bv.y = __ldg(g.bias + c + 1);
+            if (c + 2 < g.N) bv.z = __ldg(g.bias + c + 2);
+          }
+        }
+        const bool relu = MODE != kModeStreamK && g.relu;
+#pragma unroll
+        for (int rr = 0; rr < 32; rr += 8) {
+          const int r = rr + q;
+          float4 x = reinterpret_cast<const float4*>(stg + r * kChunk)[l4 ^ ((r >> 1) & 3)];
+          if (MODE != kModeStreamK) {
+            x.x += bv.x; x.y += bv.y; x.z += bv.z; x.w += bv.w;
+            // torch.relu keeps NaN: compare-and-select, not fmaxf
+            x.x = (relu && x.x < 0.f) ? 0.f : x.x;
+            x.y = (relu && x.y < 0.f) ? 0.f : x.y;
+            x.z = (relu && x.z < 0.f) ? 0.f : x.z;
+            x.w = (relu && x.w < 0.f) ? 0.f : x.w;
+          }
+          const long long off = (long long)(row0 + r) * g.ldo + c;
           if (full) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j)
-              red_add_v4(dst + 4 * j, __uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]),
-                         __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
-          } else {
-#pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (col0 + j < g.N) atomicAdd(dst + j, __uint_as_float(v[j]));
-          }
-        } else {
-          float f[32];
-#pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            float x = __uint_as_float(v[j]);
-            if (g.bias && (full || col0 + j < g.N)) x += __ldg(g.bias + col0 + j);
-            f[j] = g.relu ? fmaxf(x, 0.f) : x;
-          }
-          if (g.out_bf16) {
-            __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(g.out) + (long long)row * g.ldo + col0;
-            if (full) {
-#pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                uint4 pk;
-                __nv_bfloat162 t0 = __floats2bfloat162_rn(f[8 * j + 0], f[8 * j + 1]);
-                __nv_bfloat162 t1 = __floats2bfloat162_rn(f[8 * j + 2], f[8 * j + 3]);
-                __nv_bfloat162 t2 = __floats2bfloat162_rn(f[8 * j + 4], f[8 * j + 5]);
-                __nv_bfloat162 t3 = __floats2bfloat162_rn(f[8 * j + 6], f[8 * j + 7]);
-                pk.x = *reinterpret_cast<uint32_t*>(&t0);
-                pk.y = *reinterpret_cast<uint32_t*>(&t1);
-                pk.z = *reinterpret_cast<uint32_t*>(&t2);
-                pk.w = *reinterpret_cast<uint32_t*>(&t3);
-                *reinterpret_cast<uint4*>(dst + 8 * j) = pk;
-              }
+            if (MODE == kModeStreamK) {
+              red_add_v4(reinterpret_cast<float*>(g.out) + off, x.x, x.y, x.z, x.w);
+            } else if (MODE == kModeF32) {
+              *reinterpret_cast<float4*>(reinterpret_cast<float*>(g.out) + off) = x;
             } else {
-#pragma unroll
-              for (int j = 0; j < 32; ++j)
-                if (col0 + j < g.N) dst[j] = __float2bfloat16_rn(f[j]);
+              __nv_bfloat162 lo = __floats2bfloat162_rn(x.x, x.y), hi = __floats2bfloat162_rn(x.z, x.w);
+              uint2 pk;
+              pk.x = *reinterpret_cast<uint32_t*>(&lo);
+              pk.y = *reinterpret_cast<uint32_t*>(&hi);
+              *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(g.out) + off) = pk;
             }
-          } else {
-            float* dst = reinterpret_cast<float*>(g.out) + (long long)row * g.ldo + col0;
-            if (full) {
+          } else if (row0 + r < g.M) {   // tile edge: element-wise
+            const float xs[4] = {x.x, x.y, x.z, x.w};
 #pragma unroll
-              for (int j = 0; j < 8; ++j)
-                *reinterpret_cast<float4*>(dst + 4 * j) = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
-            } else {
-#pragma unroll
-              for (int j = 0; j < 32; ++j)
-                if (col0 + j < g.N) dst[j] = f[j];
+            for (int e = 0; e < 4; ++e) {
+              if (c + e >= g.N) continue;
+              if (MODE == kModeStreamK) atomicAdd(reinterpret_cast<float*>(g.out) + off + e, xs[e]);
+              else if (MODE == kModeF32) reinterpret_cast<float*>(g.out)[off + e] = xs[e];
+              else reinterpret_cast<__nv_bfloat16*>(g.out)[off + e] = __float2bfloat16_rn(xs[e]);
             }
           }
         }
@@ -342,10 +395,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1;
     }
+    if (threadIdx.x == 64) trace_stamp(g, 6);     // epilogue done
   }
 
   tcgen05_fence_before();
   __syncthreads();
+  if (threadIdx.x == 0) trace_stamp(g, 7);
   if (warp == 2) {
     tcgen05_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)Sh::kTmemCols) : "memory");
@@ -365,8 +420,8 @@ __global__ void bias_act_kernel(const float* __restrict__ in, long long ldi, con
     const float4 b = *reinterpret_cast<const float4*>(bias + j);
     v.x += b.x; v.y += b.y; v.z += b.z; v.w += b.w;
   }
-  if (relu) {
-    v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f);
+  if (relu) {   // torch.relu keeps NaN
+    v.x = v.x < 0.f ? 0.f : v.x; v.y = v.y < 0.f ? 0.f : v.y; v.z = v.z < 0.f ? 0.f : v.z; v.w = v.w < 0.f ? 0.f : v.w;
   }
   if (out_bf16) {
     __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y), b = __floats2bfloat162_rn(v.z, v.w);
@@ -427,17 +482,24 @@ int make_map(CUtensorMap* map, const void* ptr, int64_t rows, int64_t cols, int6
   return OVM_OK;
 }
 
-template <int BN>
-int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& g, int grid, cudaStream_t stream) {
+template <int BN, int MODE>
+int launch_gemm_mode(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& g, int grid, cudaStream_t stream) {
   static bool attr_done = false;
   if (!attr_done) {
-    OVM_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    OVM_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel<BN, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)GemmShape<BN>::kSmemBytes));
     attr_done = true;
   }
-  gemm_bf16_kernel<BN><<<grid, kGemmThreads, GemmShape<BN>::kSmemBytes, stream>>>(tmA, tmB, g);
+  gemm_bf16_kernel<BN, MODE><<<grid, kGemmThreads, GemmShape<BN>::kSmemBytes, stream>>>(tmA, tmB, g);
   OVM_LAUNCHED("gemm_bf16_kernel");
   return OVM_OK;
+}
+
+template <int BN>
+int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& g, int grid, cudaStream_t stream) {
+  if (g.streamk) return launch_gemm_mode<BN, kModeStreamK>(tmA, tmB, g, grid, stream);
+  if (g.out_bf16) return launch_gemm_mode<BN, kModeBF16>(tmA, tmB, g, grid, stream);
+  return launch_gemm_mode<BN, kModeF32>(tmA, tmB, g, grid, stream);
 }
 
 }  // namespace
@@ -484,6 +546,7 @@ int gemm_bf16_launch(const void* A, int64_t lda, const void* B, int64_t ldb, int
   g.bias = bias;
   g.out = out;
   g.ldo = ldo;
+  g.trace = g_gemm_trace;
   CUtensorMap tmA, tmB;
   int rc = make_map(&tmA, A, M, K, lda, BM);
   if (rc != OVM_OK) return rc;
@@ -497,6 +560,8 @@ int gemm_bf16_launch(const void* A, int64_t lda, const void* B, int64_t ldb, int
     default: return launch_gemm<64>(tmA, tmB, g, grid, stream);
   }
 }
+
+void gemm_set_trace(unsigned long long* buf) { g_gemm_trace = buf; }
 
 int bias_act_launch(const float* in, int64_t ldi, const float* bias, int32_t relu, int32_t M, int32_t N, void* out,
                     int32_t out_dtype, int64_t ldo, cudaStream_t stream) {

@@ -25,7 +25,7 @@ namespace ovm {
 
 namespace {
 
-constexpr int kWarpsPerBlock = 8;
+constexpr int kWarpsPerBlock = 4;
 
 struct DecodeArgs {
   ovm_decode_cfg_t cfg;
@@ -48,25 +48,44 @@ __device__ __forceinline__ float warp_sum(float v) {
   return v;
 }
 
-// <w_row, feat> + bias over K elements; every lane returns the full sum.
-__device__ __forceinline__ float head_dot(const float* __restrict__ w_row, const float* __restrict__ feat, int K,
-                                          float bias, int lane, bool vec4) {
-  float acc = 0.f;
+constexpr int kMaxRows = 13;   // deltas 2 + dims 3 + pose <= 6 + z 1 + uncertainty 1
+
+// All selected head rows in one pass over the feature vector(s): out[r] = <w[r], f[r]> + bias[r].
+// Lane i owns float4 i, i+32, ... of every row, so the loads of one row are coalesced across the warp and the
+// kMaxRows accumulation chains are independent (the loop is load-latency bound otherwise).  With SHARED the rows
+// all read the same feature vector and it is loaded once.  Every lane returns every sum.
+template <bool SHARED>
+__device__ __forceinline__ void head_rows(const float* const (&w)[kMaxRows], const float* const (&f)[kMaxRows],
+                                          const float (&bias)[kMaxRows], int nrows, int K, int lane, bool vec4,
+                                          float (&out)[kMaxRows]) {
+  float acc[kMaxRows];
+#pragma unroll
+  for (int r = 0; r < kMaxRows; ++r) acc[r] = 0.f;
   if (vec4) {
-    const float4* w4 = reinterpret_cast<const float4*>(w_row);
-    const float4* f4 = reinterpret_cast<const float4*>(feat);
     for (int i = lane; i < (K >> 2); i += 32) {
-      const float4 a = __ldg(w4 + i);
-      const float4 b = f4[i];
-      acc = fmaf(a.x, b.x, acc);
-      acc = fmaf(a.y, b.y, acc);
-      acc = fmaf(a.z, b.z, acc);
-      acc = fmaf(a.w, b.w, acc);
+      float4 fs = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (SHARED) fs = reinterpret_cast<const float4*>(f[0])[i];
+#pragma unroll
+      for (int r = 0; r < kMaxRows; ++r) {
+        if (r < nrows) {
+          const float4 a = __ldg(reinterpret_cast<const float4*>(w[r]) + i);
+          const float4 b = SHARED ? fs : reinterpret_cast<const float4*>(f[r])[i];
+          acc[r] = fmaf(a.x, b.x, acc[r]);
+          acc[r] = fmaf(a.y, b.y, acc[r]);
+          acc[r] = fmaf(a.z, b.z, acc[r]);
+          acc[r] = fmaf(a.w, b.w, acc[r]);
+        }
+      }
     }
   } else {
-    for (int i = lane; i < K; i += 32) acc = fmaf(__ldg(w_row + i), feat[i], acc);
+    for (int i = lane; i < K; i += 32) {
+#pragma unroll
+      for (int r = 0; r < kMaxRows; ++r)
+        if (r < nrows) acc[r] = fmaf(__ldg(w[r] + i), f[r][i], acc[r]);
+    }
   }
-  return warp_sum(acc) + bias;
+#pragma unroll
+  for (int r = 0; r < kMaxRows; ++r) out[r] = warp_sum(acc[r]) + bias[r];
 }
 
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + expf(-x)); }
@@ -121,39 +140,15 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) head_decode_kernel(const 
   const float virtual_to_real = cfg.virtual_depth ? (h_cur * focal) / (cfg.virtual_focal * h_orig) : 1.f;
 
   const float* frow = a.feats + (long long)box * a.ld_feats;
-  const bool vec4 = (K & 3) == 0 && (a.ld_feats & 3) == 0 && ((reinterpret_cast<uintptr_t>(a.feats) & 15) == 0);
-  const float* f_deltas = frow + cfg.feat_offset[0];
-  const float* f_dims = frow + cfg.feat_offset[1];
-  const float* f_pose = frow + cfg.feat_offset[2];
-  const float* f_z = frow + cfg.feat_offset[3];
-  const float* f_unc = frow + cfg.feat_offset[4];
-  // a feature vector that does not start on a 16-byte boundary falls back to scalar loads
-  const bool v_deltas = vec4 && !(cfg.feat_offset[0] & 3), v_dims = vec4 && !(cfg.feat_offset[1] & 3);
-  const bool v_pose = vec4 && !(cfg.feat_offset[2] & 3), v_z = vec4 && !(cfg.feat_offset[3] & 3);
-  const bool v_unc = vec4 && !(cfg.feat_offset[4] & 3);
+  bool vec4 = (K & 3) == 0 && (a.ld_feats & 3) == 0 && ((reinterpret_cast<uintptr_t>(a.feats) & 15) == 0);
+  bool shared = true;
+#pragma unroll
+  for (int i = 0; i < 5; ++i) {
+    vec4 = vec4 && !(cfg.feat_offset[i] & 3);   // a vector off a 16-byte boundary: scalar loads
+    shared = shared && cfg.feat_offset[i] == cfg.feat_offset[0];
+  }
 
-  // ---- heads: only the rows [fg, box_classes] keeps (roi_heads.py:452-477)
-  float deltas[2], dims_raw[3], pose_raw[6];
-#pragma unroll
-  for (int j = 0; j < 2; ++j) {
-    const int row = csel * 2 + j;
-    deltas[j] = head_dot(a.w.w_deltas + (long long)row * K, f_deltas, K, a.w.b_deltas[row], lane, v_deltas);
-  }
-#pragma unroll
-  for (int j = 0; j < 3; ++j) {
-    const int row = csel * 3 + j;
-    dims_raw[j] = head_dot(a.w.w_dims + (long long)row * K, f_dims, K, a.w.b_dims[row], lane, v_dims);
-  }
-  const int pose_n = cfg.pose_type == OVM_POSE_6D ? 6 : (cfg.pose_type == OVM_POSE_QUATERNION ? 4 : 3);
-#pragma unroll
-  for (int j = 0; j < 6; ++j) {
-    pose_raw[j] = 0.f;
-    if (j < pose_n) {
-      const int row = csel * pose_n + j;
-      pose_raw[j] = head_dot(a.w.w_pose + (long long)row * K, f_pose, K, a.w.b_pose[row], lane, v_pose);
-    }
-  }
-  // depth bin: nearest priors_z_scales[class, bin] to the 2-D diagonal, first minimum wins (roi_heads.py:436-444)
+  // depth bin: nearest priors_z_scales[class, bin] to the 2-D diagonal (roi_heads.py:436-444)
   int bin = 0;
   if (cfg.cluster_bins > 1) {
     // torch.argmin: first minimum wins, and a NaN counts as smaller than everything
@@ -166,14 +161,68 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) head_decode_kernel(const 
       }
     }
   }
+
+  // ---- heads: only the rows [fg, box_classes] keeps (roi_heads.py:452-477), all in one pass.
+  // row order: deltas 0-1, dims 2-4, z 5, uncertainty 6 (if any), pose after that
+  const int pose_n = cfg.pose_type == OVM_POSE_6D ? 6 : (cfg.pose_type == OVM_POSE_QUATERNION ? 4 : 3);
   // box_z.view(n, bins, C, -1)[i, bin, class] / view(n, C, -1)[i, class] (cube_head.py:192-201)
   const int z_row = cfg.cluster_bins > 1 ? bin * NC + cls : csel;
-  const float z_raw = head_dot(a.w.w_z + (long long)z_row * K, f_z, K, a.w.b_z[z_row], lane, v_z);
-  float uncert = 0.f;
-  if (cfg.use_confidence) {
-    uncert = head_dot(a.w.w_uncert + (long long)csel * K, f_unc, K, a.w.b_uncert[csel], lane, v_unc);
-    uncert = clip_min(uncert, 0.01f);  // .clip(0.01), cube_head.py:164
+  const float* wr[kMaxRows];
+  const float* fr[kMaxRows];
+  float bs[kMaxRows], hv[kMaxRows];
+#pragma unroll
+  for (int r = 0; r < kMaxRows; ++r) {
+    wr[r] = a.w.w_deltas;
+    fr[r] = frow;
+    bs[r] = 0.f;
   }
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    wr[j] = a.w.w_deltas + (long long)(csel * 2 + j) * K;
+    fr[j] = frow + cfg.feat_offset[0];
+    bs[j] = a.w.b_deltas[csel * 2 + j];
+  }
+#pragma unroll
+  for (int j = 0; j < 3; ++j) {
+    wr[2 + j] = a.w.w_dims + (long long)(csel * 3 + j) * K;
+    fr[2 + j] = frow + cfg.feat_offset[1];
+    bs[2 + j] = a.w.b_dims[csel * 3 + j];
+  }
+  wr[5] = a.w.w_z + (long long)z_row * K;
+  fr[5] = frow + cfg.feat_offset[3];
+  bs[5] = a.w.b_z[z_row];
+  const int conf_rows = cfg.use_confidence ? 1 : 0;
+  if (conf_rows) {
+    wr[6] = a.w.w_uncert + (long long)csel * K;
+    fr[6] = frow + cfg.feat_offset[4];
+    bs[6] = a.w.b_uncert[csel];
+  }
+#pragma unroll
+  for (int j = 0; j < 6; ++j) {
+    if (j < pose_n) {
+      // 6 + conf_rows + j, written so that the register arrays keep compile-time indices
+      const float* wp = a.w.w_pose + (long long)(csel * pose_n + j) * K;
+      const float bp = a.w.b_pose[csel * pose_n + j];
+      if (conf_rows) {
+        wr[7 + j] = wp; fr[7 + j] = frow + cfg.feat_offset[2]; bs[7 + j] = bp;
+      } else {
+        wr[6 + j] = wp; fr[6 + j] = frow + cfg.feat_offset[2]; bs[6 + j] = bp;
+      }
+    }
+  }
+  const int nrows = 6 + conf_rows + pose_n;
+  if (shared)
+    head_rows<true>(wr, fr, bs, nrows, K, lane, vec4, hv);
+  else
+    head_rows<false>(wr, fr, bs, nrows, K, lane, vec4, hv);
+  const float deltas[2] = {hv[0], hv[1]};
+  const float dims_raw[3] = {hv[2], hv[3], hv[4]};
+  const float z_raw = hv[5];
+  float uncert = 0.f;
+  if (conf_rows) uncert = clip_min(hv[6], 0.01f);  // .clip(0.01), cube_head.py:164
+  float pose_raw[6];
+#pragma unroll
+  for (int j = 0; j < 6; ++j) pose_raw[j] = j < pose_n ? (conf_rows ? hv[7 + j] : hv[6 + j]) : 0.f;
 
   // ---- pose -> R (rows), cube_head.py:176-186
   float R[9];
