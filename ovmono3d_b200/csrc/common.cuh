@@ -1,6 +1,7 @@
 // Shared helpers for the lift kernels (sm_100a only).
 #pragma once
 
+#include <cuda.h>
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -47,6 +48,12 @@ constexpr int kNumSMs = 148;  // B200
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
+
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no -lcuda link dependency); NULL if absent.
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn tensormap_encode_fn();
 
 // Entry points implemented per translation unit (host side, called from lift_api.cu).
 int roi_align_launch(const ovm_pooler_t* pooler, const float* boxes, const int32_t* batch_idx, int32_t n,

@@ -5,21 +5,32 @@
 // per-sample rule restated from torchvision/ops/roi_align.py:113-190 + the C++ kernel's range test).
 //
 // Design (NCHW fp32 in, (c,ph,pw)-major fp32/bf16 out):
-//   * one CTA per (box, group of 4 channel chunks); a chunk = 32 channels = one warp, lane == channel.
+//   * one CTA per (box, range of 32-channel chunks); 8 warps: warps 0..6 each own one output bin-row ph
+//     (lane == channel), warp 7 is the TMA producer.
 //   * per box the bilinear taps of all samples are folded ONCE into two separable weight tables in shared
 //     memory: Wx[pixel column][pw] and Wy[ph][pixel row] (sum of hx/lx resp. hy/ly over the bin's sample grid).
 //     out[c,ph,pw] = (sum_y sum_x Wy[ph][y] * Wx[x][pw] * f[c,y,x]) / count  -- identical to the reference's
 //     sum over samples of w1..w4 * f up to fp32 re-association.
-//   * each warp streams the rows a bin-row needs ("band") for its 32 channels from global memory into its
-//     private shared-memory buffer with 16-byte cp.async (footprint columns aligned down to 4 floats), laid
-//     out [channel][row][col] with a channel stride of 4*odd floats, so the compute phase reads 128-bit
-//     vectors with lane == channel free of bank conflicts.  No block-wide barrier after the tables are built.
-//   * results are staged through shared memory and written as one contiguous run of 32*49 values per chunk.
-//   * geometry the tables cannot hold (footprint wider than 124 columns, a bin taller than 64 rows), NHWC
-//     input and P != 7 take the direct path: one thread per output, sampling global memory like torchvision.
+//   * the box's pixel footprint is brought from the NCHW map into shared memory by TMA
+//     (cp.async.bulk.tensor.3d over [x, y, n*C+c]): one instruction per footprint row moves a
+//     {Wt columns, 1 row, 32 channels} box, Wt in {8, 16, 32} floats with the matching 32/64/128-byte swizzle,
+//     so that a lane reading 128-bit pieces of ITS channel's row is bank-conflict free.  Footprints wider than
+//     Wt are walked in column tiles; a pipeline stage = (channel chunk, column tile), kStages deep, guarded by
+//     full/empty mbarriers.  The start column is the footprint's first column rounded down to 4 floats (the
+//     innermost TMA coordinate must be 16-byte aligned) and every footprint row is fetched exactly once per chunk.
+//   * the seven warps read the same stage (each the rows of its own bin-row), keep 7 accumulators per lane,
+//     and after the last column tile of a chunk the 32 x 49 results are staged through shared memory and
+//     written as one contiguous run.
+//   * geometry the stage cannot hold (rows x Wt floats per channel > kStageFloats / 32, footprints wider than
+//     kMaxW), maps TMA cannot address (NHWC, width not a multiple of 4, unaligned base) and P != 7 take the
+//     direct path: one thread per output, sampling global memory like torchvision.
 #include <cfloat>
 #include <climits>
 #include <cmath>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <tuple>
 
 #include "common.cuh"
 
@@ -28,16 +39,19 @@ namespace ovm {
 namespace {
 
 constexpr int kP = 7;
-constexpr int kWarps = 4;
-constexpr int kThreads = kWarps * 32;
-constexpr int kMaxW = 124;                 // staged columns (multiple of 4)
+constexpr int kThreads = 256;              // 7 consumer warps + 1 producer warp
+constexpr int kConsumers = kP * 32;
+constexpr int kStages = 2;
+constexpr int kStageFloats = 44 * 8 * 32;  // 44 KB: rows x Wt <= 352 floats per channel (44 rows at Wt = 8)
+constexpr int kMaxW = 128;                 // footprint columns the Wx table holds
 constexpr int kMaxRows = 64;               // rows one output bin-row may touch
-constexpr int kSMax = 128;                 // per-channel floats in a band buffer (4*odd <= 128 after padding)
-constexpr int kBufFloats = 32 * kSMax;     // 16 KB per warp
 constexpr int kWxFloats = kMaxW * 8;
 constexpr int kWyFloats = kP * kMaxRows;
+constexpr int kOutFloats = 32 * kP * kP;   // one chunk of results
 constexpr int kMetaInts = 64;
-constexpr size_t kSmemBytes = (size_t)(kWarps * kBufFloats + kWxFloats + kWyFloats) * 4 + kMetaInts * 4;
+constexpr size_t kSmemBytes = 1024 + (size_t)kStages * kStageFloats * 4 + (size_t)(2 * kOutFloats + kWxFloats + kWyFloats) * 4 +
+                              kMetaInts * 4 + 64;
+constexpr int kWidths = 3;                 // tensor maps per level: Wt = 8, 16, 32
 
 struct RoiLevel {
   const float* data;
@@ -59,16 +73,41 @@ struct RoiArgs {
   long long out_ld;
   int* level_out;
   int splits, chunks_per_split;
+  int tma_ok[OVM_MAX_LEVELS];   // level has tensor maps (NCHW, 16-byte aligned base, width % 4 == 0)
 };
 
-__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+struct RoiMaps {
+  CUtensorMap m[OVM_MAX_LEVELS * kWidths];   // [level][log2(Wt) - 3]
+};
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
 }
-__device__ __forceinline__ void cp_async4(uint32_t dst, const void* src, int src_bytes) {
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
-__device__ __forceinline__ void cp_async_wait_all() {
-  asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done;
+  do {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t"
+        "}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+  } while (!done);
+}
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int x, int y, int c) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(dst),
+      "l"(map), "r"(bar), "r"(x), "r"(y), "r"(c)
+      : "memory");
 }
 
 // One sample coordinate along an axis, op for op as torchvision computes it (no FMA contraction):
@@ -201,27 +240,31 @@ __device__ void direct_path(const RoiArgs& a, const BoxGeom& g, int box, int c_b
 }
 
 // meta layout (ints): [0..6] x bin lo, [7..13] x bin hi, [14..20] y bin lo, [21..27] y bin hi (lo > hi: no valid sample)
-template <bool ALIGNED16>
-__global__ void __launch_bounds__(kThreads) roi_align_kernel(const RoiArgs a) {
-  extern __shared__ float4 smem_f4[];
-  float* smem = reinterpret_cast<float*>(smem_f4);
-  float* bufs = smem;                                   // kWarps * kBufFloats
-  float* Wx = bufs + kWarps * kBufFloats;               // [col][8]
-  float* Wy = Wx + kWxFloats;                           // [ph][kMaxRows]
+__global__ void __launch_bounds__(kThreads) roi_align_kernel(const __grid_constant__ RoiMaps maps, const RoiArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;   // swizzled TMA slabs need 1024-byte alignment
+  uint8_t* aligned = smem_raw + (base - raw);
+  float* stages = reinterpret_cast<float*>(aligned);                 // kStages * kStageFloats
+  float* outbuf = stages + kStages * kStageFloats;                   // 2 * kOutFloats
+  float* Wx = outbuf + 2 * kOutFloats;                               // [col][8]
+  float* Wy = Wx + kWxFloats;                                        // [ph][kMaxRows]
   int* meta = reinterpret_cast<int*>(Wy + kWyFloats);
+  const uint32_t bars = smem_u32(meta + kMetaInts);                  // full[kStages], empty[kStages]
 
   const int box = blockIdx.x / a.splits;
   const int split = blockIdx.x % a.splits;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int chunk_begin = split * a.chunks_per_split;
+  const int chunk_end = min((a.C + 31) / 32, chunk_begin + a.chunks_per_split);
   const int c_begin = chunk_begin * 32;
-  const int c_end = min(a.C, (chunk_begin + a.chunks_per_split) * 32);
+  const int c_end = min(a.C, chunk_end * 32);
 
   const BoxGeom g = box_geometry(a, box);
   if (split == 0 && tid == 0 && a.level_out) a.level_out[box] = g.level;
 
   bool direct = (a.P != kP) || g.level < 0 || g.gw <= 0 || g.gh <= 0;
-  if (!direct) direct = a.lv[g.level].layout != OVM_LAYOUT_NCHW || (ALIGNED16 && (a.lv[g.level].W & 3));
+  if (!direct) direct = !a.tma_ok[g.level];
   if (direct) {  // block-uniform
     direct_path(a, g, box, c_begin, c_end);
     return;
@@ -245,28 +288,52 @@ __global__ void __launch_bounds__(kThreads) roi_align_kernel(const RoiArgs a) {
     meta[(is_x ? 0 : 14) + lane] = mn;
     meta[(is_x ? 7 : 21) + lane] = mx;
   }
+  if (tid == 0) {
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(bars + 8 * s, 1);                    // full: the producer's expect_tx arrive
+      mbar_init(bars + 8 * (kStages + s), kP);       // empty: one arrive per consumer warp
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
   __syncthreads();
-  int x_lo = INT_MAX, x_hi = -1, ny_max = 0;
+  int x_lo = INT_MAX, x_hi = -1, y_lo = INT_MAX, y_hi = -1, ny_max = 0;
 #pragma unroll
   for (int p = 0; p < kP; ++p) {
     x_lo = min(x_lo, meta[p]);
     x_hi = max(x_hi, meta[7 + p]);
+    y_lo = min(y_lo, meta[14 + p]);
+    y_hi = max(y_hi, meta[21 + p]);
     ny_max = max(ny_max, meta[21 + p] - meta[14 + p] + 1);
   }
   const long long out_row = (long long)box * a.out_ld;
-  if (x_hi < 0 || ny_max <= 0) {  // every sample out of range: the reference's sum is empty
+  if (x_hi < 0 || y_hi < 0) {  // every sample out of range: the reference's sum is empty
     for (int o = tid; o < (c_end - c_begin) * kP * kP; o += kThreads)
       store_out(a, out_row + (long long)c_begin * kP * kP + o, 0.f);
     return;
   }
-  const int x0 = ALIGNED16 ? (x_lo & ~3) : x_lo;
-  const int fwp = (x_hi - x0 + 1 + 3) & ~3;
-  if (fwp > kMaxW || ny_max > kMaxRows) {
+  // ---- column tiling: the tile width with the least padding that lets all footprint rows sit in one stage
+  // the innermost TMA coordinate must be a multiple of 16 bytes (measured: anything else faults), so the footprint
+  // starts at the 4-float boundary at or below its first column
+  const int x0 = x_lo & ~3;
+  const int fw = x_hi - x0 + 1, rows_total = y_hi - y_lo + 1;
+  int wsel = -1, best_pad = INT_MAX;
+#pragma unroll
+  for (int k = kWidths - 1; k >= 0; --k) {
+    const int wt = 8 << k;
+    const int pad = (fw + wt - 1) / wt * wt;
+    if (rows_total * wt * 32 <= kStageFloats && pad < best_pad) {
+      best_pad = pad;
+      wsel = k;
+    }
+  }
+  if (wsel < 0 || best_pad > kMaxW || ny_max > kMaxRows) {
     direct_path(a, g, box, c_begin, c_end);
     return;
   }
+  const int Wt = 8 << wsel;
+  const int ntiles = best_pad / Wt;
   // ---- pass B: fold the taps into Wx / Wy
-  for (int i = tid; i < fwp * 8; i += kThreads) Wx[i] = 0.f;
+  for (int i = tid; i < best_pad * 8; i += kThreads) Wx[i] = 0.f;
   for (int i = tid; i < kWyFloats; i += kThreads) Wy[i] = 0.f;
   __syncthreads();
   if (lane < kP && warp < 2) {
@@ -288,68 +355,56 @@ __global__ void __launch_bounds__(kThreads) roi_align_kernel(const RoiArgs a) {
   }
   __syncthreads();
 
-  // ---- per-warp streaming over channel chunks
-  const int nx4 = fwp >> 2;
-  int R = min(ny_max, kSMax / fwp);          // rows per staged group (>= 1 because fwp <= kMaxW < kSMax)
-  int S4 = (R * fwp) >> 2;
-  if (!(S4 & 1)) {                           // channel stride must be 4*odd floats
-    if ((S4 + 1) * 4 <= kSMax) S4 += 1;
-    else { R -= 1; S4 = (R * fwp) >> 2; if (!(S4 & 1)) S4 += 1; }
-  }
-  if (R < 1) {  // only when fwp*1 is 4*even and no room to pad: cannot happen with kMaxW=124 < 128, kept for safety
-    direct_path(a, g, box, c_begin, c_end);
+  const int slab_floats = 32 * Wt;               // one footprint row of one chunk: [32 channels][Wt]
+  const int nchunks = chunk_end - chunk_begin;
+  const int nitems = nchunks * ntiles;
+
+  if (warp == kP) {
+    // ===== TMA producer
+    if (lane == 0) {
+      const CUtensorMap* map = &maps.m[g.level * kWidths + wsel];
+      const uint32_t stage_bytes = (uint32_t)(rows_total * slab_floats * 4);
+      for (int it = 0; it < nitems; ++it) {
+        const int s = it % kStages;
+        const uint32_t ph = (uint32_t)(it / kStages) & 1u;
+        mbar_wait(bars + 8 * (kStages + s), ph ^ 1u);
+        const int chunk = chunk_begin + it / ntiles, tile = it % ntiles;
+        const uint32_t full = bars + 8 * s;
+        mbar_expect_tx(full, stage_bytes);
+        const uint32_t dst = base + (uint32_t)(s * kStageFloats) * 4u;
+        const int xc = x0 + tile * Wt, cc = g.b * a.C + chunk * 32;
+        for (int r = 0; r < rows_total; ++r)
+          tma_load_3d(dst + (uint32_t)(r * slab_floats) * 4u, map, full, xc, y_lo + r, cc);
+      }
+    }
     return;
   }
-  const int S = S4 * 4;
-  float* buf = bufs + warp * kBufFloats;
-  const uint32_t buf_s = smem_u32(buf);
-  const float inv_div = g.count;
-  const long long HW = (long long)H * W;
 
-  for (int chunk = chunk_begin + warp; chunk < chunk_begin + a.chunks_per_split && chunk * 32 < a.C; chunk += kWarps) {
-    const int c0 = chunk * 32;
-    const int nch = min(32, a.C - c0);
-    const float* img = lv.data + ((long long)g.b * a.C + c0) * HW;
-    float acc[kP][kP];
+  // ===== consumers: warp == ph, lane == channel
+  const int ph = warp;
+  const int ys = meta[14 + ph];
+  const int ny = meta[21 + ph] - ys + 1;          // <= 0: bin-row has no valid sample
+  const float* wy = Wy + ph * kMaxRows;
+  const float inv_count = 1.f / g.count;
+  // 16-byte unit j of lane c's row sits at unit j ^ sw (the TMA swizzle of the slab, see the header comment)
+  const int sw = wsel == 2 ? (lane & 7) : (wsel == 1 ? ((lane >> 1) & 3) : ((lane >> 2) & 1));
+  const int nx4_tile = Wt >> 2;
+  int it = 0;
+  for (int chunk = chunk_begin; chunk < chunk_end; ++chunk) {
+    float acc[kP];
 #pragma unroll
-    for (int i = 0; i < kP; ++i)
-#pragma unroll
-      for (int j = 0; j < kP; ++j) acc[i][j] = 0.f;
-
-#pragma unroll
-    for (int ph = 0; ph < kP; ++ph) {
-      const int ys = meta[14 + ph];
-      const int ny = meta[21 + ph] - ys + 1;   // <= 0: bin-row has no valid sample
-      for (int r0 = 0; r0 < ny; r0 += R) {
-        const int rows = min(R, ny - r0);
-        __syncwarp();  // everyone finished reading the previous band
-        const int items = rows * nx4;
-        for (int it = lane; it < items; it += 32) {
-          const int r = it / nx4, x4 = it - r * nx4;
-          const float* src = img + (long long)(ys + r0 + r) * W + x0 + 4 * x4;
-          const uint32_t dst = buf_s + (uint32_t)(r * fwp + 4 * x4) * 4u;
-          if (ALIGNED16) {
-            for (int cc = 0; cc < nch; ++cc) cp_async16(dst + (uint32_t)(cc * S) * 4u, src + cc * HW);
-          } else {
-            const int xb = x0 + 4 * x4;
-            for (int cc = 0; cc < nch; ++cc) {
-#pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                const bool in = xb + e < W;
-                cp_async4(dst + (uint32_t)(cc * S + e) * 4u, in ? (src + cc * HW + e) : img, in ? 4 : 0);
-              }
-            }
-          }
-        }
-        cp_async_wait_all();
-        __syncwarp();
-        // compute: v[4 cols] = sum_rows Wy * f ; acc[ph][pw] += Wx[col][pw] * v
-        const float* wy = Wy + ph * kMaxRows + r0;
-        const float* mine = buf + lane * S;
-        for (int x4 = 0; x4 < nx4; ++x4) {
+    for (int j = 0; j < kP; ++j) acc[j] = 0.f;
+    for (int tile = 0; tile < ntiles; ++tile, ++it) {
+      const int s = it % kStages;
+      mbar_wait(bars + 8 * s, (uint32_t)(it / kStages) & 1u);
+      if (ny > 0) {
+        const float* slab0 = stages + s * kStageFloats + (ys - y_lo) * slab_floats + lane * Wt;
+        const int ncol4 = min(nx4_tile, (fw - tile * Wt + 3) >> 2);   // columns past the footprint carry zero weight
+        for (int x4 = 0; x4 < ncol4; ++x4) {
+          const float* p = slab0 + 4 * (x4 ^ sw);
           float v0 = 0.f, v1 = 0.f, v2 = 0.f, v3 = 0.f;
-          for (int r = 0; r < rows; ++r) {
-            const float4 f = *reinterpret_cast<const float4*>(mine + r * fwp + 4 * x4);
+          for (int r = 0; r < ny; ++r) {
+            const float4 f = *reinterpret_cast<const float4*>(p + r * slab_floats);
             const float w = wy[r];
             v0 = fmaf(w, f.x, v0);
             v1 = fmaf(w, f.y, v1);
@@ -357,40 +412,42 @@ __global__ void __launch_bounds__(kThreads) roi_align_kernel(const RoiArgs a) {
             v3 = fmaf(w, f.w, v3);
           }
           const float vv[4] = {v0, v1, v2, v3};
+          const float* wx = Wx + (tile * Wt + 4 * x4) * 8;
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
-            const float4 wa = *reinterpret_cast<const float4*>(Wx + (4 * x4 + e) * 8);
-            const float4 wb = *reinterpret_cast<const float4*>(Wx + (4 * x4 + e) * 8 + 4);
-            acc[ph][0] = fmaf(wa.x, vv[e], acc[ph][0]);
-            acc[ph][1] = fmaf(wa.y, vv[e], acc[ph][1]);
-            acc[ph][2] = fmaf(wa.z, vv[e], acc[ph][2]);
-            acc[ph][3] = fmaf(wa.w, vv[e], acc[ph][3]);
-            acc[ph][4] = fmaf(wb.x, vv[e], acc[ph][4]);
-            acc[ph][5] = fmaf(wb.y, vv[e], acc[ph][5]);
-            acc[ph][6] = fmaf(wb.z, vv[e], acc[ph][6]);
+            const float4 wa = *reinterpret_cast<const float4*>(wx + e * 8);
+            const float4 wb = *reinterpret_cast<const float4*>(wx + e * 8 + 4);
+            acc[0] = fmaf(wa.x, vv[e], acc[0]);
+            acc[1] = fmaf(wa.y, vv[e], acc[1]);
+            acc[2] = fmaf(wa.z, vv[e], acc[2]);
+            acc[3] = fmaf(wa.w, vv[e], acc[3]);
+            acc[4] = fmaf(wb.x, vv[e], acc[4]);
+            acc[5] = fmaf(wb.y, vv[e], acc[5]);
+            acc[6] = fmaf(wb.z, vv[e], acc[6]);
           }
         }
       }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bars + 8 * (kStages + s));
     }
-    // ---- stage the 32 x 49 results and write them as one contiguous run
-    __syncwarp();
+    // ---- stage the chunk's 32 x 49 results and write them as one contiguous run
+    float* ob = outbuf + ((chunk - chunk_begin) & 1) * kOutFloats;
 #pragma unroll
-    for (int i = 0; i < kP; ++i)
-#pragma unroll
-      for (int j = 0; j < kP; ++j) buf[lane * (kP * kP) + i * kP + j] = acc[i][j] / inv_div;
-    __syncwarp();
-    const int nvals = nch * kP * kP;
+    for (int j = 0; j < kP; ++j) ob[lane * (kP * kP) + ph * kP + j] = acc[j] * inv_count;
+    asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory");
+    const int c0 = chunk * 32;
+    const int nvals = min(32, a.C - c0) * kP * kP;
     const long long o0 = out_row + (long long)c0 * kP * kP;
     if (a.out_bf16) {
-      __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(a.out) + o0;  // o0 is even: c0 % 32 == 0, out_ld % 8 == 0
-      for (int i = lane; i < (nvals >> 1); i += 32) {
-        const float2 v = *reinterpret_cast<const float2*>(buf + 2 * i);
+      __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(a.out) + o0;  // o0 is even: c0 % 32 == 0, out_ld is even
+      for (int i = tid; i < (nvals >> 1); i += kConsumers) {
+        const float2 v = *reinterpret_cast<const float2*>(ob + 2 * i);
         *reinterpret_cast<__nv_bfloat162*>(out + 2 * i) = __floats2bfloat162_rn(v.x, v.y);
       }
-      if ((nvals & 1) && lane == 0) out[nvals - 1] = __float2bfloat16_rn(buf[nvals - 1]);
+      if ((nvals & 1) && tid == 0) out[nvals - 1] = __float2bfloat16_rn(ob[nvals - 1]);
     } else {
       float* out = reinterpret_cast<float*>(a.out) + o0;
-      for (int i = lane; i < nvals; i += 32) out[i] = buf[i];
+      for (int i = tid; i < nvals; i += kConsumers) out[i] = ob[i];
     }
   }
 }
@@ -410,6 +467,60 @@ float level_threshold(int k, int canonical_level) {
     for (int i = 0; i < 64 && level_of(s) < (float)k; ++i) s = nextafterf(s, INFINITY);
   }
   return s;
+}
+
+// Tensor maps of one pyramid level, Wt = 8 / 16 / 32.  fp32 [N*C, H, W] seen as 3-D {W, H, N*C}; box {Wt, 1, 32};
+// out-of-range elements (columns past W, channels past N*C) read as zero.
+int encode_level_maps(const float* data, int H, int W, long long NC, CUtensorMap* out3) {
+  EncodeTiledFn enc = tensormap_encode_fn();
+  if (!enc) {
+    set_error("cuTensorMapEncodeTiled not available from the driver");
+    return OVM_ECUDA;
+  }
+  static const CUtensorMapSwizzle swz[kWidths] = {CU_TENSOR_MAP_SWIZZLE_32B, CU_TENSOR_MAP_SWIZZLE_64B,
+                                                 CU_TENSOR_MAP_SWIZZLE_128B};
+  for (int k = 0; k < kWidths; ++k) {
+    cuuint64_t dims[3] = {(cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)NC};
+    cuuint64_t strides[2] = {(cuuint64_t)W * 4, (cuuint64_t)H * W * 4};
+    cuuint32_t box[3] = {(cuuint32_t)(8 << k), 1, 32};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = enc(&out3[k], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(data), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, swz[k], CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+      set_error("cuTensorMapEncodeTiled(feature map %dx%d, %lld planes, Wt=%d) failed with CUresult %d", H, W, NC,
+                8 << k, (int)r);
+      return OVM_ECUDA;
+    }
+  }
+  return OVM_OK;
+}
+
+// The maps depend only on (pointer, H, W, N*C): keep the last few so that a steady-state caller re-encodes nothing.
+struct MapKey {
+  const void* p;
+  int H, W;
+  long long NC;
+  bool operator<(const MapKey& o) const { return std::tie(p, H, W, NC) < std::tie(o.p, o.H, o.W, o.NC); }
+};
+struct MapVal {
+  CUtensorMap m[kWidths];
+};
+int level_maps(const float* data, int H, int W, long long NC, CUtensorMap* out3) {
+  static std::mutex mu;
+  static std::map<MapKey, MapVal> cache;
+  std::lock_guard<std::mutex> lock(mu);
+  const MapKey key{data, H, W, NC};
+  auto it = cache.find(key);
+  if (it == cache.end()) {
+    MapVal v;
+    int rc = encode_level_maps(data, H, W, NC, v.m);
+    if (rc != OVM_OK) return rc;
+    if (cache.size() >= 256) cache.clear();
+    it = cache.emplace(key, v).first;
+  }
+  for (int k = 0; k < kWidths; ++k) out3[k] = it->second.m[k];
+  return OVM_OK;
 }
 
 }  // namespace
@@ -437,14 +548,20 @@ int roi_align_launch(const ovm_pooler_t* p, const float* boxes, const int32_t* b
   const int max_level = (int)(-std::log2(p->levels[a.L - 1].spatial_scale));
   OVM_REQUIRE(a.L == max_level - min_level + 1, "[ROIPooler] Sizes of input featuremaps do not form a pyramid!");
   OVM_REQUIRE(0 <= min_level && min_level <= max_level, "[ROIPooler] bad level range %d..%d", min_level, max_level);
-  bool aligned16 = true;
+  RoiMaps maps;
+  memset(&maps, 0, sizeof(maps));
   for (int l = 0; l < a.L; ++l) {
     const ovm_level_t& s = p->levels[l];
     OVM_REQUIRE(s.data && s.height > 0 && s.width > 0, "ovm_roi_align: level %d is empty", l);
     OVM_REQUIRE(s.layout == OVM_LAYOUT_NCHW || s.layout == OVM_LAYOUT_NHWC, "ovm_roi_align: level %d layout", l);
     a.lv[l] = RoiLevel{s.data, s.height, s.width, (float)s.spatial_scale, s.layout};
     a.thr[l] = l == 0 ? 0.f : level_threshold(min_level + l, p->canonical_level);
-    if ((reinterpret_cast<uintptr_t>(s.data) & 15) || (s.width & 3)) aligned16 = false;
+    a.tma_ok[l] = s.layout == OVM_LAYOUT_NCHW && !(reinterpret_cast<uintptr_t>(s.data) & 15) && !(s.width & 3) &&
+                  p->pooler_resolution == kP;
+    if (a.tma_ok[l]) {
+      int rc = level_maps(s.data, s.height, s.width, (long long)p->num_images * p->channels, &maps.m[l * kWidths]);
+      if (rc != OVM_OK) return rc;
+    }
   }
   a.N = p->num_images;
   a.C = p->channels;
@@ -459,21 +576,20 @@ int roi_align_launch(const ovm_pooler_t* p, const float* boxes, const int32_t* b
   a.out_bf16 = out_dtype == OVM_BF16;
   a.out_ld = out_ld;
   a.level_out = level_out;
+  // enough CTAs for two waves of two CTAs per SM: split the channel chunks of a box over several CTAs when n is small
   const int chunks = (a.C + 31) / 32;
-  a.chunks_per_split = chunks < kWarps ? chunks : kWarps;
+  int splits = (4 * kNumSMs + n - 1) / n;
+  splits = splits < 1 ? 1 : (splits > chunks ? chunks : splits);
+  a.chunks_per_split = (chunks + splits - 1) / splits;
   a.splits = (chunks + a.chunks_per_split - 1) / a.chunks_per_split;
 
   static bool attr_done = false;
   if (!attr_done) {
-    OVM_CUDA(cudaFuncSetAttribute(roi_align_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
-    OVM_CUDA(cudaFuncSetAttribute(roi_align_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
+    OVM_CUDA(cudaFuncSetAttribute(roi_align_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
     attr_done = true;
   }
   const dim3 grid((unsigned)((long long)n * a.splits));
-  if (aligned16)
-    roi_align_kernel<true><<<grid, kThreads, kSmemBytes, stream>>>(a);
-  else
-    roi_align_kernel<false><<<grid, kThreads, kSmemBytes, stream>>>(a);
+  roi_align_kernel<<<grid, kThreads, kSmemBytes, stream>>>(maps, a);
   OVM_LAUNCHED("roi_align_kernel");
   return OVM_OK;
 }
