@@ -94,6 +94,11 @@ int ovm_gemm_bf16(const void* A, int64_t lda, const void* B, int64_t ldb, int32_
  * chunks of the last accumulator read out of TMEM.  NULL switches it off.                                     */
 int ovm_gemm_set_trace(uint64_t* buf);
 
+/* Same for ovm_roi_align (tools/roi_trace.py): sixteen slots per CTA, buf[cta*16 + k]: 0 entry, 1 bin ranges known,
+ * 2 tap tables built, 3 first stage landed, 4..11 channel chunk k written, 12 exit, 15 packed
+ * (rows << 48 | footprint width << 32 | tile-width index << 24 | SM id).  CTAs on the direct path stamp slot 0 only. */
+int ovm_roi_set_trace(uint64_t* buf);
+
 /* out[m, j] = act(in[m, j] + bias[j]) for j < N; in fp32 [M, ldi], out out_dtype [M, ldo]. */
 int ovm_bias_act(const float* in, int64_t ldi, const float* bias, int32_t relu, int32_t M, int32_t N,
                  void* out, int32_t out_dtype, int64_t ldo, void* stream);

@@ -41,8 +41,8 @@ namespace {
 constexpr int kP = 7;
 constexpr int kThreads = 256;              // 7 consumer warps + 1 producer warp
 constexpr int kConsumers = kP * 32;
-constexpr int kStages = 2;
-constexpr int kStageFloats = 44 * 8 * 32;  // 44 KB: rows x Wt <= 352 floats per channel (44 rows at Wt = 8)
+constexpr int kStages = 3;
+constexpr int kStageFloats = 30 * 8 * 32;  // 30 KB: rows x Wt <= 240 floats per channel (30 rows at Wt = 8, 15 at 16)
 constexpr int kMaxW = 128;                 // footprint columns the Wx table holds
 constexpr int kMaxRows = 64;               // rows one output bin-row may touch
 constexpr int kWxFloats = kMaxW * 8;
@@ -52,6 +52,7 @@ constexpr int kMetaInts = 64;
 constexpr size_t kSmemBytes = 1024 + (size_t)kStages * kStageFloats * 4 + (size_t)(2 * kOutFloats + kWxFloats + kWyFloats) * 4 +
                               kMetaInts * 4 + 64;
 constexpr int kWidths = 3;                 // tensor maps per level: Wt = 8, 16, 32
+constexpr int kUnroll = 4;                 // pixel rows of a bin-row handled by the unrolled path
 
 struct RoiLevel {
   const float* data;
@@ -74,7 +75,18 @@ struct RoiArgs {
   int* level_out;
   int splits, chunks_per_split;
   int tma_ok[OVM_MAX_LEVELS];   // level has tensor maps (NCHW, 16-byte aligned base, width % 4 == 0)
+  unsigned long long* trace;    // optional [grid, 16] %globaltimer stamps (ovm_roi_set_trace), else NULL
 };
+
+thread_local unsigned long long* g_roi_trace = nullptr;
+
+__device__ __forceinline__ void trace_stamp(const RoiArgs& a, int slot) {
+  if (a.trace) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    a.trace[(size_t)blockIdx.x * 16 + slot] = t;
+  }
+}
 
 struct RoiMaps {
   CUtensorMap m[OVM_MAX_LEVELS * kWidths];   // [level][log2(Wt) - 3]
@@ -102,6 +114,35 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         : "r"(bar), "r"(parity)
         : "memory");
   } while (!done);
+}
+__device__ __forceinline__ void mbar_wait_sleep(uint32_t bar, uint32_t parity) {
+  uint32_t done;
+  for (;;) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t"
+        "}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (done) break;
+    __nanosleep(64);   // keep the issue slots for the warps that have data
+  }
+}
+// packed fp32 pairs (FFMA2 on sm_100): two independent fused multiply-adds per instruction
+__device__ __forceinline__ uint64_t pack2(float lo, float hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ float lo2(uint64_t v) { return __uint_as_float((uint32_t)v); }
+__device__ __forceinline__ float hi2(uint64_t v) { return __uint_as_float((uint32_t)(v >> 32)); }
+__device__ __forceinline__ uint64_t ffma2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
 }
 __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int x, int y, int c) {
   asm volatile(
@@ -260,6 +301,7 @@ __global__ void __launch_bounds__(kThreads) roi_align_kernel(const __grid_consta
   const int c_begin = chunk_begin * 32;
   const int c_end = min(a.C, chunk_end * 32);
 
+  if (tid == 0) trace_stamp(a, 0);
   const BoxGeom g = box_geometry(a, box);
   if (split == 0 && tid == 0 && a.level_out) a.level_out[box] = g.level;
 
@@ -296,6 +338,7 @@ __global__ void __launch_bounds__(kThreads) roi_align_kernel(const __grid_consta
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
+  if (tid == 0) trace_stamp(a, 1);
   int x_lo = INT_MAX, x_hi = -1, y_lo = INT_MAX, y_hi = -1, ny_max = 0;
 #pragma unroll
   for (int p = 0; p < kP; ++p) {
@@ -324,6 +367,30 @@ __global__ void __launch_bounds__(kThreads) roi_align_kernel(const __grid_consta
     if (rows_total * wt * 32 <= kStageFloats && pad < best_pad) {
       best_pad = pad;
       wsel = k;
+    }
+  }
+  // Footprints too tall for one stage even at Wt = 8 are walked in two row groups: bin-rows 0..3, then 4..6
+  // (each consumer warp works only in its own group's stages).
+  int ngroups = 1;
+  int gy0[2] = {y_lo, y_lo}, gy1[2] = {y_hi, y_hi};
+  if (wsel < 0) {
+    ngroups = 2;
+    gy0[0] = gy0[1] = INT_MAX;
+    gy1[0] = gy1[1] = -1;
+#pragma unroll
+    for (int p = 0; p < kP; ++p) {
+      const int h = p < 4 ? 0 : 1;
+      if (meta[21 + p] >= meta[14 + p]) {
+        gy0[h] = min(gy0[h], meta[14 + p]);
+        gy1[h] = max(gy1[h], meta[21 + p]);
+      }
+    }
+    wsel = 0;
+    best_pad = (fw + 7) / 8 * 8;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      if (gy1[h] < gy0[h]) gy0[h] = gy1[h] = y_lo;   // group without a valid sample: one dummy row
+      if ((gy1[h] - gy0[h] + 1) * 8 * 32 > kStageFloats) wsel = -1;
     }
   }
   if (wsel < 0 || best_pad > kMaxW || ny_max > kMaxRows) {
@@ -355,26 +422,38 @@ __global__ void __launch_bounds__(kThreads) roi_align_kernel(const __grid_consta
   }
   __syncthreads();
 
+  if (tid == 0) {
+    trace_stamp(a, 2);
+    if (a.trace) {
+      unsigned smid;
+      asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+      a.trace[(size_t)blockIdx.x * 16 + 15] = ((unsigned long long)(rows_total) << 48) | ((unsigned long long)fw << 32) |
+                                                ((unsigned long long)wsel << 24) | smid;
+    }
+  }
   const int slab_floats = 32 * Wt;               // one footprint row of one chunk: [32 channels][Wt]
   const int nchunks = chunk_end - chunk_begin;
-  const int nitems = nchunks * ntiles;
+  const int per_chunk = ntiles * ngroups;        // pipeline items of a chunk: (row group, column tile)
+  const int nitems = nchunks * per_chunk;
 
   if (warp == kP) {
     // ===== TMA producer
     if (lane == 0) {
       const CUtensorMap* map = &maps.m[g.level * kWidths + wsel];
-      const uint32_t stage_bytes = (uint32_t)(rows_total * slab_floats * 4);
       for (int it = 0; it < nitems; ++it) {
         const int s = it % kStages;
-        const uint32_t ph = (uint32_t)(it / kStages) & 1u;
-        mbar_wait(bars + 8 * (kStages + s), ph ^ 1u);
-        const int chunk = chunk_begin + it / ntiles, tile = it % ntiles;
+        const uint32_t par = (uint32_t)(it / kStages) & 1u;
+        mbar_wait(bars + 8 * (kStages + s), par ^ 1u);
+        const int chunk = chunk_begin + it / per_chunk, sub = it % per_chunk;
+        const int grp = sub / ntiles, tile = sub % ntiles;
+        const int gy = grp ? gy0[1] : gy0[0];
+        const int rows = (grp ? gy1[1] : gy1[0]) - gy + 1;
         const uint32_t full = bars + 8 * s;
-        mbar_expect_tx(full, stage_bytes);
+        mbar_expect_tx(full, (uint32_t)(rows * slab_floats * 4));
         const uint32_t dst = base + (uint32_t)(s * kStageFloats) * 4u;
         const int xc = x0 + tile * Wt, cc = g.b * a.C + chunk * 32;
-        for (int r = 0; r < rows_total; ++r)
-          tma_load_3d(dst + (uint32_t)(r * slab_floats) * 4u, map, full, xc, y_lo + r, cc);
+        for (int r = 0; r < rows; ++r)
+          tma_load_3d(dst + (uint32_t)(r * slab_floats) * 4u, map, full, xc, gy + r, cc);
       }
     }
     return;
@@ -382,6 +461,7 @@ __global__ void __launch_bounds__(kThreads) roi_align_kernel(const __grid_consta
 
   // ===== consumers: warp == ph, lane == channel
   const int ph = warp;
+  const int my_grp = ngroups == 2 && ph >= 4 ? 1 : 0;
   const int ys = meta[14 + ph];
   const int ny = meta[21 + ph] - ys + 1;          // <= 0: bin-row has no valid sample
   const float* wy = Wy + ph * kMaxRows;
@@ -389,41 +469,59 @@ __global__ void __launch_bounds__(kThreads) roi_align_kernel(const __grid_consta
   // 16-byte unit j of lane c's row sits at unit j ^ sw (the TMA swizzle of the slab, see the header comment)
   const int sw = wsel == 2 ? (lane & 7) : (wsel == 1 ? ((lane >> 1) & 3) : ((lane >> 2) & 1));
   const int nx4_tile = Wt >> 2;
+  const int row_off = (ys - (my_grp ? gy0[1] : gy0[0])) * slab_floats + lane * Wt;
+  // bin-rows of up to kUnroll pixel rows (the common case: a bin is rarely taller than 2-3 pixels) run fully
+  // unrolled with the row weights in registers; missing rows repeat the last one with weight zero
+  uint64_t wy2[kUnroll];
+  int roff[kUnroll];
+#pragma unroll
+  for (int r = 0; r < kUnroll; ++r) {
+    const int rr = min(r, max(ny - 1, 0));
+    const float w = r < ny ? wy[r] : 0.f;
+    wy2[r] = pack2(w, w);
+    roff[r] = rr * slab_floats;
+  }
   int it = 0;
   for (int chunk = chunk_begin; chunk < chunk_end; ++chunk) {
-    float acc[kP];
-#pragma unroll
-    for (int j = 0; j < kP; ++j) acc[j] = 0.f;
-    for (int tile = 0; tile < ntiles; ++tile, ++it) {
+    uint64_t acc01 = 0, acc23 = 0, acc45 = 0;
+    float acc6 = 0.f;
+    for (int sub = 0; sub < per_chunk; ++sub, ++it) {
       const int s = it % kStages;
-      mbar_wait(bars + 8 * s, (uint32_t)(it / kStages) & 1u);
-      if (ny > 0) {
-        const float* slab0 = stages + s * kStageFloats + (ys - y_lo) * slab_floats + lane * Wt;
+      const int grp = sub / ntiles, tile = sub - grp * ntiles;
+      mbar_wait_sleep(bars + 8 * s, (uint32_t)(it / kStages) & 1u);
+      if (tid == 0 && it == 0) trace_stamp(a, 3);
+      if (ny > 0 && grp == my_grp) {
+        const float* slab0 = stages + s * kStageFloats + row_off;
         const int ncol4 = min(nx4_tile, (fw - tile * Wt + 3) >> 2);   // columns past the footprint carry zero weight
         for (int x4 = 0; x4 < ncol4; ++x4) {
           const float* p = slab0 + 4 * (x4 ^ sw);
-          float v0 = 0.f, v1 = 0.f, v2 = 0.f, v3 = 0.f;
-          for (int r = 0; r < ny; ++r) {
-            const float4 f = *reinterpret_cast<const float4*>(p + r * slab_floats);
-            const float w = wy[r];
-            v0 = fmaf(w, f.x, v0);
-            v1 = fmaf(w, f.y, v1);
-            v2 = fmaf(w, f.z, v2);
-            v3 = fmaf(w, f.w, v3);
+          uint64_t v01 = 0, v23 = 0;
+          if (ny <= kUnroll) {
+#pragma unroll
+            for (int r = 0; r < kUnroll; ++r) {
+              const float4 f = *reinterpret_cast<const float4*>(p + roff[r]);
+              v01 = ffma2(wy2[r], pack2(f.x, f.y), v01);
+              v23 = ffma2(wy2[r], pack2(f.z, f.w), v23);
+            }
+          } else {
+            for (int r = 0; r < ny; ++r) {
+              const float4 f = *reinterpret_cast<const float4*>(p + r * slab_floats);
+              const uint64_t w2 = pack2(wy[r], wy[r]);
+              v01 = ffma2(w2, pack2(f.x, f.y), v01);
+              v23 = ffma2(w2, pack2(f.z, f.w), v23);
+            }
           }
-          const float vv[4] = {v0, v1, v2, v3};
+          const float vv[4] = {lo2(v01), hi2(v01), lo2(v23), hi2(v23)};
           const float* wx = Wx + (tile * Wt + 4 * x4) * 8;
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
             const float4 wa = *reinterpret_cast<const float4*>(wx + e * 8);
             const float4 wb = *reinterpret_cast<const float4*>(wx + e * 8 + 4);
-            acc[0] = fmaf(wa.x, vv[e], acc[0]);
-            acc[1] = fmaf(wa.y, vv[e], acc[1]);
-            acc[2] = fmaf(wa.z, vv[e], acc[2]);
-            acc[3] = fmaf(wa.w, vv[e], acc[3]);
-            acc[4] = fmaf(wb.x, vv[e], acc[4]);
-            acc[5] = fmaf(wb.y, vv[e], acc[5]);
-            acc[6] = fmaf(wb.z, vv[e], acc[6]);
+            const uint64_t v2 = pack2(vv[e], vv[e]);
+            acc01 = ffma2(pack2(wa.x, wa.y), v2, acc01);
+            acc23 = ffma2(pack2(wa.z, wa.w), v2, acc23);
+            acc45 = ffma2(pack2(wb.x, wb.y), v2, acc45);
+            acc6 = fmaf(wb.z, vv[e], acc6);
           }
         }
       }
@@ -432,24 +530,51 @@ __global__ void __launch_bounds__(kThreads) roi_align_kernel(const __grid_consta
     }
     // ---- stage the chunk's 32 x 49 results and write them as one contiguous run
     float* ob = outbuf + ((chunk - chunk_begin) & 1) * kOutFloats;
-#pragma unroll
-    for (int j = 0; j < kP; ++j) ob[lane * (kP * kP) + ph * kP + j] = acc[j] * inv_count;
+    {
+      float* o = ob + lane * (kP * kP) + ph * kP;
+      o[0] = lo2(acc01) * inv_count; o[1] = hi2(acc01) * inv_count;
+      o[2] = lo2(acc23) * inv_count; o[3] = hi2(acc23) * inv_count;
+      o[4] = lo2(acc45) * inv_count; o[5] = hi2(acc45) * inv_count;
+      o[6] = acc6 * inv_count;
+    }
     asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory");
+    if (tid == 0 && chunk - chunk_begin < 8) trace_stamp(a, 4 + chunk - chunk_begin);
     const int c0 = chunk * 32;
     const int nvals = min(32, a.C - c0) * kP * kP;
     const long long o0 = out_row + (long long)c0 * kP * kP;
     if (a.out_bf16) {
       __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(a.out) + o0;  // o0 is even: c0 % 32 == 0, out_ld is even
-      for (int i = tid; i < (nvals >> 1); i += kConsumers) {
-        const float2 v = *reinterpret_cast<const float2*>(ob + 2 * i);
-        *reinterpret_cast<__nv_bfloat162*>(out + 2 * i) = __floats2bfloat162_rn(v.x, v.y);
+      if (!(reinterpret_cast<uintptr_t>(out) & 15) && !(nvals & 7)) {
+        for (int i = tid; i < (nvals >> 3); i += kConsumers) {   // 8 values -> one 16-byte store
+          const float4 lo = *reinterpret_cast<const float4*>(ob + 8 * i);
+          const float4 hi = *reinterpret_cast<const float4*>(ob + 8 * i + 4);
+          __nv_bfloat162 b0 = __floats2bfloat162_rn(lo.x, lo.y), b1 = __floats2bfloat162_rn(lo.z, lo.w);
+          __nv_bfloat162 b2 = __floats2bfloat162_rn(hi.x, hi.y), b3 = __floats2bfloat162_rn(hi.z, hi.w);
+          uint4 pk;
+          pk.x = *reinterpret_cast<uint32_t*>(&b0);
+          pk.y = *reinterpret_cast<uint32_t*>(&b1);
+          pk.z = *reinterpret_cast<uint32_t*>(&b2);
+          pk.w = *reinterpret_cast<uint32_t*>(&b3);
+          *reinterpret_cast<uint4*>(out + 8 * i) = pk;
+        }
+      } else {
+        for (int i = tid; i < (nvals >> 1); i += kConsumers) {
+          const float2 v = *reinterpret_cast<const float2*>(ob + 2 * i);
+          *reinterpret_cast<__nv_bfloat162*>(out + 2 * i) = __floats2bfloat162_rn(v.x, v.y);
+        }
+        if ((nvals & 1) && tid == 0) out[nvals - 1] = __float2bfloat16_rn(ob[nvals - 1]);
       }
-      if ((nvals & 1) && tid == 0) out[nvals - 1] = __float2bfloat16_rn(ob[nvals - 1]);
     } else {
       float* out = reinterpret_cast<float*>(a.out) + o0;
-      for (int i = tid; i < nvals; i += kConsumers) out[i] = ob[i];
+      if (!(reinterpret_cast<uintptr_t>(out) & 15) && !(nvals & 3)) {
+        for (int i = tid; i < (nvals >> 2); i += kConsumers)
+          *reinterpret_cast<float4*>(out + 4 * i) = *reinterpret_cast<const float4*>(ob + 4 * i);
+      } else {
+        for (int i = tid; i < nvals; i += kConsumers) out[i] = ob[i];
+      }
     }
   }
+  if (tid == 0) trace_stamp(a, 12);
 }
 
 // Smallest fp32 s with floor(canonical_level + log2(s)) >= k, evaluated the way the reference's torch CPU
@@ -525,6 +650,8 @@ int level_maps(const float* data, int H, int W, long long NC, CUtensorMap* out3)
 
 }  // namespace
 
+void roi_set_trace(unsigned long long* buf) { g_roi_trace = buf; }
+
 int roi_align_launch(const ovm_pooler_t* p, const float* boxes, const int32_t* batch_idx, int32_t n, void* out,
                      int32_t out_dtype, int64_t out_ld, int32_t* level_out, cudaStream_t stream) {
   OVM_REQUIRE(p != nullptr, "ovm_roi_align: pooler is NULL");
@@ -576,6 +703,7 @@ int roi_align_launch(const ovm_pooler_t* p, const float* boxes, const int32_t* b
   a.out_bf16 = out_dtype == OVM_BF16;
   a.out_ld = out_ld;
   a.level_out = level_out;
+  a.trace = g_roi_trace;
   // enough CTAs for two waves of two CTAs per SM: split the channel chunks of a box over several CTAs when n is small
   const int chunks = (a.C + 31) / 32;
   int splits = (4 * kNumSMs + n - 1) / n;

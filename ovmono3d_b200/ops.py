@@ -32,7 +32,8 @@ REC_SCORE = 45
 REC_CLASS = 46
 
 EXPORTS = ("ovm_abi_version", "ovm_last_error", "ovm_launch_count", "ovm_struct_size", "ovm_roi_align", "ovm_gemm_bf16",
-           "ovm_bias_act", "ovm_cast_bf16", "ovm_head_decode", "ovm_lift_forward", "ovm_set_stage_events", "ovm_gemm_set_trace")
+           "ovm_bias_act", "ovm_cast_bf16", "ovm_head_decode", "ovm_lift_forward", "ovm_set_stage_events", "ovm_gemm_set_trace",
+           "ovm_roi_set_trace")
 
 
 class LiftError(RuntimeError):
@@ -112,6 +113,7 @@ def load_library() -> C.CDLL:
                                      C.POINTER(ovm_head_weights_t), vp, vp, vp, vp, vp, i32,
                                      C.POINTER(ovm_workspace_t), vp, vp, vp]
     lib.ovm_gemm_set_trace.argtypes = [vp]
+    lib.ovm_roi_set_trace.argtypes = [vp]
     lib.ovm_set_stage_events.argtypes = [C.POINTER(C.c_void_p), i32]
     for name in EXPORTS[3:]:
         getattr(lib, name).restype = C.c_int
