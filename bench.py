@@ -283,8 +283,10 @@ def run_ours(args) -> Dict[str, object]:
     gathered = None
     g0.record()
     if world > 1:   # the path's one exchange: detections gathered once at the end (omni3d_evaluation.py:717-720)
-        gathered = torch.empty((world,) + tuple(records_all.shape), device=device, dtype=torch.float32)
-        dist.all_gather_into_tensor(gathered, records_all)
+        from ovmono3d_b200 import shard
+
+        gathered, counts, _ = shard.gather_records(records_all.view(-1, ops.RECORD_WIDTH))
+        assert int(counts.sum()) == world * K * n
     g1.record()
     barrier()
     loop_wall_ms = (time.perf_counter() - t_wall0) * 1e3
