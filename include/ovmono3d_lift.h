@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define OVM_ABI_VERSION 1
+#define OVM_ABI_VERSION 2
 #define OVM_MAX_LEVELS 8
 #define OVM_RECORD_WIDTH 48   /* floats per detection record, see ovm_head_decode */
 
@@ -64,6 +64,8 @@ typedef struct {
   int32_t canonical_level;       /* d2 default 4 */
   float scale_roi_boxes;         /* SCALE_ROI_BOXES; <= 0 disables (roi_heads.py:310-327) */
   int32_t _pad;
+  int32_t* order_ws;             /* optional device scratch [n] int32: when given, boxes are scheduled largest
+                                    footprint first (one extra tiny launch); NULL = in input order */
 } ovm_pooler_t;
 
 /* Multi-level ROIAlignV2.  boxes [n,4] xyxy fp32, batch_idx [n] int32 (image of each box), both

@@ -41,8 +41,9 @@ namespace {
 constexpr int kP = 7;
 constexpr int kThreads = 256;              // 7 consumer warps + 1 producer warp
 constexpr int kConsumers = kP * 32;
-constexpr int kStages = 3;
-constexpr int kStageFloats = 30 * 8 * 32;  // 30 KB: rows x Wt <= 240 floats per channel (30 rows at Wt = 8, 15 at 16)
+constexpr int kStages = 2;
+constexpr int kStageFloats = 24 * 8 * 32;  // 24 KB: rows x Wt <= 192 floats per channel (24 rows at Wt = 8, 12 at 16);
+                                           // two stages + tables + output staging = 68 KB per CTA, three CTAs per SM
 constexpr int kMaxW = 128;                 // footprint columns the Wx table holds
 constexpr int kMaxRows = 64;               // rows one output bin-row may touch
 constexpr int kWxFloats = kMaxW * 8;
@@ -52,7 +53,6 @@ constexpr int kMetaInts = 64;
 constexpr size_t kSmemBytes = 1024 + (size_t)kStages * kStageFloats * 4 + (size_t)(2 * kOutFloats + kWxFloats + kWyFloats) * 4 +
                               kMetaInts * 4 + 64;
 constexpr int kWidths = 3;                 // tensor maps per level: Wt = 8, 16, 32
-constexpr int kUnroll = 4;                 // pixel rows of a bin-row handled by the unrolled path
 
 struct RoiLevel {
   const float* data;
@@ -73,6 +73,7 @@ struct RoiArgs {
   int out_bf16;
   long long out_ld;
   int* level_out;
+  const int* order;             // boxes in descending cost (roi_order_kernel), or NULL: natural order
   int splits, chunks_per_split;
   int tma_ok[OVM_MAX_LEVELS];   // level has tensor maps (NCHW, 16-byte aligned base, width % 4 == 0)
   unsigned long long* trace;    // optional [grid, 16] %globaltimer stamps (ovm_roi_set_trace), else NULL
@@ -280,6 +281,37 @@ __device__ void direct_path(const RoiArgs& a, const BoxGeom& g, int box, int c_b
   }
 }
 
+// Cheapest useful schedule for a grid of CTAs with very different run times: longest first.  One CTA buckets the
+// boxes by footprint area (64 buckets, biggest first) with a counting sort in shared memory and writes the order.
+__global__ void __launch_bounds__(1024) roi_order_kernel(const RoiArgs a, int* __restrict__ order) {
+  __shared__ int hist[64], offs[64];
+  const int tid = threadIdx.x;
+  if (tid < 64) hist[tid] = 0;
+  __syncthreads();
+  auto bucket_of = [&](int box) {
+    const BoxGeom g = box_geometry(a, box);
+    if (g.level < 0) return 63;
+    const RoiLevel lv = a.lv[g.level];
+    // pixel rows x columns of the footprint, clipped to the map
+    const float w = fminf(fmaxf(g.bin_w * (float)a.P, 0.f), (float)lv.W) + 2.f;
+    const float h = fminf(fmaxf(g.bin_h * (float)a.P, 0.f), (float)lv.H) + 2.f;
+    const float area = w * h;                       // NaN -> bucket 63 through the comparison below
+    int b = 63 - (int)fminf(area * (1.f / 16.f), 63.f);
+    return (area == area) ? b : 63;
+  };
+  for (int box = tid; box < a.n; box += blockDim.x) atomicAdd(&hist[bucket_of(box)], 1);
+  __syncthreads();
+  if (tid == 0) {
+    int run = 0;
+    for (int b = 0; b < 64; ++b) {
+      offs[b] = run;
+      run += hist[b];
+    }
+  }
+  __syncthreads();
+  for (int box = tid; box < a.n; box += blockDim.x) order[atomicAdd(&offs[bucket_of(box)], 1)] = box;
+}
+
 // meta layout (ints): [0..6] x bin lo, [7..13] x bin hi, [14..20] y bin lo, [21..27] y bin hi (lo > hi: no valid sample)
 __global__ void __launch_bounds__(kThreads) roi_align_kernel(const __grid_constant__ RoiMaps maps, const RoiArgs a) {
   extern __shared__ uint8_t smem_raw[];
@@ -293,7 +325,7 @@ __global__ void __launch_bounds__(kThreads) roi_align_kernel(const __grid_consta
   int* meta = reinterpret_cast<int*>(Wy + kWyFloats);
   const uint32_t bars = smem_u32(meta + kMetaInts);                  // full[kStages], empty[kStages]
 
-  const int box = blockIdx.x / a.splits;
+  const int box = a.order ? a.order[blockIdx.x / a.splits] : (int)(blockIdx.x / a.splits);
   const int split = blockIdx.x % a.splits;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int chunk_begin = split * a.chunks_per_split;
@@ -399,10 +431,40 @@ __global__ void __launch_bounds__(kThreads) roi_align_kernel(const __grid_consta
   }
   const int Wt = 8 << wsel;
   const int ntiles = best_pad / Wt;
-  // ---- pass B: fold the taps into Wx / Wy
-  for (int i = tid; i < best_pad * 8; i += kThreads) Wx[i] = 0.f;
-  for (int i = tid; i < kWyFloats; i += kThreads) Wy[i] = 0.f;
-  __syncthreads();
+  const int slab_floats = 32 * Wt;               // one footprint row of one chunk: [32 channels][Wt]
+  const int nchunks = chunk_end - chunk_begin;
+  const int per_chunk = ntiles * ngroups;        // pipeline items of a chunk: (row group, column tile)
+
+  if (warp == kP) {
+    // ===== TMA producer: starts as soon as the footprint is known, while the other warps build the tap tables
+    if (lane == 0) {
+      const CUtensorMap* map = &maps.m[g.level * kWidths + wsel];
+      int it = 0;
+      for (int chunk = chunk_begin; chunk < chunk_end; ++chunk) {
+        const int cc = g.b * a.C + chunk * 32;
+        for (int grp = 0; grp < ngroups; ++grp) {
+          const int gy = grp ? gy0[1] : gy0[0];
+          const int rows = (grp ? gy1[1] : gy1[0]) - gy + 1;
+          for (int tile = 0; tile < ntiles; ++tile, ++it) {
+            const int s = it % kStages;
+            mbar_wait(bars + 8 * (kStages + s), ((uint32_t)(it / kStages) & 1u) ^ 1u);
+            const uint32_t full = bars + 8 * s;
+            mbar_expect_tx(full, (uint32_t)(rows * slab_floats * 4));
+            const uint32_t dst = base + (uint32_t)(s * kStageFloats) * 4u;
+            const int xc = x0 + tile * Wt;
+            for (int r = 0; r < rows; ++r)
+              tma_load_3d(dst + (uint32_t)(r * slab_floats) * 4u, map, full, xc, gy + r, cc);
+          }
+        }
+      }
+    }
+    return;
+  }
+
+  // ---- pass B (the seven consumer warps): fold the taps into Wx / Wy
+  for (int i = tid; i < best_pad * 8; i += kConsumers) Wx[i] = 0.f;
+  for (int i = tid; i < kWyFloats; i += kConsumers) Wy[i] = 0.f;
+  asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory");
   if (lane < kP && warp < 2) {
     const bool is_x = warp == 0;
     const float start = is_x ? g.start_w : g.start_h, bin = is_x ? g.bin_w : g.bin_h;
@@ -420,8 +482,7 @@ __global__ void __launch_bounds__(kThreads) roi_align_kernel(const __grid_consta
       }
     }
   }
-  __syncthreads();
-
+  asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory");
   if (tid == 0) {
     trace_stamp(a, 2);
     if (a.trace) {
@@ -430,33 +491,6 @@ __global__ void __launch_bounds__(kThreads) roi_align_kernel(const __grid_consta
       a.trace[(size_t)blockIdx.x * 16 + 15] = ((unsigned long long)(rows_total) << 48) | ((unsigned long long)fw << 32) |
                                                 ((unsigned long long)wsel << 24) | smid;
     }
-  }
-  const int slab_floats = 32 * Wt;               // one footprint row of one chunk: [32 channels][Wt]
-  const int nchunks = chunk_end - chunk_begin;
-  const int per_chunk = ntiles * ngroups;        // pipeline items of a chunk: (row group, column tile)
-  const int nitems = nchunks * per_chunk;
-
-  if (warp == kP) {
-    // ===== TMA producer
-    if (lane == 0) {
-      const CUtensorMap* map = &maps.m[g.level * kWidths + wsel];
-      for (int it = 0; it < nitems; ++it) {
-        const int s = it % kStages;
-        const uint32_t par = (uint32_t)(it / kStages) & 1u;
-        mbar_wait(bars + 8 * (kStages + s), par ^ 1u);
-        const int chunk = chunk_begin + it / per_chunk, sub = it % per_chunk;
-        const int grp = sub / ntiles, tile = sub % ntiles;
-        const int gy = grp ? gy0[1] : gy0[0];
-        const int rows = (grp ? gy1[1] : gy1[0]) - gy + 1;
-        const uint32_t full = bars + 8 * s;
-        mbar_expect_tx(full, (uint32_t)(rows * slab_floats * 4));
-        const uint32_t dst = base + (uint32_t)(s * kStageFloats) * 4u;
-        const int xc = x0 + tile * Wt, cc = g.b * a.C + chunk * 32;
-        for (int r = 0; r < rows; ++r)
-          tma_load_3d(dst + (uint32_t)(r * slab_floats) * 4u, map, full, xc, gy + r, cc);
-      }
-    }
-    return;
   }
 
   // ===== consumers: warp == ph, lane == channel
@@ -470,25 +504,14 @@ __global__ void __launch_bounds__(kThreads) roi_align_kernel(const __grid_consta
   const int sw = wsel == 2 ? (lane & 7) : (wsel == 1 ? ((lane >> 1) & 3) : ((lane >> 2) & 1));
   const int nx4_tile = Wt >> 2;
   const int row_off = (ys - (my_grp ? gy0[1] : gy0[0])) * slab_floats + lane * Wt;
-  // bin-rows of up to kUnroll pixel rows (the common case: a bin is rarely taller than 2-3 pixels) run fully
-  // unrolled with the row weights in registers; missing rows repeat the last one with weight zero
-  uint64_t wy2[kUnroll];
-  int roff[kUnroll];
-#pragma unroll
-  for (int r = 0; r < kUnroll; ++r) {
-    const int rr = min(r, max(ny - 1, 0));
-    const float w = r < ny ? wy[r] : 0.f;
-    wy2[r] = pack2(w, w);
-    roff[r] = rr * slab_floats;
-  }
   int it = 0;
   for (int chunk = chunk_begin; chunk < chunk_end; ++chunk) {
     uint64_t acc01 = 0, acc23 = 0, acc45 = 0;
     float acc6 = 0.f;
-    for (int sub = 0; sub < per_chunk; ++sub, ++it) {
+    for (int grp = 0; grp < ngroups; ++grp)
+    for (int tile = 0; tile < ntiles; ++tile, ++it) {
       const int s = it % kStages;
-      const int grp = sub / ntiles, tile = sub - grp * ntiles;
-      mbar_wait_sleep(bars + 8 * s, (uint32_t)(it / kStages) & 1u);
+      mbar_wait(bars + 8 * s, (uint32_t)(it / kStages) & 1u);
       if (tid == 0 && it == 0) trace_stamp(a, 3);
       if (ny > 0 && grp == my_grp) {
         const float* slab0 = stages + s * kStageFloats + row_off;
@@ -496,20 +519,21 @@ __global__ void __launch_bounds__(kThreads) roi_align_kernel(const __grid_consta
         for (int x4 = 0; x4 < ncol4; ++x4) {
           const float* p = slab0 + 4 * (x4 ^ sw);
           uint64_t v01 = 0, v23 = 0;
-          if (ny <= kUnroll) {
+          // a bin-row is rarely taller than 2-3 pixels: the first four rows are unrolled under uniform predicates
 #pragma unroll
-            for (int r = 0; r < kUnroll; ++r) {
-              const float4 f = *reinterpret_cast<const float4*>(p + roff[r]);
-              v01 = ffma2(wy2[r], pack2(f.x, f.y), v01);
-              v23 = ffma2(wy2[r], pack2(f.z, f.w), v23);
-            }
-          } else {
-            for (int r = 0; r < ny; ++r) {
+          for (int r = 0; r < 4; ++r) {
+            if (r < ny) {
               const float4 f = *reinterpret_cast<const float4*>(p + r * slab_floats);
               const uint64_t w2 = pack2(wy[r], wy[r]);
               v01 = ffma2(w2, pack2(f.x, f.y), v01);
               v23 = ffma2(w2, pack2(f.z, f.w), v23);
             }
+          }
+          for (int r = 4; r < ny; ++r) {
+            const float4 f = *reinterpret_cast<const float4*>(p + r * slab_floats);
+            const uint64_t w2 = pack2(wy[r], wy[r]);
+            v01 = ffma2(w2, pack2(f.x, f.y), v01);
+            v23 = ffma2(w2, pack2(f.z, f.w), v23);
           }
           const float vv[4] = {lo2(v01), hi2(v01), lo2(v23), hi2(v23)};
           const float* wx = Wx + (tile * Wt + 4 * x4) * 8;
@@ -703,6 +727,7 @@ int roi_align_launch(const ovm_pooler_t* p, const float* boxes, const int32_t* b
   a.out_bf16 = out_dtype == OVM_BF16;
   a.out_ld = out_ld;
   a.level_out = level_out;
+  a.order = p->order_ws;
   a.trace = g_roi_trace;
   // enough CTAs for two waves of two CTAs per SM: split the channel chunks of a box over several CTAs when n is small
   const int chunks = (a.C + 31) / 32;
@@ -715,6 +740,10 @@ int roi_align_launch(const ovm_pooler_t* p, const float* boxes, const int32_t* b
   if (!attr_done) {
     OVM_CUDA(cudaFuncSetAttribute(roi_align_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
     attr_done = true;
+  }
+  if (a.order) {
+    roi_order_kernel<<<1, 1024, 0, stream>>>(a, p->order_ws);
+    OVM_LAUNCHED("roi_order_kernel");
   }
   const dim3 grid((unsigned)((long long)n * a.splits));
   roi_align_kernel<<<grid, kThreads, kSmemBytes, stream>>>(maps, a);

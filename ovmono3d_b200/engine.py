@@ -160,6 +160,7 @@ class LiftEngine:
             act_b=torch.empty((cap, self.fc_dim), device=device, dtype=torch.bfloat16),
             feats=torch.empty((cap, groups * self.fc_dim), device=device, dtype=torch.float32),
             levels=torch.empty((cap,), device=device, dtype=torch.int32),
+            order=torch.empty((cap,), device=device, dtype=torch.int32),
         )
         ws = ops.ovm_workspace_t(t["pooled"].data_ptr(), ld_pooled, t["acc"].data_ptr(), t["act_a"].data_ptr(),
                                  t["act_b"].data_ptr(), t["feats"].data_ptr(), t["levels"].data_ptr())
@@ -191,6 +192,7 @@ class LiftEngine:
             raise ops.LiftError("fc1 expects %d inputs but the pyramid gives C*P*P = %d"
                                 % (self.in_dim, pooler.channels * self.P * self.P))
         ws = self._workspace(n, device)
+        pooler.order_ws = self._ws_tensors["order"].data_ptr()
         ops._need_cuda(boxes, "boxes", torch.float32)
         ops._need_cuda(classes, "classes", torch.int64)
         ops._need_cuda(batch_idx, "batch_idx", torch.int32)
