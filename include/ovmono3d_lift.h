@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define OVM_ABI_VERSION 2
+#define OVM_ABI_VERSION 3
 #define OVM_MAX_LEVELS 8
 #define OVM_RECORD_WIDTH 48   /* floats per detection record, see ovm_head_decode */
 
@@ -44,6 +44,9 @@ enum { OVM_Z_DIRECT = 0, OVM_Z_SIGMOID = 1, OVM_Z_LOG = 2, OVM_Z_CLUSTERS = 3 };
 enum { OVM_POSE_6D = 0, OVM_POSE_QUATERNION = 1, OVM_POSE_EULER = 2 };
 enum { OVM_DIMS_EXP = 0, OVM_DIMS_SIGMOID = 1 };
 enum { OVM_GEMM_AUTO = 0, OVM_GEMM_DIRECT = 1, OVM_GEMM_STREAMK = 2 };
+
+/* int32 elements of ovm_pooler_t.order_ws that are always enough for n boxes */
+#define OVM_ORDER_WS_LEN(n) (6 * (int64_t)(n) + 1200)
 
 /* One pyramid level: fp32 feature map of N images, C channels, contiguous in `layout`. */
 typedef struct {
@@ -63,9 +66,11 @@ typedef struct {
   int32_t canonical_box_size;    /* d2 default 224 */
   int32_t canonical_level;       /* d2 default 4 */
   float scale_roi_boxes;         /* SCALE_ROI_BOXES; <= 0 disables (roi_heads.py:310-327) */
-  int32_t _pad;
-  int32_t* order_ws;             /* optional device scratch [n] int32: when given, boxes are scheduled largest
-                                    footprint first (one extra tiny launch); NULL = in input order */
+  int32_t order_ws_len;          /* int32 elements in order_ws; OVM_ORDER_WS_LEN(n) is enough for n boxes */
+  int32_t* order_ws;             /* optional device scratch: when given, one extra tiny launch turns the boxes into
+                                    work items (large footprints are cut along the channels, largest item first)
+                                    so that no single CTA sets the kernel time; NULL = one CTA per box in input
+                                    order */
 } ovm_pooler_t;
 
 /* Multi-level ROIAlignV2.  boxes [n,4] xyxy fp32, batch_idx [n] int32 (image of each box), both
@@ -159,7 +164,8 @@ typedef struct {
 typedef struct {
   void* pooled;        /* bf16 [n, ld_pooled], ld_pooled = roundup(C*P*P, 8) */
   int64_t ld_pooled;
-  float* acc;          /* fp32 [n, fc_dim] split-K accumulator */
+  float* acc;          /* fp32 [n, fc_dim] split-K accumulator: ZERO-FILLED by the caller once, when it is
+                          allocated; ovm_lift_forward leaves it zero-filled again (no per-call memset) */
   void* act_a;         /* bf16 [n, fc_dim] ping */
   void* act_b;         /* bf16 [n, fc_dim] pong */
   float* feats;        /* fp32 [n, num_groups * fc_dim] */

@@ -408,14 +408,16 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 }
 
 // ------------------------------------------------------------------ small elementwise kernels
-__global__ void bias_act_kernel(const float* __restrict__ in, long long ldi, const float* __restrict__ bias, int relu,
-                                int M, int N, void* out, int out_bf16, long long ldo) {
+__global__ void bias_act_kernel(const float* in, long long ldi, const float* __restrict__ bias, int relu,
+                                int M, int N, void* out, int out_bf16, long long ldo, int clear_in) {
   // one thread per 4 consecutive columns (N % 4 == 0 is required by the launcher)
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const int n4 = N >> 2;
   if (idx >= (long long)M * n4) return;
   const int m = (int)(idx / n4), j = (int)(idx - (long long)m * n4) * 4;
   float4 v = *reinterpret_cast<const float4*>(in + (long long)m * ldi + j);
+  // split-K accumulator: hand it back zeroed so that the next layer / call needs no memset launch
+  if (clear_in) *reinterpret_cast<float4*>(const_cast<float*>(in) + (long long)m * ldi + j) = make_float4(0.f, 0.f, 0.f, 0.f);
   if (bias) {
     const float4 b = *reinterpret_cast<const float4*>(bias + j);
     v.x += b.x; v.y += b.y; v.z += b.z; v.w += b.w;
@@ -504,10 +506,11 @@ int gemm_bf16_launch(const void* A, int64_t lda, const void* B, int64_t ldb, int
 
   // Tile width: the widest of 256/128/64 that still yields enough tiles; small N uses 64 (B rows past N are
   // zero-filled by TMA and masked in the epilogue).
-  const int BN = N >= 256 ? 256 : (N >= 128 ? 128 : 64);
+  int BN = N >= 256 ? 256 : (N >= 128 ? 128 : 64);
   GemmArgs g{};
   g.M = M; g.N = N; g.K = K;
   const int num_m_tiles = (M + BM - 1) / BM;
+
   g.num_n_tiles = (N + BN - 1) / BN;
   g.num_tiles = num_m_tiles * g.num_n_tiles;
   g.kb_per_tile = (K + BK - 1) / BK;
@@ -518,6 +521,14 @@ int gemm_bf16_launch(const void* A, int64_t lda, const void* B, int64_t ldb, int
     const bool ragged = g.num_tiles < kNumSMs || (g.num_tiles % kNumSMs) * 2 < kNumSMs;
     mode = (out_dtype == OVM_F32 && g.kb_per_tile >= 32 && g.num_tiles < 2 * kNumSMs && ragged && !bias && !relu)
                ? OVM_GEMM_STREAMK : OVM_GEMM_DIRECT;
+  }
+  if (mode == OVM_GEMM_DIRECT) {
+    // a grid that does not fill the SMs is bound by the per-CTA critical path (prologue + K loop + epilogue of one
+    // tile): narrower tiles shorten it as long as they still fit one wave (fc2: 52 tiles of 256 -> 104 of 128)
+    while (BN > 64 && num_m_tiles * ((N + BN / 2 - 1) / (BN / 2)) <= kNumSMs) BN /= 2;
+    g.num_n_tiles = (N + BN - 1) / BN;
+    g.num_tiles = num_m_tiles * g.num_n_tiles;
+    g.total_kb = (long long)g.num_tiles * g.kb_per_tile;
   }
   if (mode == OVM_GEMM_STREAMK) {
     OVM_REQUIRE(out_dtype == OVM_F32 && !bias && !relu,
@@ -548,14 +559,14 @@ int gemm_bf16_launch(const void* A, int64_t lda, const void* B, int64_t ldb, int
 void gemm_set_trace(unsigned long long* buf) { g_gemm_trace = buf; }
 
 int bias_act_launch(const float* in, int64_t ldi, const float* bias, int32_t relu, int32_t M, int32_t N, void* out,
-                    int32_t out_dtype, int64_t ldo, cudaStream_t stream) {
+                    int32_t out_dtype, int64_t ldo, cudaStream_t stream, bool clear_in) {
   if (M == 0) return OVM_OK;
   OVM_REQUIRE(in && out && M > 0 && N > 0, "ovm_bias_act: bad arguments");
   OVM_REQUIRE(N % 4 == 0 && ldi % 4 == 0 && ldo % 4 == 0, "ovm_bias_act: N, ldi, ldo must be multiples of 4");
   OVM_REQUIRE(out_dtype == OVM_F32 || out_dtype == OVM_BF16, "ovm_bias_act: out_dtype %d", out_dtype);
   const long long total = (long long)M * (N / 4);
   bias_act_kernel<<<(unsigned)((total + 255) / 256), 256, 0, stream>>>(in, ldi, bias, relu, M, N, out,
-                                                                     out_dtype == OVM_BF16, ldo);
+                                                                     out_dtype == OVM_BF16, ldo, clear_in ? 1 : 0);
   OVM_LAUNCHED("bias_act_kernel");
   return OVM_OK;
 }

@@ -25,7 +25,7 @@ namespace ovm {
 
 namespace {
 
-constexpr int kWarpsPerBlock = 4;
+constexpr int kWarpsPerBlock = 12;   // 148 CTAs x 12 warps take 1776 boxes in one pass
 
 struct DecodeArgs {
   ovm_decode_cfg_t cfg;
@@ -52,24 +52,53 @@ constexpr int kMaxRows = 13;   // deltas 2 + dims 3 + pose <= 6 + z 1 + uncertai
 
 // All selected head rows in one pass over the feature vector(s): out[r] = <w[r], f[r]> + bias[r].
 // Lane i owns float4 i, i+32, ... of every row, so the loads of one row are coalesced across the warp and the
-// kMaxRows accumulation chains are independent (the loop is load-latency bound otherwise).  With SHARED the rows
-// all read the same feature vector and it is loaded once.  Every lane returns every sum.
-template <bool SHARED>
+// kMaxRows accumulation chains are independent.  With SHARED the rows all read the same feature vector: it is
+// loaded once, 8 float4 per lane at a time with all loads in flight together (the loop is load-latency bound
+// otherwise).  With STAGED the weight rows are the CTA's shared-memory copy (class-agnostic heads: every box uses
+// the same rows).  Every lane returns every sum.
+template <bool SHARED, bool STAGED>
 __device__ __forceinline__ void head_rows(const float* const (&w)[kMaxRows], const float* const (&f)[kMaxRows],
                                           const float (&bias)[kMaxRows], int nrows, int K, int lane, bool vec4,
                                           float (&out)[kMaxRows]) {
   float acc[kMaxRows];
 #pragma unroll
   for (int r = 0; r < kMaxRows; ++r) acc[r] = 0.f;
-  if (vec4) {
-    for (int i = lane; i < (K >> 2); i += 32) {
-      float4 fs = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (SHARED) fs = reinterpret_cast<const float4*>(f[0])[i];
+  auto wload = [&](int r, int i) {
+    return STAGED ? reinterpret_cast<const float4*>(w[r])[i] : __ldg(reinterpret_cast<const float4*>(w[r]) + i);
+  };
+  if (vec4 && SHARED) {
+    const int K4 = K >> 2;
+    for (int base = 0; base < K4; base += 256) {
+      float4 fs[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int i = base + lane + 32 * j;
+        fs[j] = i < K4 ? reinterpret_cast<const float4*>(f[0])[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
 #pragma unroll
       for (int r = 0; r < kMaxRows; ++r) {
         if (r < nrows) {
-          const float4 a = __ldg(reinterpret_cast<const float4*>(w[r]) + i);
-          const float4 b = SHARED ? fs : reinterpret_cast<const float4*>(f[r])[i];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const int i = base + lane + 32 * j;
+            if (i < K4) {
+              const float4 a = wload(r, i);
+              acc[r] = fmaf(a.x, fs[j].x, acc[r]);
+              acc[r] = fmaf(a.y, fs[j].y, acc[r]);
+              acc[r] = fmaf(a.z, fs[j].z, acc[r]);
+              acc[r] = fmaf(a.w, fs[j].w, acc[r]);
+            }
+          }
+        }
+      }
+    }
+  } else if (vec4) {
+    for (int i = lane; i < (K >> 2); i += 32) {
+#pragma unroll
+      for (int r = 0; r < kMaxRows; ++r) {
+        if (r < nrows) {
+          const float4 a = wload(r, i);
+          const float4 b = reinterpret_cast<const float4*>(f[r])[i];
           acc[r] = fmaf(a.x, b.x, acc[r]);
           acc[r] = fmaf(a.y, b.y, acc[r]);
           acc[r] = fmaf(a.z, b.z, acc[r]);
@@ -81,7 +110,7 @@ __device__ __forceinline__ void head_rows(const float* const (&w)[kMaxRows], con
     for (int i = lane; i < K; i += 32) {
 #pragma unroll
       for (int r = 0; r < kMaxRows; ++r)
-        if (r < nrows) acc[r] = fmaf(__ldg(w[r] + i), f[r][i], acc[r]);
+        if (r < nrows) acc[r] = fmaf(STAGED ? w[r][i] : __ldg(w[r] + i), f[r][i], acc[r]);
     }
   }
 #pragma unroll
@@ -113,10 +142,9 @@ __device__ __forceinline__ void matmul3(const float* A, const float* B, float* C
     for (int c = 0; c < 3; ++c) C[3 * r + c] = A[3 * r] * B[c] + A[3 * r + 1] * B[3 + c] + A[3 * r + 2] * B[6 + c];
 }
 
-__global__ void __launch_bounds__(kWarpsPerBlock * 32) head_decode_kernel(const DecodeArgs a) {
-  const int lane = threadIdx.x & 31;
-  const int box = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
-  if (box >= a.n) return;  // warp-uniform
+// One box, one warp.  STAGED: `staged` is the CTA's shared-memory copy of the head rows in the row order below.
+template <bool STAGED>
+__device__ __forceinline__ void decode_box(const DecodeArgs& a, const int box, const int lane, const float* staged) {
   const ovm_decode_cfg_t& cfg = a.cfg;
   const int K = cfg.fc_dim;
   const int NC = cfg.num_classes;
@@ -211,10 +239,14 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) head_decode_kernel(const 
     }
   }
   const int nrows = 6 + conf_rows + pose_n;
+  if (STAGED) {
+#pragma unroll
+    for (int r = 0; r < kMaxRows; ++r) wr[r] = staged + (r < nrows ? r : 0) * K;
+  }
   if (shared)
-    head_rows<true>(wr, fr, bs, nrows, K, lane, vec4, hv);
+    head_rows<true, STAGED>(wr, fr, bs, nrows, K, lane, vec4, hv);
   else
-    head_rows<false>(wr, fr, bs, nrows, K, lane, vec4, hv);
+    head_rows<false, STAGED>(wr, fr, bs, nrows, K, lane, vec4, hv);
   const float deltas[2] = {hv[0], hv[1]};
   const float dims_raw[3] = {hv[2], hv[3], hv[4]};
   const float z_raw = hv[5];
@@ -355,6 +387,40 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) head_decode_kernel(const 
   }
 }
 
+// Grid-stride over boxes, one warp per box.  STAGED (class-agnostic heads without depth bins: every box uses the
+// same <= 13 rows): the CTA first copies those rows into shared memory, in decode_box's row order.
+template <bool STAGED>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32) head_decode_kernel(const DecodeArgs a) {
+  extern __shared__ float4 staged4[];
+  float* staged = reinterpret_cast<float*>(staged4);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (STAGED) {
+    const ovm_decode_cfg_t& cfg = a.cfg;
+    const int K = cfg.fc_dim;
+    const int pose_n = cfg.pose_type == OVM_POSE_6D ? 6 : (cfg.pose_type == OVM_POSE_QUATERNION ? 4 : 3);
+    const int conf_rows = cfg.use_confidence ? 1 : 0;
+    const int nrows = 6 + conf_rows + pose_n;
+    for (int r = warp; r < nrows; r += kWarpsPerBlock) {
+      const float* src;
+      if (r < 2) src = a.w.w_deltas + (long long)r * K;
+      else if (r < 5) src = a.w.w_dims + (long long)(r - 2) * K;
+      else if (r == 5) src = a.w.w_z;
+      else if (r == 6 && conf_rows) src = a.w.w_uncert;
+      else src = a.w.w_pose + (long long)(r - 6 - conf_rows) * K;
+      float* dst = staged + (long long)r * K;
+      if (!(K & 3) && !(reinterpret_cast<uintptr_t>(src) & 15)) {
+        for (int i = lane; i < (K >> 2); i += 32)
+          reinterpret_cast<float4*>(dst)[i] = __ldg(reinterpret_cast<const float4*>(src) + i);
+      } else {
+        for (int i = lane; i < K; i += 32) dst[i] = __ldg(src + i);
+      }
+    }
+    __syncthreads();
+  }
+  for (int box = blockIdx.x * kWarpsPerBlock + warp; box < a.n; box += gridDim.x * kWarpsPerBlock)
+    decode_box<STAGED>(a, box, lane, staged);
+}
+
 }  // namespace
 
 int head_decode_launch(const ovm_decode_cfg_t* cfg, const ovm_head_weights_t* w, const float* feats, int64_t ld_feats,
@@ -402,7 +468,22 @@ int head_decode_launch(const ovm_decode_cfg_t* cfg, const ovm_head_weights_t* w,
   a.n = n;
   a.records = records;
   a.raw = raw;
-  head_decode_kernel<<<(n + kWarpsPerBlock - 1) / kWarpsPerBlock, kWarpsPerBlock * 32, 0, stream>>>(a);
+  const int pose_n = cfg->pose_type == OVM_POSE_6D ? 6 : (cfg->pose_type == OVM_POSE_QUATERNION ? 4 : 3);
+  const size_t stage_bytes = (size_t)(6 + (cfg->use_confidence ? 1 : 0) + pose_n) * cfg->fc_dim * sizeof(float);
+  const bool staged = !cfg->dims_priors_enabled && cfg->cluster_bins == 1 && stage_bytes <= 160 * 1024 &&
+                      cfg->fc_dim % 4 == 0;   // K % 4: rows stay 16-byte aligned in shared memory
+  int grid = (n + kWarpsPerBlock - 1) / kWarpsPerBlock;
+  if (grid > kNumSMs) grid = kNumSMs;
+  if (staged) {
+    static size_t attr_bytes = 0;
+    if (stage_bytes > attr_bytes) {
+      OVM_CUDA(cudaFuncSetAttribute(head_decode_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stage_bytes));
+      attr_bytes = stage_bytes;
+    }
+    head_decode_kernel<true><<<grid, kWarpsPerBlock * 32, stage_bytes, stream>>>(a);
+  } else {
+    head_decode_kernel<false><<<grid, kWarpsPerBlock * 32, 0, stream>>>(a);
+  }
   OVM_LAUNCHED("head_decode_kernel");
   return OVM_OK;
 }

@@ -72,12 +72,11 @@ int run_fc_group(const ovm_fc_layer_t* layers, int num_fc, const void* x, int64_
       if (kb >= 32 && tiles < 2 * kNumSMs && ragged && ws->acc) mode = OVM_GEMM_STREAMK;
     }
     if (mode == OVM_GEMM_STREAMK) {
-      OVM_CUDA(cudaMemsetAsync(ws->acc, 0, (size_t)n * L.N * sizeof(float), stream));
-      g_launches.fetch_add(1, std::memory_order_relaxed);
+      // ws->acc is zero on entry (workspace contract) and bias_act hands it back zeroed
       int rc = gemm_bf16_launch(in, ld_in, L.weight, L.ldw, n, L.N, L.K, nullptr, 0, ws->acc, OVM_F32, L.N,
                                 OVM_GEMM_STREAMK, nullptr, stream);
       if (rc != OVM_OK) return rc;
-      rc = bias_act_launch(ws->acc, L.N, L.bias, 1, n, L.N, out, out_dtype, ldo, stream);
+      rc = bias_act_launch(ws->acc, L.N, L.bias, 1, n, L.N, out, out_dtype, ldo, stream, /*clear_in=*/true);
       if (rc != OVM_OK) return rc;
     } else {
       int rc = gemm_bf16_launch(in, ld_in, L.weight, L.ldw, n, L.N, L.K, L.bias, 1, out, out_dtype, ldo,

@@ -27,6 +27,7 @@
 #include <cfloat>
 #include <climits>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <mutex>
@@ -41,8 +42,7 @@ namespace {
 constexpr int kP = 7;
 constexpr int kThreads = 256;              // 7 consumer warps + 1 producer warp
 constexpr int kConsumers = kP * 32;
-constexpr int kStages = 2;
-constexpr int kStageFloats = 24 * 8 * 32;  // 24 KB: rows x Wt <= 192 floats per channel (24 rows at Wt = 8, 12 at 16);
+constexpr int kStageFloatsA = 24 * 8 * 32;  // 24 KB: rows x Wt <= 192 floats per channel (24 rows at Wt = 8, 12 at 16);
                                            // two stages + tables + output staging = 68 KB per CTA, three CTAs per SM
 constexpr int kMaxW = 128;                 // footprint columns the Wx table holds
 constexpr int kMaxRows = 64;               // rows one output bin-row may touch
@@ -50,9 +50,13 @@ constexpr int kWxFloats = kMaxW * 8;
 constexpr int kWyFloats = kP * kMaxRows;
 constexpr int kOutFloats = 32 * kP * kP;   // one chunk of results
 constexpr int kMetaInts = 64;
-constexpr size_t kSmemBytes = 1024 + (size_t)kStages * kStageFloats * 4 + (size_t)(2 * kOutFloats + kWxFloats + kWyFloats) * 4 +
-                              kMetaInts * 4 + 64;
-constexpr int kWidths = 3;                 // tensor maps per level: Wt = 8, 16, 32
+constexpr int kMaxSlots = 8;               // ring slots (a slot is as large as the box's stage, not kStageFloats)
+constexpr size_t roi_smem_bytes(int ring_floats) {
+  return 1024 + (size_t)ring_floats * 4 + (size_t)(2 * kOutFloats + kWxFloats + kWyFloats) * 4 + kMetaInts * 4 + 2 * kMaxSlots * 8;
+}
+constexpr int kWidths = 3;                 // tensor-map tile widths: Wt = 8, 16, 32
+constexpr int kHeights = 5;                // tensor-map tile heights: 1, 2, 4, 8, 16 footprint rows per TMA instruction
+constexpr int kMapsPerLevel = kWidths * kHeights;
 
 struct RoiLevel {
   const float* data;
@@ -76,10 +80,32 @@ struct RoiArgs {
   const int* order;             // boxes in descending cost (roi_order_kernel), or NULL: natural order
   int splits, chunks_per_split;
   int tma_ok[OVM_MAX_LEVELS];   // level has tensor maps (NCHW, 16-byte aligned base, width % 4 == 0)
+  float split_factor;           // roi_order_kernel: an item may cost this many average boxes before the box is cut
+  int xalign_mask;              // footprint start column is rounded down to this mask (~3 or ~7)
   unsigned long long* trace;    // optional [grid, 16] %globaltimer stamps (ovm_roi_set_trace), else NULL
 };
 
 thread_local unsigned long long* g_roi_trace = nullptr;
+
+// Development knobs (environment, read once): used by tools/roi_bench.py to compare schedules on the device.
+struct RoiTune {
+  int split_pct;    // OVM_ROI_SPLIT   cost of a work item, in % of the average box, above which a box is cut along the channels
+  int promo;        // OVM_ROI_PROMO   L2 promotion of the tensor maps: 0 none, 1 64 B, 2 128 B, 3 256 B
+  int align8;       // OVM_ROI_ALIGN8  footprint starts on a 32-byte sector (8 floats) instead of 16 bytes
+  int stages;       // OVM_ROI_STAGES  2 or 3 pipeline stages
+};
+const RoiTune& roi_tune() {
+  static RoiTune t = [] {
+    auto env = [](const char* k, int d) { const char* v = getenv(k); return v ? atoi(v) : d; };
+    RoiTune r;
+    r.split_pct = env("OVM_ROI_SPLIT", 100000);
+    r.promo = env("OVM_ROI_PROMO", 2);
+    r.align8 = env("OVM_ROI_ALIGN8", 0);
+    r.stages = env("OVM_ROI_STAGES", 2);
+    return r;
+  }();
+  return t;
+}
 
 __device__ __forceinline__ void trace_stamp(const RoiArgs& a, int slot) {
   if (a.trace) {
@@ -90,7 +116,7 @@ __device__ __forceinline__ void trace_stamp(const RoiArgs& a, int slot) {
 }
 
 struct RoiMaps {
-  CUtensorMap m[OVM_MAX_LEVELS * kWidths];   // [level][log2(Wt) - 3]
+  CUtensorMap m[OVM_MAX_LEVELS * kMapsPerLevel];   // [level][log2(Wt) - 3][log2(rows)]
 };
 
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
@@ -108,29 +134,13 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     asm volatile(
         "{\n\t"
         ".reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
         "selp.u32 %0, 1, 0, p;\n\t"
         "}"
         : "=r"(done)
-        : "r"(bar), "r"(parity)
+        : "r"(bar), "r"(parity), "r"(0x989680u)   // suspend-time hint: sleep in the barrier unit, not in a spin loop
         : "memory");
   } while (!done);
-}
-__device__ __forceinline__ void mbar_wait_sleep(uint32_t bar, uint32_t parity) {
-  uint32_t done;
-  for (;;) {
-    asm volatile(
-        "{\n\t"
-        ".reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t"
-        "}"
-        : "=r"(done)
-        : "r"(bar), "r"(parity)
-        : "memory");
-    if (done) break;
-    __nanosleep(64);   // keep the issue slots for the warps that have data
-  }
 }
 // packed fp32 pairs (FFMA2 on sm_100): two independent fused multiply-adds per instruction
 __device__ __forceinline__ uint64_t pack2(float lo, float hi) {
@@ -281,61 +291,190 @@ __device__ void direct_path(const RoiArgs& a, const BoxGeom& g, int box, int c_b
   }
 }
 
-// Cheapest useful schedule for a grid of CTAs with very different run times: longest first.  One CTA buckets the
-// boxes by footprint area (64 buckets, biggest first) with a counting sort in shared memory and writes the order.
-__global__ void __launch_bounds__(1024) roi_order_kernel(const RoiArgs a, int* __restrict__ order) {
+// One (chunk, column tile) of one bin-row for one channel (lane): the vertical weighted sum over the bin-row's NY
+// pixel rows (NY = 1..4 unrolled with the row weights in registers; NY = 0: any height, weights from shared memory),
+// then the 7-wide horizontal one.  `slab0` is the lane's channel row in the first pixel row of the bin-row; 16-byte
+// unit j of it sits at unit j ^ sw (TMA swizzle).
+struct PoolAcc {
+  uint64_t a01, a23, a45;
+  float a6;
+};
+template <int NY>
+__device__ __forceinline__ void consume_tile(const float* __restrict__ slab0, int slab_floats, int sw, int ncol4,
+                                             const float (&wyr)[4], const float* __restrict__ wy, int ny,
+                                             const float* __restrict__ wx, PoolAcc& acc) {
+#pragma unroll 2
+  for (int x4 = 0; x4 < ncol4; ++x4) {
+    const float* p = slab0 + 4 * (x4 ^ sw);
+    uint64_t v01 = 0, v23 = 0;
+    if (NY > 0) {
+#pragma unroll
+      for (int r = 0; r < NY; ++r) {
+        const float4 f = *reinterpret_cast<const float4*>(p + r * slab_floats);
+        const uint64_t w2 = pack2(wyr[r], wyr[r]);
+        v01 = ffma2(w2, pack2(f.x, f.y), v01);
+        v23 = ffma2(w2, pack2(f.z, f.w), v23);
+      }
+    } else {
+      for (int r = 0; r < ny; ++r) {
+        const float4 f = *reinterpret_cast<const float4*>(p + r * slab_floats);
+        const uint64_t w2 = pack2(wy[r], wy[r]);
+        v01 = ffma2(w2, pack2(f.x, f.y), v01);
+        v23 = ffma2(w2, pack2(f.z, f.w), v23);
+      }
+    }
+    const float vv[4] = {lo2(v01), hi2(v01), lo2(v23), hi2(v23)};
+    const float* w = wx + 32 * x4;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float4 wa = *reinterpret_cast<const float4*>(w + e * 8);
+      const float4 wb = *reinterpret_cast<const float4*>(w + e * 8 + 4);
+      const uint64_t v2 = pack2(vv[e], vv[e]);
+      acc.a01 = ffma2(pack2(wa.x, wa.y), v2, acc.a01);
+      acc.a23 = ffma2(pack2(wa.z, wa.w), v2, acc.a23);
+      acc.a45 = ffma2(pack2(wb.x, wb.y), v2, acc.a45);
+      acc.a6 = fmaf(wb.z, vv[e], acc.a6);
+    }
+  }
+}
+
+// Work items for a grid of CTAs with very different run times.  One CTA turns the boxes into items
+// (box, first chunk, chunks) so that no item is much more expensive than the average box -- a box whose footprint
+// is k times the mean is cut into up to k pieces along the channel chunks (otherwise the largest box alone, walked
+// by one CTA, sets the kernel time: measured 89 us for a 34 x 34 pixel footprint) -- and orders the items by
+// cost, largest first, with a counting sort in shared memory.  ws layout: [0] item count, [1] unused,
+// [2 + 2 i] box, [3 + 2 i] first chunk | chunks << 16.   At most max(3, splits) * n items (see roi_align_launch).
+__global__ void __launch_bounds__(1024) roi_order_kernel(const RoiArgs a, int* __restrict__ ws) {
   __shared__ int hist[64], offs[64];
-  const int tid = threadIdx.x;
+  __shared__ float warp_sum[32];
+  __shared__ float mean_area;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid < 64) hist[tid] = 0;
-  __syncthreads();
-  auto bucket_of = [&](int box) {
+  auto area_of = [&](int box) {
     const BoxGeom g = box_geometry(a, box);
-    if (g.level < 0) return 63;
+    if (g.level < 0) return 1.f;
     const RoiLevel lv = a.lv[g.level];
     // pixel rows x columns of the footprint, clipped to the map
     const float w = fminf(fmaxf(g.bin_w * (float)a.P, 0.f), (float)lv.W) + 2.f;
     const float h = fminf(fmaxf(g.bin_h * (float)a.P, 0.f), (float)lv.H) + 2.f;
-    const float area = w * h;                       // NaN -> bucket 63 through the comparison below
-    int b = 63 - (int)fminf(area * (1.f / 16.f), 63.f);
-    return (area == area) ? b : 63;
+    const float area = w * h;
+    return (area == area) ? area : 1.f;
   };
-  for (int box = tid; box < a.n; box += blockDim.x) atomicAdd(&hist[bucket_of(box)], 1);
+  constexpr int kKeep = 4;   // areas of the first 4096 boxes stay in registers between the passes
+  float areas[kKeep];
+  float sum = 0.f;
+#pragma unroll
+  for (int k = 0; k < kKeep; ++k) {
+    const int box = tid + k * 1024;
+    areas[k] = box < a.n ? area_of(box) : 0.f;
+    sum += areas[k];
+  }
+  for (int box = tid + kKeep * 1024; box < a.n; box += 1024) sum += area_of(box);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  if (lane == 0) warp_sum[warp] = sum;
   __syncthreads();
-  if (tid == 0) {
-    int run = 0;
-    for (int b = 0; b < 64; ++b) {
-      offs[b] = run;
-      run += hist[b];
+  if (warp == 0) {
+    float t = warp_sum[lane];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+    if (lane == 0) mean_area = t / (float)a.n;
+  }
+  __syncthreads();
+  const int chunks = (a.C + 31) / 32;
+  const float mean = mean_area * a.split_factor;
+  // chunks per item: the largest power of two with area * cpi <= mean * chunks (never more than the launch's
+  // chunks_per_split, which spreads a small batch over the SMs); pieces per box <= max(1, 2 area / mean)
+  auto cpi_of = [&](float area) {
+    int cpi = 1;
+    while (cpi * 2 <= a.chunks_per_split && area * (float)(cpi * 2) <= mean * (float)chunks) cpi *= 2;
+    if (cpi * 2 > a.chunks_per_split && area * (float)a.chunks_per_split <= mean * (float)chunks) cpi = a.chunks_per_split;
+    if (chunks > 8 * cpi) cpi = (chunks + 7) / 8;   // at most 8 pieces per box
+    return cpi;
+  };
+  auto bucket_of = [&](float area, int cpi) {
+    const float cost = area * (float)cpi / (mean_area * (float)chunks);   // in units of the average box
+    return 63 - (int)fminf(cost * 8.f, 63.f);
+  };
+#pragma unroll
+  for (int k = 0; k < kKeep; ++k) {
+    if (tid + k * 1024 < a.n) {
+      const int cpi = cpi_of(areas[k]);
+      atomicAdd(&hist[bucket_of(areas[k], cpi)], (chunks + cpi - 1) / cpi);
+    }
+  }
+  for (int box = tid + kKeep * 1024; box < a.n; box += 1024) {
+    const float ar = area_of(box);
+    const int cpi = cpi_of(ar);
+    atomicAdd(&hist[bucket_of(ar, cpi)], (chunks + cpi - 1) / cpi);
+  }
+  __syncthreads();
+  if (warp == 0) {   // exclusive scan of the 64 buckets: two per lane
+    const int h0 = hist[2 * lane], h1 = hist[2 * lane + 1];
+    int incl = h0 + h1;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += t;
+    }
+    offs[2 * lane] = incl - h0 - h1;
+    offs[2 * lane + 1] = incl - h1;
+    if (lane == 31) {
+      ws[0] = incl;
+      ws[1] = 0;
     }
   }
   __syncthreads();
-  for (int box = tid; box < a.n; box += blockDim.x) order[atomicAdd(&offs[bucket_of(box)], 1)] = box;
+  auto emit = [&](int box, float ar) {
+    const int cpi = cpi_of(ar);
+    const int pieces = (chunks + cpi - 1) / cpi;
+    const int at = atomicAdd(&offs[bucket_of(ar, cpi)], pieces);
+    for (int j = 0; j < pieces; ++j) {
+      ws[2 + 2 * (at + j)] = box;
+      ws[3 + 2 * (at + j)] = (j * cpi) | (min(cpi, chunks - j * cpi) << 16);
+    }
+  };
+#pragma unroll
+  for (int k = 0; k < kKeep; ++k)
+    if (tid + k * 1024 < a.n) emit(tid + k * 1024, areas[k]);
+  for (int box = tid + kKeep * 1024; box < a.n; box += 1024) emit(box, area_of(box));
 }
 
 // meta layout (ints): [0..6] x bin lo, [7..13] x bin hi, [14..20] y bin lo, [21..27] y bin hi (lo > hi: no valid sample)
+// kRingFloats: shared-memory ring of footprint stages; kStageFloats: largest stage (rows x Wt x 32 channels) the TMA
+// path accepts.
+template <int kRingFloats, int kStageFloats>
 __global__ void __launch_bounds__(kThreads) roi_align_kernel(const __grid_constant__ RoiMaps maps, const RoiArgs a) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;   // swizzled TMA slabs need 1024-byte alignment
   uint8_t* aligned = smem_raw + (base - raw);
   float* stages = reinterpret_cast<float*>(aligned);                 // kStages * kStageFloats
-  float* outbuf = stages + kStages * kStageFloats;                   // 2 * kOutFloats
+  float* outbuf = stages + kRingFloats;                   // 2 * kOutFloats
   float* Wx = outbuf + 2 * kOutFloats;                               // [col][8]
   float* Wy = Wx + kWxFloats;                                        // [ph][kMaxRows]
   int* meta = reinterpret_cast<int*>(Wy + kWyFloats);
   const uint32_t bars = smem_u32(meta + kMetaInts);                  // full[kStages], empty[kStages]
 
-  const int box = a.order ? a.order[blockIdx.x / a.splits] : (int)(blockIdx.x / a.splits);
-  const int split = blockIdx.x % a.splits;
+  int box, chunk_begin, chunk_end;
+  if (a.order) {   // work items of roi_order_kernel; the grid is an upper bound of their number
+    if ((int)blockIdx.x >= a.order[0]) return;
+    const int2 item = *reinterpret_cast<const int2*>(a.order + 2 + 2 * blockIdx.x);
+    box = item.x;
+    chunk_begin = item.y & 0xffff;
+    chunk_end = chunk_begin + (item.y >> 16);
+  } else {
+    box = (int)(blockIdx.x / a.splits);
+    chunk_begin = (int)(blockIdx.x % a.splits) * a.chunks_per_split;
+    chunk_end = min((a.C + 31) / 32, chunk_begin + a.chunks_per_split);
+  }
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int chunk_begin = split * a.chunks_per_split;
-  const int chunk_end = min((a.C + 31) / 32, chunk_begin + a.chunks_per_split);
   const int c_begin = chunk_begin * 32;
   const int c_end = min(a.C, chunk_end * 32);
 
   if (tid == 0) trace_stamp(a, 0);
   const BoxGeom g = box_geometry(a, box);
-  if (split == 0 && tid == 0 && a.level_out) a.level_out[box] = g.level;
+  if (chunk_begin == 0 && tid == 0 && a.level_out) a.level_out[box] = g.level;
 
   bool direct = (a.P != kP) || g.level < 0 || g.gw <= 0 || g.gh <= 0;
   if (!direct) direct = !a.tma_ok[g.level];
@@ -363,9 +502,9 @@ __global__ void __launch_bounds__(kThreads) roi_align_kernel(const __grid_consta
     meta[(is_x ? 7 : 21) + lane] = mx;
   }
   if (tid == 0) {
-    for (int s = 0; s < kStages; ++s) {
+    for (int s = 0; s < kMaxSlots; ++s) {
       mbar_init(bars + 8 * s, 1);                    // full: the producer's expect_tx arrive
-      mbar_init(bars + 8 * (kStages + s), kP);       // empty: one arrive per consumer warp
+      mbar_init(bars + 8 * (kMaxSlots + s), kP);     // empty: one arrive per consumer warp
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -389,7 +528,7 @@ __global__ void __launch_bounds__(kThreads) roi_align_kernel(const __grid_consta
   // ---- column tiling: the tile width with the least padding that lets all footprint rows sit in one stage
   // the innermost TMA coordinate must be a multiple of 16 bytes (measured: anything else faults), so the footprint
   // starts at the 4-float boundary at or below its first column
-  const int x0 = x_lo & ~3;
+  const int x0 = x_lo & a.xalign_mask;
   const int fw = x_hi - x0 + 1, rows_total = y_hi - y_lo + 1;
   int wsel = -1, best_pad = INT_MAX;
 #pragma unroll
@@ -432,31 +571,49 @@ __global__ void __launch_bounds__(kThreads) roi_align_kernel(const __grid_consta
   const int Wt = 8 << wsel;
   const int ntiles = best_pad / Wt;
   const int slab_floats = 32 * Wt;               // one footprint row of one chunk: [32 channels][Wt]
-  const int nchunks = chunk_end - chunk_begin;
-  const int per_chunk = ntiles * ngroups;        // pipeline items of a chunk: (row group, column tile)
+  // The ring is cut into slots of this box's stage size: small footprints get up to kMaxSlots stages in flight.
+  const int slot_floats = max(gy1[0] - gy0[0] + 1, ngroups == 2 ? gy1[1] - gy0[1] + 1 : 0) * slab_floats;
+  const int nslots = min(kMaxSlots, kRingFloats / slot_floats);
 
   if (warp == kP) {
-    // ===== TMA producer: starts as soon as the footprint is known, while the other warps build the tap tables
+    // ===== TMA producer (one lane): starts as soon as the footprint is known, while the other warps build the tap
+    // tables.  The maps view the level as {W, N*C, H}, so one instruction with box {Wt, 32, R} writes R footprint
+    // rows of the chunk as R consecutive [32 channels][Wt] slabs; a stage is the binary decomposition of its row
+    // count over R = 16, 8, 4, 2, 1 (each TMA instruction costs ~60 issue slots of operand marshalling).
     if (lane == 0) {
-      const CUtensorMap* map = &maps.m[g.level * kWidths + wsel];
-      int it = 0;
+      const CUtensorMap* map = &maps.m[g.level * kMapsPerLevel + wsel * kHeights];
+      int s = 0;
+      uint32_t phase = 0;
+      long long waited = 0;
       for (int chunk = chunk_begin; chunk < chunk_end; ++chunk) {
         const int cc = g.b * a.C + chunk * 32;
         for (int grp = 0; grp < ngroups; ++grp) {
           const int gy = grp ? gy0[1] : gy0[0];
           const int rows = (grp ? gy1[1] : gy1[0]) - gy + 1;
-          for (int tile = 0; tile < ntiles; ++tile, ++it) {
-            const int s = it % kStages;
-            mbar_wait(bars + 8 * (kStages + s), ((uint32_t)(it / kStages) & 1u) ^ 1u);
+          for (int tile = 0; tile < ntiles; ++tile) {
             const uint32_t full = bars + 8 * s;
+            const long long tw = a.trace ? clock64() : 0;
+            mbar_wait(bars + 8 * (kMaxSlots + s), phase ^ 1u);
+            if (a.trace) waited += clock64() - tw;
             mbar_expect_tx(full, (uint32_t)(rows * slab_floats * 4));
-            const uint32_t dst = base + (uint32_t)(s * kStageFloats) * 4u;
+            const uint32_t dst = base + (uint32_t)(s * slot_floats) * 4u;
             const int xc = x0 + tile * Wt;
-            for (int r = 0; r < rows; ++r)
-              tma_load_3d(dst + (uint32_t)(r * slab_floats) * 4u, map, full, xc, gy + r, cc);
+            int r = 0;
+#pragma unroll
+            for (int k = kHeights - 1; k >= 0; --k) {
+              while (rows - r >= (1 << k)) {
+                tma_load_3d(dst + (uint32_t)(r * slab_floats) * 4u, map + k, full, xc, cc, gy + r);
+                r += 1 << k;
+              }
+            }
+            if (++s == nslots) {
+              s = 0;
+              phase ^= 1u;
+            }
           }
         }
       }
+      if (a.trace) a.trace[(size_t)blockIdx.x * 16 + 14] = (unsigned long long)waited;   // clocks waiting for a free stage
     }
     return;
   }
@@ -504,62 +661,49 @@ __global__ void __launch_bounds__(kThreads) roi_align_kernel(const __grid_consta
   const int sw = wsel == 2 ? (lane & 7) : (wsel == 1 ? ((lane >> 1) & 3) : ((lane >> 2) & 1));
   const int nx4_tile = Wt >> 2;
   const int row_off = (ys - (my_grp ? gy0[1] : gy0[0])) * slab_floats + lane * Wt;
-  int it = 0;
+  float wyr[4];   // row weights of a bin-row of up to 4 pixel rows (the table is zero past the bin-row's rows)
+#pragma unroll
+  for (int r = 0; r < 4; ++r) wyr[r] = wy[r];
+  int s = 0;
+  uint32_t phase = 0;
+  bool first = true;
+  long long waited = 0;
   for (int chunk = chunk_begin; chunk < chunk_end; ++chunk) {
-    uint64_t acc01 = 0, acc23 = 0, acc45 = 0;
-    float acc6 = 0.f;
+    PoolAcc acc{0, 0, 0, 0.f};
     for (int grp = 0; grp < ngroups; ++grp)
-    for (int tile = 0; tile < ntiles; ++tile, ++it) {
-      const int s = it % kStages;
-      mbar_wait(bars + 8 * s, (uint32_t)(it / kStages) & 1u);
-      if (tid == 0 && it == 0) trace_stamp(a, 3);
+    for (int tile = 0; tile < ntiles; ++tile) {
+      const long long tw = a.trace ? clock64() : 0;
+      mbar_wait(bars + 8 * s, phase);
+      if (a.trace) waited += clock64() - tw;
+      if (tid == 0 && first) trace_stamp(a, 3);
+      first = false;
       if (ny > 0 && grp == my_grp) {
-        const float* slab0 = stages + s * kStageFloats + row_off;
+        const float* slab0 = stages + s * slot_floats + row_off;
         const int ncol4 = min(nx4_tile, (fw - tile * Wt + 3) >> 2);   // columns past the footprint carry zero weight
-        for (int x4 = 0; x4 < ncol4; ++x4) {
-          const float* p = slab0 + 4 * (x4 ^ sw);
-          uint64_t v01 = 0, v23 = 0;
-          // a bin-row is rarely taller than 2-3 pixels: the first four rows are unrolled under uniform predicates
-#pragma unroll
-          for (int r = 0; r < 4; ++r) {
-            if (r < ny) {
-              const float4 f = *reinterpret_cast<const float4*>(p + r * slab_floats);
-              const uint64_t w2 = pack2(wy[r], wy[r]);
-              v01 = ffma2(w2, pack2(f.x, f.y), v01);
-              v23 = ffma2(w2, pack2(f.z, f.w), v23);
-            }
-          }
-          for (int r = 4; r < ny; ++r) {
-            const float4 f = *reinterpret_cast<const float4*>(p + r * slab_floats);
-            const uint64_t w2 = pack2(wy[r], wy[r]);
-            v01 = ffma2(w2, pack2(f.x, f.y), v01);
-            v23 = ffma2(w2, pack2(f.z, f.w), v23);
-          }
-          const float vv[4] = {lo2(v01), hi2(v01), lo2(v23), hi2(v23)};
-          const float* wx = Wx + (tile * Wt + 4 * x4) * 8;
-#pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const float4 wa = *reinterpret_cast<const float4*>(wx + e * 8);
-            const float4 wb = *reinterpret_cast<const float4*>(wx + e * 8 + 4);
-            const uint64_t v2 = pack2(vv[e], vv[e]);
-            acc01 = ffma2(pack2(wa.x, wa.y), v2, acc01);
-            acc23 = ffma2(pack2(wa.z, wa.w), v2, acc23);
-            acc45 = ffma2(pack2(wb.x, wb.y), v2, acc45);
-            acc6 = fmaf(wb.z, vv[e], acc6);
-          }
+        const float* wxt = Wx + tile * Wt * 8;
+        switch (ny) {   // warp-uniform; a bin-row is rarely taller than 2-3 pixels
+          case 1: consume_tile<1>(slab0, slab_floats, sw, ncol4, wyr, wy, ny, wxt, acc); break;
+          case 2: consume_tile<2>(slab0, slab_floats, sw, ncol4, wyr, wy, ny, wxt, acc); break;
+          case 3: consume_tile<3>(slab0, slab_floats, sw, ncol4, wyr, wy, ny, wxt, acc); break;
+          case 4: consume_tile<4>(slab0, slab_floats, sw, ncol4, wyr, wy, ny, wxt, acc); break;
+          default: consume_tile<0>(slab0, slab_floats, sw, ncol4, wyr, wy, ny, wxt, acc); break;
         }
       }
       __syncwarp();
-      if (lane == 0) mbar_arrive(bars + 8 * (kStages + s));
+      if (lane == 0) mbar_arrive(bars + 8 * (kMaxSlots + s));
+      if (++s == nslots) {
+        s = 0;
+        phase ^= 1u;
+      }
     }
     // ---- stage the chunk's 32 x 49 results and write them as one contiguous run
     float* ob = outbuf + ((chunk - chunk_begin) & 1) * kOutFloats;
     {
       float* o = ob + lane * (kP * kP) + ph * kP;
-      o[0] = lo2(acc01) * inv_count; o[1] = hi2(acc01) * inv_count;
-      o[2] = lo2(acc23) * inv_count; o[3] = hi2(acc23) * inv_count;
-      o[4] = lo2(acc45) * inv_count; o[5] = hi2(acc45) * inv_count;
-      o[6] = acc6 * inv_count;
+      o[0] = lo2(acc.a01) * inv_count; o[1] = hi2(acc.a01) * inv_count;
+      o[2] = lo2(acc.a23) * inv_count; o[3] = hi2(acc.a23) * inv_count;
+      o[4] = lo2(acc.a45) * inv_count; o[5] = hi2(acc.a45) * inv_count;
+      o[6] = acc.a6 * inv_count;
     }
     asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory");
     if (tid == 0 && chunk - chunk_begin < 8) trace_stamp(a, 4 + chunk - chunk_begin);
@@ -598,7 +742,10 @@ __global__ void __launch_bounds__(kThreads) roi_align_kernel(const __grid_consta
       }
     }
   }
-  if (tid == 0) trace_stamp(a, 12);
+  if (tid == 0) {
+    trace_stamp(a, 12);
+    if (a.trace) a.trace[(size_t)blockIdx.x * 16 + 13] = (unsigned long long)waited;   // warp 0: clocks waiting for data
+  }
 }
 
 // Smallest fp32 s with floor(canonical_level + log2(s)) >= k, evaluated the way the reference's torch CPU
@@ -618,9 +765,11 @@ float level_threshold(int k, int canonical_level) {
   return s;
 }
 
-// Tensor maps of one pyramid level, Wt = 8 / 16 / 32.  fp32 [N*C, H, W] seen as 3-D {W, H, N*C}; box {Wt, 1, 32};
-// out-of-range elements (columns past W, channels past N*C) read as zero.
-int encode_level_maps(const float* data, int H, int W, long long NC, CUtensorMap* out3) {
+// Tensor maps of one pyramid level: fp32 [N*C, H, W] seen as 3-D {W, N*C, H} (the row dimension outermost, so
+// that a box {Wt, 32, R} lands in shared memory as R consecutive [32 channels][Wt] slabs), Wt = 8 / 16 / 32 with
+// the 32 / 64 / 128-byte swizzle, R = 1, 2, 4, 8, 16.  Out-of-range elements (columns past W, rows past H, channels
+// past N*C) read as zero.
+int encode_level_maps(const float* data, int H, int W, long long NC, CUtensorMap* out) {
   EncodeTiledFn enc = tensormap_encode_fn();
   if (!enc) {
     set_error("cuTensorMapEncodeTiled not available from the driver");
@@ -628,18 +777,22 @@ int encode_level_maps(const float* data, int H, int W, long long NC, CUtensorMap
   }
   static const CUtensorMapSwizzle swz[kWidths] = {CU_TENSOR_MAP_SWIZZLE_32B, CU_TENSOR_MAP_SWIZZLE_64B,
                                                  CU_TENSOR_MAP_SWIZZLE_128B};
+  static const CUtensorMapL2promotion promo[4] = {CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_64B,
+                                                  CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B};
   for (int k = 0; k < kWidths; ++k) {
-    cuuint64_t dims[3] = {(cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)NC};
-    cuuint64_t strides[2] = {(cuuint64_t)W * 4, (cuuint64_t)H * W * 4};
-    cuuint32_t box[3] = {(cuuint32_t)(8 << k), 1, 32};
-    cuuint32_t estr[3] = {1, 1, 1};
-    CUresult r = enc(&out3[k], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(data), dims, strides, box, estr,
-                     CU_TENSOR_MAP_INTERLEAVE_NONE, swz[k], CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) {
-      set_error("cuTensorMapEncodeTiled(feature map %dx%d, %lld planes, Wt=%d) failed with CUresult %d", H, W, NC,
-                8 << k, (int)r);
-      return OVM_ECUDA;
+    for (int j = 0; j < kHeights; ++j) {
+      cuuint64_t dims[3] = {(cuuint64_t)W, (cuuint64_t)NC, (cuuint64_t)H};
+      cuuint64_t strides[2] = {(cuuint64_t)H * W * 4, (cuuint64_t)W * 4};
+      cuuint32_t box[3] = {(cuuint32_t)(8 << k), 32, (cuuint32_t)(1 << j)};
+      cuuint32_t estr[3] = {1, 1, 1};
+      CUresult r = enc(&out[k * kHeights + j], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(data), dims,
+                       strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz[k], promo[roi_tune().promo & 3],
+                       CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+      if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled(feature map %dx%d, %lld planes, box %dx32x%d) failed with CUresult %d", H, W,
+                  NC, 8 << k, 1 << j, (int)r);
+        return OVM_ECUDA;
+      }
     }
   }
   return OVM_OK;
@@ -653,9 +806,9 @@ struct MapKey {
   bool operator<(const MapKey& o) const { return std::tie(p, H, W, NC) < std::tie(o.p, o.H, o.W, o.NC); }
 };
 struct MapVal {
-  CUtensorMap m[kWidths];
+  CUtensorMap m[kMapsPerLevel];
 };
-int level_maps(const float* data, int H, int W, long long NC, CUtensorMap* out3) {
+int level_maps(const float* data, int H, int W, long long NC, CUtensorMap* out) {
   static std::mutex mu;
   static std::map<MapKey, MapVal> cache;
   std::lock_guard<std::mutex> lock(mu);
@@ -668,7 +821,7 @@ int level_maps(const float* data, int H, int W, long long NC, CUtensorMap* out3)
     if (cache.size() >= 256) cache.clear();
     it = cache.emplace(key, v).first;
   }
-  for (int k = 0; k < kWidths; ++k) out3[k] = it->second.m[k];
+  memcpy(out, it->second.m, sizeof(it->second.m));
   return OVM_OK;
 }
 
@@ -710,7 +863,7 @@ int roi_align_launch(const ovm_pooler_t* p, const float* boxes, const int32_t* b
     a.tma_ok[l] = s.layout == OVM_LAYOUT_NCHW && !(reinterpret_cast<uintptr_t>(s.data) & 15) && !(s.width & 3) &&
                   p->pooler_resolution == kP;
     if (a.tma_ok[l]) {
-      int rc = level_maps(s.data, s.height, s.width, (long long)p->num_images * p->channels, &maps.m[l * kWidths]);
+      int rc = level_maps(s.data, s.height, s.width, (long long)p->num_images * p->channels, &maps.m[l * kMapsPerLevel]);
       if (rc != OVM_OK) return rc;
     }
   }
@@ -736,17 +889,30 @@ int roi_align_launch(const ovm_pooler_t* p, const float* boxes, const int32_t* b
   a.chunks_per_split = (chunks + splits - 1) / splits;
   a.splits = (chunks + a.chunks_per_split - 1) / a.chunks_per_split;
 
+  const RoiTune& tune = roi_tune();
+  a.split_factor = 0.01f * (float)(tune.split_pct < 100 ? 100 : tune.split_pct);   // < 1 would break the item bound
+  // with work items: a box yields at most max(splits, 2 area / (split_factor mean area)) of them
+  const long long nitems = (long long)n * a.splits + (a.order ? (long long)(2.0 * n / a.split_factor) + 8 : 0);
+  OVM_REQUIRE(!a.order || 2 + 2 * nitems <= (long long)p->order_ws_len,
+              "ovm_roi_align: order_ws holds %d int32, %lld needed (OVM_ORDER_WS_LEN)", p->order_ws_len, 2 + 2 * nitems);
+  a.xalign_mask = tune.align8 ? ~7 : ~3;
   static bool attr_done = false;
+  auto kA = roi_align_kernel<12288, 6144>;   // 48 KB ring, stages up to 24 KB: 69 KB of shared memory, 3 CTAs / SM
+  auto kB = roi_align_kernel<18432, 6144>;   // 72 KB ring: 2 CTAs / SM (measured slower; kept for tools/roi_bench.py)
   if (!attr_done) {
-    OVM_CUDA(cudaFuncSetAttribute(roi_align_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
+    OVM_CUDA(cudaFuncSetAttribute(kA, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)roi_smem_bytes(12288)));
+    OVM_CUDA(cudaFuncSetAttribute(kB, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)roi_smem_bytes(18432)));
     attr_done = true;
   }
   if (a.order) {
     roi_order_kernel<<<1, 1024, 0, stream>>>(a, p->order_ws);
     OVM_LAUNCHED("roi_order_kernel");
   }
-  const dim3 grid((unsigned)((long long)n * a.splits));
-  roi_align_kernel<<<grid, kThreads, kSmemBytes, stream>>>(maps, a);
+  const dim3 grid((unsigned)nitems);
+  if (tune.stages == 3)
+    kB<<<grid, kThreads, roi_smem_bytes(18432), stream>>>(maps, a);
+  else
+    kA<<<grid, kThreads, roi_smem_bytes(12288), stream>>>(maps, a);
   OVM_LAUNCHED("roi_align_kernel");
   return OVM_OK;
 }

@@ -155,12 +155,12 @@ class LiftEngine:
         ld_pooled = _round_up(self.in_dim, 8)
         t = dict(
             pooled=torch.empty((cap, ld_pooled), device=device, dtype=torch.bfloat16),
-            acc=torch.empty((cap, self.fc_dim), device=device, dtype=torch.float32),
+            acc=torch.zeros((cap, self.fc_dim), device=device, dtype=torch.float32),   # zero on entry / exit of every lift
             act_a=torch.empty((cap, self.fc_dim), device=device, dtype=torch.bfloat16),
             act_b=torch.empty((cap, self.fc_dim), device=device, dtype=torch.bfloat16),
             feats=torch.empty((cap, groups * self.fc_dim), device=device, dtype=torch.float32),
             levels=torch.empty((cap,), device=device, dtype=torch.int32),
-            order=torch.empty((cap,), device=device, dtype=torch.int32),
+            order=torch.empty((ops.order_ws_len(cap),), device=device, dtype=torch.int32),
         )
         ws = ops.ovm_workspace_t(t["pooled"].data_ptr(), ld_pooled, t["acc"].data_ptr(), t["act_a"].data_ptr(),
                                  t["act_b"].data_ptr(), t["feats"].data_ptr(), t["levels"].data_ptr())
@@ -193,6 +193,7 @@ class LiftEngine:
                                 % (self.in_dim, pooler.channels * self.P * self.P))
         ws = self._workspace(n, device)
         pooler.order_ws = self._ws_tensors["order"].data_ptr()
+        pooler.order_ws_len = self._ws_tensors["order"].numel()
         ops._need_cuda(boxes, "boxes", torch.float32)
         ops._need_cuda(classes, "classes", torch.int64)
         ops._need_cuda(batch_idx, "batch_idx", torch.int32)

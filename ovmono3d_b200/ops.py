@@ -11,7 +11,7 @@ from typing import List, Optional, Sequence, Tuple
 
 import torch
 
-OVM_ABI_VERSION = 2
+OVM_ABI_VERSION = 3
 OVM_MAX_LEVELS = 8
 RECORD_WIDTH = 48
 LAYOUT_NCHW, LAYOUT_NHWC = 0, 1
@@ -49,7 +49,7 @@ class ovm_pooler_t(C.Structure):
     _fields_ = [("num_levels", C.c_int32), ("levels", ovm_level_t * OVM_MAX_LEVELS), ("num_images", C.c_int32),
                 ("channels", C.c_int32), ("pooler_resolution", C.c_int32), ("sampling_ratio", C.c_int32),
                 ("canonical_box_size", C.c_int32), ("canonical_level", C.c_int32), ("scale_roi_boxes", C.c_float),
-                ("_pad", C.c_int32), ("order_ws", C.c_void_p)]
+                ("order_ws_len", C.c_int32), ("order_ws", C.c_void_p)]
 
 
 class ovm_decode_cfg_t(C.Structure):
@@ -171,6 +171,11 @@ def dtype_code(dt: torch.dtype) -> int:
     raise LiftError("unsupported output dtype %s" % dt)
 
 
+def order_ws_len(n: int) -> int:
+    """OVM_ORDER_WS_LEN(n) of include/ovmono3d_lift.h."""
+    return 6 * max(int(n), 1) + 1200
+
+
 def make_pooler(features: Sequence[torch.Tensor], scales: Sequence[float], output_size: int, sampling_ratio: int,
                 canonical_box_size: int = 224, canonical_level: int = 4, scale_roi_boxes: float = 0.0
                 ) -> Tuple[ovm_pooler_t, List[torch.Tensor]]:
@@ -217,8 +222,8 @@ def roi_align(features: Sequence[torch.Tensor], scales: Sequence[float], boxes: 
     Cc, P = pooler.channels, output_size
     out = torch.empty((n, Cc, P, P), device=boxes.device, dtype=out_dtype)
     levels = torch.empty((n,), device=boxes.device, dtype=torch.int32)
-    order = torch.empty((max(n, 1),), device=boxes.device, dtype=torch.int32)
-    pooler.order_ws = order.data_ptr()
+    order = torch.empty((order_ws_len(n),), device=boxes.device, dtype=torch.int32)
+    pooler.order_ws, pooler.order_ws_len = order.data_ptr(), order.numel()
     if n:
         _check(lib.ovm_roi_align(C.byref(pooler), boxes.data_ptr(), batch_idx.data_ptr(), n, out.data_ptr(),
                                  dtype_code(out_dtype), Cc * P * P, levels.data_ptr(), _stream()), "ovm_roi_align")

@@ -42,6 +42,9 @@ def main():
                     ("chunk 0 -> chunk 7", d(4, 11)), ("whole CTA", d(0, 12))]:
         print("  %-32s mean %6.2f  median %6.2f  p90 %6.2f  max %6.2f us" % (name, v.mean(), np.median(v),
                                                                         np.percentile(v, 90), v.max()))
+    print("  consumer warp 0 waiting for data: mean %.2f us/CTA (%.0f%% of the chunk loop); producer waiting for a free "
+          "stage: mean %.2f us/CTA" % (tt[:, 13].mean() / 1965.0, 100 * tt[:, 13].sum() / 1965.0 / max(d(3, 12).sum(), 1e-9),
+                                        tt[:, 14].mean() / 1965.0))
     packed = t[tma][:, 15]
     smid = packed & 0xFFFFFF
     rows, fw, wsel = packed >> 48, (packed >> 32) & 0xFFFF, (packed >> 24) & 0xFF
