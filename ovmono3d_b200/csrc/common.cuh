@@ -45,6 +45,30 @@ inline int check_cuda(cudaError_t e, const char* what) {
 
 constexpr int kNumSMs = 148;  // B200
 
+// Programmatic dependent launch: every kernel of the lift is launched with the programmatic-stream-serialization
+// attribute, tells the scheduler right away that its dependents may be launched (pdl_trigger), and waits for the
+// kernel before it in the stream (pdl_wait: full completion, memory visible) only where it first touches that
+// kernel's results.  What sits before the wait -- barrier / TMEM set-up, tensor-map prefetch, staging of weights --
+// overlaps the tail of the previous kernel, and the launch latency disappears from the chain.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }

@@ -234,6 +234,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
   if (threadIdx.x == 0) trace_stamp(g, 1);
+  pdl_trigger();
+  pdl_wait();   // A (and, split-K, the zeroed accumulator) come from the kernels before; set-up above overlapped them
 
   if (warp == 0) {
     if (lane == 0) {
@@ -413,6 +415,8 @@ __global__ void bias_act_kernel(const float* in, long long ldi, const float* __r
   // one thread per 4 consecutive columns (N % 4 == 0 is required by the launcher)
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const int n4 = N >> 2;
+  pdl_trigger();
+  pdl_wait();
   if (idx >= (long long)M * n4) return;
   const int m = (int)(idx / n4), j = (int)(idx - (long long)m * n4) * 4;
   float4 v = *reinterpret_cast<const float4*>(in + (long long)m * ldi + j);
@@ -476,7 +480,8 @@ int launch_gemm_mode(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmA
                                   (int)GemmShape<BN>::kSmemBytes));
     attr_done = true;
   }
-  gemm_bf16_kernel<BN, MODE><<<grid, kGemmThreads, GemmShape<BN>::kSmemBytes, stream>>>(tmA, tmB, g);
+  OVM_CUDA(launch_pdl(gemm_bf16_kernel<BN, MODE>, dim3(grid), dim3(kGemmThreads), GemmShape<BN>::kSmemBytes, stream, tmA,
+                      tmB, g));
   OVM_LAUNCHED("gemm_bf16_kernel");
   return OVM_OK;
 }
@@ -565,8 +570,8 @@ int bias_act_launch(const float* in, int64_t ldi, const float* bias, int32_t rel
   OVM_REQUIRE(N % 4 == 0 && ldi % 4 == 0 && ldo % 4 == 0, "ovm_bias_act: N, ldi, ldo must be multiples of 4");
   OVM_REQUIRE(out_dtype == OVM_F32 || out_dtype == OVM_BF16, "ovm_bias_act: out_dtype %d", out_dtype);
   const long long total = (long long)M * (N / 4);
-  bias_act_kernel<<<(unsigned)((total + 255) / 256), 256, 0, stream>>>(in, ldi, bias, relu, M, N, out,
-                                                                     out_dtype == OVM_BF16, ldo, clear_in ? 1 : 0);
+  OVM_CUDA(launch_pdl(bias_act_kernel, dim3((unsigned)((total + 255) / 256)), dim3(256), 0, stream, in, (long long)ldi, bias,
+                      (int)relu, (int)M, (int)N, out, (int)(out_dtype == OVM_BF16), (long long)ldo, clear_in ? 1 : 0));
   OVM_LAUNCHED("bias_act_kernel");
   return OVM_OK;
 }

@@ -394,7 +394,8 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) head_decode_kernel(const 
   extern __shared__ float4 staged4[];
   float* staged = reinterpret_cast<float*>(staged4);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  if (STAGED) {
+  pdl_trigger();
+  if (STAGED) {   // head weights are parameters: staged while the FC kernel before this one is still running
     const ovm_decode_cfg_t& cfg = a.cfg;
     const int K = cfg.fc_dim;
     const int pose_n = cfg.pose_type == OVM_POSE_6D ? 6 : (cfg.pose_type == OVM_POSE_QUATERNION ? 4 : 3);
@@ -417,6 +418,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) head_decode_kernel(const 
     }
     __syncthreads();
   }
+  pdl_wait();   // the FC features
   for (int box = blockIdx.x * kWarpsPerBlock + warp; box < a.n; box += gridDim.x * kWarpsPerBlock)
     decode_box<STAGED>(a, box, lane, staged);
 }
@@ -480,9 +482,9 @@ int head_decode_launch(const ovm_decode_cfg_t* cfg, const ovm_head_weights_t* w,
       OVM_CUDA(cudaFuncSetAttribute(head_decode_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stage_bytes));
       attr_bytes = stage_bytes;
     }
-    head_decode_kernel<true><<<grid, kWarpsPerBlock * 32, stage_bytes, stream>>>(a);
+    OVM_CUDA(launch_pdl(head_decode_kernel<true>, dim3(grid), dim3(kWarpsPerBlock * 32), stage_bytes, stream, a));
   } else {
-    head_decode_kernel<false><<<grid, kWarpsPerBlock * 32, 0, stream>>>(a);
+    OVM_CUDA(launch_pdl(head_decode_kernel<false>, dim3(grid), dim3(kWarpsPerBlock * 32), 0, stream, a));
   }
   OVM_LAUNCHED("head_decode_kernel");
   return OVM_OK;

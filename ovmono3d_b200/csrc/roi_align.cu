@@ -349,6 +349,8 @@ __global__ void __launch_bounds__(1024) roi_order_kernel(const RoiArgs a, int* _
   __shared__ float warp_sum[32];
   __shared__ float mean_area;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  pdl_trigger();
+  pdl_wait();   // ws may still be read by the ROIAlign kernel of the previous call
   if (tid < 64) hist[tid] = 0;
   auto area_of = [&](int box) {
     const BoxGeom g = box_geometry(a, box);
@@ -456,6 +458,8 @@ __global__ void __launch_bounds__(kThreads) roi_align_kernel(const __grid_consta
   int* meta = reinterpret_cast<int*>(Wy + kWyFloats);
   const uint32_t bars = smem_u32(meta + kMetaInts);                  // full[kStages], empty[kStages]
 
+  pdl_trigger();
+  pdl_wait();      // the work items come from roi_order_kernel
   int box, chunk_begin, chunk_end;
   if (a.order) {   // work items of roi_order_kernel; the grid is an upper bound of their number
     if ((int)blockIdx.x >= a.order[0]) return;
@@ -905,14 +909,14 @@ int roi_align_launch(const ovm_pooler_t* p, const float* boxes, const int32_t* b
     attr_done = true;
   }
   if (a.order) {
-    roi_order_kernel<<<1, 1024, 0, stream>>>(a, p->order_ws);
+    OVM_CUDA(launch_pdl(roi_order_kernel, dim3(1), dim3(1024), 0, stream, a, p->order_ws));
     OVM_LAUNCHED("roi_order_kernel");
   }
   const dim3 grid((unsigned)nitems);
   if (tune.stages == 3)
-    kB<<<grid, kThreads, roi_smem_bytes(18432), stream>>>(maps, a);
+    OVM_CUDA(launch_pdl(kB, grid, dim3(kThreads), roi_smem_bytes(18432), stream, maps, a));
   else
-    kA<<<grid, kThreads, roi_smem_bytes(12288), stream>>>(maps, a);
+    OVM_CUDA(launch_pdl(kA, grid, dim3(kThreads), roi_smem_bytes(12288), stream, maps, a));
   OVM_LAUNCHED("roi_align_kernel");
   return OVM_OK;
 }

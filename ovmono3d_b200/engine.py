@@ -54,6 +54,7 @@ class LiftEngine:
         if settings.z_type not in ops.Z_TYPES:
             raise ValueError("Z type {} is not recognized".format(settings.z_type))
         self._weights_key = None
+        self._params = None
         self._fc_weights: List[torch.Tensor] = []
         self._fc_layers = None
         self._fc_stack = None
@@ -74,8 +75,10 @@ class LiftEngine:
         return gens
 
     def _state_key(self, priors: Sequence[Optional[torch.Tensor]]):
-        ts = [p for p in self.cube_head.parameters()] + [p for p in priors if p is not None]
-        return tuple((t.data_ptr(), t._version, t.device) for t in ts)
+        if self._params is None:   # the module structure is fixed after construction
+            self._params = list(self.cube_head.parameters())
+        ts = self._params + [p for p in priors if p is not None]
+        return tuple((t.data_ptr(), t._version) for t in ts)
 
     def prepare(self, device: torch.device, priors_dims_per_cat: Optional[torch.Tensor],
                 priors_z_scales: Optional[torch.Tensor], priors_z_stats: Optional[torch.Tensor]) -> None:

@@ -295,6 +295,14 @@ class ROIHeads3DB200(nn.Module):
             out.append(Boxes(torch.stack([x1, y1, x2, y2], dim=1)))
         return out
 
+    def _staging(self, words: int):
+        """Two alternating pinned host buffers (4-byte words, viewed as fp32) with the event of their last H2D copy."""
+        bufs = self.__dict__.setdefault("_stage_bufs", [None, None])
+        turn = self.__dict__["_stage_turn"] = 1 - self.__dict__.get("_stage_turn", 0)
+        if bufs[turn] is None or bufs[turn][0].numel() < words:
+            bufs[turn] = (torch.empty(max(words, 4096), dtype=torch.float32, pin_memory=True), torch.cuda.Event())
+        return bufs[turn]
+
     def _get_engine(self) -> LiftEngine:
         if self._engine is None:
             settings = DecodeSettings(
@@ -327,44 +335,63 @@ class ROIHeads3DB200(nn.Module):
         N = len(instances)
         assert N == feats[0].shape[0] == len(Ks) == len(im_scales_ratio) == len(im_current_dims)
 
-        # one pinned staging buffer -> one H2D copy: cams [N,12] fp32 (K, ratio, H_cur, 0) then batch_idx [n] int32
-        stage = torch.empty(N * 12 + n, dtype=torch.float32, pin_memory=True)
-        cams_h = stage[: N * 12].view(N, 12)
-        for i in range(N):
-            cams_h[i, :9] = torch.as_tensor(Ks[i], dtype=torch.float32).reshape(9)
-            cams_h[i, 9] = float(im_scales_ratio[i])
-            cams_h[i, 10] = float(im_current_dims[i][0])
-            cams_h[i, 11] = 0.0
-        stage[N * 12:].view(torch.int32).copy_(
-            torch.from_numpy(np.repeat(np.arange(N, dtype=np.int32), num_boxes_per_image)))
-        stage_d = stage.to(device, non_blocking=True)
-        cams = stage_d[: N * 12].view(N, 12)
-        batch_idx = stage_d[N * 12:].view(torch.int32)
-
-        boxes = torch.cat([x.pred_boxes.tensor for x in instances]).to(device=device, dtype=torch.float32).contiguous()
-        classes = torch.cat([x.pred_classes for x in instances]).to(device=device, dtype=torch.int64).contiguous()
+        # One pinned staging buffer -> one H2D copy (the reference builds four per-box tensors on the CPU with Python
+        # loops and copies each, roi_heads.py:378-400): cams [N,12] fp32 (K, ratio, H_cur, 0) | batch_idx [n] int32 |
+        # and, when the Instances live on the host, boxes [n,4] fp32 | scores [n] fp32 | classes [n] int64.
+        first = instances[0]
+        on_host = first.pred_boxes.tensor.device.type == "cpu"
         have_scores = [x.has("scores") for x in instances]
-        if all(have_scores):
-            scores = torch.cat([x.scores for x in instances]).to(device=device, dtype=torch.float32).contiguous()
-        elif not any(have_scores):
-            scores = None
-        else:  # mixed: a NaN marks "no score" -- handled per image below
+        if any(have_scores) and not all(have_scores):
             raise ops.LiftError("either every Instances or none must carry `scores`")
+        with_scores = have_scores[0]
+        words = N * 12 + n + (n * 4 + n + 2 * n + 2 if on_host else 0)      # 4-byte words
+        stage, done = self._staging(words)
+        done.synchronize()                                  # the copy that last used this buffer has finished
+        cams_h = stage[: N * 12].view(N, 12)
+        cams_np = cams_h.numpy()
+        cams_np[:, :9] = torch.stack([torch.as_tensor(k, dtype=torch.float32).reshape(9) for k in Ks]).numpy()
+        cams_np[:, 9] = np.asarray(im_scales_ratio, dtype=np.float32)
+        cams_np[:, 10] = np.asarray([d[0] for d in im_current_dims], dtype=np.float32)
+        cams_np[:, 11] = 0.0
+        o_idx = N * 12
+        stage[o_idx:o_idx + n].view(torch.int32).numpy()[:] = np.repeat(np.arange(N, dtype=np.int32), num_boxes_per_image)
+        if on_host:
+            o_box, o_sc = o_idx + n, o_idx + 5 * n
+            o_cls = (o_sc + n + 1) // 2 * 2                                    # int64 needs an 8-byte boundary
+            def as_(ts, dt):   # the usual case (fp32 boxes / scores, int64 classes) converts nothing
+                return ts if all(t.dtype is dt for t in ts) else [t.to(dt) for t in ts]
+
+            torch.cat(as_([x.pred_boxes.tensor for x in instances], torch.float32), out=stage[o_box:o_sc].view(n, 4))
+            if with_scores:
+                torch.cat(as_([x.scores for x in instances], torch.float32), out=stage[o_sc:o_sc + n])
+            torch.cat(as_([x.pred_classes for x in instances], torch.int64),
+                      out=stage[o_cls:o_cls + 2 * n].view(torch.int64))
+        stage_d = stage[:words].to(device, non_blocking=True)
+        done.record()
+        cams = stage_d[: N * 12].view(N, 12)
+        batch_idx = stage_d[o_idx:o_idx + n].view(torch.int32)
+        if on_host:
+            boxes = stage_d[o_box:o_sc].view(n, 4)
+            scores = stage_d[o_sc:o_sc + n] if with_scores else None
+            classes = stage_d[o_cls:o_cls + 2 * n].view(torch.int64)
+        else:
+            boxes = torch.cat([x.pred_boxes.tensor for x in instances]).to(device=device, dtype=torch.float32).contiguous()
+            classes = torch.cat([x.pred_classes for x in instances]).to(device=device, dtype=torch.int64).contiguous()
+            scores = (torch.cat([x.scores for x in instances]).to(device=device, dtype=torch.float32).contiguous()
+                      if with_scores else None)
 
         eng = self._get_engine()
         eng.prepare(device, self.priors_dims_per_cat, self.priors_z_scales, getattr(self, "priors_z_stats", None))
         records, raw = eng.forward(feats, boxes, classes, scores, batch_idx, cams, want_raw=return_raw)
 
-        start = 0
-        for inst, k in zip(instances, num_boxes_per_image):
-            rec = records[start:start + k]
-            start += k
-            inst.scores = rec[:, ops.REC_SCORE]
-            inst.pred_bbox3D = rec[:, ops.REC_BBOX3D].view(k, 8, 3)
-            inst.pred_center_cam = rec[:, ops.REC_CENTER_CAM]
-            inst.pred_center_2D = rec[:, ops.REC_CENTER_2D]
-            inst.pred_dimensions = rec[:, ops.REC_DIMENSIONS]
-            inst.pred_pose = rec[:, ops.REC_POSE].view(k, 3, 3)
+        # write-back (roi_heads.py:811-843): the Instances fields are views into the [n,48] records
+        fields = (("scores", records[:, ops.REC_SCORE]), ("pred_bbox3D", records[:, ops.REC_BBOX3D].view(n, 8, 3)),
+                  ("pred_center_cam", records[:, ops.REC_CENTER_CAM]), ("pred_center_2D", records[:, ops.REC_CENTER_2D]),
+                  ("pred_dimensions", records[:, ops.REC_DIMENSIONS]), ("pred_pose", records[:, ops.REC_POSE].view(n, 3, 3)))
+        for name, t in fields:
+            # lengths match by construction: skip Instances.set()'s per-field len() assertion (96 of them per batch)
+            for inst, part in zip(instances, t.split(num_boxes_per_image)):
+                inst._fields[name] = part
         self.last_records, self.last_raw = records, raw
         return instances
 

@@ -278,7 +278,7 @@ def test_head_decode_fp32_matches_oracle(case):
 
 
 # --------------------------------------------------------------------------- the plugin end to end (bf16 head)
-def _run_plugin(case, return_raw=False, bf16_operands=False):
+def _run_plugin(case, return_raw=False, bf16_operands=False, host_instances=False, repeat=1):
     from ovmono3d_b200.compat import Boxes, Instances, ShapeSpec
     from ovmono3d_b200.roi_heads import build_roi_heads
 
@@ -297,16 +297,18 @@ def _run_plugin(case, return_raw=False, bf16_operands=False):
             head.priors_z_stats.data = priors[2].clone()
     head = head.to(dev).eval()
     feats = {f: t.to(dev) for f, t in zip(case.in_features, inp.features)}
-    instances = []
-    for i in range(len(inp.boxes)):
-        inst = Instances(tuple(inp.im_dims[i]))
-        inst.pred_boxes = Boxes(inp.boxes[i].clone().to(dev))
-        inst.pred_classes = inp.classes[i].clone().to(dev)
-        if case.with_scores:
-            inst.scores = inp.scores[i].clone().to(dev)
-        instances.append(inst)
-    res = head._forward_cube(feats, instances, [k.clone() for k in inp.Ks], [tuple(d) for d in inp.im_dims],
-                             list(inp.im_scales_ratio), return_raw=return_raw)
+    idev = torch.device("cpu") if host_instances else dev
+    for _ in range(repeat):     # a repeated call must see a clean split-K accumulator and fresh staging buffers
+        instances = []
+        for i in range(len(inp.boxes)):
+            inst = Instances(tuple(inp.im_dims[i]))
+            inst.pred_boxes = Boxes(inp.boxes[i].clone().to(idev))
+            inst.pred_classes = inp.classes[i].clone().to(idev)
+            if case.with_scores:
+                inst.scores = inp.scores[i].clone().to(idev)
+            instances.append(inst)
+        res = head._forward_cube(feats, instances, [k.clone() for k in inp.Ks], [tuple(d) for d in inp.im_dims],
+                                 list(inp.im_scales_ratio), return_raw=return_raw)
     torch.cuda.synchronize()
     return inp, out, head, res
 
@@ -338,6 +340,19 @@ def test_plugin_forward_cube_matches_oracle_and_golden(case):
 def test_plugin_bf16_head_matches_bf16_operand_oracle(case):
     """Kernel correctness of the whole plugin path: same operand rounding on both sides, 1e-3 on every field."""
     inp, out, head, res = _run_plugin(case, bf16_operands=True)
+    for i, inst in enumerate(res):
+        if len(inp.boxes[i]) == 0:
+            continue
+        for f in FIELDS:
+            e = _field_err(inst.get(f), getattr(out, f)[i])
+            assert e <= BF16_KERNEL_TOL, "%s: %.3g" % (f, e)
+
+
+@pytest.mark.parametrize("name", ["c1_full", "dinov2_no_scores", "non_shared_fc", "ragged_with_empty"])
+def test_plugin_host_instances_repeated_calls(name):
+    """Instances held on the host (boxes / classes / scores ride the one staging copy), three calls in a row."""
+    case = gc.CASE_BY_NAME[name]
+    inp, out, head, res = _run_plugin(case, bf16_operands=True, host_instances=True, repeat=3)
     for i, inst in enumerate(res):
         if len(inp.boxes[i]) == 0:
             continue
