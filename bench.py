@@ -81,6 +81,37 @@ class ClockSampler:
         self.thread: Optional[threading.Thread] = None
 
     def start(self) -> None:
+        # NVML in-process (a query is tens of microseconds); an `nvidia-smi -lms` child holds the driver lock for
+        # ~20 ms per sample, which showed up as 20 ms stalls of synchronising calls inside the timed region
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            h = pynvml.nvmlDeviceGetHandleByIndex(self._physical_index(pynvml))
+            bits = (("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20),
+                    ("sw_power_cap", 0x4))
+            mx = pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM)
+            self._stop = threading.Event()
+
+            def poll():
+                while not self._stop.is_set():
+                    try:
+                        sm = pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)
+                        try:
+                            r = pynvml.nvmlDeviceGetCurrentClocksEventReasons(h)
+                        except Exception:
+                            r = pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                        self.rows.append([str(sm), str(mx)] + ["Active" if r & b else "Not Active" for _, b in bits])
+                    except Exception:
+                        pass
+                    self._stop.wait(0.02)
+
+            self.thread = threading.Thread(target=poll, daemon=True)
+            self.thread.start()
+            self.nvml = True
+            return
+        except Exception:
+            self.nvml = False
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.QUERY, "--format=csv,noheader,nounits",
@@ -96,16 +127,28 @@ class ClockSampler:
         self.thread = threading.Thread(target=pump, daemon=True)
         self.thread.start()
 
+    def _physical_index(self, pynvml) -> int:
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        if vis:
+            ids = [v.strip() for v in vis.split(",") if v.strip()]
+            if self.index < len(ids) and ids[self.index].isdigit():
+                return int(ids[self.index])
+        return self.index
+
     def stop(self) -> Dict[str, object]:
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except subprocess.TimeoutExpired:
-            self.proc.kill()
-        if self.thread:
+        if getattr(self, "nvml", False):
+            self._stop.set()
             self.thread.join(timeout=2)
+        elif self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        else:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except subprocess.TimeoutExpired:
+                self.proc.kill()
+            if self.thread:
+                self.thread.join(timeout=2)
         sm, mx, reasons = [], [], set()
         for r in self.rows:
             if len(r) < 6:
@@ -266,6 +309,10 @@ def run_ours(args) -> Dict[str, object]:
     for i in range(W):
         flush.zero_()
         lift(dbs[i % num_sets])
+    if world > 1:   # the communicator and the gather's buffers are set up before the timed region
+        from ovmono3d_b200 import shard
+
+        shard.gather_records(records_all.view(-1, ops.RECORD_WIDTH))
     barrier()
     starts = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
     stops = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
@@ -281,13 +328,18 @@ def run_ours(args) -> Dict[str, object]:
         stops[i].record()
     g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     gathered = None
+    if world > 1:
+        # the L2 flushes between the steps are outside the step event pairs and let the ranks drift apart; line them
+        # up again so that the gather's events time the exchange, not the wait for the slowest rank's flushes
+        barrier()
     g0.record()
     if world > 1:   # the path's one exchange: detections gathered once at the end (omni3d_evaluation.py:717-720)
         from ovmono3d_b200 import shard
 
         gathered, counts, _ = shard.gather_records(records_all.view(-1, ops.RECORD_WIDTH))
-        assert int(counts.sum()) == world * K * n
     g1.record()
+    if world > 1:
+        assert int(counts.cpu().sum()) == world * K * n and gathered.shape[0] == world * K * n
     barrier()
     loop_wall_ms = (time.perf_counter() - t_wall0) * 1e3
     launches = ops.launch_count() - launches0
@@ -523,6 +575,10 @@ def main() -> None:
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    # exactly one JSON line on stdout: libraries that print there (NCCL's version banner under NCCL_DEBUG) go to stderr
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         if args.steps == 50 and args.warmup == 5:
             args.steps, args.warmup = 10, 2
@@ -530,8 +586,9 @@ def main() -> None:
     else:
         out = run_ours(args)
     rank = int(os.environ.get("RANK", "0"))
+    sys.stdout.flush()
     if rank == 0 and out is not None:
-        print(json.dumps(out))
+        os.write(real_stdout, (json.dumps(out) + "\n").encode())
 
 
 if __name__ == "__main__":

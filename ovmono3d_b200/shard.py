@@ -9,6 +9,7 @@ tensors, gloo for CPU tensors (tests).  There is no collective inside the lift i
 """
 from __future__ import annotations
 
+import os
 from typing import List, Optional, Tuple
 
 import torch
@@ -42,9 +43,20 @@ def gather_records(records: torch.Tensor, image_index: Optional[torch.Tensor] = 
         return records, torch.tensor([records.shape[0]], dtype=torch.int64, device=records.device), image_index
     world = dist.get_world_size(group)
     device = records.device
+    dbg = os.environ.get("OVM_GATHER_DEBUG") and device.type == "cuda"
+    marks = []
+
+    def mark(name):
+        if dbg:
+            e = torch.cuda.Event(enable_timing=True)
+            e.record()
+            marks.append((name, e))
+
+    mark("start")
     n = torch.tensor([records.shape[0]], dtype=torch.int64, device=device)
     counts = torch.empty(world, dtype=torch.int64, device=device)
     dist.all_gather_into_tensor(counts, n, group=group)
+    mark("counts")
     cap = int(counts.max().item())          # the one host sync of the exchange; payload is ~19 KB per image
     width = RECORD_WIDTH + (1 if image_index is not None else 0)
     block = torch.zeros((cap, width), dtype=torch.float32, device=device)
@@ -52,12 +64,20 @@ def gather_records(records: torch.Tensor, image_index: Optional[torch.Tensor] = 
     if image_index is not None:
         # image ids ride along as exact fp32 integers (< 2^24 images)
         block[: records.shape[0], RECORD_WIDTH] = image_index.to(torch.float32)
+    mark("block")
     out = torch.empty((world * cap, width), dtype=torch.float32, device=device)
     dist.all_gather_into_tensor(out, block, group=group)
+    mark("all_gather")
     out = out.view(world, cap, width)
     keep = torch.arange(cap, device=device).unsqueeze(0) < counts.unsqueeze(1)
     flat = out[keep]
     idx = flat[:, RECORD_WIDTH].to(torch.int64) if image_index is not None else None
+    if dbg:
+        mark("compact")
+        torch.cuda.synchronize()
+        import sys
+        sys.stderr.write("gather_records: " + ", ".join("%s %.3f ms" % (b[0], a[1].elapsed_time(b[1]))
+                                                         for a, b in zip(marks, marks[1:])) + "\n")
     return flat[:, :RECORD_WIDTH].contiguous(), counts, idx
 
 
