@@ -80,6 +80,7 @@ struct RoiArgs {
   const int* order;             // boxes in descending cost (roi_order_kernel), or NULL: natural order
   int splits, chunks_per_split;
   int tma_ok[OVM_MAX_LEVELS];   // level has tensor maps (NCHW, 16-byte aligned base, width % 4 == 0)
+  int min_slots;                // ring slots a stage geometry should leave (OVM_ROI_MINSLOTS)
   float split_factor;           // roi_order_kernel: an item may cost this many average boxes before the box is cut
   int xalign_mask;              // footprint start column is rounded down to this mask (~3 or ~7)
   unsigned long long* trace;    // optional [grid, 16] %globaltimer stamps (ovm_roi_set_trace), else NULL
@@ -92,7 +93,8 @@ struct RoiTune {
   int split_pct;    // OVM_ROI_SPLIT   cost of a work item, in % of the average box, above which a box is cut along the channels
   int promo;        // OVM_ROI_PROMO   L2 promotion of the tensor maps: 0 none, 1 64 B, 2 128 B, 3 256 B
   int align8;       // OVM_ROI_ALIGN8  footprint starts on a 32-byte sector (8 floats) instead of 16 bytes
-  int stages;       // OVM_ROI_STAGES  2 or 3 pipeline stages
+  int stages;       // OVM_ROI_STAGES  2: 48 KB ring (3 CTAs / SM), 3: 72 KB ring (2 CTAs / SM)
+  int min_slots;    // OVM_ROI_MINSLOTS  prefer stage geometries (narrower tiles, row groups) that leave this many ring slots
 };
 const RoiTune& roi_tune() {
   static RoiTune t = [] {
@@ -102,6 +104,7 @@ const RoiTune& roi_tune() {
     r.promo = env("OVM_ROI_PROMO", 2);
     r.align8 = env("OVM_ROI_ALIGN8", 0);
     r.stages = env("OVM_ROI_STAGES", 2);
+    r.min_slots = env("OVM_ROI_MINSLOTS", 1);
     return r;
   }();
   return t;
@@ -534,49 +537,63 @@ __global__ void __launch_bounds__(kThreads) roi_align_kernel(const __grid_consta
   // starts at the 4-float boundary at or below its first column
   const int x0 = x_lo & a.xalign_mask;
   const int fw = x_hi - x0 + 1, rows_total = y_hi - y_lo + 1;
-  int wsel = -1, best_pad = INT_MAX;
-#pragma unroll
-  for (int k = kWidths - 1; k >= 0; --k) {
-    const int wt = 8 << k;
-    const int pad = (fw + wt - 1) / wt * wt;
-    if (rows_total * wt * 32 <= kStageFloats && pad < best_pad) {
-      best_pad = pad;
-      wsel = k;
-    }
-  }
-  // Footprints too tall for one stage even at Wt = 8 are walked in two row groups: bin-rows 0..3, then 4..6
-  // (each consumer warp works only in its own group's stages).
-  int ngroups = 1;
-  int gy0[2] = {y_lo, y_lo}, gy1[2] = {y_hi, y_hi};
-  if (wsel < 0) {
-    ngroups = 2;
-    gy0[0] = gy0[1] = INT_MAX;
-    gy1[0] = gy1[1] = -1;
-#pragma unroll
-    for (int p = 0; p < kP; ++p) {
-      const int h = p < 4 ? 0 : 1;
+  // Row groups: a stage holds the pixel rows of G consecutive bin-rows (G = 7: the whole footprint; 4, 2, 1: tall
+  // footprints are walked group by group, each consumer warp working only in its own group's stages).  Pick the
+  // largest G -- and for it the tile width with the least padding, wider on ties -- whose stage fits kStageFloats and
+  // leaves at least a.min_slots ring slots; if nothing gives that depth, the largest G that fits at all.
+  auto group_span = [&](int G, int h, int& gy, int& rows) {   // pixel rows of group h (one dummy row if it has no sample)
+    int lo = INT_MAX, hi = -1;
+    for (int p = h * G; p < min(kP, (h + 1) * G); ++p) {
       if (meta[21 + p] >= meta[14 + p]) {
-        gy0[h] = min(gy0[h], meta[14 + p]);
-        gy1[h] = max(gy1[h], meta[21 + p]);
+        lo = min(lo, meta[14 + p]);
+        hi = max(hi, meta[21 + p]);
       }
     }
-    wsel = 0;
-    best_pad = (fw + 7) / 8 * 8;
-#pragma unroll
-    for (int h = 0; h < 2; ++h) {
-      if (gy1[h] < gy0[h]) gy0[h] = gy1[h] = y_lo;   // group without a valid sample: one dummy row
-      if ((gy1[h] - gy0[h] + 1) * 8 * 32 > kStageFloats) wsel = -1;
+    if (hi < lo) lo = hi = y_lo;
+    gy = lo;
+    rows = hi - lo + 1;
+  };
+  int wsel = -1, best_pad = INT_MAX, G = kP, rmax = rows_total;
+  auto try_cfg = [&](int g, int need_slots) {
+    int rm = 0;
+    for (int h = 0; h * g < kP; ++h) {
+      int gy, rows;
+      group_span(g, h, gy, rows);
+      rm = max(rm, rows);
     }
+    int ws = -1, bp = INT_MAX;
+#pragma unroll
+    for (int k = kWidths - 1; k >= 0; --k) {
+      const int wt = 8 << k;
+      const int pad = (fw + wt - 1) / wt * wt;
+      const int stage = rm * wt * 32;
+      if (stage <= kStageFloats && kRingFloats / stage >= need_slots && pad < bp) {
+        bp = pad;
+        ws = k;
+      }
+    }
+    if (ws < 0) return false;
+    wsel = ws; best_pad = bp; G = g; rmax = rm;
+    return true;
+  };
+  {
+    const int gs[4] = {7, 4, 2, 1};
+    bool ok = false;
+#pragma unroll
+    for (int i = 0; i < 4 && !ok; ++i) ok = try_cfg(gs[i], a.min_slots);
+#pragma unroll
+    for (int i = 0; i < 4 && !ok; ++i) ok = try_cfg(gs[i], 1);
   }
   if (wsel < 0 || best_pad > kMaxW || ny_max > kMaxRows) {
     direct_path(a, g, box, c_begin, c_end);
     return;
   }
+  const int ngroups = (kP + G - 1) / G;
   const int Wt = 8 << wsel;
   const int ntiles = best_pad / Wt;
   const int slab_floats = 32 * Wt;               // one footprint row of one chunk: [32 channels][Wt]
   // The ring is cut into slots of this box's stage size: small footprints get up to kMaxSlots stages in flight.
-  const int slot_floats = max(gy1[0] - gy0[0] + 1, ngroups == 2 ? gy1[1] - gy0[1] + 1 : 0) * slab_floats;
+  const int slot_floats = rmax * slab_floats;
   const int nslots = min(kMaxSlots, kRingFloats / slot_floats);
 
   if (warp == kP) {
@@ -592,8 +609,8 @@ __global__ void __launch_bounds__(kThreads) roi_align_kernel(const __grid_consta
       for (int chunk = chunk_begin; chunk < chunk_end; ++chunk) {
         const int cc = g.b * a.C + chunk * 32;
         for (int grp = 0; grp < ngroups; ++grp) {
-          const int gy = grp ? gy0[1] : gy0[0];
-          const int rows = (grp ? gy1[1] : gy1[0]) - gy + 1;
+          int gy, rows;
+          group_span(G, grp, gy, rows);
           for (int tile = 0; tile < ntiles; ++tile) {
             const uint32_t full = bars + 8 * s;
             const long long tw = a.trace ? clock64() : 0;
@@ -656,7 +673,9 @@ __global__ void __launch_bounds__(kThreads) roi_align_kernel(const __grid_consta
 
   // ===== consumers: warp == ph, lane == channel
   const int ph = warp;
-  const int my_grp = ngroups == 2 && ph >= 4 ? 1 : 0;
+  const int my_grp = ph / G;
+  int my_gy, my_rows;
+  group_span(G, my_grp, my_gy, my_rows);
   const int ys = meta[14 + ph];
   const int ny = meta[21 + ph] - ys + 1;          // <= 0: bin-row has no valid sample
   const float* wy = Wy + ph * kMaxRows;
@@ -664,7 +683,7 @@ __global__ void __launch_bounds__(kThreads) roi_align_kernel(const __grid_consta
   // 16-byte unit j of lane c's row sits at unit j ^ sw (the TMA swizzle of the slab, see the header comment)
   const int sw = wsel == 2 ? (lane & 7) : (wsel == 1 ? ((lane >> 1) & 3) : ((lane >> 2) & 1));
   const int nx4_tile = Wt >> 2;
-  const int row_off = (ys - (my_grp ? gy0[1] : gy0[0])) * slab_floats + lane * Wt;
+  const int row_off = (ys - my_gy) * slab_floats + lane * Wt;
   float wyr[4];   // row weights of a bin-row of up to 4 pixel rows (the table is zero past the bin-row's rows)
 #pragma unroll
   for (int r = 0; r < 4; ++r) wyr[r] = wy[r];
@@ -900,6 +919,7 @@ int roi_align_launch(const ovm_pooler_t* p, const float* boxes, const int32_t* b
   OVM_REQUIRE(!a.order || 2 + 2 * nitems <= (long long)p->order_ws_len,
               "ovm_roi_align: order_ws holds %d int32, %lld needed (OVM_ORDER_WS_LEN)", p->order_ws_len, 2 + 2 * nitems);
   a.xalign_mask = tune.align8 ? ~7 : ~3;
+  a.min_slots = tune.min_slots < 1 ? 1 : (tune.min_slots > kMaxSlots ? kMaxSlots : tune.min_slots);
   static bool attr_done = false;
   auto kA = roi_align_kernel<12288, 6144>;   // 48 KB ring, stages up to 24 KB: 69 KB of shared memory, 3 CTAs / SM
   auto kB = roi_align_kernel<18432, 6144>;   // 72 KB ring: 2 CTAs / SM (measured slower; kept for tools/roi_bench.py)

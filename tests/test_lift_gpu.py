@@ -117,6 +117,40 @@ def test_roi_align_bf16_out_and_channels_last():
     assert _field_err(pcl, out.pooled) <= FP32_TOL
 
 
+@pytest.mark.parametrize("strides,canvas", [((4, 8, 16, 32), 512), ((7, 14, 28), 448), ((4, 8, 16, 32, 64), 512)])
+def test_roi_align_tall_wide_and_huge_boxes(strides, canvas):
+    """Footprints that do not fit one stage: tall / wide slivers (small area -> fine level, hundreds of pixel rows),
+    near-full-image boxes on every pyramid, and the row-group depth knob's geometries (G = 7, 4, 2, 1 bin-rows per
+    stage, or the direct path past that) must all give the reference's numbers."""
+    from oracle import thirdparty as tp
+    from ovmono3d_b200 import ops
+
+    g = torch.Generator().manual_seed(99)
+    N, C = 2, 64
+    feats = [torch.randn(N, C, canvas // s, canvas // s, generator=g) for s in strides]
+    S = float(canvas)
+    rows = []
+    for frac in (0.15, 0.3, 0.5, 0.7, 0.9, 1.0):
+        for thin in (4.0, 9.0, 20.0, 45.0, 90.0):
+            rows.append([10.0, 3.0, 10.0 + thin, 3.0 + frac * (S - 6)])          # tall sliver
+            rows.append([2.0, 11.0, 2.0 + frac * (S - 4), 11.0 + thin])          # wide sliver
+        rows.append([1.5, 2.5, 1.5 + frac * (S - 3), 2.5 + frac * (S - 5)])      # big box
+        rows.append([S * (1 - frac) * 0.5, 0.0, S, S * frac])                    # touching the border
+    b0 = torch.tensor(rows)
+    boxes = [b0, b0.flip(0) * 0.97]
+    scales = [1.0 / s for s in strides]
+    want = tp.ROIPoolerOracle(7, scales, 0, "ROIAlignV2")(feats, boxes)
+    want_lv = tp.ROIPoolerOracle(7, scales, 0, "ROIAlignV2").levels(boxes)
+    dev = _dev()
+    bd = torch.cat(boxes).to(dev)
+    bi = torch.from_numpy(np.repeat(np.arange(N, dtype=np.int32), [len(b) for b in boxes])).to(dev)
+    got, lv = ops.roi_align([f.to(dev) for f in feats], scales, bd, bi, 7, 0, torch.float32)
+    assert torch.equal(lv.cpu().long(), want_lv)
+    ref = want.flatten(1)
+    err = (got.flatten(1).cpu() - ref).abs().amax(dim=1) / ref.abs().amax(dim=1).clamp_min(1e-6)
+    assert float(err.max()) <= FP32_TOL, "box %d: %.3g" % (int(err.argmax()), float(err.max()))
+
+
 def test_level_assignment_ulp_sweep():
     """Every fp32 box size within +-64 ulp of each level break point, for power-of-two and 7/14/28 pyramids."""
     from oracle import thirdparty as tp

@@ -15,13 +15,18 @@ from ovmono3d_b200 import ops, synth  # noqa: E402
 def main():
     lib = ops.load_library()
     dev = torch.device("cuda:0")
-    inp = synth.make_inputs(1235, 16, 100)
+    # optional: strides (comma list), canvas, images, boxes per image   e.g.  4,8,16,32 1024 16 100
+    strides = tuple(int(v) for v in sys.argv[1].split(",")) if len(sys.argv) > 1 else (7, 14, 28)
+    canvas = int(sys.argv[2]) if len(sys.argv) > 2 else 896
+    N = int(sys.argv[3]) if len(sys.argv) > 3 else 16
+    k = int(sys.argv[4]) if len(sys.argv) > 4 else 100
+    inp = synth.make_inputs(1235 if len(sys.argv) == 1 else 4321, N, k, strides=strides, canvas=canvas)
     feats = [f.to(dev) for f in inp.features]
     counts = [len(b) for b in inp.boxes]
     boxes = torch.cat(inp.boxes).to(dev)
-    bidx = torch.from_numpy(np.repeat(np.arange(16, dtype=np.int32), counts)).to(dev)
-    scales = [1 / 7, 1 / 14, 1 / 28]
-    trace = torch.zeros(8192 * 16, dtype=torch.int64, device=dev)
+    bidx = torch.from_numpy(np.repeat(np.arange(N, dtype=np.int32), counts)).to(dev)
+    scales = [1.0 / v for v in strides]
+    trace = torch.zeros(65536 * 16, dtype=torch.int64, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     for it in range(3):
         flush.zero_()
@@ -35,6 +40,9 @@ def main():
     t0 = t[:, 0].min()
     tma = t[:, 12] > 0
     print("CTAs %d, on the TMA path %d; kernel span %.1f us" % (len(t), tma.sum(), (t[:, :13].max() - t0) / 1e3))
+    if (~tma).any():
+        dd = t[~tma]
+        print("  direct-path / early-exit CTAs: %d (they stamp only slot 0)" % len(dd))
     tt = t[tma].astype(np.float64)
     d = lambda a, b: (tt[:, b] - tt[:, a]) / 1e3
     for name, v in [("entry -> bin ranges", d(0, 1)), ("bin ranges -> tables", d(1, 2)),
