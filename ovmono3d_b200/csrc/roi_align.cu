@@ -100,7 +100,7 @@ const RoiTune& roi_tune() {
   static RoiTune t = [] {
     auto env = [](const char* k, int d) { const char* v = getenv(k); return v ? atoi(v) : d; };
     RoiTune r;
-    r.split_pct = env("OVM_ROI_SPLIT", 100000);
+    r.split_pct = env("OVM_ROI_SPLIT", 400);
     r.promo = env("OVM_ROI_PROMO", 2);
     r.align8 = env("OVM_ROI_ALIGN8", 0);
     r.stages = env("OVM_ROI_STAGES", 2);
@@ -542,6 +542,11 @@ __global__ void __launch_bounds__(kThreads) roi_align_kernel(const __grid_consta
   // largest G -- and for it the tile width with the least padding, wider on ties -- whose stage fits kStageFloats and
   // leaves at least a.min_slots ring slots; if nothing gives that depth, the largest G that fits at all.
   auto group_span = [&](int G, int h, int& gy, int& rows) {   // pixel rows of group h (one dummy row if it has no sample)
+    if (G == kP) {   // the common case: the whole footprint in one stage
+      gy = y_lo;
+      rows = rows_total;
+      return;
+    }
     int lo = INT_MAX, hi = -1;
     for (int p = h * G; p < min(kP, (h + 1) * G); ++p) {
       if (meta[21 + p] >= meta[14 + p]) {
@@ -555,11 +560,14 @@ __global__ void __launch_bounds__(kThreads) roi_align_kernel(const __grid_consta
   };
   int wsel = -1, best_pad = INT_MAX, G = kP, rmax = rows_total;
   auto try_cfg = [&](int g, int need_slots) {
-    int rm = 0;
-    for (int h = 0; h * g < kP; ++h) {
-      int gy, rows;
-      group_span(g, h, gy, rows);
-      rm = max(rm, rows);
+    int rm = rows_total;
+    if (g != kP) {
+      rm = 0;
+      for (int h = 0; h * g < kP; ++h) {
+        int gy, rows;
+        group_span(g, h, gy, rows);
+        rm = max(rm, rows);
+      }
     }
     int ws = -1, bp = INT_MAX;
 #pragma unroll
