@@ -407,7 +407,7 @@ def kernel_breakdown(eng, dbs, flush, lift, K: int, peaks) -> Dict[str, object]:
                       "peak": peaks["hbm"], "unit": "GB/s", "algorithmic_bytes": roi_bytes},
         "fc1": {"ms": ms["fc1"], "bound": "tensor", "achieved": fc1_flops / (ms["fc1"] * 1e-3) / 1e12,
                 "peak": peaks["tf_burst"], "unit": "TFLOP/s", "algorithmic_flops": fc1_flops,
-                "note": "memset + split-K tcgen05 GEMM + bias/ReLU"},
+                "note": "split-K tcgen05 GEMM; the CTA that completes a tile applies bias/ReLU (one launch)"},
         "fc2": {"ms": ms["fc2"], "bound": "tensor", "achieved": fc2_flops / (ms["fc2"] * 1e-3) / 1e12,
                 "peak": peaks["tf_burst"], "unit": "TFLOP/s", "algorithmic_flops": fc2_flops},
         "head_decode": {"ms": ms["head_decode"]},

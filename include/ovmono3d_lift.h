@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define OVM_ABI_VERSION 3
+#define OVM_ABI_VERSION 4
 #define OVM_MAX_LEVELS 8
 #define OVM_RECORD_WIDTH 48   /* floats per detection record, see ovm_head_decode */
 
@@ -106,6 +106,11 @@ int ovm_gemm_set_trace(uint64_t* buf);
  * (rows << 48 | footprint width << 32 | tile-width index << 24 | SM id).  CTAs on the direct path stamp slot 0 only. */
 int ovm_roi_set_trace(uint64_t* buf);
 
+/* Same for the heads + decode kernel: [grid, 8] stamps of each CTA's warp 0 -- 0 entry, 1 head rows staged,
+ * 2 FC features available (programmatic-launch wait returned), 3 box / camera loads done, 4 dot products done,
+ * 5 record written.  NULL switches it off.                                                                  */
+int ovm_head_set_trace(uint64_t* buf);
+
 /* out[m, j] = act(in[m, j] + bias[j]) for j < N; in fp32 [M, ldi], out out_dtype [M, ldo]. */
 int ovm_bias_act(const float* in, int64_t ldi, const float* bias, int32_t relu, int32_t M, int32_t N,
                  void* out, int32_t out_dtype, int64_t ldo, void* stream);
@@ -170,6 +175,11 @@ typedef struct {
   void* act_b;         /* bf16 [n, fc_dim] pong */
   float* feats;        /* fp32 [n, num_groups * fc_dim] */
   int32_t* levels;     /* int32 [n] */
+  int32_t* tile_counters;      /* optional int32 [num_tile_counters], ZERO-FILLED once like acc (left zeroed): with
+                                  it the split-K FC layer finishes (bias, ReLU, cast) inside the GEMM launch; NULL:
+                                  a separate bias/ReLU launch follows.  ceil(n/128) * ceil(fc_dim/256) are needed */
+  int32_t num_tile_counters;
+  int32_t _pad;
 } ovm_workspace_t;
 
 /* ROIAlign (bf16 out) -> FC stack -> heads + decode on `stream`. */

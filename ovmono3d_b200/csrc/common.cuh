@@ -82,11 +82,23 @@ EncodeTiledFn tensormap_encode_fn();
 // Entry points implemented per translation unit (host side, called from lift_api.cu).
 int roi_align_launch(const ovm_pooler_t* pooler, const float* boxes, const int32_t* batch_idx, int32_t n,
                      void* out, int32_t out_dtype, int64_t out_ld, int32_t* level_out, cudaStream_t stream);
+// Split-K with a fused finish (lift_api.cu): `out` of gemm_bf16_launch is the zeroed fp32 accumulator, the CTA that
+// completes a tile writes act(acc + bias) to `out` here and zeroes accumulator and counter again.
+struct GemmFinish {
+  int32_t* tile_counters;   // device, zero on entry, >= num_counters entries
+  int32_t num_counters;
+  const float* bias;
+  int32_t relu;
+  void* out;
+  int32_t out_dtype;
+  int64_t ldo;
+};
 int gemm_bf16_launch(const void* A, int64_t lda, const void* B, int64_t ldb, int32_t M, int32_t N, int32_t K,
                      const float* bias, int32_t relu, void* out, int32_t out_dtype, int64_t ldo, int32_t mode,
-                     int32_t* mode_used, cudaStream_t stream);
+                     int32_t* mode_used, cudaStream_t stream, const GemmFinish* fin = nullptr);
 void gemm_set_trace(unsigned long long* buf);
 void roi_set_trace(unsigned long long* buf);
+void head_set_trace(unsigned long long* buf);
 int bias_act_launch(const float* in, int64_t ldi, const float* bias, int32_t relu, int32_t M, int32_t N,
                     void* out, int32_t out_dtype, int64_t ldo, cudaStream_t stream, bool clear_in = false);
 int cast_bf16_launch(const float* in, int64_t ld_in, int32_t rows, int32_t cols, void* out, int64_t ld_out,

@@ -59,6 +59,12 @@ struct GemmArgs {
   void* out;
   long long ldo;
   unsigned long long* trace;   // optional [grid, 16] globaltimer stamps (ovm_gemm_set_trace), else NULL
+  // split-K with a fused finish: the CTA whose segment completes a tile (per-tile counter of K blocks) reads the
+  // accumulated tile back, applies bias / ReLU, writes `fin_out` and hands accumulator and counter back zeroed
+  int* tile_counters;          // NULL: raw accumulation only (a bias_act pass follows)
+  void* fin_out;
+  long long fin_ldo;
+  int fin_bf16;
 };
 
 thread_local unsigned long long* g_gemm_trace = nullptr;
@@ -396,6 +402,63 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       if (lane == 0) mbar_arrive(tempty_bar + 8 * acc);
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1;
+      if (MODE == kModeStreamK && g.tile_counters) {
+        // ---- fused finish (threadFenceReduction pattern): publish this segment, count its K blocks on the tile
+        __threadfence();
+        asm volatile("bar.sync 2, %0;" ::"n"(kEpiWarps * 32) : "memory");
+        int* flag = reinterpret_cast<int*>(smem_raw + (tmem_slot - raw)) + 2;
+        const int tile = s.m_tile * g.num_n_tiles + s.n_tile;
+        if (threadIdx.x == 64) {
+          const int done = atomicAdd(g.tile_counters + tile, s.k1 - s.k0) + (s.k1 - s.k0);
+          *flag = done == g.kb_per_tile;
+          if (done == g.kb_per_tile) g.tile_counters[tile] = 0;   // nobody else touches this tile any more
+        }
+        asm volatile("bar.sync 2, %0;" ::"n"(kEpiWarps * 32) : "memory");
+        if (*flag) {
+          __threadfence();
+          float* accp = reinterpret_cast<float*>(g.out);
+          const int colw = BN / 2;                      // this warp's half of the tile's columns
+          const int cbase = s.n_tile * BN + half * colw;
+          // 16 rows per batch with all loads in flight: the finish sits on the kernel's tail, its L2 round trips
+          // must overlap (one row at a time cost 20 us)
+          constexpr int kRows = 16;
+          for (int c = cbase + 4 * lane; c < cbase + colw && c < g.N; c += 128) {
+            float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (g.bias) bv = __ldg(reinterpret_cast<const float4*>(g.bias + c));
+            for (int rb = 0; rb < 32; rb += kRows) {
+              float4 x[kRows];
+#pragma unroll
+              for (int r = 0; r < kRows; ++r) {
+                const int row = row0 + rb + r;
+                x[r] = row < g.M ? __ldcg(reinterpret_cast<const float4*>(accp + (long long)row * g.ldo + c))
+                                 : make_float4(0.f, 0.f, 0.f, 0.f);      // L2: other SMs wrote it
+              }
+#pragma unroll
+              for (int r = 0; r < kRows; ++r) {
+                const int row = row0 + rb + r;
+                if (row >= g.M) continue;
+                __stcg(reinterpret_cast<float4*>(accp + (long long)row * g.ldo + c), make_float4(0.f, 0.f, 0.f, 0.f));
+                float4 v = x[r];
+                v.x += bv.x; v.y += bv.y; v.z += bv.z; v.w += bv.w;
+                if (g.relu) {   // torch.relu keeps NaN
+                  v.x = v.x < 0.f ? 0.f : v.x; v.y = v.y < 0.f ? 0.f : v.y;
+                  v.z = v.z < 0.f ? 0.f : v.z; v.w = v.w < 0.f ? 0.f : v.w;
+                }
+                const long long off = (long long)row * g.fin_ldo + c;
+                if (g.fin_bf16) {
+                  __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+                  uint2 pk;
+                  pk.x = *reinterpret_cast<uint32_t*>(&lo);
+                  pk.y = *reinterpret_cast<uint32_t*>(&hi);
+                  *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(g.fin_out) + off) = pk;
+                } else {
+                  *reinterpret_cast<float4*>(reinterpret_cast<float*>(g.fin_out) + off) = v;
+                }
+              }
+            }
+          }
+        }
+      }
     }
     if (threadIdx.x == 64) trace_stamp(g, 6);     // epilogue done
   }
@@ -497,7 +560,7 @@ int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& 
 
 int gemm_bf16_launch(const void* A, int64_t lda, const void* B, int64_t ldb, int32_t M, int32_t N, int32_t K,
                      const float* bias, int32_t relu, void* out, int32_t out_dtype, int64_t ldo, int32_t mode,
-                     int32_t* mode_used, cudaStream_t stream) {
+                     int32_t* mode_used, cudaStream_t stream, const GemmFinish* fin) {
   OVM_REQUIRE(M >= 0 && N > 0 && K > 0, "ovm_gemm_bf16: bad shape M=%d N=%d K=%d", M, N, K);
   if (M == 0) return OVM_OK;
   OVM_REQUIRE(A && B && out, "ovm_gemm_bf16: NULL pointer");
@@ -547,6 +610,17 @@ int gemm_bf16_launch(const void* A, int64_t lda, const void* B, int64_t ldb, int
   g.out = out;
   g.ldo = ldo;
   g.trace = g_gemm_trace;
+  if (fin) {
+    OVM_REQUIRE(g.streamk && fin->tile_counters && fin->out && fin->num_counters >= g.num_tiles && N % 4 == 0 &&
+                    fin->ldo >= N && fin->ldo % 4 == 0 && !(reinterpret_cast<uintptr_t>(fin->out) & 15),
+                "ovm_gemm_bf16: fused split-K finish needs STREAMK, %d tile counters and an aligned output", g.num_tiles);
+    g.tile_counters = fin->tile_counters;
+    g.bias = fin->bias;
+    g.relu = fin->relu;
+    g.fin_out = fin->out;
+    g.fin_ldo = fin->ldo;
+    g.fin_bf16 = fin->out_dtype == OVM_BF16;
+  }
   CUtensorMap tmA, tmB;
   int rc = make_map(&tmA, A, M, K, lda, BM);
   if (rc != OVM_OK) return rc;

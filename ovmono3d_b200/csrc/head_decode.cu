@@ -40,7 +40,18 @@ struct DecodeArgs {
   int num_images, n;
   float* records;
   float* raw;
+  unsigned long long* trace;   // optional [grid, 8] %globaltimer stamps of warp 0 (ovm_head_set_trace), else NULL
 };
+
+thread_local unsigned long long* g_head_trace = nullptr;
+
+__device__ __forceinline__ void head_stamp(const DecodeArgs& a, int slot) {
+  if (a.trace && threadIdx.x == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    a.trace[(size_t)blockIdx.x * 8 + slot] = t;
+  }
+}
 
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
@@ -243,10 +254,12 @@ __device__ __forceinline__ void decode_box(const DecodeArgs& a, const int box, c
 #pragma unroll
     for (int r = 0; r < kMaxRows; ++r) wr[r] = staged + (r < nrows ? r : 0) * K;
   }
+  head_stamp(a, 3);
   if (shared)
     head_rows<true, STAGED>(wr, fr, bs, nrows, K, lane, vec4, hv);
   else
     head_rows<false, STAGED>(wr, fr, bs, nrows, K, lane, vec4, hv);
+  head_stamp(a, 4);
   const float deltas[2] = {hv[0], hv[1]};
   const float dims_raw[3] = {hv[2], hv[3], hv[4]};
   const float z_raw = hv[5];
@@ -385,6 +398,7 @@ __device__ __forceinline__ void decode_box(const DecodeArgs& a, const int box, c
     ro[2] = make_float4(pose_raw[1], pose_raw[2], pose_raw[3], pose_raw[4]);
     ro[3] = make_float4(pose_raw[5], 0.f, 0.f, 0.f);
   }
+  head_stamp(a, 5);
 }
 
 // Grid-stride over boxes, one warp per box.  STAGED (class-agnostic heads without depth bins: every box uses the
@@ -395,6 +409,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) head_decode_kernel(const 
   float* staged = reinterpret_cast<float*>(staged4);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   pdl_trigger();
+  head_stamp(a, 0);
   if (STAGED) {   // head weights are parameters: staged while the FC kernel before this one is still running
     const ovm_decode_cfg_t& cfg = a.cfg;
     const int K = cfg.fc_dim;
@@ -418,12 +433,16 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) head_decode_kernel(const 
     }
     __syncthreads();
   }
+  head_stamp(a, 1);
   pdl_wait();   // the FC features
+  head_stamp(a, 2);
   for (int box = blockIdx.x * kWarpsPerBlock + warp; box < a.n; box += gridDim.x * kWarpsPerBlock)
     decode_box<STAGED>(a, box, lane, staged);
 }
 
 }  // namespace
+
+void head_set_trace(unsigned long long* buf) { g_head_trace = buf; }
 
 int head_decode_launch(const ovm_decode_cfg_t* cfg, const ovm_head_weights_t* w, const float* feats, int64_t ld_feats,
                        const float* boxes, const int64_t* classes, const float* scores, const int32_t* batch_idx,
@@ -470,6 +489,7 @@ int head_decode_launch(const ovm_decode_cfg_t* cfg, const ovm_head_weights_t* w,
   a.n = n;
   a.records = records;
   a.raw = raw;
+  a.trace = g_head_trace;
   const int pose_n = cfg->pose_type == OVM_POSE_6D ? 6 : (cfg->pose_type == OVM_POSE_QUATERNION ? 4 : 3);
   const size_t stage_bytes = (size_t)(6 + (cfg->use_confidence ? 1 : 0) + pose_n) * cfg->fc_dim * sizeof(float);
   const bool staged = !cfg->dims_priors_enabled && cfg->cluster_bins == 1 && stage_bytes <= 160 * 1024 &&

@@ -72,12 +72,20 @@ int run_fc_group(const ovm_fc_layer_t* layers, int num_fc, const void* x, int64_
       if (kb >= 32 && tiles < 2 * kNumSMs && ragged && ws->acc) mode = OVM_GEMM_STREAMK;
     }
     if (mode == OVM_GEMM_STREAMK) {
-      // ws->acc is zero on entry (workspace contract) and bias_act hands it back zeroed
-      int rc = gemm_bf16_launch(in, ld_in, L.weight, L.ldw, n, L.N, L.K, nullptr, 0, ws->acc, OVM_F32, L.N,
-                                OVM_GEMM_STREAMK, nullptr, stream);
-      if (rc != OVM_OK) return rc;
-      rc = bias_act_launch(ws->acc, L.N, L.bias, 1, n, L.N, out, out_dtype, ldo, stream, /*clear_in=*/true);
-      if (rc != OVM_OK) return rc;
+      // ws->acc (and the tile counters) are zero on entry (workspace contract) and handed back zeroed
+      if (ws->tile_counters && ws->num_tile_counters >= ((n + 127) / 128) * ((L.N + 255) / 256)) {
+        // one launch: the CTA that completes a tile applies bias + ReLU and writes the layer's output
+        const GemmFinish fin{ws->tile_counters, ws->num_tile_counters, L.bias, 1, out, out_dtype, ldo};
+        int rc = gemm_bf16_launch(in, ld_in, L.weight, L.ldw, n, L.N, L.K, nullptr, 0, ws->acc, OVM_F32, L.N,
+                                  OVM_GEMM_STREAMK, nullptr, stream, &fin);
+        if (rc != OVM_OK) return rc;
+      } else {
+        int rc = gemm_bf16_launch(in, ld_in, L.weight, L.ldw, n, L.N, L.K, nullptr, 0, ws->acc, OVM_F32, L.N,
+                                  OVM_GEMM_STREAMK, nullptr, stream);
+        if (rc != OVM_OK) return rc;
+        rc = bias_act_launch(ws->acc, L.N, L.bias, 1, n, L.N, out, out_dtype, ldo, stream, /*clear_in=*/true);
+        if (rc != OVM_OK) return rc;
+      }
     } else {
       int rc = gemm_bf16_launch(in, ld_in, L.weight, L.ldw, n, L.N, L.K, L.bias, 1, out, out_dtype, ldo,
                                 OVM_GEMM_DIRECT, nullptr, stream);
@@ -147,6 +155,11 @@ int ovm_gemm_set_trace(uint64_t* buf) {
 
 int ovm_roi_set_trace(uint64_t* buf) {
   roi_set_trace(reinterpret_cast<unsigned long long*>(buf));
+  return OVM_OK;
+}
+
+int ovm_head_set_trace(uint64_t* buf) {
+  head_set_trace(reinterpret_cast<unsigned long long*>(buf));
   return OVM_OK;
 }
 

@@ -163,10 +163,13 @@ class LiftEngine:
             act_b=torch.empty((cap, self.fc_dim), device=device, dtype=torch.bfloat16),
             feats=torch.empty((cap, groups * self.fc_dim), device=device, dtype=torch.float32),
             levels=torch.empty((cap,), device=device, dtype=torch.int32),
+            counters=torch.zeros((_round_up(cap, 128) // 128 * (_round_up(self.fc_dim, 256) // 256),), device=device,
+                                 dtype=torch.int32),   # split-K tile counters: zero on entry / exit
             order=torch.empty((ops.order_ws_len(cap),), device=device, dtype=torch.int32),
         )
         ws = ops.ovm_workspace_t(t["pooled"].data_ptr(), ld_pooled, t["acc"].data_ptr(), t["act_a"].data_ptr(),
-                                 t["act_b"].data_ptr(), t["feats"].data_ptr(), t["levels"].data_ptr())
+                                 t["act_b"].data_ptr(), t["feats"].data_ptr(), t["levels"].data_ptr(),
+                                 t["counters"].data_ptr(), t["counters"].numel(), 0)
         self._ws_tensors, self._ws, self._cap = t, ws, cap
         return ws
 

@@ -11,7 +11,7 @@ from typing import List, Optional, Sequence, Tuple
 
 import torch
 
-OVM_ABI_VERSION = 3
+OVM_ABI_VERSION = 4
 OVM_MAX_LEVELS = 8
 RECORD_WIDTH = 48
 LAYOUT_NCHW, LAYOUT_NHWC = 0, 1
@@ -33,7 +33,7 @@ REC_CLASS = 46
 
 EXPORTS = ("ovm_abi_version", "ovm_last_error", "ovm_launch_count", "ovm_struct_size", "ovm_roi_align", "ovm_gemm_bf16",
            "ovm_bias_act", "ovm_cast_bf16", "ovm_head_decode", "ovm_lift_forward", "ovm_set_stage_events", "ovm_gemm_set_trace",
-           "ovm_roi_set_trace")
+           "ovm_roi_set_trace", "ovm_head_set_trace")
 
 
 class LiftError(RuntimeError):
@@ -75,7 +75,8 @@ class ovm_fc_stack_t(C.Structure):
 
 class ovm_workspace_t(C.Structure):
     _fields_ = [("pooled", C.c_void_p), ("ld_pooled", C.c_int64), ("acc", C.c_void_p), ("act_a", C.c_void_p),
-                ("act_b", C.c_void_p), ("feats", C.c_void_p), ("levels", C.c_void_p)]
+                ("act_b", C.c_void_p), ("feats", C.c_void_p), ("levels", C.c_void_p),
+                ("tile_counters", C.c_void_p), ("num_tile_counters", C.c_int32), ("_pad", C.c_int32)]
 
 
 ABI_STRUCTS = (ovm_level_t, ovm_pooler_t, ovm_decode_cfg_t, ovm_head_weights_t, ovm_fc_layer_t, ovm_fc_stack_t,
@@ -114,6 +115,7 @@ def load_library() -> C.CDLL:
                                      C.POINTER(ovm_workspace_t), vp, vp, vp]
     lib.ovm_gemm_set_trace.argtypes = [vp]
     lib.ovm_roi_set_trace.argtypes = [vp]
+    lib.ovm_head_set_trace.argtypes = [vp]
     lib.ovm_set_stage_events.argtypes = [C.POINTER(C.c_void_p), i32]
     for name in EXPORTS[3:]:
         getattr(lib, name).restype = C.c_int
