@@ -19,6 +19,7 @@
 // tiles for 148 SMs, which is why it needs the K split.
 #include <cuda.h>
 
+#include <cstdlib>
 #include <cstring>
 
 #include "common.cuh"
@@ -472,6 +473,322 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   }
 }
 
+// ------------------------------------------------------------------ split-K GEMM on CTA pairs (cta_group::2)
+// fc1 of the lift is fed from L2: with 128 x 256 tiles per CTA the operand traffic of one launch is 494 MB (every
+// A tile read by 4 column tiles, every W1 tile by 13 row tiles).  A CTA pair (cluster of 2, same TPC) works on a
+// 256 x 256 tile instead: each CTA loads its own 128 rows of A and HALF of the B tile (128 of its 256 rows), the
+// leader issues tcgen05.mma.cta_group::2 (M = 256: rows 0-127 accumulate in the leader's TMEM, 128-255 in the
+// peer's; the B operand is read from both CTAs' shared memory) -- 32 KB instead of 48 KB per CTA and K block.
+//   * full[s]   (leader's copy is used): the leader's producer arms it with the bytes of BOTH CTAs; the peer's TMA
+//               loads (cta_group::2 form) complete on the leader's barrier.
+//   * empty[s]  (one per CTA): tcgen05.commit multicast from the leader's MMA thread frees the slot in both CTAs.
+//   * tfull[a]  (one per CTA): commit multicast, accumulator stage a is complete in both CTAs' TMEM.
+//   * tempty[a] (leader's copy): 2 x kEpiWarps arrivals, the peer's epilogue warps arrive remotely.
+// Work is the flat list of (pair tile, K block); cluster c of G owns a contiguous range (stream-K), partial tiles are
+// added into the zeroed fp32 accumulator and finished by whichever CTA completes a 128-row tile (see above).
+constexpr int kPairStages = 6;
+constexpr int kPairBN = 256;
+constexpr int kPairABytes = BM * BK * 2;                 // this CTA's 128 rows of A
+constexpr int kPairBBytes = (kPairBN / 2) * BK * 2;      // this CTA's half of the B tile
+constexpr int kPairStageBytes = kPairABytes + kPairBBytes;
+constexpr size_t kPairSmemBytes = 1024 + (size_t)kPairStages * kPairStageBytes + (2 * kPairStages + 4) * 8 + 16 +
+                                  kEpiWarps * kStgFloats * 4;
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ uint32_t mapa_shared(uint32_t addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive_remote(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+// TMA load whose completion is signalled on a barrier of either CTA of the pair
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap* map, uint32_t bar_cluster, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
+      "l"(map), "r"(bar_cluster), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tcgen05_commit_pair(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+               "h"((uint16_t)3)
+               : "memory");
+}
+__device__ __forceinline__ void umma_bf16_pair(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
+struct PairSegment {
+  int m_pair, n_tile, k0, k1;
+};
+struct PairIter {
+  long long cur, end;
+  int kb_per_tile, num_n_tiles;
+  __device__ PairIter(const GemmArgs& g, int num_pair_tiles) {
+    const long long total = (long long)num_pair_tiles * g.kb_per_tile;
+    const int cluster = blockIdx.x >> 1, nclusters = gridDim.x >> 1;
+    cur = total * cluster / nclusters;
+    end = total * (cluster + 1) / nclusters;
+    kb_per_tile = g.kb_per_tile;
+    num_n_tiles = g.num_n_tiles;
+  }
+  __device__ bool next(PairSegment& s) {
+    if (cur >= end) return false;
+    const int tile = (int)(cur / kb_per_tile);
+    s.k0 = (int)(cur - (long long)tile * kb_per_tile);
+    const long long left = end - cur;
+    s.k1 = (int)((long long)s.k0 + left < (long long)kb_per_tile ? (long long)s.k0 + left : (long long)kb_per_tile);
+    s.m_pair = tile / num_n_tiles;
+    s.n_tile = tile - s.m_pair * num_n_tiles;
+    cur += s.k1 - s.k0;
+    return true;
+  }
+};
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
+gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmArgs g,
+                 const int num_pair_tiles) {
+  constexpr int BN = kPairBN;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  const uint32_t smem_a = base;
+  const uint32_t smem_b = base + kPairStages * kPairABytes;
+  const uint32_t bars = base + kPairStages * kPairStageBytes;
+  const uint32_t full_bar = bars;
+  const uint32_t empty_bar = bars + 8 * kPairStages;
+  const uint32_t tfull_bar = bars + 16 * kPairStages;
+  const uint32_t tempty_bar = tfull_bar + 16;
+  const uint32_t tmem_slot = tempty_bar + 16;
+  const uint32_t stage_buf = tmem_slot + 16;
+  uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - raw));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < kPairStages; ++s) {
+      mbar_init(full_bar + 8 * s, 1);
+      mbar_init(empty_bar + 8 * s, 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(tfull_bar + 8 * s, 1);
+      mbar_init(tempty_bar + 8 * s, 2 * kEpiWarps);   // both CTAs' epilogue warps (used in the leader only)
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 2) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"((uint32_t)(2 * BN))
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  tcgen05_fence_before();
+  cluster_sync_all();        // both CTAs' barriers are initialised and both TMEM allocations are done
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+  pdl_trigger();
+  pdl_wait();
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ===== TMA producer (both CTAs): own rows of A, own half of the B tile; completion on the LEADER's barrier
+      PairIter it(g, num_pair_tiles);
+      PairSegment s;
+      int stage = 0;
+      uint32_t phase = 0;
+      while (it.next(s)) {
+        const int a_row = s.m_pair * (2 * BM) + (int)rank * BM;
+        const int b_row = s.n_tile * BN + (int)rank * (BN / 2);
+        for (int kb = s.k0; kb < s.k1; ++kb) {
+          mbar_wait(empty_bar + 8 * stage, phase ^ 1);
+          const uint32_t full_leader = mapa_shared(full_bar + 8 * stage, 0);
+          if (leader) mbar_expect_tx(full_bar + 8 * stage, 2 * kPairStageBytes);
+          tma_load_2d_pair(smem_a + stage * kPairABytes, &tmA, full_leader, kb * BK, a_row);
+          tma_load_2d_pair(smem_b + stage * kPairBBytes, &tmB, full_leader, kb * BK, b_row);
+          if (++stage == kPairStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0 && leader) {
+      // ===== MMA issuer (leader only): M = 256 over both CTAs, N = 256, K = 16 x 4 per stage
+      constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)((2 * BM) >> 4) << 24);
+      PairIter it(g, num_pair_tiles);
+      PairSegment s;
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      while (it.next(s)) {
+        mbar_wait(tempty_bar + 8 * acc, acc_phase ^ 1);
+        tcgen05_fence_after();
+        const uint32_t tmem_d = tmem_base + (uint32_t)(acc * BN);
+        for (int kb = s.k0; kb < s.k1; ++kb) {
+          mbar_wait(full_bar + 8 * stage, phase);
+          tcgen05_fence_after();
+          const uint64_t adesc = make_smem_desc(smem_a + stage * kPairABytes);
+          const uint64_t bdesc = make_smem_desc(smem_b + stage * kPairBBytes);
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k)
+            umma_bf16_pair(tmem_d, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (kb > s.k0 || k > 0) ? 1u : 0u);
+          tcgen05_commit_pair(empty_bar + 8 * stage);   // frees the slot in both CTAs once these MMAs retire
+          if (++stage == kPairStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        tcgen05_commit_pair(tfull_bar + 8 * acc);        // accumulator complete in both CTAs
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1;
+      }
+    }
+  } else {
+    // ===== epilogue warps (both CTAs): this CTA's 128 accumulator rows; same transpose as gemm_bf16_kernel
+    const int quad = warp & 3;
+    const int half = (warp - 2) >> 2;
+    float* stg = reinterpret_cast<float*>(smem_raw + (stage_buf - raw)) + (warp - 2) * kStgFloats;
+    const int q = lane >> 2, l4 = lane & 3;
+    constexpr int kChunksPerWarp = BN / kChunk / 2;
+    const uint32_t tempty_leader = mapa_shared(tempty_bar, 0);
+    int* flag = reinterpret_cast<int*>(smem_raw + (tmem_slot - raw)) + 2;
+    float* accp = reinterpret_cast<float*>(g.out);
+    PairIter it(g, num_pair_tiles);
+    PairSegment s;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    while (it.next(s)) {
+      mbar_wait(tfull_bar + 8 * acc, acc_phase);
+      tcgen05_fence_after();
+      const int m_tile = s.m_pair * 2 + (int)rank;
+      const int row0 = m_tile * BM + quad * 32;
+      const bool rows_full = row0 + 32 <= g.M;
+#pragma unroll 1
+      for (int ci = 0; ci < kChunksPerWarp; ++ci) {
+        const int ch = half * kChunksPerWarp + ci;
+        uint32_t v[kChunk];
+        __syncwarp();
+        tmem_ld16(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN + ch * kChunk), v);
+        const int col0 = s.n_tile * BN + ch * kChunk;
+        if (row0 >= g.M || col0 >= g.N) continue;   // warp-uniform
+        {
+          float4* wr = reinterpret_cast<float4*>(stg + lane * kChunk);
+          const int sw = (lane >> 1) & 3;
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            wr[k ^ sw] = make_float4(__uint_as_float(v[4 * k]), __uint_as_float(v[4 * k + 1]),
+                                     __uint_as_float(v[4 * k + 2]), __uint_as_float(v[4 * k + 3]));
+        }
+        __syncwarp();
+        const int c = col0 + 4 * l4;
+        const bool full = rows_full && col0 + kChunk <= g.N;
+#pragma unroll
+        for (int rr = 0; rr < 32; rr += 8) {
+          const int r = rr + q;
+          const float4 x = reinterpret_cast<const float4*>(stg + r * kChunk)[l4 ^ ((r >> 1) & 3)];
+          const long long off = (long long)(row0 + r) * g.ldo + c;
+          if (full) {
+            red_add_v4(accp + off, x.x, x.y, x.z, x.w);
+          } else if (row0 + r < g.M) {
+            const float xs[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e)
+              if (c + e < g.N) atomicAdd(accp + off + e, xs[e]);
+          }
+        }
+      }
+      tcgen05_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_remote(tempty_leader + 8 * acc);
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1;
+      if (g.tile_counters && m_tile * BM < g.M) {   // CTA-uniform; the odd last row tile of a pair may not exist
+        // ---- fused finish of this CTA's 128-row tile (see gemm_bf16_kernel)
+        __threadfence();
+        asm volatile("bar.sync 2, %0;" ::"n"(kEpiWarps * 32) : "memory");
+        const int tile = m_tile * g.num_n_tiles + s.n_tile;
+        if (threadIdx.x == 64) {
+          const int done = atomicAdd(g.tile_counters + tile, s.k1 - s.k0) + (s.k1 - s.k0);
+          *flag = done == g.kb_per_tile;
+          if (done == g.kb_per_tile) g.tile_counters[tile] = 0;
+        }
+        asm volatile("bar.sync 2, %0;" ::"n"(kEpiWarps * 32) : "memory");
+        if (*flag && row0 < g.M) {
+          __threadfence();
+          const int colw = BN / 2;
+          const int cbase = s.n_tile * BN + half * colw;
+          constexpr int kRows = 16;
+          for (int c = cbase + 4 * lane; c < cbase + colw && c < g.N; c += 128) {
+            float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (g.bias) bv = __ldg(reinterpret_cast<const float4*>(g.bias + c));
+            for (int rb = 0; rb < 32; rb += kRows) {
+              float4 x[kRows];
+#pragma unroll
+              for (int r = 0; r < kRows; ++r) {
+                const int row = row0 + rb + r;
+                x[r] = row < g.M ? __ldcg(reinterpret_cast<const float4*>(accp + (long long)row * g.ldo + c))
+                                 : make_float4(0.f, 0.f, 0.f, 0.f);
+              }
+#pragma unroll
+              for (int r = 0; r < kRows; ++r) {
+                const int row = row0 + rb + r;
+                if (row >= g.M) continue;
+                __stcg(reinterpret_cast<float4*>(accp + (long long)row * g.ldo + c), make_float4(0.f, 0.f, 0.f, 0.f));
+                float4 w = x[r];
+                w.x += bv.x; w.y += bv.y; w.z += bv.z; w.w += bv.w;
+                if (g.relu) {
+                  w.x = w.x < 0.f ? 0.f : w.x; w.y = w.y < 0.f ? 0.f : w.y;
+                  w.z = w.z < 0.f ? 0.f : w.z; w.w = w.w < 0.f ? 0.f : w.w;
+                }
+                const long long off = (long long)row * g.fin_ldo + c;
+                if (g.fin_bf16) {
+                  __nv_bfloat162 lo = __floats2bfloat162_rn(w.x, w.y), hi = __floats2bfloat162_rn(w.z, w.w);
+                  uint2 pk;
+                  pk.x = *reinterpret_cast<uint32_t*>(&lo);
+                  pk.y = *reinterpret_cast<uint32_t*>(&hi);
+                  *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(g.fin_out) + off) = pk;
+                } else {
+                  *reinterpret_cast<float4*>(reinterpret_cast<float*>(g.fin_out) + off) = w;
+                }
+              }
+            }
+          }
+        }
+      }
+    }
+  }
+
+  tcgen05_fence_before();
+  cluster_sync_all();        // the leader's MMAs write the peer's TMEM: neither CTA may release before both are done
+  if (warp == 2) {
+    tcgen05_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)(2 * BN)) : "memory");
+  }
+}
+
 // ------------------------------------------------------------------ small elementwise kernels
 __global__ void bias_act_kernel(const float* in, long long ldi, const float* __restrict__ bias, int relu,
                                 int M, int N, void* out, int out_bf16, long long ldo, int clear_in) {
@@ -624,6 +941,24 @@ int gemm_bf16_launch(const void* A, int64_t lda, const void* B, int64_t ldb, int
   CUtensorMap tmA, tmB;
   int rc = make_map(&tmA, A, M, K, lda, BM);
   if (rc != OVM_OK) return rc;
+  static const bool pair_ok = [] { const char* v = getenv("OVM_GEMM_PAIR"); return !v || atoi(v) != 0; }();
+  if (fin && BN == kPairBN && pair_ok && num_m_tiles >= 2) {
+    // CTA pairs on 256 x 256 tiles: a third less operand traffic out of L2 (see gemm_pair_kernel)
+    rc = make_map(&tmB, B, N, K, ldb, kPairBN / 2);
+    if (rc != OVM_OK) return rc;
+    const int num_pair_tiles = ((num_m_tiles + 1) / 2) * g.num_n_tiles;
+    const long long total = (long long)num_pair_tiles * g.kb_per_tile;
+    const int clusters = (int)(total < kNumSMs / 2 ? total : kNumSMs / 2);
+    static bool attr_done = false;
+    if (!attr_done) {
+      OVM_CUDA(cudaFuncSetAttribute(gemm_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPairSmemBytes));
+      attr_done = true;
+    }
+    OVM_CUDA(launch_pdl(gemm_pair_kernel, dim3(2 * clusters), dim3(kGemmThreads), kPairSmemBytes, stream, tmA, tmB, g,
+                        num_pair_tiles));
+    OVM_LAUNCHED("gemm_pair_kernel");
+    return OVM_OK;
+  }
   rc = make_map(&tmB, B, N, K, ldb, BN);
   if (rc != OVM_OK) return rc;
   int grid = g.num_tiles;
