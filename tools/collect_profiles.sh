@@ -22,7 +22,7 @@ traffic = {}
 for r in rows[2:]:
     d = dict(zip(h, r))
     name = d["Kernel Name"]
-    key = ("roi_align" if "roi_align_kernel" in name else "fc1" if "gemm_bf16_kernel<256, 2>" in name or "<(int)256, (int)2>" in name
+    key = ("roi_align" if "roi_align_kernel" in name else "fc1" if "gemm_pair_kernel" in name or "gemm_bf16_kernel<256, 2>" in name
            else "fc2" if "gemm_bf16_kernel" in name else "head_decode" if "head_decode" in name else None)
     if key and key not in traffic:
         traffic[key] = (float(d["dram__bytes_read.sum"].replace(",", "")) + float(d["dram__bytes_write.sum"].replace(",", ""))) * 1e6
@@ -38,7 +38,7 @@ python -m pytest tests -m gpu -x -q 2>&1 | tail -3 > $o/${tag}_pytest_gpu.log
 python bench.py > $o/${tag}_bench.json 2> $o/${tag}_bench.err
 python bench.py --impl reference > $o/${tag}_bench_reference_arm.json 2> $o/${tag}_bench_ref.err
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $o/${tag}_launches.csv python bench.py --steps 2 --warmup 1 --no-cpu-baseline > $o/${tag}_ncu_l.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:"roi_align_kernel|gemm_bf16|head_decode|roi_order" --launch-skip 20 --launch-count 5 -o $o/${tag}_full -f python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $o/${tag}_ncu_f.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:"roi_align_kernel|gemm_bf16|gemm_pair|head_decode|roi_order" --launch-skip 20 --launch-count 5 -o $o/${tag}_full -f python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $o/${tag}_ncu_f.log 2>&1
 python tools/sweep.py > $o/${tag}_sweep_c3_c5.jsonl 2> $o/${tag}_sweep.err
 python tools/roi_trace.py > $o/${tag}_roi_trace.txt 2>&1
 python tools/head_trace.py > $o/${tag}_head_trace.txt 2>&1
