@@ -249,7 +249,7 @@ class HostBatch:
 
 
 # --------------------------------------------------------------------------------------------- our arm
-STAGES = ("roi_align", "fc1", "fc2", "head_decode")
+STAGES = ("roi_order", "roi_align", "fc1", "fc2", "head_decode")
 
 
 def _dist_env():
@@ -411,6 +411,7 @@ def kernel_breakdown(eng, dbs, flush, lift, K: int, peaks) -> Dict[str, object]:
         "fc2": {"ms": ms["fc2"], "bound": "tensor", "achieved": fc2_flops / (ms["fc2"] * 1e-3) / 1e12,
                 "peak": peaks["tf_burst"], "unit": "TFLOP/s", "algorithmic_flops": fc2_flops},
         "head_decode": {"ms": ms["head_decode"]},
+        "roi_order": {"ms": ms["roi_order"], "note": "work-item planner of the ROIAlign kernel (one CTA)"},
     }
     for k in kernels.values():
         if "peak" in k:

@@ -46,7 +46,7 @@ enum { OVM_DIMS_EXP = 0, OVM_DIMS_SIGMOID = 1 };
 enum { OVM_GEMM_AUTO = 0, OVM_GEMM_DIRECT = 1, OVM_GEMM_STREAMK = 2 };
 
 /* int32 elements of ovm_pooler_t.order_ws that are always enough for n boxes */
-#define OVM_ORDER_WS_LEN(n) (6 * (int64_t)(n) + 1200)
+#define OVM_ORDER_WS_LEN(n) (24 * (int64_t)(n) + 4808)
 
 /* One pyramid level: fp32 feature map of N images, C channels, contiguous in `layout`. */
 typedef struct {
@@ -67,7 +67,7 @@ typedef struct {
   int32_t canonical_level;       /* d2 default 4 */
   float scale_roi_boxes;         /* SCALE_ROI_BOXES; <= 0 disables (roi_heads.py:310-327) */
   int32_t order_ws_len;          /* int32 elements in order_ws; OVM_ORDER_WS_LEN(n) is enough for n boxes */
-  int32_t* order_ws;             /* optional device scratch: when given, one extra tiny launch turns the boxes into
+  int32_t* order_ws;             /* optional device scratch (16-byte aligned): when given, one extra tiny launch turns the boxes into
                                     work items (large footprints are cut along the channels, largest item first)
                                     so that no single CTA sets the kernel time; NULL = one CTA per box in input
                                     order */

@@ -80,8 +80,12 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
 EncodeTiledFn tensormap_encode_fn();
 
 // Entry points implemented per translation unit (host side, called from lift_api.cu).
+// bench.py's per-stage timing hook (ovm_set_stage_events): records the idx-th event if one was supplied, ++idx
+int stage_mark(int& idx, cudaStream_t stream);
+// stage_idx (optional): a stage mark is recorded between the work-item kernel and the pooling kernel
 int roi_align_launch(const ovm_pooler_t* pooler, const float* boxes, const int32_t* batch_idx, int32_t n,
-                     void* out, int32_t out_dtype, int64_t out_ld, int32_t* level_out, cudaStream_t stream);
+                     void* out, int32_t out_dtype, int64_t out_ld, int32_t* level_out, cudaStream_t stream,
+                     int* stage_idx = nullptr);
 // Split-K with a fused finish (lift_api.cu): `out` of gemm_bf16_launch is the zeroed fp32 accumulator, the CTA that
 // completes a tile writes act(acc + bias) to `out` here and zeroes accumulator and counter again.
 struct GemmFinish {

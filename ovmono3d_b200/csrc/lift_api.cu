@@ -18,12 +18,13 @@ constexpr int kMaxStageEvents = 32;
 thread_local cudaEvent_t g_stage_events[kMaxStageEvents];
 thread_local int g_num_stage_events = 0;
 
+}
+
 // bench.py's per-stage timing hook (ovm_set_stage_events): record the idx-th event if one was supplied
 int stage_mark(int& idx, cudaStream_t stream) {
   if (idx < g_num_stage_events) OVM_CUDA(cudaEventRecord(g_stage_events[idx], stream));
   ++idx;
   return OVM_OK;
-}
 }
 
 EncodeTiledFn tensormap_encode_fn() {
@@ -198,7 +199,7 @@ int ovm_lift_forward(const ovm_pooler_t* pooler, const ovm_fc_stack_t* fc, const
   int stage = 0;
   int rc = stage_mark(stage, stream);
   if (rc != OVM_OK) return rc;
-  rc = roi_align_launch(pooler, boxes, batch_idx, n, ws->pooled, OVM_BF16, ws->ld_pooled, ws->levels, stream);
+  rc = roi_align_launch(pooler, boxes, batch_idx, n, ws->pooled, OVM_BF16, ws->ld_pooled, ws->levels, stream, &stage);
   if (rc != OVM_OK) return rc;
   rc = stage_mark(stage, stream);
   if (rc != OVM_OK) return rc;

@@ -201,10 +201,8 @@ struct BoxGeom {
   float count;
 };
 
-__device__ __forceinline__ BoxGeom box_geometry(const RoiArgs& a, int box) {
+__device__ __forceinline__ BoxGeom box_geometry_xy(const RoiArgs& a, float x1, float y1, float x2, float y2, int b) {
   BoxGeom g;
-  float x1 = a.boxes[4 * box + 0], y1 = a.boxes[4 * box + 1];
-  float x2 = a.boxes[4 * box + 2], y2 = a.boxes[4 * box + 3];
   if (a.roi_scale > 0.f) {
     // ROIHeads3D.scale_proposals (roi_heads.py:310-327); heights use x2-x1 exactly as :317 does.
     float cx = __fdiv_rn(__fadd_rn(x1, x2), 2.f), cy = __fdiv_rn(__fadd_rn(y1, y2), 2.f);
@@ -215,7 +213,7 @@ __device__ __forceinline__ BoxGeom box_geometry(const RoiArgs& a, int box) {
     y1 = __fsub_rn(cy, hw);
     y2 = __fadd_rn(cy, hw);
   }
-  g.b = a.batch_idx[box];
+  g.b = b;
   int level = 0;
   if (a.L > 1) {
     // d2 assign_boxes_to_levels: floor(canonical_level + log2(sqrt(area)/canonical_size + 1e-8)), clamped.
@@ -243,6 +241,10 @@ __device__ __forceinline__ BoxGeom box_geometry(const RoiArgs& a, int box) {
   g.gh = a.sampling_ratio > 0 ? a.sampling_ratio : (int)ceilf(__fdiv_rn(roi_h, (float)a.P));
   g.count = (float)max(g.gh * g.gw, 1);
   return g;
+}
+__device__ __forceinline__ BoxGeom box_geometry(const RoiArgs& a, int box) {
+  return box_geometry_xy(a, a.boxes[4 * box + 0], a.boxes[4 * box + 1], a.boxes[4 * box + 2], a.boxes[4 * box + 3],
+                         a.batch_idx[box]);
 }
 
 __device__ __forceinline__ void store_out(const RoiArgs& a, long long idx, float v) {
@@ -345,8 +347,8 @@ __device__ __forceinline__ void consume_tile(const float* __restrict__ slab0, in
 // (box, first chunk, chunks) so that no item is much more expensive than the average box -- a box whose footprint
 // is k times the mean is cut into up to k pieces along the channel chunks (otherwise the largest box alone, walked
 // by one CTA, sets the kernel time: measured 89 us for a 34 x 34 pixel footprint) -- and orders the items by
-// cost, largest first, with a counting sort in shared memory.  ws layout: [0] item count, [1] unused,
-// [2 + 2 i] box, [3 + 2 i] first chunk | chunks << 16.   At most max(3, splits) * n items (see roi_align_launch).
+// cost, largest first, with a counting sort in shared memory.  ws layout: [0] item count, [1..7] unused, then
+// 8 int32 per item: box, first chunk | chunks << 16, x1, y1, x2, y2 (fp32 bits), image, 0.   At most max(3, splits) * n items (see roi_align_launch).
 __global__ void __launch_bounds__(1024) roi_order_kernel(const RoiArgs a, int* __restrict__ ws) {
   __shared__ int hist[64], offs[64];
   __shared__ float warp_sum[32];
@@ -435,8 +437,11 @@ __global__ void __launch_bounds__(1024) roi_order_kernel(const RoiArgs a, int* _
     const int pieces = (chunks + cpi - 1) / cpi;
     const int at = atomicAdd(&offs[bucket_of(ar, cpi)], pieces);
     for (int j = 0; j < pieces; ++j) {
-      ws[2 + 2 * (at + j)] = box;
-      ws[3 + 2 * (at + j)] = (j * cpi) | (min(cpi, chunks - j * cpi) << 16);
+      // 32-byte item: box, first chunk | chunks << 16, the box itself and its image -- the pooling CTA needs one load
+      int4* it = reinterpret_cast<int4*>(ws + 8 + 8 * (at + j));
+      it[0] = make_int4(box, (j * cpi) | (min(cpi, chunks - j * cpi) << 16), __float_as_int(a.boxes[4 * box + 0]),
+                        __float_as_int(a.boxes[4 * box + 1]));
+      it[1] = make_int4(__float_as_int(a.boxes[4 * box + 2]), __float_as_int(a.boxes[4 * box + 3]), a.batch_idx[box], 0);
     }
   };
 #pragma unroll
@@ -463,13 +468,19 @@ __global__ void __launch_bounds__(kThreads) roi_align_kernel(const __grid_consta
 
   pdl_trigger();
   pdl_wait();      // the work items come from roi_order_kernel
-  int box, chunk_begin, chunk_end;
+  int box, chunk_begin, chunk_end, bb = 0;
+  float bx1 = 0.f, by1 = 0.f, bx2 = 0.f, by2 = 0.f;
   if (a.order) {   // work items of roi_order_kernel; the grid is an upper bound of their number
-    if ((int)blockIdx.x >= a.order[0]) return;
-    const int2 item = *reinterpret_cast<const int2*>(a.order + 2 + 2 * blockIdx.x);
-    box = item.x;
-    chunk_begin = item.y & 0xffff;
-    chunk_end = chunk_begin + (item.y >> 16);
+    const int count = a.order[0];                       // the two loads are independent: one round trip
+    const int4* itp = reinterpret_cast<const int4*>(a.order + 8 + 8 * blockIdx.x);
+    const int4 i0 = itp[0], i1 = itp[1];
+    if ((int)blockIdx.x >= count) return;
+    box = i0.x;
+    chunk_begin = i0.y & 0xffff;
+    chunk_end = chunk_begin + (i0.y >> 16);
+    bx1 = __int_as_float(i0.z); by1 = __int_as_float(i0.w);
+    bx2 = __int_as_float(i1.x); by2 = __int_as_float(i1.y);
+    bb = i1.z;
   } else {
     box = (int)(blockIdx.x / a.splits);
     chunk_begin = (int)(blockIdx.x % a.splits) * a.chunks_per_split;
@@ -480,7 +491,7 @@ __global__ void __launch_bounds__(kThreads) roi_align_kernel(const __grid_consta
   const int c_end = min(a.C, chunk_end * 32);
 
   if (tid == 0) trace_stamp(a, 0);
-  const BoxGeom g = box_geometry(a, box);
+  const BoxGeom g = a.order ? box_geometry_xy(a, bx1, by1, bx2, by2, bb) : box_geometry(a, box);
   if (chunk_begin == 0 && tid == 0 && a.level_out) a.level_out[box] = g.level;
 
   bool direct = (a.P != kP) || g.level < 0 || g.gw <= 0 || g.gh <= 0;
@@ -861,7 +872,7 @@ int level_maps(const float* data, int H, int W, long long NC, CUtensorMap* out) 
 void roi_set_trace(unsigned long long* buf) { g_roi_trace = buf; }
 
 int roi_align_launch(const ovm_pooler_t* p, const float* boxes, const int32_t* batch_idx, int32_t n, void* out,
-                     int32_t out_dtype, int64_t out_ld, int32_t* level_out, cudaStream_t stream) {
+                     int32_t out_dtype, int64_t out_ld, int32_t* level_out, cudaStream_t stream, int* stage_idx) {
   OVM_REQUIRE(p != nullptr, "ovm_roi_align: pooler is NULL");
   OVM_REQUIRE(p->num_levels >= 1 && p->num_levels <= OVM_MAX_LEVELS, "ovm_roi_align: num_levels %d not in [1,%d]",
               p->num_levels, OVM_MAX_LEVELS);
@@ -924,8 +935,9 @@ int roi_align_launch(const ovm_pooler_t* p, const float* boxes, const int32_t* b
   a.split_factor = 0.01f * (float)(tune.split_pct < 100 ? 100 : tune.split_pct);   // < 1 would break the item bound
   // with work items: a box yields at most max(splits, 2 area / (split_factor mean area)) of them
   const long long nitems = (long long)n * a.splits + (a.order ? (long long)(2.0 * n / a.split_factor) + 8 : 0);
-  OVM_REQUIRE(!a.order || 2 + 2 * nitems <= (long long)p->order_ws_len,
-              "ovm_roi_align: order_ws holds %d int32, %lld needed (OVM_ORDER_WS_LEN)", p->order_ws_len, 2 + 2 * nitems);
+  OVM_REQUIRE(!a.order || (8 + 8 * nitems <= (long long)p->order_ws_len && !(reinterpret_cast<uintptr_t>(a.order) & 15)),
+              "ovm_roi_align: order_ws holds %d int32, %lld needed (OVM_ORDER_WS_LEN), 16-byte aligned", p->order_ws_len,
+              8 + 8 * nitems);
   a.xalign_mask = tune.align8 ? ~7 : ~3;
   a.min_slots = tune.min_slots < 1 ? 1 : (tune.min_slots > kMaxSlots ? kMaxSlots : tune.min_slots);
   static bool attr_done = false;
@@ -939,6 +951,10 @@ int roi_align_launch(const ovm_pooler_t* p, const float* boxes, const int32_t* b
   if (a.order) {
     OVM_CUDA(launch_pdl(roi_order_kernel, dim3(1), dim3(1024), 0, stream, a, p->order_ws));
     OVM_LAUNCHED("roi_order_kernel");
+  }
+  if (stage_idx) {
+    int rc = stage_mark(*stage_idx, stream);
+    if (rc != OVM_OK) return rc;
   }
   const dim3 grid((unsigned)nitems);
   if (tune.stages == 3)

@@ -175,7 +175,7 @@ def dtype_code(dt: torch.dtype) -> int:
 
 def order_ws_len(n: int) -> int:
     """OVM_ORDER_WS_LEN(n) of include/ovmono3d_lift.h."""
-    return 6 * max(int(n), 1) + 1200
+    return 24 * max(int(n), 1) + 4808
 
 
 def make_pooler(features: Sequence[torch.Tensor], scales: Sequence[float], output_size: int, sampling_ratio: int,
