@@ -519,6 +519,9 @@ __global__ void __launch_bounds__(kThreads) roi_align_kernel(const __grid_consta
     meta[(is_x ? 0 : 14) + lane] = mn;
     meta[(is_x ? 7 : 21) + lane] = mx;
   }
+  // the tap tables are cleared here, by everybody, while the 14 range threads above are still busy
+  for (int i = tid; i < (kWxFloats + kWyFloats) / 4; i += kThreads)
+    reinterpret_cast<float4*>(Wx)[i] = make_float4(0.f, 0.f, 0.f, 0.f);   // Wy follows Wx
   if (tid == 0) {
     for (int s = 0; s < kMaxSlots; ++s) {
       mbar_init(bars + 8 * s, 1);                    // full: the producer's expect_tx arrive
@@ -658,10 +661,7 @@ __global__ void __launch_bounds__(kThreads) roi_align_kernel(const __grid_consta
     return;
   }
 
-  // ---- pass B (the seven consumer warps): fold the taps into Wx / Wy
-  for (int i = tid; i < best_pad * 8; i += kConsumers) Wx[i] = 0.f;
-  for (int i = tid; i < kWyFloats; i += kConsumers) Wy[i] = 0.f;
-  asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory");
+  // ---- pass B (the seven consumer warps): fold the taps into Wx / Wy (zeroed before the first barrier, above)
   if (lane < kP && warp < 2) {
     const bool is_x = warp == 0;
     const float start = is_x ? g.start_w : g.start_h, bin = is_x ? g.bin_w : g.bin_h;
