@@ -93,7 +93,7 @@ struct RoiTune {
   int split_pct;    // OVM_ROI_SPLIT   cost of a work item, in % of the average box, above which a box is cut along the channels
   int promo;        // OVM_ROI_PROMO   L2 promotion of the tensor maps: 0 none, 1 64 B, 2 128 B, 3 256 B
   int align8;       // OVM_ROI_ALIGN8  footprint starts on a 32-byte sector (8 floats) instead of 16 bytes
-  int stages;       // OVM_ROI_STAGES  2: 48 KB ring (3 CTAs / SM), 3: 72 KB ring (2 CTAs / SM)
+  int stages;       // OVM_ROI_STAGES  2: 48 KB ring (3 CTAs / SM), 3: 36 KB ring and 64 registers (4 CTAs / SM)
   int min_slots;    // OVM_ROI_MINSLOTS  prefer stage geometries (narrower tiles, row groups) that leave this many ring slots
 };
 const RoiTune& roi_tune() {
@@ -453,8 +453,8 @@ __global__ void __launch_bounds__(1024) roi_order_kernel(const RoiArgs a, int* _
 // meta layout (ints): [0..6] x bin lo, [7..13] x bin hi, [14..20] y bin lo, [21..27] y bin hi (lo > hi: no valid sample)
 // kRingFloats: shared-memory ring of footprint stages; kStageFloats: largest stage (rows x Wt x 32 channels) the TMA
 // path accepts.
-template <int kRingFloats, int kStageFloats>
-__global__ void __launch_bounds__(kThreads) roi_align_kernel(const __grid_constant__ RoiMaps maps, const RoiArgs a) {
+template <int kRingFloats, int kStageFloats, int kMinBlocks>
+__global__ void __launch_bounds__(kThreads, kMinBlocks) roi_align_kernel(const __grid_constant__ RoiMaps maps, const RoiArgs a) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;   // swizzled TMA slabs need 1024-byte alignment
@@ -941,11 +941,11 @@ int roi_align_launch(const ovm_pooler_t* p, const float* boxes, const int32_t* b
   a.xalign_mask = tune.align8 ? ~7 : ~3;
   a.min_slots = tune.min_slots < 1 ? 1 : (tune.min_slots > kMaxSlots ? kMaxSlots : tune.min_slots);
   static bool attr_done = false;
-  auto kA = roi_align_kernel<12288, 6144>;   // 48 KB ring, stages up to 24 KB: 69 KB of shared memory, 3 CTAs / SM
-  auto kB = roi_align_kernel<18432, 6144>;   // 72 KB ring: 2 CTAs / SM (measured slower; kept for tools/roi_bench.py)
+  auto kA = roi_align_kernel<12288, 6144, 0>;   // 48 KB ring, stages up to 24 KB: 69 KB of shared memory, 3 CTAs / SM
+  auto kB = roi_align_kernel<9216, 4608, 4>;    // 36 KB ring, stages up to 18 KB, 64 registers: 4 CTAs / SM -- measured 125 vs 104 us (OVM_ROI_STAGES=3, tools/roi_bench.py)
   if (!attr_done) {
     OVM_CUDA(cudaFuncSetAttribute(kA, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)roi_smem_bytes(12288)));
-    OVM_CUDA(cudaFuncSetAttribute(kB, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)roi_smem_bytes(18432)));
+    OVM_CUDA(cudaFuncSetAttribute(kB, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)roi_smem_bytes(9216)));
     attr_done = true;
   }
   if (a.order) {
@@ -958,7 +958,7 @@ int roi_align_launch(const ovm_pooler_t* p, const float* boxes, const int32_t* b
   }
   const dim3 grid((unsigned)nitems);
   if (tune.stages == 3)
-    OVM_CUDA(launch_pdl(kB, grid, dim3(kThreads), roi_smem_bytes(18432), stream, maps, a));
+    OVM_CUDA(launch_pdl(kB, grid, dim3(kThreads), roi_smem_bytes(9216), stream, maps, a));
   else
     OVM_CUDA(launch_pdl(kA, grid, dim3(kThreads), roi_smem_bytes(12288), stream, maps, a));
   OVM_LAUNCHED("roi_align_kernel");
