@@ -394,6 +394,13 @@ def kernel_breakdown(eng, dbs, flush, lift, K: int, peaks) -> Dict[str, object]:
     ops.set_stage_events(None)
     torch.cuda.synchronize()
     ms = {s: float(np.mean([evs[i][j].elapsed_time(evs[i][j + 1]) for i in range(K)])) for j, s in enumerate(STAGES)}
+    # what a stage interval holds besides the kernel: two event records back to back, nothing between
+    pairs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(64)]
+    for a_, b_ in pairs:
+        a_.record()
+        b_.record()
+    torch.cuda.synchronize()
+    event_pair_us = float(np.median([a_.elapsed_time(b_) for a_, b_ in pairs])) * 1e3
 
     n = dbs[0].n
     levels = eng.last_levels[:n].cpu().numpy()      # of the last batch run
@@ -426,7 +433,11 @@ def kernel_breakdown(eng, dbs, flush, lift, K: int, peaks) -> Dict[str, object]:
     roofline = {"kernel": top, "bound": t["bound"], "achieved": t["achieved"], "peak": t["peak"], "unit": t["unit"],
                 "frac": t["frac"], "traffic": traffic, "peak_source": peaks["source"] + " (burst: kernel timed alone "
                 "between its own events)"}
-    return {"roofline": roofline, "kernels": kernels}
+    return {"roofline": roofline, "kernels": kernels,
+            "stage_timing": {"event_pair_overhead_us": event_pair_us, "stage_sum_us": sum(ms.values()) * 1e3,
+                             "note": "kernels[*].ms are event-to-event intervals around each launch inside the step "
+                                     "(launch latency and the event records included, nothing subtracted); an empty "
+                                     "interval measures event_pair_overhead_us"}}
 
 
 def run_e2e(head, names, inputs, device, K: int, W: int, world: int, lift) -> Dict[str, object]:

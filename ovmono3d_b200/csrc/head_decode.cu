@@ -128,6 +128,62 @@ __device__ __forceinline__ void head_rows(const float* const (&w)[kMaxRows], con
   for (int r = 0; r < kMaxRows; ++r) out[r] = warp_sum(acc[r]) + bias[r];
 }
 
+// Sums of 16 per-lane values over the warp in 16 shuffles instead of 80: every step halves the number of values a
+// lane carries (lanes with the step's bit set keep the upper half), so after the 16/8/4/2 steps lane L holds the
+// partial of value (L >> 1) & 15 over its lane pair, and one more exchange completes it.  out[r] is then read from
+// lane 2 r.
+__device__ __forceinline__ void warp_sum16(float (&v)[16], int lane, float (&out)[kMaxRows]) {
+#pragma unroll
+  for (int half = 8, bit = 16; half >= 1; half >>= 1, bit >>= 1) {
+    const bool up = lane & bit;
+#pragma unroll
+    for (int i = 0; i < half; ++i) {
+      const float send = up ? v[i] : v[i + half];
+      const float keep = up ? v[i + half] : v[i];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, bit);
+    }
+  }
+  const float total = v[0] + __shfl_xor_sync(0xffffffffu, v[0], 1);
+#pragma unroll
+  for (int r = 0; r < kMaxRows; ++r) out[r] = __shfl_sync(0xffffffffu, total, 2 * r);
+}
+
+// The common case (class-agnostic heads staged in shared memory as [nrows][K] + nrows biases, one feature vector
+// for all heads, K a multiple of 1024): per 1024 features a lane loads 8 float4 of the feature row (all in flight),
+// then per head row 8 LDS.128 at immediate offsets from one row pointer and 32 FMAs.
+__device__ __forceinline__ void head_rows_staged(const float* staged, const float* f, int nrows, int K, int lane,
+                                                 float (&out)[kMaxRows]) {
+  float acc[16];
+#pragma unroll
+  for (int r = 0; r < 16; ++r) acc[r] = 0.f;
+  const int K4 = K >> 2;
+  const float4* f4 = reinterpret_cast<const float4*>(f) + lane;
+  const float4* w4 = reinterpret_cast<const float4*>(staged) + lane;
+  for (int base = 0; base < K4; base += 256) {
+    float4 fs[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) fs[j] = f4[base + 32 * j];
+#pragma unroll
+    for (int r = 0; r < kMaxRows; ++r) {
+      if (r < nrows) {
+        const float4* wp = w4 + r * K4 + base;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float4 a = wp[32 * j];
+          acc[r] = fmaf(a.x, fs[j].x, acc[r]);
+          acc[r] = fmaf(a.y, fs[j].y, acc[r]);
+          acc[r] = fmaf(a.z, fs[j].z, acc[r]);
+          acc[r] = fmaf(a.w, fs[j].w, acc[r]);
+        }
+      }
+    }
+  }
+  warp_sum16(acc, lane, out);
+  const float* bias = staged + (size_t)nrows * K;
+#pragma unroll
+  for (int r = 0; r < kMaxRows; ++r) out[r] += bias[r < nrows ? r : 0];
+}
+
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + expf(-x)); }
 // torch .clip(min): NaN-transparent, unlike fmaxf
 __device__ __forceinline__ float clip_min(float x, float lo) { return x < lo ? lo : x; }
@@ -153,28 +209,47 @@ __device__ __forceinline__ void matmul3(const float* A, const float* B, float* C
     for (int c = 0; c < 3; ++c) C[3 * r + c] = A[3 * r] * B[c] + A[3 * r + 1] * B[3 + c] + A[3 * r + 2] * B[6 + c];
 }
 
+// What a box needs from the call's inputs (not from the FC stack): loaded ahead of the wait on the FC kernel.
+struct BoxIn {
+  float x1, y1, x2, y2;
+  float k00, k02, k11, k12, ratio, h_cur;
+  float score;
+  int cls;
+};
+__device__ __forceinline__ BoxIn load_box_in(const DecodeArgs& a, int box) {
+  BoxIn b;
+  const int image = a.batch_idx[box];
+  b.cls = (int)a.classes[box];
+  b.x1 = a.boxes[4 * box + 0]; b.y1 = a.boxes[4 * box + 1];
+  b.x2 = a.boxes[4 * box + 2]; b.y2 = a.boxes[4 * box + 3];
+  b.score = a.scores ? a.scores[box] : 0.f;
+  const float* cam = a.cams + 12 * image;
+  b.k00 = cam[0]; b.k02 = cam[2]; b.k11 = cam[4]; b.k12 = cam[5];
+  b.ratio = cam[9]; b.h_cur = cam[10];
+  return b;
+}
+
 // One box, one warp.  STAGED: `staged` is the CTA's shared-memory copy of the head rows in the row order below.
 template <bool STAGED>
-__device__ __forceinline__ void decode_box(const DecodeArgs& a, const int box, const int lane, const float* staged) {
+__device__ __forceinline__ void decode_box(const DecodeArgs& a, const int box, const BoxIn& in, const int lane,
+                                           const float* staged) {
   const ovm_decode_cfg_t& cfg = a.cfg;
   const int K = cfg.fc_dim;
   const int NC = cfg.num_classes;
   const bool per_class = cfg.dims_priors_enabled != 0;
-  const int cls = (int)a.classes[box];
+  const int cls = in.cls;
   const int csel = per_class ? cls : 0;
 
-  const float x1 = a.boxes[4 * box + 0], y1 = a.boxes[4 * box + 1];
-  const float x2 = a.boxes[4 * box + 2], y2 = a.boxes[4 * box + 3];
+  const float x1 = in.x1, y1 = in.y1, x2 = in.x2, y2 = in.y2;
   // roi_heads.py:414-419
   const float src_w = x2 - x1, src_h = y2 - y1;
   const float src_scale = sqrtf(src_h * src_h + src_w * src_w);
   const float ctr_x = x1 + 0.5f * src_w, ctr_y = y1 + 0.5f * src_h;
 
   // roi_heads.py:378-408: K / ratio with [2,2] forced to 1; focal is the un-scaled K[1,1]
-  const float* cam = a.cams + 12 * a.batch_idx[box];
-  const float ratio = cam[9], h_cur = cam[10];
-  const float fx = cam[0] / ratio, fy = cam[4] / ratio, px = cam[2] / ratio, py = cam[5] / ratio;
-  const float focal = cam[4];
+  const float ratio = in.ratio, h_cur = in.h_cur;
+  const float fx = in.k00 / ratio, fy = in.k11 / ratio, px = in.k02 / ratio, py = in.k12 / ratio;
+  const float focal = in.k11;
   const float h_orig = h_cur * ratio;
   const float virtual_to_real = cfg.virtual_depth ? (h_cur * focal) / (cfg.virtual_focal * h_orig) : 1.f;
 
@@ -255,7 +330,9 @@ __device__ __forceinline__ void decode_box(const DecodeArgs& a, const int box, c
     for (int r = 0; r < kMaxRows; ++r) wr[r] = staged + (r < nrows ? r : 0) * K;
   }
   head_stamp(a, 3);
-  if (shared)
+  if (STAGED && shared && vec4 && !(K & 1023))
+    head_rows_staged(staged, frow + cfg.feat_offset[0], nrows, K, lane, hv);
+  else if (shared)
     head_rows<true, STAGED>(wr, fr, bs, nrows, K, lane, vec4, hv);
   else
     head_rows<false, STAGED>(wr, fr, bs, nrows, K, lane, vec4, hv);
@@ -364,7 +441,7 @@ __device__ __forceinline__ void decode_box(const DecodeArgs& a, const int box, c
   const float Y = z * (v - py) / fy;
   const float u_out = u * ratio, v_out = v * ratio;
   const float last = cfg.use_confidence ? expf(-uncert) : v_out;  // cube_3D[:, -1]
-  const float score = a.scores ? sqrtf(a.scores[box] * last) : last;
+  const float score = a.scores ? sqrtf(in.score * last) : last;
 
   if (lane != 0) return;
   // ---- corners (math_util.py:172-193): x <-> L, y <-> H, z <-> W; box order is X,Y,Z,W,H,L
@@ -430,14 +507,30 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) head_decode_kernel(const 
       } else {
         for (int i = lane; i < K; i += 32) dst[i] = __ldg(src + i);
       }
+      if (lane == 0) {   // the row's bias, after the rows
+        float b;
+        if (r < 2) b = a.w.b_deltas[r];
+        else if (r < 5) b = a.w.b_dims[r - 2];
+        else if (r == 5) b = a.w.b_z[0];
+        else if (r == 6 && conf_rows) b = a.w.b_uncert[0];
+        else b = a.w.b_pose[r - 6 - conf_rows];
+        staged[(long long)nrows * K + r] = b;
+      }
     }
-    __syncthreads();
   }
+  // boxes, classes, scores and cameras are inputs of the call (complete before its first kernel, see
+  // roi_order_kernel): the first box of every warp is loaded while the FC kernel is still running
+  int box = blockIdx.x * kWarpsPerBlock + warp;
+  BoxIn in{};
+  if (box < a.n) in = load_box_in(a, box);
+  if (STAGED) __syncthreads();
   head_stamp(a, 1);
   pdl_wait();   // the FC features
   head_stamp(a, 2);
-  for (int box = blockIdx.x * kWarpsPerBlock + warp; box < a.n; box += gridDim.x * kWarpsPerBlock)
-    decode_box<STAGED>(a, box, lane, staged);
+  for (bool first = true; box < a.n; box += gridDim.x * kWarpsPerBlock, first = false) {
+    if (!first) in = load_box_in(a, box);
+    decode_box<STAGED>(a, box, in, lane, staged);
+  }
 }
 
 }  // namespace
@@ -491,7 +584,8 @@ int head_decode_launch(const ovm_decode_cfg_t* cfg, const ovm_head_weights_t* w,
   a.raw = raw;
   a.trace = g_head_trace;
   const int pose_n = cfg->pose_type == OVM_POSE_6D ? 6 : (cfg->pose_type == OVM_POSE_QUATERNION ? 4 : 3);
-  const size_t stage_bytes = (size_t)(6 + (cfg->use_confidence ? 1 : 0) + pose_n) * cfg->fc_dim * sizeof(float);
+  const int stage_rows = 6 + (cfg->use_confidence ? 1 : 0) + pose_n;
+  const size_t stage_bytes = ((size_t)stage_rows * cfg->fc_dim + 16) * sizeof(float);   // rows, then their biases
   const bool staged = !cfg->dims_priors_enabled && cfg->cluster_bins == 1 && stage_bytes <= 160 * 1024 &&
                       cfg->fc_dim % 4 == 0;   // K % 4: rows stay 16-byte aligned in shared memory
   int grid = (n + kWarpsPerBlock - 1) / kWarpsPerBlock;

@@ -42,8 +42,8 @@ namespace {
 constexpr int kP = 7;
 constexpr int kThreads = 256;              // 7 consumer warps + 1 producer warp
 constexpr int kConsumers = kP * 32;
-constexpr int kStageFloatsA = 24 * 8 * 32;  // 24 KB: rows x Wt <= 192 floats per channel (24 rows at Wt = 8, 12 at 16);
-                                           // two stages + tables + output staging = 68 KB per CTA, three CTAs per SM
+// (stage limit of the default kernel: 24 KB = rows x Wt <= 192 floats per channel; 48 KB ring + tables + output
+//  staging = 68 KB per CTA, three CTAs per SM)
 constexpr int kMaxW = 128;                 // footprint columns the Wx table holds
 constexpr int kMaxRows = 64;               // rows one output bin-row may touch
 constexpr int kWxFloats = kMaxW * 8;
@@ -350,15 +350,22 @@ __device__ __forceinline__ void consume_tile(const float* __restrict__ slab0, in
 // cost, largest first, with a counting sort in shared memory.  ws layout: [0] item count, [1..7] unused, then
 // 8 int32 per item: box, first chunk | chunks << 16, x1, y1, x2, y2 (fp32 bits), image, 0.   At most max(3, splits) * n items (see roi_align_launch).
 __global__ void __launch_bounds__(1024) roi_order_kernel(const RoiArgs a, int* __restrict__ ws) {
-  __shared__ int hist[64], offs[64];
+  // one histogram per warp ([bucket][warp], rows padded to 33 words): boxes crowd into a few cost buckets, and a
+  // single shared histogram serialised ~n atomics on the same word, twice
+  __shared__ int hist[64 * 33];
+  __shared__ int warp_tot[32];
   __shared__ float warp_sum[32];
   __shared__ float mean_area;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  // First kernel of the lift: everything the caller's stream did before the call is complete and visible once this
+  // wait returns, and the trigger comes after it -- so no later kernel of the chain can start before that point, and
+  // they may read the call's inputs (boxes, classes, cameras, weights) ahead of their own wait.  It also covers ws,
+  // which the ROIAlign kernel of the previous call may still be reading.
+  pdl_wait();
   pdl_trigger();
-  pdl_wait();   // ws may still be read by the ROIAlign kernel of the previous call
-  if (tid < 64) hist[tid] = 0;
-  auto area_of = [&](int box) {
-    const BoxGeom g = box_geometry(a, box);
+  for (int i = tid; i < 64 * 33; i += 1024) hist[i] = 0;
+  auto area_of = [&](const float4 b) {
+    const BoxGeom g = box_geometry_xy(a, b.x, b.y, b.z, b.w, 0);
     if (g.level < 0) return 1.f;
     const RoiLevel lv = a.lv[g.level];
     // pixel rows x columns of the footprint, clipped to the map
@@ -367,16 +374,26 @@ __global__ void __launch_bounds__(1024) roi_order_kernel(const RoiArgs a, int* _
     const float area = w * h;
     return (area == area) ? area : 1.f;
   };
-  constexpr int kKeep = 4;   // areas of the first 4096 boxes stay in registers between the passes
+  auto load_box = [&](int box) {
+    return make_float4(a.boxes[4 * box + 0], a.boxes[4 * box + 1], a.boxes[4 * box + 2], a.boxes[4 * box + 3]);
+  };
+  constexpr int kKeep = 4;   // the first 4096 boxes (and their areas) stay in registers between the passes
+  float4 bx[kKeep];
+  int img[kKeep];
   float areas[kKeep];
   float sum = 0.f;
 #pragma unroll
-  for (int k = 0; k < kKeep; ++k) {
+  for (int k = 0; k < kKeep; ++k) {   // all loads of the pass in flight together (cold: they come from DRAM)
     const int box = tid + k * 1024;
-    areas[k] = box < a.n ? area_of(box) : 0.f;
+    bx[k] = box < a.n ? load_box(box) : make_float4(0.f, 0.f, 0.f, 0.f);
+    img[k] = box < a.n ? a.batch_idx[box] : 0;
+  }
+#pragma unroll
+  for (int k = 0; k < kKeep; ++k) {
+    areas[k] = tid + k * 1024 < a.n ? area_of(bx[k]) : 0.f;
     sum += areas[k];
   }
-  for (int box = tid + kKeep * 1024; box < a.n; box += 1024) sum += area_of(box);
+  for (int box = tid + kKeep * 1024; box < a.n; box += 1024) sum += area_of(load_box(box));
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
   if (lane == 0) warp_sum[warp] = sum;
@@ -399,55 +416,73 @@ __global__ void __launch_bounds__(1024) roi_order_kernel(const RoiArgs a, int* _
     if (chunks > 8 * cpi) cpi = (chunks + 7) / 8;   // at most 8 pieces per box
     return cpi;
   };
-  auto bucket_of = [&](float area, int cpi) {
+  auto slot_of = [&](float area, int cpi) {
     const float cost = area * (float)cpi / (mean_area * (float)chunks);   // in units of the average box
-    return 63 - (int)fminf(cost * 8.f, 63.f);
+    return (63 - (int)fminf(cost * 8.f, 63.f)) * 33 + warp;
   };
 #pragma unroll
   for (int k = 0; k < kKeep; ++k) {
     if (tid + k * 1024 < a.n) {
       const int cpi = cpi_of(areas[k]);
-      atomicAdd(&hist[bucket_of(areas[k], cpi)], (chunks + cpi - 1) / cpi);
+      atomicAdd(&hist[slot_of(areas[k], cpi)], (chunks + cpi - 1) / cpi);
     }
   }
   for (int box = tid + kKeep * 1024; box < a.n; box += 1024) {
-    const float ar = area_of(box);
+    const float ar = area_of(load_box(box));
     const int cpi = cpi_of(ar);
-    atomicAdd(&hist[bucket_of(ar, cpi)], (chunks + cpi - 1) / cpi);
+    atomicAdd(&hist[slot_of(ar, cpi)], (chunks + cpi - 1) / cpi);
   }
   __syncthreads();
-  if (warp == 0) {   // exclusive scan of the 64 buckets: two per lane
-    const int h0 = hist[2 * lane], h1 = hist[2 * lane + 1];
+  {   // exclusive scan of the 64 x 32 counters in (bucket, warp) order: two per thread
+    const int e0 = 2 * tid, e1 = 2 * tid + 1;
+    const int i0 = (e0 >> 5) * 33 + (e0 & 31), i1 = (e1 >> 5) * 33 + (e1 & 31);
+    const int h0 = hist[i0], h1 = hist[i1];
     int incl = h0 + h1;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
       const int t = __shfl_up_sync(0xffffffffu, incl, o);
       if (lane >= o) incl += t;
     }
-    offs[2 * lane] = incl - h0 - h1;
-    offs[2 * lane + 1] = incl - h1;
-    if (lane == 31) {
-      ws[0] = incl;
-      ws[1] = 0;
+    if (lane == 31) warp_tot[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+      const int own = warp_tot[lane];
+      int t = own;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int u = __shfl_up_sync(0xffffffffu, t, o);
+        if (lane >= o) t += u;
+      }
+      warp_tot[lane] = t - own;
+      if (lane == 31) {
+        ws[0] = t;
+        ws[1] = 0;
+      }
     }
+    __syncthreads();
+    const int before = warp_tot[warp] + incl - h0 - h1;
+    hist[i0] = before;
+    hist[i1] = before + h0;
   }
   __syncthreads();
-  auto emit = [&](int box, float ar) {
+  auto emit = [&](int box, const float4 b, int image, float ar) {
     const int cpi = cpi_of(ar);
     const int pieces = (chunks + cpi - 1) / cpi;
-    const int at = atomicAdd(&offs[bucket_of(ar, cpi)], pieces);
+    const int at = atomicAdd(&hist[slot_of(ar, cpi)], pieces);
     for (int j = 0; j < pieces; ++j) {
       // 32-byte item: box, first chunk | chunks << 16, the box itself and its image -- the pooling CTA needs one load
       int4* it = reinterpret_cast<int4*>(ws + 8 + 8 * (at + j));
-      it[0] = make_int4(box, (j * cpi) | (min(cpi, chunks - j * cpi) << 16), __float_as_int(a.boxes[4 * box + 0]),
-                        __float_as_int(a.boxes[4 * box + 1]));
-      it[1] = make_int4(__float_as_int(a.boxes[4 * box + 2]), __float_as_int(a.boxes[4 * box + 3]), a.batch_idx[box], 0);
+      it[0] = make_int4(box, (j * cpi) | (min(cpi, chunks - j * cpi) << 16), __float_as_int(b.x), __float_as_int(b.y));
+      it[1] = make_int4(__float_as_int(b.z), __float_as_int(b.w), image, 0);
     }
   };
 #pragma unroll
   for (int k = 0; k < kKeep; ++k)
-    if (tid + k * 1024 < a.n) emit(tid + k * 1024, areas[k]);
-  for (int box = tid + kKeep * 1024; box < a.n; box += 1024) emit(box, area_of(box));
+    if (tid + k * 1024 < a.n) emit(tid + k * 1024, bx[k], img[k], areas[k]);
+  for (int box = tid + kKeep * 1024; box < a.n; box += 1024) {
+    const float4 b = load_box(box);
+    emit(box, b, a.batch_idx[box], area_of(b));
+  }
 }
 
 // meta layout (ints): [0..6] x bin lo, [7..13] x bin hi, [14..20] y bin lo, [21..27] y bin hi (lo > hi: no valid sample)
