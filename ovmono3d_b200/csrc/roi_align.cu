@@ -83,6 +83,7 @@ struct RoiArgs {
   int min_slots;                // ring slots a stage geometry should leave (OVM_ROI_MINSLOTS)
   float split_factor;           // roi_order_kernel: an item may cost this many average boxes before the box is cut
   int xalign_mask;              // footprint start column is rounded down to this mask (~3 or ~7)
+  int evict_first;              // feature loads carry the L2 evict_first policy (OVM_ROI_EVICT)
   unsigned long long* trace;    // optional [grid, 16] %globaltimer stamps (ovm_roi_set_trace), else NULL
 };
 
@@ -95,6 +96,8 @@ struct RoiTune {
   int align8;       // OVM_ROI_ALIGN8  footprint starts on a 32-byte sector (8 floats) instead of 16 bytes
   int stages;       // OVM_ROI_STAGES  2: 48 KB ring (3 CTAs / SM), 3: 36 KB ring and 64 registers (4 CTAs / SM)
   int min_slots;    // OVM_ROI_MINSLOTS  prefer stage geometries (narrower tiles, row groups) that leave this many ring slots
+  int evict;        // OVM_ROI_EVICT   1: the pyramid streams through the L2 as evict_first (to keep the pooled output there
+                    //                 for fc1) -- measured 96 -> 126 us: boxes do reuse each other's footprint through the L2
 };
 const RoiTune& roi_tune() {
   static RoiTune t = [] {
@@ -105,6 +108,7 @@ const RoiTune& roi_tune() {
     r.align8 = env("OVM_ROI_ALIGN8", 0);
     r.stages = env("OVM_ROI_STAGES", 2);
     r.min_slots = env("OVM_ROI_MINSLOTS", 1);
+    r.evict = env("OVM_ROI_EVICT", 0);
     return r;
   }();
   return t;
@@ -162,6 +166,14 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map
   asm volatile(
       "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(dst),
       "l"(map), "r"(bar), "r"(x), "r"(y), "r"(c)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_3d_hint(uint32_t dst, const CUtensorMap* map, uint32_t bar, int x, int y, int c,
+                                                 uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, %4, %5}], "
+      "[%2], %6;" ::"r"(dst),
+      "l"(map), "r"(bar), "r"(x), "r"(y), "r"(c), "l"(policy)
       : "memory");
 }
 
@@ -538,21 +550,29 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) roi_align_kernel(const _
   const RoiLevel lv = a.lv[g.level];
   const int H = lv.H, W = lv.W;
 
-  // ---- pass A: pixel range of every bin (threads 0..6: x bins, 32..38: y bins)
-  if (lane < kP && warp < 2) {
-    const bool is_x = warp == 0;
+  // ---- pass A: pixel range of every bin.  The sample coordinate is monotone in the sample index (every rounding
+  // step of make_tap is), so a bin's range is [lo of its first valid sample, hi of its last valid one]: warps 0/1
+  // take the first sample of the x / y bins, warps 2/3 the last; only a bin whose end sample is off the map scans.
+  if (lane < kP && warp < 4) {
+    const bool is_x = !(warp & 1), from_end = warp >= 2;
     const float start = is_x ? g.start_w : g.start_h, bin = is_x ? g.bin_w : g.bin_h;
     const int grid = is_x ? g.gw : g.gh, size = is_x ? W : H;
-    int mn = INT_MAX, mx = -1;
-    for (int i = 0; i < grid; ++i) {
-      Tap t = make_tap(start, bin, grid, lane, i, size);
-      if (t.valid) {
-        mn = min(mn, t.lo);
-        mx = max(mx, t.hi);
+    int v = from_end ? -1 : INT_MAX;
+    if (bin >= 0.f) {
+      for (int k = 0; k < grid; ++k) {
+        const Tap t = make_tap(start, bin, grid, lane, from_end ? grid - 1 - k : k, size);
+        if (t.valid) {
+          v = from_end ? t.hi : t.lo;
+          break;
+        }
+      }
+    } else {   // inverted box with a fixed sampling ratio: coordinates decrease, every sample is looked at
+      for (int i = 0; i < grid; ++i) {
+        const Tap t = make_tap(start, bin, grid, lane, i, size);
+        if (t.valid) v = from_end ? max(v, t.hi) : min(v, t.lo);
       }
     }
-    meta[(is_x ? 0 : 14) + lane] = mn;
-    meta[(is_x ? 7 : 21) + lane] = mx;
+    meta[(is_x ? 0 : 14) + (from_end ? 7 : 0) + lane] = v;
   }
   // the tap tables are cleared here, by everybody, while the 14 range threads above are still busy
   for (int i = tid; i < (kWxFloats + kWyFloats) / 4; i += kThreads)
@@ -624,7 +644,7 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) roi_align_kernel(const _
       const int wt = 8 << k;
       const int pad = (fw + wt - 1) / wt * wt;
       const int stage = rm * wt * 32;
-      if (stage <= kStageFloats && kRingFloats / stage >= need_slots && pad < bp) {
+      if (stage <= kStageFloats && stage * need_slots <= kRingFloats && pad < bp) {
         bp = pad;
         ws = k;
       }
@@ -663,6 +683,8 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) roi_align_kernel(const _
       int s = 0;
       uint32_t phase = 0;
       long long waited = 0;
+      uint64_t policy = 0;
+      if (a.evict_first) asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
       for (int chunk = chunk_begin; chunk < chunk_end; ++chunk) {
         const int cc = g.b * a.C + chunk * 32;
         for (int grp = 0; grp < ngroups; ++grp) {
@@ -680,7 +702,10 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) roi_align_kernel(const _
 #pragma unroll
             for (int k = kHeights - 1; k >= 0; --k) {
               while (rows - r >= (1 << k)) {
-                tma_load_3d(dst + (uint32_t)(r * slab_floats) * 4u, map + k, full, xc, cc, gy + r);
+                if (a.evict_first)
+                  tma_load_3d_hint(dst + (uint32_t)(r * slab_floats) * 4u, map + k, full, xc, cc, gy + r, policy);
+                else
+                  tma_load_3d(dst + (uint32_t)(r * slab_floats) * 4u, map + k, full, xc, cc, gy + r);
                 r += 1 << k;
               }
             }
@@ -974,7 +999,7 @@ int roi_align_launch(const ovm_pooler_t* p, const float* boxes, const int32_t* b
               "ovm_roi_align: order_ws holds %d int32, %lld needed (OVM_ORDER_WS_LEN), 16-byte aligned", p->order_ws_len,
               8 + 8 * nitems);
   a.xalign_mask = tune.align8 ? ~7 : ~3;
-  a.min_slots = tune.min_slots < 1 ? 1 : (tune.min_slots > kMaxSlots ? kMaxSlots : tune.min_slots);
+  a.evict_first = tune.evict;
   static bool attr_done = false;
   auto kA = roi_align_kernel<12288, 6144, 0>;   // 48 KB ring, stages up to 24 KB: 69 KB of shared memory, 3 CTAs / SM
   auto kB = roi_align_kernel<9216, 4608, 4>;    // 36 KB ring, stages up to 18 KB, 64 registers: 4 CTAs / SM -- measured 125 vs 104 us (OVM_ROI_STAGES=3, tools/roi_bench.py)
