@@ -582,6 +582,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
   const bool leader = rank == 0;
+  if (threadIdx.x == 0) trace_stamp(g, 0);
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
@@ -608,7 +609,9 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
   pdl_trigger();
+  if (threadIdx.x == 0) trace_stamp(g, 1);
   pdl_wait();
+  if (threadIdx.x == 0) trace_stamp(g, 3);   // the kernel before has completed
 
   if (warp == 0) {
     if (lane == 0) {
@@ -632,6 +635,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           }
         }
       }
+      trace_stamp(g, 2);   // last TMA issued
     }
   } else if (warp == 1) {
     if (lane == 0 && leader) {
@@ -665,6 +669,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1;
       }
+      trace_stamp(g, 4);   // last MMA issued
     }
   } else {
     // ===== epilogue warps (both CTAs): this CTA's 128 accumulator rows; same transpose as gemm_bf16_kernel
@@ -683,6 +688,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     while (it.next(s)) {
       mbar_wait(tfull_bar + 8 * acc, acc_phase);
       tcgen05_fence_after();
+      if (threadIdx.x == 64) trace_stamp(g, 5);   // (last) accumulator ready
       const int m_tile = s.m_pair * 2 + (int)rank;
       const int row0 = m_tile * BM + quad * 32;
       const bool rows_full = row0 + 32 <= g.M;
@@ -725,6 +731,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       if (lane == 0) mbar_arrive_remote(tempty_leader + 8 * acc);
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1;
+      if (threadIdx.x == 64) trace_stamp(g, 7);   // (last) partial tile added to the accumulator
       if (g.tile_counters && m_tile * BM < g.M) {   // CTA-uniform; the odd last row tile of a pair may not exist
         // ---- fused finish of this CTA's 128-row tile (see gemm_bf16_kernel)
         __threadfence();
@@ -781,6 +788,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
   }
 
+  if (threadIdx.x == 64) trace_stamp(g, 6);   // epilogue (and finish) done
   tcgen05_fence_before();
   cluster_sync_all();        // the leader's MMAs write the peer's TMEM: neither CTA may release before both are done
   if (warp == 2) {

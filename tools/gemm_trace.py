@@ -45,5 +45,45 @@ def main():
                 print("  %-12s %8.2f %8.2f %8.2f" % (nm, col.min(), np.median(col), col.max()))
 
 
+def pipeline():
+    """fc1 / fc2 as they run inside the lift at C2 (after ROIAlign, 256 MiB L2 flush before the step): the pair kernel's
+    stamps are entry, set-up done, last TMA, wait on the previous kernel over, last MMA issued, (last) accumulator ready,
+    epilogue + finish done, (last) partial tile added."""
+    import bench
+    lib = ops.load_library()
+    dev = torch.device("cuda:0")
+    head, _ = bench.build_head(dev)
+    db = bench.DeviceBatch(bench.make_batch(1235), dev)
+    eng = head._get_engine()
+    eng.prepare(dev, head.priors_dims_per_cat, head.priors_z_scales, getattr(head, "priors_z_stats", None))
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    trace = torch.zeros(4096 * 16, dtype=torch.int64, device=dev)
+    for it in range(4):
+        flush.zero_()
+        if it == 3:
+            lib.ovm_gemm_set_trace(trace.data_ptr())
+        eng.forward(db.features, db.boxes, db.classes, db.scores, db.batch_idx, db.cams)
+    lib.ovm_gemm_set_trace(None)
+    torch.cuda.synchronize()
+    t = trace.cpu().numpy().reshape(-1, 16)[104:148]    # fc2 (104 CTAs) overwrote rows 0..103: fc1's CTAs 104..147
+    t = t[t[:, 0] > 0].astype(np.float64)
+    names = ["entry", "setup", "last_tma", "prev_done", "last_mma", "acc_ready", "epi_done", "partial_added"]
+    t0 = t[:, 0].min()
+    print("fc1 in the lift (cold L2), CTAs 104..147, us since their first entry: min / median / max")
+    for k, nm in enumerate(names):
+        col = t[:, k][t[:, k] > 0]
+        if len(col):
+            col = (col - t0) / 1e3
+            print("  %-14s %8.2f %8.2f %8.2f" % (nm, col.min(), np.median(col), col.max()))
+    d = lambda a, b: (t[:, a] - t[:, b]) / 1e3
+    for nm, v in (("main loop (prev_done -> last_mma)", d(4, 3)[t[:, 4] > 0]), ("drain (last_mma -> acc_ready)", d(5, 4)[t[:, 4] > 0]),
+                  ("partial add (acc_ready -> added)", d(7, 5)), ("finish (added -> epi_done)", d(6, 7))):
+        print("  %-36s min %6.2f  median %6.2f  p90 %6.2f  max %6.2f   sorted: %s" % (
+            nm, v.min(), np.median(v), np.percentile(v, 90), v.max(), " ".join("%.1f" % x for x in np.sort(v)[::4])))
+
+
 if __name__ == "__main__":
-    main()
+    if len(sys.argv) > 1 and sys.argv[1] == "pipeline":
+        pipeline()
+    else:
+        main()
