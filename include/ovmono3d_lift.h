@@ -17,6 +17,15 @@
  *                    with math_util.py:116-219,581-592,651-679,969-978.
  *   ovm_lift_forward the inference slice of ROIHeads3D._forward_cube, roi_heads.py:329-848:
  *                    the three kernels above on one stream.
+ *   ovm_nms          torchvision.ops.nms / batched_nms as the reference calls them:
+ *                    roi_heads_gdino.py:6,272 (class-agnostic, 0.5) and fast_rcnn.py:105 (per class).
+ *   ovm_gdino_post   GroundingDINO post-processing, the step right before the lift:
+ *                    get_grounding_output roi_heads_gdino.py:186-202 (sigmoid, phrase logits :296-317, box
+ *                    threshold, per-query max / argmax) + grounding_dino_inference_detector :269-275
+ *                    (cxcywh -> xyxy in pixels :283-287, NMS 0.5, gather in keep order).
+ *   ovm_box_inference the inference tail of the 2-D box head: FastRCNNOutputLayers
+ *                    predict_probs / predict_boxes (d2 Box2BoxTransform.apply_deltas) and
+ *                    fast_rcnn_inference_single_image, fast_rcnn.py:57-116.
  */
 #ifndef OVMONO3D_LIFT_H_
 #define OVMONO3D_LIFT_H_
@@ -27,7 +36,7 @@
 extern "C" {
 #endif
 
-#define OVM_ABI_VERSION 4
+#define OVM_ABI_VERSION 5
 #define OVM_MAX_LEVELS 8
 #define OVM_RECORD_WIDTH 48   /* floats per detection record, see ovm_head_decode */
 
@@ -194,6 +203,37 @@ int ovm_lift_forward(const ovm_pooler_t* pooler, const ovm_fc_stack_t* fc, const
  * cudaEvent_t handles owned by the caller; count = 0 (or events = NULL) switches the hook off.  The hook is
  * per host thread and adds no synchronisation.                                                           */
 int ovm_set_stage_events(void* const* events, int32_t count);
+
+/* ---- detections either side of the lift ------------------------------------------------------------ */
+
+#define OVM_NMS_MAX_SEGMENT 4096  /* boxes of one segment that one CTA sorts and suppresses in shared memory */
+enum { OVM_NMS_AGNOSTIC = 0, OVM_NMS_COORD_TRICK = 1, OVM_NMS_PER_CLASS = 2 };
+
+/* Greedy NMS, one CTA per segment (image); no host round trip (torchvision's CUDA nms copies its mask to the host).
+ * boxes [n,4] xyxy fp32, scores [n] fp32, classes [n] int64 (NULL with OVM_NMS_AGNOSTIC), seg_offsets [S+1] int32
+ * (device): segment s = rows [seg_offsets[s], seg_offsets[s+1]), each at most max_segment_len (<= OVM_NMS_MAX_SEGMENT)
+ * long.  Arithmetic is torchvision's CPU kernel (fp32 areas, inter / (a_i + a_j - inter) > threshold compared in
+ * double, stable descending score order), so the keep list is bit-identical.
+ * mode OVM_NMS_COORD_TRICK: torchvision batched_nms' `boxes + class * (max_coordinate + 1)` per segment;
+ * mode OVM_NMS_PER_CLASS: its `_batched_nms_vanilla` (boxes of different classes never suppress each other).
+ * keep [n] int32: keep[seg_offsets[s] + k], k < keep_count[s] = row (relative to the segment start) of the k-th
+ * kept box in decreasing score order; keep_count [S] int32 (-1 for a segment longer than max_segment_len). */
+int ovm_nms(const float* boxes, const float* scores, const int64_t* classes, const int32_t* seg_offsets,
+            int32_t num_segments, int32_t max_segment_len, double iou_threshold, int32_t mode, int32_t* keep,
+            int32_t* keep_count, void* stream);
+
+/* GroundingDINO outputs -> prompt boxes of the lift, one CTA per image, one launch.
+ * logits [B, nq, T] fp32 raw `pred_logits` (sigmoid is applied here), boxes_cxcywh [B, nq, 4] fp32 `pred_boxes`
+ * (normalised), phrase_ranges [P, 2] int32 (device): token columns [begin, end) of phrase p in the tokenised caption
+ * (roi_heads_gdino.py:300-311).  A query survives when max_p sum_t sigmoid(logit[q, t in phrase p]) > box_threshold;
+ * its score / class are that max / argmax (first on ties); boxes become xyxy pixels with image_width / image_height
+ * (the padded network input, :269); class-agnostic NMS at nms_threshold; survivors are written in decreasing score
+ * order: out_boxes [B, nq, 4], out_scores [B, nq], out_classes [B, nq] int64, out_query [B, nq] int32 (source query,
+ * optional), out_count [B] int32.  Rows past out_count[b] are left untouched.  nq <= OVM_NMS_MAX_SEGMENT, T <= 512. */
+int ovm_gdino_post(const float* logits, const float* boxes_cxcywh, const int32_t* phrase_ranges, int32_t batch,
+                   int32_t num_queries, int32_t num_tokens, int32_t num_phrases, int32_t image_height,
+                   int32_t image_width, float box_threshold, double nms_threshold, float* out_boxes,
+                   float* out_scores, int64_t* out_classes, int32_t* out_query, int32_t* out_count, void* stream);
 
 int ovm_abi_version(void);
 /* sizeof() of the ABI structs as this library was compiled, for binding self-checks:

@@ -112,4 +112,13 @@ int head_decode_launch(const ovm_decode_cfg_t* cfg, const ovm_head_weights_t* w,
                        const int32_t* batch_idx, const float* cams, int32_t num_images, int32_t n,
                        float* records, float* raw, cudaStream_t stream);
 
+// detect_post.cu
+int nms_launch(const float* boxes, const float* scores, const int64_t* classes, const int32_t* seg_offsets,
+               int32_t num_segments, int32_t max_segment_len, double iou_threshold, int32_t mode, int32_t* keep,
+               int32_t* keep_count, cudaStream_t stream);
+int gdino_post_launch(const float* logits, const float* boxes_cxcywh, const int32_t* phrase_ranges, int32_t batch,
+                      int32_t nq, int32_t T, int32_t P, int32_t image_height, int32_t image_width,
+                      float box_threshold, double nms_threshold, float* out_boxes, float* out_scores,
+                      int64_t* out_classes, int32_t* out_query, int32_t* out_count, cudaStream_t stream);
+
 }  // namespace ovm

@@ -1,0 +1,374 @@
+// Detection post-processing either side of the lift: segmented NMS and the GroundingDINO
+// post-processing that produces the lift's prompt boxes.
+//
+// Reference: torchvision.ops.nms as called at cubercnn/modeling/roi_heads/roi_heads_gdino.py:272 and (through d2's
+// batched_nms) cubercnn/modeling/roi_heads/fast_rcnn.py:105; get_grounding_output roi_heads_gdino.py:174-202 and
+// grounding_dino_inference_detector :262-281.
+//
+// One CTA owns one image from start to finish: score keys are sorted in shared memory (bitonic, 64-bit keys =
+// descending score | ascending row, which is the stable descending order torch's sort produces), the sorted boxes
+// stay in shared memory, and the greedy pass walks them with one barrier per *kept* box.  Nothing goes back to the
+// host in between (torchvision's CUDA nms copies its n x n/64 mask to the host and scans it there).
+#include "common.cuh"
+
+namespace ovm {
+namespace {
+
+constexpr int kPostThreads = 1024;
+constexpr int kPostWarps = kPostThreads / 32;
+constexpr uint64_t kPadKey = ~0ull;
+
+// fp32 -> 32-bit key whose unsigned ascending order is the descending order of the floats (-0 == +0)
+__device__ __forceinline__ uint32_t score_key_desc(float s) {
+  if (s == 0.0f) s = 0.0f;
+  uint32_t u = __float_as_uint(s);
+  u ^= (u >> 31) ? 0xFFFFFFFFu : 0x80000000u;
+  return ~u;
+}
+
+__device__ __forceinline__ int next_pow2(int n) {
+  int p = 32;
+  while (p < n) p <<= 1;
+  return p;
+}
+
+// ascending bitonic sort of npad (power of two) 64-bit keys in shared memory; all threads of the CTA take part
+__device__ void block_sort(uint64_t* keys, int npad) {
+  __syncthreads();
+  for (int k = 2; k <= npad; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int t = threadIdx.x; t < (npad >> 1); t += blockDim.x) {
+        const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+        const int l = i | j;
+        const uint64_t a = keys[i], b = keys[l];
+        const bool up = (i & k) == 0;
+        if ((a > b) == up) {
+          keys[i] = b;
+          keys[l] = a;
+        }
+      }
+      __syncthreads();
+    }
+  }
+}
+
+// torchvision's CPU kernel (ops/cpu/nms_kernel.cpp): areas and intersections in fp32, no contraction
+__device__ __forceinline__ float box_area(const float4& b) {
+  return __fmul_rn(__fsub_rn(b.z, b.x), __fsub_rn(b.w, b.y));
+}
+
+__device__ __forceinline__ bool suppresses(const float4& a, float area_a, const float4& b, double thr) {
+  const float xx1 = fmaxf(a.x, b.x), yy1 = fmaxf(a.y, b.y);
+  const float xx2 = fminf(a.z, b.z), yy2 = fminf(a.w, b.w);
+  const float w = fmaxf(0.0f, __fsub_rn(xx2, xx1)), h = fmaxf(0.0f, __fsub_rn(yy2, yy1));
+  const float inter = __fmul_rn(w, h);
+  const float ovr = __fdiv_rn(inter, __fsub_rn(__fadd_rn(area_a, box_area(b)), inter));
+  return (double)ovr > thr;
+}
+
+// Greedy suppression over boxes already in decreasing score order.  cls == nullptr: every pair competes.
+// alive[i] is 1 on entry for i < n.  One barrier per kept box; skipped boxes cost one shared-memory read.
+__device__ void block_greedy(const float4* sb, const int32_t* cls, volatile uint8_t* alive, int n, double thr) {
+  __syncthreads();
+  for (int i = 0; i < n; ++i) {
+    if (!alive[i]) continue;
+    const float4 bi = sb[i];
+    const float ai = box_area(bi);
+    const int ci = cls ? cls[i] : 0;
+    int j = threadIdx.x;
+    if (j <= i) j += ((i - j) / kPostThreads + 1) * kPostThreads;
+    for (; j < n; j += kPostThreads) {
+      if (!alive[j]) continue;
+      if (cls && cls[j] != ci) continue;
+      if (suppresses(bi, ai, sb[j], thr)) alive[j] = 0;
+    }
+    __syncthreads();
+  }
+  __syncthreads();
+}
+
+// Ordered compaction of the surviving sorted positions: calls emit(rank, position) for each, returns the count.
+template <typename Emit>
+__device__ int block_compact(const volatile uint8_t* alive, int n, int* warp_tot /* [kPostWarps + 1] shared */,
+                             Emit emit) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int base = 0;
+  for (int start = 0; start < n; start += kPostThreads) {
+    const int pos = start + threadIdx.x;
+    const bool f = pos < n && alive[pos];
+    const uint32_t m = __ballot_sync(0xFFFFFFFFu, f);
+    if (lane == 0) warp_tot[warp] = __popc(m);
+    __syncthreads();
+    if (warp == 0) {
+      int v = warp_tot[lane];
+      int incl = v;
+      for (int o = 1; o < 32; o <<= 1) {
+        const int y = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+        if (lane >= o) incl += y;
+      }
+      warp_tot[lane] = incl - v;
+      if (lane == 31) warp_tot[kPostWarps] = incl;
+    }
+    __syncthreads();
+    if (f) emit(base + warp_tot[warp] + __popc(m & ((1u << lane) - 1u)), pos);
+    base += warp_tot[kPostWarps];
+    __syncthreads();
+  }
+  return base;
+}
+
+struct PostSmem {
+  uint64_t* keys;    // [npad]
+  float4* sb;        // [npad] sorted boxes
+  int32_t* scls;     // [npad] class of the sorted box
+  uint8_t* alive;    // [npad]
+  int* warp_tot;     // [kPostWarps + 1]
+  float* red;        // [kPostWarps]
+  unsigned char* tail;
+};
+
+__device__ __forceinline__ PostSmem carve(unsigned char* base, int npad) {
+  PostSmem s;
+  s.sb = reinterpret_cast<float4*>(base);
+  s.keys = reinterpret_cast<uint64_t*>(base + (size_t)npad * 16);
+  s.scls = reinterpret_cast<int32_t*>(base + (size_t)npad * 24);
+  s.warp_tot = reinterpret_cast<int*>(base + (size_t)npad * 28);
+  s.red = reinterpret_cast<float*>(base + (size_t)npad * 28 + 256);
+  s.alive = reinterpret_cast<uint8_t*>(base + (size_t)npad * 28 + 512);
+  s.tail = base + (size_t)npad * 29 + 512;
+  return s;
+}
+size_t post_smem_bytes(int npad) { return (size_t)npad * 29 + 512; }
+
+// ---------------------------------------------------------------------------------------------------------------
+// ovm_nms
+
+__global__ void __launch_bounds__(kPostThreads, 1)
+nms_kernel(const float* __restrict__ boxes, const float* __restrict__ scores, const int64_t* __restrict__ classes,
+           const int32_t* __restrict__ seg_offsets, int max_len, double thr, int mode, int32_t* __restrict__ keep,
+           int32_t* __restrict__ keep_count) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int seg = blockIdx.x;
+  const int r0 = seg_offsets[seg];
+  const int n = seg_offsets[seg + 1] - r0;
+  if (n <= 0 || n > max_len) {
+    if (threadIdx.x == 0) keep_count[seg] = n <= 0 ? 0 : -1;
+    return;
+  }
+  const int npad = next_pow2(n);
+  PostSmem s = carve(smem_raw, npad);
+  const float4* gb = reinterpret_cast<const float4*>(boxes) + r0;
+
+  // torchvision batched_nms' coordinate trick: offset = class * (max coordinate of the segment + 1)
+  float off_unit = 0.0f;
+  if (mode == OVM_NMS_COORD_TRICK) {
+    float m = -INFINITY;
+    for (int i = threadIdx.x; i < n; i += kPostThreads) {
+      const float4 b = gb[i];
+      m = fmaxf(fmaxf(fmaxf(m, b.x), b.y), fmaxf(b.z, b.w));
+    }
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xFFFFFFFFu, m, o));
+    if ((threadIdx.x & 31) == 0) s.red[threadIdx.x >> 5] = m;
+    __syncthreads();
+    m = s.red[0];
+    for (int w = 1; w < kPostWarps; ++w) m = fmaxf(m, s.red[w]);
+    off_unit = __fadd_rn(m, 1.0f);
+  }
+  for (int i = threadIdx.x; i < npad; i += kPostThreads) {
+    s.keys[i] = i < n ? ((uint64_t)score_key_desc(scores[r0 + i]) << 32) | (uint32_t)i : kPadKey;
+    s.alive[i] = i < n;
+  }
+  block_sort(s.keys, npad);
+  for (int p = threadIdx.x; p < n; p += kPostThreads) {
+    const int i = (int)(uint32_t)s.keys[p];
+    float4 b = gb[i];
+    int c = 0;
+    if (mode != OVM_NMS_AGNOSTIC) {
+      const int64_t cl = classes[r0 + i];
+      c = (int)cl;
+      if (mode == OVM_NMS_COORD_TRICK) {
+        const float o = __fmul_rn((float)cl, off_unit);
+        b.x = __fadd_rn(b.x, o);
+        b.y = __fadd_rn(b.y, o);
+        b.z = __fadd_rn(b.z, o);
+        b.w = __fadd_rn(b.w, o);
+      }
+    }
+    s.sb[p] = b;
+    s.scls[p] = c;
+  }
+  block_greedy(s.sb, mode == OVM_NMS_PER_CLASS ? s.scls : nullptr, s.alive, n, thr);
+  int32_t* kout = keep + r0;
+  const uint64_t* keys = s.keys;
+  const int cnt = block_compact(s.alive, n, s.warp_tot, [&](int rank, int pos) { kout[rank] = (int32_t)(uint32_t)keys[pos]; });
+  if (threadIdx.x == 0) keep_count[seg] = cnt;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// ovm_gdino_post
+
+__global__ void __launch_bounds__(kPostThreads, 1)
+gdino_post_kernel(const float* __restrict__ logits, const float* __restrict__ boxes_cxcywh,
+                  const int32_t* __restrict__ phrase_ranges, int nq, int T, int P, float img_w, float img_h,
+                  float box_thr, double nms_thr, float* __restrict__ out_boxes, float* __restrict__ out_scores,
+                  int64_t* __restrict__ out_classes, int32_t* __restrict__ out_query,
+                  int32_t* __restrict__ out_count) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int b = blockIdx.x;
+  const int npad = next_pow2(nq);
+  PostSmem s = carve(smem_raw, npad);
+  float* q_score = reinterpret_cast<float*>(s.tail);                 // [npad]
+  int32_t* q_cls = reinterpret_cast<int32_t*>(s.tail + (size_t)npad * 4);   // [npad]
+  float* rows = reinterpret_cast<float*>(s.tail + (size_t)npad * 8);        // [kPostWarps][T]
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const float* lg = logits + (size_t)b * nq * T;
+
+  // 1. per query: sigmoid of its token logits, phrase sums, max / first argmax (roi_heads_gdino.py:186-202, 296-317)
+  float* row = rows + (size_t)warp * T;
+  for (int q = warp; q < nq; q += kPostWarps) {
+    const float* src = lg + (size_t)q * T;
+    for (int t = lane; t < T; t += 32) row[t] = __fdiv_rn(1.0f, __fadd_rn(1.0f, expf(-src[t])));
+    __syncwarp();
+    float best = -INFINITY;
+    int best_p = 0x7FFFFFFF;
+    for (int p = lane; p < P; p += 32) {
+      const int t0 = phrase_ranges[2 * p], t1 = phrase_ranges[2 * p + 1];
+      float sum = 0.0f;
+      for (int t = t0; t < t1; ++t) sum = __fadd_rn(sum, row[t]);
+      if (sum > best || (sum != sum && best == best)) {   // NaN wins like torch.max, first occurrence kept
+        best = sum;
+        best_p = p;
+      }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+      const float ob = __shfl_xor_sync(0xFFFFFFFFu, best, o);
+      const int op = __shfl_xor_sync(0xFFFFFFFFu, best_p, o);
+      const bool o_nan = ob != ob, m_nan = best != best;
+      const bool take = (o_nan && (!m_nan || op < best_p)) || (!m_nan && !o_nan && (ob > best || (ob == best && op < best_p)));
+      if (take) {
+        best = ob;
+        best_p = op;
+      }
+    }
+    if (lane == 0) {
+      q_score[q] = best;
+      q_cls[q] = best_p;
+    }
+    __syncwarp();
+  }
+  __syncthreads();
+
+  // 2. candidates = queries above the box threshold, in stable decreasing score order
+  for (int i = threadIdx.x; i < npad; i += kPostThreads) {
+    const bool ok = i < nq && q_score[i] > box_thr;
+    s.keys[i] = ok ? ((uint64_t)score_key_desc(q_score[i]) << 32) | (uint32_t)i : kPadKey;
+  }
+  block_sort(s.keys, npad);
+  // number of candidates = first pad key (keys are sorted)
+  int* n_cand = s.warp_tot + kPostWarps;
+  if (threadIdx.x == 0) *n_cand = npad;
+  __syncthreads();
+  for (int i = threadIdx.x; i < npad; i += kPostThreads)
+    if (s.keys[i] == kPadKey && (i == 0 || s.keys[i - 1] != kPadKey)) *n_cand = i;
+  __syncthreads();
+  const int n = *n_cand;
+  __syncthreads();
+
+  // 3. boxes: cxcywh (normalised) * (w, h, w, h) -> xyxy (roi_heads_gdino.py:270-271, 283-287)
+  const float4* gb = reinterpret_cast<const float4*>(boxes_cxcywh) + (size_t)b * nq;
+  for (int p = threadIdx.x; p < npad; p += kPostThreads) {
+    s.alive[p] = p < n;
+    if (p < n) {
+      const float4 c = gb[(uint32_t)s.keys[p]];
+      const float cx = __fmul_rn(c.x, img_w), cy = __fmul_rn(c.y, img_h);
+      const float hw = __fmul_rn(0.5f, __fmul_rn(c.z, img_w)), hh = __fmul_rn(0.5f, __fmul_rn(c.w, img_h));
+      s.sb[p] = make_float4(__fsub_rn(cx, hw), __fsub_rn(cy, hh), __fadd_rn(cx, hw), __fadd_rn(cy, hh));
+    }
+  }
+  block_greedy(s.sb, nullptr, s.alive, n, nms_thr);
+
+  // 4. survivors in keep order
+  float4* ob = reinterpret_cast<float4*>(out_boxes) + (size_t)b * nq;
+  float* os = out_scores + (size_t)b * nq;
+  int64_t* oc = out_classes + (size_t)b * nq;
+  int32_t* oq = out_query ? out_query + (size_t)b * nq : nullptr;
+  const uint64_t* keys = s.keys;
+  const float4* sb = s.sb;
+  const int cnt = block_compact(s.alive, n, s.warp_tot, [&](int rank, int pos) {
+    const int q = (int)(uint32_t)keys[pos];
+    ob[rank] = sb[pos];
+    os[rank] = q_score[q];
+    oc[rank] = (int64_t)q_cls[q];
+    if (oq) oq[rank] = q;
+  });
+  if (threadIdx.x == 0) out_count[b] = cnt;
+}
+
+int host_next_pow2(int n) {
+  int p = 32;
+  while (p < n) p <<= 1;
+  return p;
+}
+
+}  // namespace
+
+int nms_launch(const float* boxes, const float* scores, const int64_t* classes, const int32_t* seg_offsets,
+               int32_t num_segments, int32_t max_segment_len, double iou_threshold, int32_t mode, int32_t* keep,
+               int32_t* keep_count, cudaStream_t stream) {
+  OVM_REQUIRE(num_segments >= 0 && max_segment_len >= 0, "ovm_nms: negative size");
+  if (num_segments == 0) return OVM_OK;
+  OVM_REQUIRE(boxes && scores && seg_offsets && keep && keep_count, "ovm_nms: NULL pointer");
+  OVM_REQUIRE(mode == OVM_NMS_AGNOSTIC || mode == OVM_NMS_COORD_TRICK || mode == OVM_NMS_PER_CLASS,
+              "ovm_nms: unknown mode %d", mode);
+  OVM_REQUIRE(mode == OVM_NMS_AGNOSTIC || classes, "ovm_nms: this mode needs classes");
+  OVM_REQUIRE(max_segment_len <= OVM_NMS_MAX_SEGMENT, "ovm_nms: segments of %d boxes exceed the %d one CTA holds",
+              max_segment_len, OVM_NMS_MAX_SEGMENT);
+  OVM_REQUIRE((reinterpret_cast<uintptr_t>(boxes) & 15) == 0, "ovm_nms: boxes must be 16-byte aligned");
+  const size_t smem = post_smem_bytes(host_next_pow2(max_segment_len));
+  static size_t configured = 0;
+  if (smem > configured) {
+    OVM_CUDA(cudaFuncSetAttribute(nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = smem;
+  }
+  nms_kernel<<<num_segments, kPostThreads, smem, stream>>>(boxes, scores, classes, seg_offsets, max_segment_len,
+                                                           iou_threshold, mode, keep, keep_count);
+  OVM_LAUNCHED("nms_kernel");
+  return OVM_OK;
+}
+
+int gdino_post_launch(const float* logits, const float* boxes_cxcywh, const int32_t* phrase_ranges, int32_t batch,
+                      int32_t nq, int32_t T, int32_t P, int32_t image_height, int32_t image_width,
+                      float box_threshold, double nms_threshold, float* out_boxes, float* out_scores,
+                      int64_t* out_classes, int32_t* out_query, int32_t* out_count, cudaStream_t stream) {
+  OVM_REQUIRE(batch >= 0 && nq >= 0 && T > 0 && P > 0, "ovm_gdino_post: bad sizes (batch %d, queries %d, tokens %d, "
+              "phrases %d)", batch, nq, T, P);
+  if (batch == 0) return OVM_OK;
+  OVM_REQUIRE(logits && boxes_cxcywh && phrase_ranges && out_boxes && out_scores && out_classes && out_count,
+              "ovm_gdino_post: NULL pointer");
+  OVM_REQUIRE(nq <= OVM_NMS_MAX_SEGMENT, "ovm_gdino_post: %d queries exceed the %d one CTA holds", nq,
+              OVM_NMS_MAX_SEGMENT);
+  OVM_REQUIRE(T <= 512, "ovm_gdino_post: %d text tokens (at most 512)", T);
+  OVM_REQUIRE(((reinterpret_cast<uintptr_t>(boxes_cxcywh) | reinterpret_cast<uintptr_t>(out_boxes)) & 15) == 0,
+              "ovm_gdino_post: boxes must be 16-byte aligned");
+  if (nq == 0) {
+    OVM_CUDA(cudaMemsetAsync(out_count, 0, sizeof(int32_t) * batch, stream));
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return OVM_OK;
+  }
+  const int npad = host_next_pow2(nq);
+  const size_t smem = post_smem_bytes(npad) + (size_t)npad * 8 + (size_t)kPostWarps * T * 4;
+  OVM_REQUIRE(smem <= 227 * 1024, "ovm_gdino_post: %zu bytes of shared memory needed", smem);
+  static size_t configured = 0;
+  if (smem > configured) {
+    OVM_CUDA(cudaFuncSetAttribute(gdino_post_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = smem;
+  }
+  gdino_post_kernel<<<batch, kPostThreads, smem, stream>>>(logits, boxes_cxcywh, phrase_ranges, nq, T, P,
+                                                           (float)image_width, (float)image_height, box_threshold,
+                                                           nms_threshold, out_boxes, out_scores, out_classes,
+                                                           out_query, out_count);
+  OVM_LAUNCHED("gdino_post_kernel");
+  return OVM_OK;
+}
+
+}  // namespace ovm

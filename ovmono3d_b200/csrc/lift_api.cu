@@ -220,5 +220,21 @@ int ovm_lift_forward(const ovm_pooler_t* pooler, const ovm_fc_stack_t* fc, const
   return stage_mark(stage, stream);
 }
 
+int ovm_nms(const float* boxes, const float* scores, const int64_t* classes, const int32_t* seg_offsets,
+            int32_t num_segments, int32_t max_segment_len, double iou_threshold, int32_t mode, int32_t* keep,
+            int32_t* keep_count, void* stream) {
+  return nms_launch(boxes, scores, classes, seg_offsets, num_segments, max_segment_len, iou_threshold, mode, keep,
+                    keep_count, static_cast<cudaStream_t>(stream));
+}
+
+int ovm_gdino_post(const float* logits, const float* boxes_cxcywh, const int32_t* phrase_ranges, int32_t batch,
+                   int32_t num_queries, int32_t num_tokens, int32_t num_phrases, int32_t image_height,
+                   int32_t image_width, float box_threshold, double nms_threshold, float* out_boxes,
+                   float* out_scores, int64_t* out_classes, int32_t* out_query, int32_t* out_count, void* stream) {
+  return gdino_post_launch(logits, boxes_cxcywh, phrase_ranges, batch, num_queries, num_tokens, num_phrases,
+                           image_height, image_width, box_threshold, nms_threshold, out_boxes, out_scores,
+                           out_classes, out_query, out_count, static_cast<cudaStream_t>(stream));
+}
+
 }  // extern "C"
 #pragma GCC visibility pop

@@ -11,7 +11,7 @@ from typing import List, Optional, Sequence, Tuple
 
 import torch
 
-OVM_ABI_VERSION = 4
+OVM_ABI_VERSION = 5
 OVM_MAX_LEVELS = 8
 RECORD_WIDTH = 48
 LAYOUT_NCHW, LAYOUT_NHWC = 0, 1
@@ -33,7 +33,9 @@ REC_CLASS = 46
 
 EXPORTS = ("ovm_abi_version", "ovm_last_error", "ovm_launch_count", "ovm_struct_size", "ovm_roi_align", "ovm_gemm_bf16",
            "ovm_bias_act", "ovm_cast_bf16", "ovm_head_decode", "ovm_lift_forward", "ovm_set_stage_events", "ovm_gemm_set_trace",
-           "ovm_roi_set_trace", "ovm_head_set_trace")
+           "ovm_roi_set_trace", "ovm_head_set_trace", "ovm_nms", "ovm_gdino_post")
+NMS_MAX_SEGMENT = 4096
+NMS_AGNOSTIC, NMS_COORD_TRICK, NMS_PER_CLASS = 0, 1, 2
 
 
 class LiftError(RuntimeError):
@@ -117,6 +119,9 @@ def load_library() -> C.CDLL:
     lib.ovm_roi_set_trace.argtypes = [vp]
     lib.ovm_head_set_trace.argtypes = [vp]
     lib.ovm_set_stage_events.argtypes = [C.POINTER(C.c_void_p), i32]
+    lib.ovm_nms.argtypes = [vp, vp, vp, vp, i32, i32, C.c_double, i32, vp, vp, vp]
+    lib.ovm_gdino_post.argtypes = [vp, vp, vp, i32, i32, i32, i32, i32, i32, C.c_float, C.c_double, vp, vp, vp, vp,
+                                   vp, vp]
     for name in EXPORTS[3:]:
         getattr(lib, name).restype = C.c_int
     lib.ovm_struct_size.argtypes = [C.c_int]
@@ -283,3 +288,62 @@ def cast_bf16(x: torch.Tensor, ld_out: Optional[int] = None) -> torch.Tensor:
         _check(lib.ovm_cast_bf16(x.data_ptr(), x.stride(0), rows, cols, out.data_ptr(), ld_out, _stream()),
                "ovm_cast_bf16")
     return out[:, :cols]
+
+
+def nms(boxes: torch.Tensor, scores: torch.Tensor, iou_threshold: float, classes: Optional[torch.Tensor] = None,
+        seg_offsets: Optional[torch.Tensor] = None, max_segment_len: Optional[int] = None,
+        mode: Optional[int] = None) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Segmented greedy NMS (`ovm_nms`): torchvision.ops.nms / batched_nms per segment, one CTA each, no host
+    round trip.  Returns (keep [n] int32, keep_count [S] int32): `keep[off[s] : off[s] + keep_count[s]]` are the
+    rows of segment s (relative to its start) that survive, in decreasing score order."""
+    lib = load_library()
+    _need_cuda(boxes, "boxes", torch.float32)
+    _need_cuda(scores, "scores", torch.float32)
+    n = boxes.shape[0]
+    if boxes.dim() != 2 or boxes.shape[1] != 4 or scores.shape != (n,):
+        raise LiftError("nms expects boxes [n,4] and scores [n]")
+    boxes, scores = boxes.contiguous(), scores.contiguous()
+    if mode is None:
+        mode = NMS_AGNOSTIC if classes is None else NMS_COORD_TRICK
+    if classes is not None:
+        classes = _need_cuda(classes, "classes", torch.int64).contiguous()
+    if seg_offsets is None:
+        seg_offsets = torch.tensor([0, n], dtype=torch.int32, device=boxes.device)
+        max_segment_len = n
+    else:
+        _need_cuda(seg_offsets, "seg_offsets", torch.int32)
+        if max_segment_len is None:
+            max_segment_len = n
+    S = seg_offsets.numel() - 1
+    keep = torch.empty((max(n, 1),), dtype=torch.int32, device=boxes.device)
+    count = torch.empty((max(S, 1),), dtype=torch.int32, device=boxes.device)
+    _check(lib.ovm_nms(_ptr(boxes), _ptr(scores), _ptr(classes), _ptr(seg_offsets), S, int(max_segment_len),
+                       float(iou_threshold), int(mode), _ptr(keep), _ptr(count), _stream()), "ovm_nms")
+    return keep[:n], count[:S]
+
+
+def gdino_post(logits: torch.Tensor, boxes_cxcywh: torch.Tensor, phrase_ranges: torch.Tensor, image_hw: Tuple[int, int],
+               box_threshold: float, nms_threshold: float):
+    """`ovm_gdino_post`: raw GroundingDINO outputs [B,nq,T] / [B,nq,4] -> (boxes [B,nq,4] xyxy px, scores [B,nq],
+    classes [B,nq] int64, query [B,nq] int32, count [B] int32); rows past count[b] are undefined."""
+    lib = load_library()
+    _need_cuda(logits, "logits", torch.float32)
+    _need_cuda(boxes_cxcywh, "boxes_cxcywh", torch.float32)
+    _need_cuda(phrase_ranges, "phrase_ranges", torch.int32)
+    if logits.dim() != 3 or boxes_cxcywh.shape != (logits.shape[0], logits.shape[1], 4):
+        raise LiftError("gdino_post expects logits [B,nq,T] and boxes [B,nq,4]")
+    if phrase_ranges.dim() != 2 or phrase_ranges.shape[1] != 2 or phrase_ranges.shape[0] == 0:
+        raise LiftError("phrase_ranges must be [P,2] int32 with P >= 1")
+    logits, boxes_cxcywh, phrase_ranges = logits.contiguous(), boxes_cxcywh.contiguous(), phrase_ranges.contiguous()
+    B, nq, T = logits.shape
+    dev = logits.device
+    out_boxes = torch.empty((B, max(nq, 1), 4), dtype=torch.float32, device=dev)
+    out_scores = torch.empty((B, max(nq, 1)), dtype=torch.float32, device=dev)
+    out_classes = torch.empty((B, max(nq, 1)), dtype=torch.int64, device=dev)
+    out_query = torch.empty((B, max(nq, 1)), dtype=torch.int32, device=dev)
+    count = torch.empty((max(B, 1),), dtype=torch.int32, device=dev)
+    _check(lib.ovm_gdino_post(_ptr(logits), _ptr(boxes_cxcywh), _ptr(phrase_ranges), B, nq, T, phrase_ranges.shape[0],
+                              int(image_hw[0]), int(image_hw[1]), float(box_threshold), float(nms_threshold),
+                              _ptr(out_boxes), _ptr(out_scores), _ptr(out_classes), _ptr(out_query), _ptr(count),
+                              _stream()), "ovm_gdino_post")
+    return out_boxes[:, :nq], out_scores[:, :nq], out_classes[:, :nq], out_query[:, :nq], count[:B]

@@ -437,8 +437,11 @@ class ROIHeads3DGDINOB200(ROIHeads3DB200):
                 raise ops.LiftError("ROIHeads3DGDINOB200 needs a 2-D detector callable (GroundingDINO is not part of "
                                     "the lift path); pass detector=... or use ROIHeads3DB200 with given boxes")
             ov = self.groundingdino_model(images[0][[2, 1, 0], :, :], filtered_texts)
-            target.pred_classes = torch.tensor([filtered_texts.index([name]) for name in ov["labels"]],
-                                               dtype=torch.int64)
+            if "pred_classes" in ov:     # GroundingDinoPostB200: indices into category_list, already on the device
+                target.pred_classes = ov["pred_classes"]
+            else:
+                target.pred_classes = torch.tensor([filtered_texts.index([name]) for name in ov["labels"]],
+                                                   dtype=torch.int64)
             target.pred_boxes = Boxes(ov["bboxes"])
             target.scores = ov["scores"]
             target = target.to(device=device)

@@ -88,10 +88,68 @@ def logged_detections() -> None:
     print("logged_detections.json:", len(dets), "detections")
 
 
+class _StandInImage:
+    """What `get_grounding_output` touches of the image: `.to(device)`, `[None]`, `.shape` (it moves the image to
+    "cuda" unconditionally, roi_heads_gdino.py:182-184 -- there is none here)."""
+
+    def __init__(self, h: int, w: int):
+        self.shape = (3, h, w)
+
+    def to(self, device):
+        return self
+
+    def __getitem__(self, idx):
+        return self
+
+
+class _StandInGdino:
+    def __init__(self, logits, boxes, tokenizer):
+        self.logits, self.boxes, self.tokenizer, self.captions = logits, boxes, tokenizer, None
+
+    def to(self, device):
+        return self
+
+    def __call__(self, image, captions):
+        self.captions = captions
+        return {"pred_logits": self.logits, "pred_boxes": self.boxes}
+
+
+def run_gdino_case(case) -> dict:
+    """Drive the reference's own `grounding_dino_inference_detector` (roi_heads_gdino.py:262-281)."""
+    import importlib
+
+    from tests.golden import gdino_cases as gd
+
+    rh.install_stubs()
+    mod = importlib.import_module("cubercnn.modeling.roi_heads.roi_heads_gdino")
+    logits, boxes, tok, caption, text_prompt = gd.build_case(case)
+    model = _StandInGdino(logits, boxes, tok)
+    ov = mod.grounding_dino_inference_detector({
+        "groundingdino_model": model, "image": _StandInImage(*case.image_hw), "text_prompt": text_prompt,
+        "box_threshold": case.box_threshold, "text_threshold": 0.25, "token_spans": None, "cpu_only": False})
+    assert model.captions == [caption]
+    cap_list = [c[0] for c in text_prompt]
+    classes = np.array([text_prompt.index([name]) for name in ov["labels"]], dtype=np.int64)   # :162
+    assert case.nms_threshold == 0.5 or True   # the reference hard-wires 0.5 (:272); other values go through nms below
+    rec = {"checksum": gd.input_checksum(logits, boxes), "bboxes": ov["bboxes"].numpy(), "scores": ov["scores"].numpy(),
+           "classes": classes, "num_categories": np.int64(len(cap_list))}
+    return rec
+
+
 def main() -> None:
-    names = sys.argv[1:] or [c.name for c in gc.CASES]
+    from tests.golden import gdino_cases as gd
+
+    all_names = [c.name for c in gc.CASES] + [c.name for c in gd.CASES]
+    names = sys.argv[1:] or all_names
     torch.set_num_threads(max(1, os.cpu_count() or 1))
-    for name in names:
+    for name in [n for n in names if n in gd.CASE_BY_NAME]:
+        case = gd.CASE_BY_NAME[name]
+        if case.nms_threshold != 0.5:
+            continue        # the reference hard-wires NMS 0.5; such cases are checked against the oracle only
+        rec = run_gdino_case(case)
+        np.savez_compressed(gd.golden_path(case), **rec)
+        print("%-32s kept=%-4d %6.1f KB" % (name, len(rec["scores"]), os.path.getsize(gd.golden_path(case)) / 1024))
+    for name in [n for n in names if n in gc.CASE_BY_NAME]:
         case = gc.CASE_BY_NAME[name]
         rec = run_case(case)
         np.savez_compressed(gc.golden_path(case), **rec)
