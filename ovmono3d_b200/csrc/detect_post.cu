@@ -7,7 +7,7 @@
 //
 // One CTA owns one image from start to finish: score keys are sorted in shared memory (bitonic, 64-bit keys =
 // descending score | ascending row, which is the stable descending order torch's sort produces), the sorted boxes
-// stay in shared memory, and the greedy pass walks them with one barrier per *kept* box.  Nothing goes back to the
+// stay in shared memory, and the greedy pass walks them 32 positions per round (three barriers).  Nothing goes back to the
 // host in between (torchvision's CUDA nms copies its n x n/64 mask to the host and scans it there).
 #include "common.cuh"
 
@@ -62,29 +62,67 @@ __device__ __forceinline__ bool suppresses(const float4& a, float area_a, const 
   const float xx2 = fminf(a.z, b.z), yy2 = fminf(a.w, b.w);
   const float w = fmaxf(0.0f, __fsub_rn(xx2, xx1)), h = fmaxf(0.0f, __fsub_rn(yy2, yy1));
   const float inter = __fmul_rn(w, h);
+  if (inter <= 0.0f && thr >= 0.0) return false;   // 0 / union is 0 (or NaN for two empty boxes): never above thr
   const float ovr = __fdiv_rn(inter, __fsub_rn(__fadd_rn(area_a, box_area(b)), inter));
   return (double)ovr > thr;
 }
 
-// Greedy suppression over boxes already in decreasing score order.  cls == nullptr: every pair competes.
-// alive[i] is 1 on entry for i < n.  One barrier per kept box; skipped boxes cost one shared-memory read.
-__device__ void block_greedy(const float4* sb, const int32_t* cls, volatile uint8_t* alive, int n, double thr) {
+// Greedy suppression over boxes already in decreasing score order, 32 sorted positions per round.
+//   1. the 32 x 32 tests inside the round's block, one per thread (warp = candidate, lane = earlier candidate);
+//   2. warp 0 walks the block serially on the resulting bit rows: K = candidates of the block that are kept;
+//   3. every thread tests its own later positions against the kept candidates only.
+// Three barriers per 32 positions whatever the number of survivors (a barrier per kept box costs 0.5 us each).
+// cls == nullptr: every pair competes.  alive[i] is 1 on entry for i < n.  blockDim.x must be kPostThreads.
+__device__ void block_greedy(const float4* sb, const int32_t* cls, volatile uint8_t* alive, int n, double thr,
+                             uint32_t* mrow /* [33] shared */) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   __syncthreads();
-  for (int i = 0; i < n; ++i) {
-    if (!alive[i]) continue;
-    const float4 bi = sb[i];
-    const float ai = box_area(bi);
-    const int ci = cls ? cls[i] : 0;
-    int j = threadIdx.x;
-    if (j <= i) j += ((i - j) / kPostThreads + 1) * kPostThreads;
-    for (; j < n; j += kPostThreads) {
-      if (!alive[j]) continue;
-      if (cls && cls[j] != ci) continue;
-      if (suppresses(bi, ai, sb[j], thr)) alive[j] = 0;
+  for (int i0 = 0; i0 < n; i0 += 32) {
+    {
+      const int c = i0 + warp, e = i0 + lane;
+      bool sup = false;
+      if (lane < warp && c < n && (!cls || cls[c] == cls[e])) {
+        const float4 be = sb[e];
+        sup = suppresses(be, box_area(be), sb[c], thr);
+      }
+      const uint32_t m = __ballot_sync(0xFFFFFFFFu, sup);
+      if (lane == 0) mrow[warp] = m;
+    }
+    __syncthreads();
+    if (warp == 0) {
+      const uint32_t m = mrow[lane];
+      const uint32_t abits = __ballot_sync(0xFFFFFFFFu, i0 + lane < n && alive[i0 + lane]);
+      uint32_t K = 0;
+#pragma unroll
+      for (int c = 0; c < 32; ++c) {
+        const uint32_t mc = __shfl_sync(0xFFFFFFFFu, m, c);
+        if (((abits >> c) & 1u) && !(mc & K)) K |= 1u << c;
+      }
+      if (lane == 0) mrow[32] = K;
+      if (i0 + lane < n) alive[i0 + lane] = (K >> lane) & 1u;
+    }
+    __syncthreads();
+    const uint32_t K = mrow[32];
+    if (K) {
+      for (int j = i0 + 32 + threadIdx.x; j < n; j += kPostThreads) {
+        if (!alive[j]) continue;
+        const float4 bj = sb[j];
+        const int cj = cls ? cls[j] : 0;
+        uint32_t k = K;
+        while (k) {
+          const int c = i0 + __ffs(k) - 1;
+          k &= k - 1;
+          if (cls && cls[c] != cj) continue;
+          const float4 bc = sb[c];
+          if (suppresses(bc, box_area(bc), bj, thr)) {
+            alive[j] = 0;
+            break;
+          }
+        }
+      }
     }
     __syncthreads();
   }
-  __syncthreads();
 }
 
 // Ordered compaction of the surviving sorted positions: calls emit(rank, position) for each, returns the count.
@@ -197,7 +235,8 @@ nms_kernel(const float* __restrict__ boxes, const float* __restrict__ scores, co
     s.sb[p] = b;
     s.scls[p] = c;
   }
-  block_greedy(s.sb, mode == OVM_NMS_PER_CLASS ? s.scls : nullptr, s.alive, n, thr);
+  block_greedy(s.sb, mode == OVM_NMS_PER_CLASS ? s.scls : nullptr, s.alive, n, thr,
+               reinterpret_cast<uint32_t*>(s.warp_tot));
   int32_t* kout = keep + r0;
   const uint64_t* keys = s.keys;
   const int cnt = block_compact(s.alive, n, s.warp_tot, [&](int rank, int pos) { kout[rank] = (int32_t)(uint32_t)keys[pos]; });
@@ -285,7 +324,7 @@ gdino_post_kernel(const float* __restrict__ logits, const float* __restrict__ bo
       s.sb[p] = make_float4(__fsub_rn(cx, hw), __fsub_rn(cy, hh), __fadd_rn(cx, hw), __fadd_rn(cy, hh));
     }
   }
-  block_greedy(s.sb, nullptr, s.alive, n, nms_thr);
+  block_greedy(s.sb, nullptr, s.alive, n, nms_thr, reinterpret_cast<uint32_t*>(s.warp_tot));
 
   // 4. survivors in keep order
   float4* ob = reinterpret_cast<float4*>(out_boxes) + (size_t)b * nq;

@@ -315,6 +315,9 @@ def nms(boxes: torch.Tensor, scores: torch.Tensor, iou_threshold: float, classes
         if max_segment_len is None:
             max_segment_len = n
     S = seg_offsets.numel() - 1
+    if n == 0:                      # nothing to launch (torchvision returns an empty keep list as well)
+        return (torch.zeros((0,), dtype=torch.int32, device=boxes.device),
+                torch.zeros((S,), dtype=torch.int32, device=boxes.device))
     keep = torch.empty((max(n, 1),), dtype=torch.int32, device=boxes.device)
     count = torch.empty((max(S, 1),), dtype=torch.int32, device=boxes.device)
     _check(lib.ovm_nms(_ptr(boxes), _ptr(scores), _ptr(classes), _ptr(seg_offsets), S, int(max_segment_len),
