@@ -235,10 +235,45 @@ int ovm_gdino_post(const float* logits, const float* boxes_cxcywh, const int32_t
                    int32_t image_width, float box_threshold, double nms_threshold, float* out_boxes,
                    float* out_scores, int64_t* out_classes, int32_t* out_query, int32_t* out_count, void* stream);
 
+typedef struct {
+  int32_t num_classes;           /* K foreground classes: logits have K + 1 columns, background last */
+  int32_t cls_agnostic_bbox_reg; /* MODEL.ROI_BOX_HEAD.CLS_AGNOSTIC_BBOX_REG: deltas have 4 columns instead of 4K */
+  float reg_weights[4];          /* MODEL.ROI_BOX_HEAD.BBOX_REG_WEIGHTS (10, 10, 5, 5) */
+  float scale_clamp;             /* d2 Box2BoxTransform: log(1000 / 16) */
+  float score_thresh;            /* MODEL.ROI_HEADS.SCORE_THRESH_TEST */
+  double nms_thresh;             /* MODEL.ROI_HEADS.NMS_THRESH_TEST */
+  int32_t topk_per_image;        /* TEST.DETECTIONS_PER_IMAGE; < 0 keeps everything */
+  int32_t coord_trick_max;       /* candidates per image up to which torchvision's batched_nms offsets the boxes by
+                                    class (1000 on the CPU, 5000 on CUDA); above it runs class by class */
+} ovm_box_inference_cfg_t;
+
+typedef struct {                 /* device scratch owned by the caller; nothing needs initialising */
+  float* probs;                  /* [R, K] */
+  float* cand_boxes;             /* [R, Kb, 4], Kb = 1 when class-agnostic else K; 16-byte aligned */
+  int32_t* class_keep;           /* [N, K, max_per_image] */
+  int32_t* class_count;          /* [N, K] */
+  int32_t* image_stats;          /* [N, 2] */
+} ovm_box_inference_ws_t;
+
+/* Inference tail of the 2-D box head: softmax over logits [R, ld_logits] (K + 1 used), Box2BoxTransform.apply_deltas
+ * of deltas [R, ld_deltas] on proposals [R, 4] (xyxy), clip to image_sizes [N, 2] int32 (height, width), rows with a
+ * non-finite number dropped, score threshold, per-class NMS, first top-k per image in decreasing score order
+ * (fast_rcnn.py:57-116).  seg_offsets [N + 1] int32 (device): proposals of image i are rows
+ * [seg_offsets[i], seg_offsets[i+1]), at most max_per_image (<= OVM_NMS_MAX_SEGMENT) of them.  Three launches.
+ * Outputs, cap = topk_per_image (or K * max_per_image when < 0) rows per image: out_boxes [N, cap, 4],
+ * out_scores [N, cap], out_classes [N, cap] int64, out_index [N, cap] int32 (proposal row inside the image; the
+ * reference's kept_indices count only the finite rows), out_scores_full [N, cap, K] (optional), out_count [N]. */
+int ovm_box_inference(const ovm_box_inference_cfg_t* cfg, const float* logits, int64_t ld_logits,
+                      const float* deltas, int64_t ld_deltas, const float* proposals, const int32_t* seg_offsets,
+                      const int32_t* image_sizes, int32_t num_images, int32_t num_proposals, int32_t max_per_image,
+                      const ovm_box_inference_ws_t* ws, float* out_boxes, float* out_scores, int64_t* out_classes,
+                      int32_t* out_index, float* out_scores_full, int32_t* out_count, void* stream);
+
 int ovm_abi_version(void);
 /* sizeof() of the ABI structs as this library was compiled, for binding self-checks:
  * 0 ovm_level_t, 1 ovm_pooler_t, 2 ovm_decode_cfg_t, 3 ovm_head_weights_t, 4 ovm_fc_layer_t,
- * 5 ovm_fc_stack_t, 6 ovm_workspace_t; -1 for any other index. */
+ * 5 ovm_fc_stack_t, 6 ovm_workspace_t, 7 ovm_box_inference_cfg_t, 8 ovm_box_inference_ws_t; -1 for any other
+ * index. */
 int ovm_struct_size(int which);
 const char* ovm_last_error(void);
 /* Number of kernel launches (incl. memsets) the library has issued in this process. */

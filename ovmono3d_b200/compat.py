@@ -103,6 +103,15 @@ except Exception:  # ImportError, or a broken install
             self.tensor[:, 0::2] *= scale_x
             self.tensor[:, 1::2] *= scale_y
 
+        def clip(self, box_size: Tuple[int, int]) -> None:
+            assert torch.isfinite(self.tensor).all(), "Box tensor contains infinite or NaN!"
+            h, w = box_size
+            x1 = self.tensor[:, 0].clamp(min=0, max=w)
+            y1 = self.tensor[:, 1].clamp(min=0, max=h)
+            x2 = self.tensor[:, 2].clamp(min=0, max=w)
+            y2 = self.tensor[:, 3].clamp(min=0, max=h)
+            self.tensor = torch.stack((x1, y1, x2, y2), dim=-1)
+
         def __getitem__(self, item: Any) -> "Boxes":
             if isinstance(item, int):
                 return Boxes(self.tensor[item].view(1, -1))

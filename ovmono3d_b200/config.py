@@ -135,6 +135,15 @@ def add_lift_defaults(cfg: CfgNode) -> CfgNode:
     )
     for k, v in defaults.items():
         h.setdefault(k, v)
+    # 2-D box branch (d2 defaults; Base.yaml:60-70 overrides SCORE_THRESH_TEST to 0.01)
+    m.ROI_HEADS.setdefault("SCORE_THRESH_TEST", 0.05)
+    m.ROI_HEADS.setdefault("NMS_THRESH_TEST", 0.5)
+    m.setdefault("ROI_BOX_HEAD", CN())
+    for k, v in dict(NAME="FastRCNNConvFCHead", NUM_FC=2, FC_DIM=1024, NUM_CONV=0, POOLER_RESOLUTION=7,
+                     POOLER_SAMPLING_RATIO=0, POOLER_TYPE="ROIAlignV2", CLS_AGNOSTIC_BBOX_REG=False,
+                     BBOX_REG_WEIGHTS=(10.0, 10.0, 5.0, 5.0),
+                     BUILD=False).items():   # BUILD is this package's key: the GDINO head never uses the branch
+        m.ROI_BOX_HEAD.setdefault(k, v)
     cfg.setdefault("INPUT", CN())
     cfg.INPUT.setdefault("MIN_SIZE_TEST", 512)
     cfg.setdefault("TEST", CN())

@@ -121,4 +121,10 @@ int gdino_post_launch(const float* logits, const float* boxes_cxcywh, const int3
                       float box_threshold, double nms_threshold, float* out_boxes, float* out_scores,
                       int64_t* out_classes, int32_t* out_query, int32_t* out_count, cudaStream_t stream);
 
+int box_inference_launch(const ovm_box_inference_cfg_t* cfg, const float* logits, int64_t ld_logits,
+                         const float* deltas, int64_t ld_deltas, const float* proposals, const int32_t* seg_offsets,
+                         const int32_t* image_sizes, int32_t N, int32_t R, int32_t max_per_image,
+                         const ovm_box_inference_ws_t* ws, float* out_boxes, float* out_scores, int64_t* out_classes,
+                         int32_t* out_index, float* out_scores_full, int32_t* out_count, cudaStream_t stream);
+
 }  // namespace ovm

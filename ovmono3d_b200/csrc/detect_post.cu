@@ -9,6 +9,8 @@
 // descending score | ascending row, which is the stable descending order torch's sort produces), the sorted boxes
 // stay in shared memory, and the greedy pass walks them 32 positions per round (three barriers).  Nothing goes back to the
 // host in between (torchvision's CUDA nms copies its n x n/64 mask to the host and scans it there).
+#include <algorithm>
+
 #include "common.cuh"
 
 namespace ovm {
@@ -343,6 +345,213 @@ gdino_post_kernel(const float* __restrict__ logits, const float* __restrict__ bo
   if (threadIdx.x == 0) out_count[b] = cnt;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// ovm_box_inference: FastRCNNOutputLayers.predict_probs / predict_boxes + fast_rcnn_inference_single_image
+// (reference cubercnn/modeling/roi_heads/fast_rcnn.py:57-143; d2 Box2BoxTransform.apply_deltas, Boxes.clip).
+//   box_predict_kernel    warp per proposal: softmax, per-class boxes, clip, validity, per-image candidate stats
+//   box_class_nms_kernel  CTA per (class, image): candidates above the score threshold, sorted, suppressed
+//   box_topk_kernel       CTA per image: the per-class survivors merged in decreasing score order, first top-k
+
+struct BoxCfg {
+  int K, agnostic;
+  float wx, wy, ww, wh, scale_clamp, score_thresh;
+  double nms_thresh;
+  int topk, coord_trick_max;
+};
+
+__device__ __forceinline__ bool finite_f(float x) { return fabsf(x) <= 3.402823466e38f; }
+
+__global__ void __launch_bounds__(256)
+box_predict_kernel(BoxCfg cfg, const float* __restrict__ logits, int64_t ld_logits, const float* __restrict__ deltas,
+                   int64_t ld_deltas, const float* __restrict__ proposals, const int32_t* __restrict__ seg_offsets,
+                   const int32_t* __restrict__ image_sizes, int N, int R, float* __restrict__ probs,
+                   float* __restrict__ cand_boxes, int32_t* __restrict__ image_stats) {
+  const int lane = threadIdx.x & 31;
+  const int r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (r >= R) return;
+  const int K = cfg.K, Kb = cfg.agnostic ? 1 : K;
+  // image of this proposal (segments are sorted; N is small)
+  int img = 0;
+  {
+    int lo = 0, hi = N;           // largest i with seg_offsets[i] <= r
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (seg_offsets[mid] <= r) lo = mid; else hi = mid;
+    }
+    img = lo;
+  }
+  const float im_h = (float)image_sizes[2 * img], im_w = (float)image_sizes[2 * img + 1];
+  // softmax over the K + 1 logits (F.softmax(scores, -1), d2 fast_rcnn.py predict_probs)
+  const float* lg = logits + (size_t)r * ld_logits;
+  float mx = -INFINITY;
+  bool fin = true;
+  for (int k = lane; k <= K; k += 32) {
+    const float v = lg[k];
+    fin &= finite_f(v);
+    mx = fmaxf(mx, v);
+  }
+  for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xFFFFFFFFu, mx, o));
+  float sum = 0.0f;
+  for (int k = lane; k <= K; k += 32) sum += expf(lg[k] - mx);
+  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xFFFFFFFFu, sum, o);
+  // boxes (Box2BoxTransform.apply_deltas, then Boxes.clip to the image)
+  const float4 p = reinterpret_cast<const float4*>(proposals)[r];
+  const float pw = __fsub_rn(p.z, p.x), ph = __fsub_rn(p.w, p.y);
+  const float pcx = __fadd_rn(p.x, __fmul_rn(0.5f, pw)), pcy = __fadd_rn(p.y, __fmul_rn(0.5f, ph));
+  const float* dl = deltas + (size_t)r * ld_deltas;
+  float4* cb = reinterpret_cast<float4*>(cand_boxes) + (size_t)r * Kb;
+  for (int k = lane; k < Kb; k += 32) {
+    const float dx = __fdiv_rn(dl[4 * k], cfg.wx), dy = __fdiv_rn(dl[4 * k + 1], cfg.wy);
+    const float dw = fminf(__fdiv_rn(dl[4 * k + 2], cfg.ww), cfg.scale_clamp);
+    const float dh = fminf(__fdiv_rn(dl[4 * k + 3], cfg.wh), cfg.scale_clamp);
+    const float cx = __fadd_rn(__fmul_rn(dx, pw), pcx), cy = __fadd_rn(__fmul_rn(dy, ph), pcy);
+    const float w = __fmul_rn(expf(dw), pw), h = __fmul_rn(expf(dh), ph);
+    float4 b = make_float4(__fsub_rn(cx, __fmul_rn(0.5f, w)), __fsub_rn(cy, __fmul_rn(0.5f, h)),
+                           __fadd_rn(cx, __fmul_rn(0.5f, w)), __fadd_rn(cy, __fmul_rn(0.5f, h)));
+    fin &= finite_f(b.x) && finite_f(b.y) && finite_f(b.z) && finite_f(b.w);   // isfinite on the unclipped boxes
+    b.x = fminf(fmaxf(b.x, 0.0f), im_w);
+    b.y = fminf(fmaxf(b.y, 0.0f), im_h);
+    b.z = fminf(fmaxf(b.z, 0.0f), im_w);
+    b.w = fminf(fmaxf(b.w, 0.0f), im_h);
+    cb[k] = b;
+  }
+  __syncwarp();       // class-agnostic: every lane reads the one box lane 0 wrote
+  fin = __all_sync(0xFFFFFFFFu, fin);
+  // probabilities; a row with a non-finite number is dropped as a whole (fast_rcnn.py:75-78): NaN never passes `>`
+  int cnt = 0;
+  float cmax = 0.0f;
+  float* pr = probs + (size_t)r * K;
+  for (int k = lane; k < K; k += 32) {
+    const float pk = fin ? __fdiv_rn(expf(lg[k] - mx), sum) : __int_as_float(0x7FC00000);
+    pr[k] = pk;
+    if (pk > cfg.score_thresh) {
+      ++cnt;
+      const float4 b = cb[cfg.agnostic ? 0 : k];     // own write (k == lane-strided) or, agnostic, lane 0's
+      cmax = fmaxf(cmax, fmaxf(fmaxf(b.x, b.y), fmaxf(b.z, b.w)));
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    cnt += __shfl_xor_sync(0xFFFFFFFFu, cnt, o);
+    cmax = fmaxf(cmax, __shfl_xor_sync(0xFFFFFFFFu, cmax, o));
+  }
+  if (lane == 0 && cnt) {
+    atomicAdd(&image_stats[2 * img], cnt);
+    atomicMax(&image_stats[2 * img + 1], __float_as_int(cmax));     // clipped coordinates are >= 0: int order = float order
+  }
+}
+
+__global__ void __launch_bounds__(kPostThreads, 1)
+box_class_nms_kernel(BoxCfg cfg, const float* __restrict__ probs, const float* __restrict__ cand_boxes,
+                     const int32_t* __restrict__ seg_offsets, const int32_t* __restrict__ image_stats,
+                     int max_per_image, int32_t* __restrict__ class_keep, int32_t* __restrict__ class_count) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int k = blockIdx.x, img = blockIdx.y, K = cfg.K;
+  const int r0 = seg_offsets[img];
+  const int len = min(seg_offsets[img + 1] - r0, max_per_image);
+  int32_t* kout = class_keep + ((size_t)img * K + k) * max_per_image;
+  if (len <= 0 || image_stats[2 * img] == 0) {
+    if (threadIdx.x == 0) class_count[img * K + k] = 0;
+    return;
+  }
+  const int npad = next_pow2(len);
+  PostSmem s = carve(smem_raw, npad);
+  int* n_cand = s.warp_tot + kPostWarps;
+  for (int i = threadIdx.x; i < npad; i += kPostThreads) {
+    float sc = 0.0f;
+    const bool ok = i < len && (sc = probs[(size_t)(r0 + i) * K + k]) > cfg.score_thresh;
+    s.keys[i] = ok ? ((uint64_t)score_key_desc(sc) << 32) | (uint32_t)i : kPadKey;
+  }
+  block_sort(s.keys, npad);
+  if (threadIdx.x == 0) *n_cand = npad;
+  __syncthreads();
+  for (int i = threadIdx.x; i < npad; i += kPostThreads)
+    if (s.keys[i] == kPadKey && (i == 0 || s.keys[i - 1] != kPadKey)) *n_cand = i;
+  __syncthreads();
+  const int n = *n_cand;
+  __syncthreads();
+  if (n == 0) {
+    if (threadIdx.x == 0) class_count[img * K + k] = 0;
+    return;
+  }
+  // torchvision batched_nms: coordinate trick while the image has few candidates, plain per-class NMS above
+  float off = 0.0f;
+  if (image_stats[2 * img] <= cfg.coord_trick_max)
+    off = __fmul_rn((float)k, __fadd_rn(__int_as_float(image_stats[2 * img + 1]), 1.0f));
+  const int Kb = cfg.agnostic ? 1 : K;
+  const float4* cb = reinterpret_cast<const float4*>(cand_boxes);
+  for (int p = threadIdx.x; p < npad; p += kPostThreads) {
+    s.alive[p] = p < n;
+    if (p < n) {
+      float4 b = cb[(size_t)(r0 + (int)(uint32_t)s.keys[p]) * Kb + (cfg.agnostic ? 0 : k)];
+      b.x = __fadd_rn(b.x, off);
+      b.y = __fadd_rn(b.y, off);
+      b.z = __fadd_rn(b.z, off);
+      b.w = __fadd_rn(b.w, off);
+      s.sb[p] = b;
+    }
+  }
+  block_greedy(s.sb, nullptr, s.alive, n, cfg.nms_thresh, reinterpret_cast<uint32_t*>(s.warp_tot));
+  const uint64_t* keys = s.keys;
+  const int cnt = block_compact(s.alive, n, s.warp_tot, [&](int rank, int pos) { kout[rank] = (int32_t)(uint32_t)keys[pos]; });
+  if (threadIdx.x == 0) class_count[img * K + k] = cnt;
+}
+
+__global__ void __launch_bounds__(kPostThreads, 1)
+box_topk_kernel(BoxCfg cfg, const float* __restrict__ probs, const float* __restrict__ cand_boxes,
+                const int32_t* __restrict__ seg_offsets, int max_per_image, const int32_t* __restrict__ class_keep,
+                const int32_t* __restrict__ class_count, int npad, int cap, float* __restrict__ out_boxes,
+                float* __restrict__ out_scores, int64_t* __restrict__ out_classes, int32_t* __restrict__ out_index,
+                float* __restrict__ out_scores_full, int32_t* __restrict__ out_count) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  uint64_t* keys = reinterpret_cast<uint64_t*>(smem_raw);            // [npad]
+  int* offs = reinterpret_cast<int*>(smem_raw + (size_t)npad * 8);   // [K + 1]
+  const int img = blockIdx.x, K = cfg.K;
+  const int r0 = seg_offsets[img];
+  const int len = min(seg_offsets[img + 1] - r0, max_per_image);
+  const int per_class = cfg.topk >= 0 ? min(cfg.topk, max_per_image) : max_per_image;
+  if (threadIdx.x == 0) {
+    int acc = 0;
+    for (int k = 0; k < K; ++k) {
+      offs[k] = acc;
+      acc += len > 0 ? min(class_count[img * K + k], per_class) : 0;
+    }
+    offs[K] = acc;
+  }
+  for (int i = threadIdx.x; i < npad; i += kPostThreads) keys[i] = kPadKey;
+  __syncthreads();
+  const int total = offs[K];
+  // a class list is already in decreasing score order: only its first top-k entries can reach the image's top-k
+  for (int k = threadIdx.x >> 5; k < K; k += kPostWarps) {
+    const int c = offs[k + 1] - offs[k];
+    const int32_t* kl = class_keep + ((size_t)img * K + k) * max_per_image;
+    for (int j = threadIdx.x & 31; j < c; j += 32) {
+      const int r = kl[j];
+      const float sc = probs[(size_t)(r0 + r) * K + k];
+      keys[offs[k] + j] = ((uint64_t)score_key_desc(sc) << 32) | (uint32_t)(r * K + k);   // ties: (r, k) row-major,
+    }                                                                                      // the order of nonzero()
+  }
+  block_sort(keys, npad);
+  const int n_out = cfg.topk >= 0 ? min(total, cfg.topk) : total;
+  const int Kb = cfg.agnostic ? 1 : K;
+  const float4* cb = reinterpret_cast<const float4*>(cand_boxes);
+  for (int j = threadIdx.x; j < n_out; j += kPostThreads) {
+    const uint32_t id = (uint32_t)keys[j];
+    const int r = id / K, k = id - r * K;
+    const size_t o = (size_t)img * cap + j;
+    reinterpret_cast<float4*>(out_boxes)[o] = cb[(size_t)(r0 + r) * Kb + (cfg.agnostic ? 0 : k)];
+    out_scores[o] = probs[(size_t)(r0 + r) * K + k];
+    out_classes[o] = k;
+    out_index[o] = r;
+  }
+  if (out_scores_full)
+    for (int e = threadIdx.x; e < n_out * K; e += kPostThreads) {
+      const int j = e / K, k = e - j * K;
+      const int r = (uint32_t)keys[j] / K;
+      out_scores_full[((size_t)img * cap + j) * K + k] = probs[(size_t)(r0 + r) * K + k];
+    }
+  if (threadIdx.x == 0) out_count[img] = n_out;
+}
+
 int host_next_pow2(int n) {
   int p = 32;
   while (p < n) p <<= 1;
@@ -407,6 +616,82 @@ int gdino_post_launch(const float* logits, const float* boxes_cxcywh, const int3
                                                            nms_threshold, out_boxes, out_scores, out_classes,
                                                            out_query, out_count);
   OVM_LAUNCHED("gdino_post_kernel");
+  return OVM_OK;
+}
+
+int box_inference_launch(const ovm_box_inference_cfg_t* c, const float* logits, int64_t ld_logits, const float* deltas,
+                         int64_t ld_deltas, const float* proposals, const int32_t* seg_offsets,
+                         const int32_t* image_sizes, int32_t N, int32_t R, int32_t max_per_image,
+                         const ovm_box_inference_ws_t* ws, float* out_boxes, float* out_scores, int64_t* out_classes,
+                         int32_t* out_index, float* out_scores_full, int32_t* out_count, cudaStream_t stream) {
+  OVM_REQUIRE(c && ws, "ovm_box_inference: NULL descriptor");
+  OVM_REQUIRE(N >= 0 && R >= 0 && max_per_image >= 0, "ovm_box_inference: negative size");
+  if (N == 0) return OVM_OK;
+  OVM_REQUIRE(out_count, "ovm_box_inference: out_count is NULL");
+  if (R == 0 || max_per_image == 0) {
+    OVM_CUDA(cudaMemsetAsync(out_count, 0, sizeof(int32_t) * N, stream));
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return OVM_OK;
+  }
+  const int K = c->num_classes;
+  OVM_REQUIRE(K >= 1 && K <= 1024, "ovm_box_inference: %d classes (1..1024)", K);
+  OVM_REQUIRE(logits && deltas && proposals && seg_offsets && image_sizes && out_boxes && out_scores && out_classes &&
+              out_index, "ovm_box_inference: NULL pointer");
+  OVM_REQUIRE(ws->probs && ws->cand_boxes && ws->class_keep && ws->class_count && ws->image_stats,
+              "ovm_box_inference: incomplete workspace");
+  OVM_REQUIRE(ld_logits >= K + 1 && ld_deltas >= (c->cls_agnostic_bbox_reg ? 4 : 4 * K),
+              "ovm_box_inference: logits need %d columns, deltas %d", K + 1, c->cls_agnostic_bbox_reg ? 4 : 4 * K);
+  OVM_REQUIRE(max_per_image <= OVM_NMS_MAX_SEGMENT, "ovm_box_inference: %d proposals per image exceed the %d one CTA "
+              "holds", max_per_image, OVM_NMS_MAX_SEGMENT);
+  OVM_REQUIRE(((reinterpret_cast<uintptr_t>(proposals) | reinterpret_cast<uintptr_t>(ws->cand_boxes) |
+                reinterpret_cast<uintptr_t>(out_boxes)) & 15) == 0, "ovm_box_inference: boxes must be 16-byte aligned");
+  const int per_class = c->topk_per_image >= 0 ? std::min(c->topk_per_image, max_per_image) : max_per_image;
+  const int64_t merged = (int64_t)K * per_class;
+  if (merged > 16384) {
+    set_error("ovm_box_inference: %d classes x %d survivors per class = %lld merge candidates per image (at most "
+              "16384 in this build)", K, per_class, (long long)merged);
+    return OVM_EUNSUPPORTED;
+  }
+  const int cap = c->topk_per_image >= 0 ? c->topk_per_image : (int)merged;
+  BoxCfg b;
+  b.K = K;
+  b.agnostic = c->cls_agnostic_bbox_reg != 0;
+  b.wx = c->reg_weights[0];
+  b.wy = c->reg_weights[1];
+  b.ww = c->reg_weights[2];
+  b.wh = c->reg_weights[3];
+  b.scale_clamp = c->scale_clamp;
+  b.score_thresh = c->score_thresh;
+  b.nms_thresh = c->nms_thresh;
+  b.topk = c->topk_per_image;
+  b.coord_trick_max = c->coord_trick_max;
+  OVM_CUDA(cudaMemsetAsync(ws->image_stats, 0, sizeof(int32_t) * 2 * N, stream));
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  box_predict_kernel<<<(R + 7) / 8, 256, 0, stream>>>(b, logits, ld_logits, deltas, ld_deltas, proposals, seg_offsets,
+                                                     image_sizes, N, R, ws->probs, ws->cand_boxes, ws->image_stats);
+  OVM_LAUNCHED("box_predict_kernel");
+  const size_t smem_nms = post_smem_bytes(host_next_pow2(max_per_image));
+  static size_t conf_nms = 0;
+  if (smem_nms > conf_nms) {
+    OVM_CUDA(cudaFuncSetAttribute(box_class_nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_nms));
+    conf_nms = smem_nms;
+  }
+  box_class_nms_kernel<<<dim3(K, N), kPostThreads, smem_nms, stream>>>(b, ws->probs, ws->cand_boxes, seg_offsets,
+                                                                      ws->image_stats, max_per_image, ws->class_keep,
+                                                                      ws->class_count);
+  OVM_LAUNCHED("box_class_nms_kernel");
+  const int npad = host_next_pow2((int)std::max<int64_t>(merged, 1));
+  const size_t smem_topk = (size_t)npad * 8 + (size_t)(K + 1) * 4;
+  static size_t conf_topk = 0;
+  if (smem_topk > conf_topk) {
+    OVM_CUDA(cudaFuncSetAttribute(box_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_topk));
+    conf_topk = smem_topk;
+  }
+  box_topk_kernel<<<N, kPostThreads, smem_topk, stream>>>(b, ws->probs, ws->cand_boxes, seg_offsets, max_per_image,
+                                                          ws->class_keep, ws->class_count, npad, cap, out_boxes,
+                                                          out_scores, out_classes, out_index, out_scores_full,
+                                                          out_count);
+  OVM_LAUNCHED("box_topk_kernel");
   return OVM_OK;
 }
 

@@ -121,6 +121,8 @@ int ovm_struct_size(int which) {
     case 4: return (int)sizeof(ovm_fc_layer_t);
     case 5: return (int)sizeof(ovm_fc_stack_t);
     case 6: return (int)sizeof(ovm_workspace_t);
+    case 7: return (int)sizeof(ovm_box_inference_cfg_t);
+    case 8: return (int)sizeof(ovm_box_inference_ws_t);
     default: return -1;
   }
 }
@@ -234,6 +236,16 @@ int ovm_gdino_post(const float* logits, const float* boxes_cxcywh, const int32_t
   return gdino_post_launch(logits, boxes_cxcywh, phrase_ranges, batch, num_queries, num_tokens, num_phrases,
                            image_height, image_width, box_threshold, nms_threshold, out_boxes, out_scores,
                            out_classes, out_query, out_count, static_cast<cudaStream_t>(stream));
+}
+
+int ovm_box_inference(const ovm_box_inference_cfg_t* cfg, const float* logits, int64_t ld_logits,
+                      const float* deltas, int64_t ld_deltas, const float* proposals, const int32_t* seg_offsets,
+                      const int32_t* image_sizes, int32_t num_images, int32_t num_proposals, int32_t max_per_image,
+                      const ovm_box_inference_ws_t* ws, float* out_boxes, float* out_scores, int64_t* out_classes,
+                      int32_t* out_index, float* out_scores_full, int32_t* out_count, void* stream) {
+  return box_inference_launch(cfg, logits, ld_logits, deltas, ld_deltas, proposals, seg_offsets, image_sizes,
+                              num_images, num_proposals, max_per_image, ws, out_boxes, out_scores, out_classes,
+                              out_index, out_scores_full, out_count, static_cast<cudaStream_t>(stream));
 }
 
 }  // extern "C"

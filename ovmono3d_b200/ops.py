@@ -33,7 +33,7 @@ REC_CLASS = 46
 
 EXPORTS = ("ovm_abi_version", "ovm_last_error", "ovm_launch_count", "ovm_struct_size", "ovm_roi_align", "ovm_gemm_bf16",
            "ovm_bias_act", "ovm_cast_bf16", "ovm_head_decode", "ovm_lift_forward", "ovm_set_stage_events", "ovm_gemm_set_trace",
-           "ovm_roi_set_trace", "ovm_head_set_trace", "ovm_nms", "ovm_gdino_post")
+           "ovm_roi_set_trace", "ovm_head_set_trace", "ovm_nms", "ovm_gdino_post", "ovm_box_inference")
 NMS_MAX_SEGMENT = 4096
 NMS_AGNOSTIC, NMS_COORD_TRICK, NMS_PER_CLASS = 0, 1, 2
 
@@ -81,8 +81,18 @@ class ovm_workspace_t(C.Structure):
                 ("tile_counters", C.c_void_p), ("num_tile_counters", C.c_int32), ("_pad", C.c_int32)]
 
 
+class ovm_box_inference_cfg_t(C.Structure):
+    _fields_ = [("num_classes", C.c_int32), ("cls_agnostic_bbox_reg", C.c_int32), ("reg_weights", C.c_float * 4),
+                ("scale_clamp", C.c_float), ("score_thresh", C.c_float), ("nms_thresh", C.c_double),
+                ("topk_per_image", C.c_int32), ("coord_trick_max", C.c_int32)]
+
+
+class ovm_box_inference_ws_t(C.Structure):
+    _fields_ = [(k, C.c_void_p) for k in ("probs", "cand_boxes", "class_keep", "class_count", "image_stats")]
+
+
 ABI_STRUCTS = (ovm_level_t, ovm_pooler_t, ovm_decode_cfg_t, ovm_head_weights_t, ovm_fc_layer_t, ovm_fc_stack_t,
-               ovm_workspace_t)
+               ovm_workspace_t, ovm_box_inference_cfg_t, ovm_box_inference_ws_t)
 _LIB: Optional[C.CDLL] = None
 LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libovmono3d_lift.so")
 
@@ -120,6 +130,8 @@ def load_library() -> C.CDLL:
     lib.ovm_head_set_trace.argtypes = [vp]
     lib.ovm_set_stage_events.argtypes = [C.POINTER(C.c_void_p), i32]
     lib.ovm_nms.argtypes = [vp, vp, vp, vp, i32, i32, C.c_double, i32, vp, vp, vp]
+    lib.ovm_box_inference.argtypes = [C.POINTER(ovm_box_inference_cfg_t), vp, i64, vp, i64, vp, vp, vp, i32, i32, i32,
+                                      C.POINTER(ovm_box_inference_ws_t), vp, vp, vp, vp, vp, vp, vp]
     lib.ovm_gdino_post.argtypes = [vp, vp, vp, i32, i32, i32, i32, i32, i32, C.c_float, C.c_double, vp, vp, vp, vp,
                                    vp, vp]
     for name in EXPORTS[3:]:
@@ -350,3 +362,49 @@ def gdino_post(logits: torch.Tensor, boxes_cxcywh: torch.Tensor, phrase_ranges: 
                               _ptr(out_boxes), _ptr(out_scores), _ptr(out_classes), _ptr(out_query), _ptr(count),
                               _stream()), "ovm_gdino_post")
     return out_boxes[:, :nq], out_scores[:, :nq], out_classes[:, :nq], out_query[:, :nq], count[:B]
+
+
+def box_inference(logits: torch.Tensor, deltas: torch.Tensor, proposals: torch.Tensor, seg_offsets: torch.Tensor,
+                  image_sizes: torch.Tensor, max_per_image: int, num_classes: int, reg_weights: Sequence[float],
+                  score_thresh: float, nms_thresh: float, topk_per_image: int, cls_agnostic_bbox_reg: bool = False,
+                  coord_trick_max: int = 1000, want_scores_full: bool = True,
+                  scale_clamp: float = 4.135166556742356):
+    """`ovm_box_inference` (fast_rcnn.py:57-143).  logits [R, >=K+1], deltas [R, >=4K or 4] fp32 (row strides are
+    passed through), proposals [R,4], seg_offsets [N+1] int32, image_sizes [N,2] int32 (h, w), all CUDA.
+    Returns (boxes [N,cap,4], scores [N,cap], classes [N,cap] int64, index [N,cap] int32, scores_full [N,cap,K] or
+    None, count [N] int32)."""
+    lib = load_library()
+    for t, nm in ((logits, "logits"), (deltas, "deltas"), (proposals, "proposals")):
+        _need_cuda(t, nm, torch.float32)
+    _need_cuda(seg_offsets, "seg_offsets", torch.int32)
+    _need_cuda(image_sizes, "image_sizes", torch.int32)
+    if logits.stride(-1) != 1 or deltas.stride(-1) != 1:
+        raise LiftError("box_inference: logits / deltas rows must be contiguous")
+    proposals, image_sizes = proposals.contiguous(), image_sizes.contiguous()
+    R, K, N = proposals.shape[0], int(num_classes), seg_offsets.numel() - 1
+    dev = proposals.device
+    Kb = 1 if cls_agnostic_bbox_reg else K
+    per_class = min(topk_per_image, max_per_image) if topk_per_image >= 0 else max_per_image
+    cap = max(topk_per_image if topk_per_image >= 0 else K * per_class, 1)
+    cfg = ovm_box_inference_cfg_t(K, int(bool(cls_agnostic_bbox_reg)), (C.c_float * 4)(*[float(w) for w in reg_weights]),
+                                  float(scale_clamp), float(score_thresh), float(nms_thresh), int(topk_per_image),
+                                  int(coord_trick_max))
+    scratch = dict(probs=torch.empty((max(R, 1), K), dtype=torch.float32, device=dev),
+                   cand_boxes=torch.empty((max(R, 1), Kb, 4), dtype=torch.float32, device=dev),
+                   class_keep=torch.empty((max(N, 1), K, max(max_per_image, 1)), dtype=torch.int32, device=dev),
+                   class_count=torch.empty((max(N, 1), K), dtype=torch.int32, device=dev),
+                   image_stats=torch.empty((max(N, 1), 2), dtype=torch.int32, device=dev))
+    ws = ovm_box_inference_ws_t(*[scratch[k].data_ptr() for k in ("probs", "cand_boxes", "class_keep", "class_count",
+                                                                  "image_stats")])
+    out_boxes = torch.empty((max(N, 1), cap, 4), dtype=torch.float32, device=dev)
+    out_scores = torch.empty((max(N, 1), cap), dtype=torch.float32, device=dev)
+    out_classes = torch.empty((max(N, 1), cap), dtype=torch.int64, device=dev)
+    out_index = torch.empty((max(N, 1), cap), dtype=torch.int32, device=dev)
+    out_full = torch.empty((max(N, 1), cap, K), dtype=torch.float32, device=dev) if want_scores_full else None
+    count = torch.zeros((max(N, 1),), dtype=torch.int32, device=dev)
+    _check(lib.ovm_box_inference(C.byref(cfg), _ptr(logits) if R else None, logits.stride(0) if R else K + 1,
+                                 _ptr(deltas) if R else None, deltas.stride(0) if R else 4 * Kb,
+                                 _ptr(proposals) if R else None, _ptr(seg_offsets), _ptr(image_sizes), N, R,
+                                 int(max_per_image), C.byref(ws), _ptr(out_boxes), _ptr(out_scores), _ptr(out_classes),
+                                 _ptr(out_index), _ptr(out_full), _ptr(count), _stream()), "ovm_box_inference")
+    return out_boxes[:N], out_scores[:N], out_classes[:N], out_index[:N], (out_full[:N] if want_scores_full else None), count[:N]

@@ -180,9 +180,15 @@ class ROIHeads3DB200(nn.Module):
         scale_roi_boxes=None,
         num_classes: int = 50,
         box_in_features: Optional[List[str]] = None,
+        box_pooler: Optional[nn.Module] = None,
+        box_head: Optional[nn.Module] = None,
+        box_predictor: Optional[nn.Module] = None,
         **kwargs: Any,
     ):
         super().__init__()
+        self._box_branch = None
+        if box_head is not None:        # the 2-D box branch (roi_heads.py:252-296), same module names as the reference
+            self.box_pooler, self.box_head, self.box_predictor = box_pooler, box_head, box_predictor
         self.num_classes = num_classes
         self.in_features = self.box_in_features = list(box_in_features or [])
         self.scale_roi_boxes = scale_roi_boxes or 0.0
@@ -225,7 +231,30 @@ class ROIHeads3DB200(nn.Module):
         ret = dict(num_classes=cfg.MODEL.ROI_HEADS.NUM_CLASSES, box_in_features=list(cfg.MODEL.ROI_HEADS.IN_FEATURES))
         ret.update(cls._init_cube_head(cfg, input_shape))
         ret["priors"] = priors
+        if cfg.MODEL.get("ROI_BOX_HEAD") is not None and cfg.MODEL.ROI_BOX_HEAD.get("BUILD", False):
+            ret.update(cls._init_box_head(cfg, input_shape))
         return ret
+
+    @classmethod
+    def _init_box_head(cls, cfg, input_shape: Dict[str, ShapeSpec]):
+        """d2 `StandardROIHeads._init_box_head`.  The reference always builds the branch; here it is built on request
+        (MODEL.ROI_BOX_HEAD.BUILD) because `ROIHeads3DGDINO` only reads `image_size` and the device off its result
+        (roi_heads_gdino.py:128,131,156,168) -- 52 MB of weights and a full FC pass per image for nothing."""
+        from .box_head import build_box_branch
+        return build_box_branch(cfg, input_shape, ROIPooler)
+
+    def _forward_box(self, features: Dict[str, torch.Tensor], proposals: List[Instances]) -> List[Instances]:
+        """Inference branch of `ROIHeads3D._forward_box` (roi_heads.py:252-296): `proposal_boxes` -> `Instances` with
+        `pred_boxes`, `scores`, `scores_full`, `pred_classes` (fast_rcnn.py:111-116)."""
+        if self.training:
+            raise NotImplementedError("training losses are outside the lift path (SURVEY.md section 8)")
+        if getattr(self, "box_head", None) is None:
+            raise ops.LiftError("this head was built without its 2-D box branch (MODEL.ROI_BOX_HEAD.BUILD)")
+        if self._box_branch is None:
+            from .box_head import BoxBranchB200
+            self._box_branch = BoxBranchB200(self.box_pooler, self.box_head, self.box_predictor)
+        feats = [features[f] for f in self.box_in_features]
+        return self._box_branch.forward_box(feats, proposals)
 
     @classmethod
     def _init_cube_head(cls, cfg, input_shape: Dict[str, ShapeSpec]):
@@ -271,6 +300,8 @@ class ROIHeads3DB200(nn.Module):
                 else:
                     inst.scores = torch.ones_like(proposal["gt_classes"]).float().to(device=device)
                 pred_instances.append(inst)
+        elif proposals and all(p.has("proposal_boxes") and not p.has("pred_boxes") for p in proposals):
+            pred_instances = self._forward_box(features, proposals)       # roi_heads.py:245
         else:
             pred_instances = proposals
         if self.loss_w_3d > 0:

@@ -136,8 +136,48 @@ def run_gdino_case(case) -> dict:
     return rec
 
 
+def run_box_case(case) -> dict:
+    """Drive the reference's own `fast_rcnn_inference` (fast_rcnn.py:16-116) on boxes / probabilities computed by the
+    oracle's restatement of d2 `predict_boxes` / `predict_probs`."""
+    import importlib
+
+    from oracle import box_head_oracle as bo
+    from tests.golden import box_cases as bc
+
+    rh.install_stubs()
+    sys.modules.pop("cubercnn.modeling.roi_heads.fast_rcnn", None)
+    d2_layers = importlib.import_module("detectron2.layers")
+    d2_layers.batched_nms = lambda boxes, scores, idxs, thr: __import__("torchvision").ops.batched_nms(
+        boxes.float(), scores, idxs, thr)                       # d2 layers/nms.py
+    d2_layers.cat = torch.cat
+    mod = importlib.import_module("cubercnn.modeling.roi_heads.fast_rcnn")
+    logits, deltas, props = bc.build_case(case)
+    boxes, probs = bo.predict(logits, deltas, props, bc.REG_WEIGHTS)
+    insts, kept = mod.fast_rcnn_inference(boxes, probs, list(case.image_sizes), case.score_thresh, case.nms_thresh,
+                                          case.topk)
+    rec = {"checksum": bc.input_checksum(logits, deltas, props)}
+    for i, (inst, k) in enumerate(zip(insts, kept)):
+        rec["im%d_boxes" % i] = inst.pred_boxes.tensor.numpy()
+        rec["im%d_scores" % i] = inst.scores.numpy()
+        rec["im%d_scores_full" % i] = inst.scores_full.numpy()[:, :: max(1, case.num_classes // 5)]
+        rec["im%d_classes" % i] = inst.pred_classes.numpy()
+        rec["im%d_index" % i] = k.numpy()
+    return rec
+
+
 def main() -> None:
+    from tests.golden import box_cases as bc
     from tests.golden import gdino_cases as gd
+
+    if not sys.argv[1:] or any(n in bc.CASE_BY_NAME for n in sys.argv[1:]):
+        for case in bc.CASES:
+            if sys.argv[1:] and case.name not in sys.argv[1:]:
+                continue
+            rec = run_box_case(case)
+            np.savez_compressed(bc.golden_path(case), **rec)
+            print("%-32s kept=%s %6.1f KB" % (case.name, [len(rec["im%d_scores" % i]) for i in
+                                                          range(len(case.image_sizes))],
+                                              os.path.getsize(bc.golden_path(case)) / 1024))
 
     all_names = [c.name for c in gc.CASES] + [c.name for c in gd.CASES]
     names = sys.argv[1:] or all_names
