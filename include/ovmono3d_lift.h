@@ -120,6 +120,10 @@ int ovm_roi_set_trace(uint64_t* buf);
  * 5 record written.  NULL switches it off.                                                                  */
 int ovm_head_set_trace(uint64_t* buf);
 
+/* Same for ovm_gdino_post (tools/gdino_post_bench.py --trace): [batch, 8] stamps of each CTA's thread 0 -- 0 entry,
+ * 1 query scores done, 2 sorted, 3 boxes staged, 4 suppression done, 5 exit.  NULL switches it off.               */
+int ovm_post_set_trace(uint64_t* buf);
+
 /* out[m, j] = act(in[m, j] + bias[j]) for j < N; in fp32 [M, ldi], out out_dtype [M, ldo]. */
 int ovm_bias_act(const float* in, int64_t ldi, const float* bias, int32_t relu, int32_t M, int32_t N,
                  void* out, int32_t out_dtype, int64_t ldo, void* stream);

@@ -103,6 +103,7 @@ int gemm_bf16_launch(const void* A, int64_t lda, const void* B, int64_t ldb, int
 void gemm_set_trace(unsigned long long* buf);
 void roi_set_trace(unsigned long long* buf);
 void head_set_trace(unsigned long long* buf);
+void post_set_trace(unsigned long long* buf);
 int bias_act_launch(const float* in, int64_t ldi, const float* bias, int32_t relu, int32_t M, int32_t N,
                     void* out, int32_t out_dtype, int64_t ldo, cudaStream_t stream, bool clear_in = false);
 int cast_bf16_launch(const float* in, int64_t ld_in, int32_t rows, int32_t cols, void* out, int64_t ld_out,

@@ -20,6 +20,16 @@ constexpr int kPostThreads = 1024;
 constexpr int kPostWarps = kPostThreads / 32;
 constexpr uint64_t kPadKey = ~0ull;
 
+thread_local unsigned long long* g_post_trace = nullptr;   // ovm_post_set_trace
+
+__device__ __forceinline__ void post_stamp(unsigned long long* trace, int slot) {
+  if (trace && threadIdx.x == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    trace[blockIdx.x * 8 + slot] = t;
+  }
+}
+
 // fp32 -> 32-bit key whose unsigned ascending order is the descending order of the floats (-0 == +0)
 __device__ __forceinline__ uint32_t score_key_desc(float s) {
   if (s == 0.0f) s = 0.0f;
@@ -253,7 +263,7 @@ gdino_post_kernel(const float* __restrict__ logits, const float* __restrict__ bo
                   const int32_t* __restrict__ phrase_ranges, int nq, int T, int P, float img_w, float img_h,
                   float box_thr, double nms_thr, float* __restrict__ out_boxes, float* __restrict__ out_scores,
                   int64_t* __restrict__ out_classes, int32_t* __restrict__ out_query,
-                  int32_t* __restrict__ out_count) {
+                  int32_t* __restrict__ out_count, unsigned long long* trace) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int b = blockIdx.x;
   const int npad = next_pow2(nq);
@@ -263,17 +273,33 @@ gdino_post_kernel(const float* __restrict__ logits, const float* __restrict__ bo
   float* rows = reinterpret_cast<float*>(s.tail + (size_t)npad * 8);        // [kPostWarps][T]
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const float* lg = logits + (size_t)b * nq * T;
+  post_stamp(trace, 0);
 
   // 1. per query: sigmoid of its token logits, phrase sums, max / first argmax (roi_heads_gdino.py:186-202, 296-317)
   float* row = rows + (size_t)warp * T;
+  // only the token columns some phrase covers are ever summed: [t_lo, t_hi) (GroundingDINO fills the columns past the
+  // caption with -inf, whose sigmoid would take the slow paths of expf and the reciprocal for nothing)
+  int2* pr = reinterpret_cast<int2*>(rows + (size_t)kPostWarps * T);          // [P] phrase ranges, clamped to [0, T]
+  for (int p = threadIdx.x; p < P; p += kPostThreads)
+    pr[p] = make_int2(min(max(phrase_ranges[2 * p], 0), T), min(max(phrase_ranges[2 * p + 1], 0), T));
+  __syncthreads();
+  int t_lo = T, t_hi = 0;
+  for (int p = lane; p < P; p += 32) {
+    t_lo = min(t_lo, pr[p].x);
+    t_hi = max(t_hi, pr[p].y);
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    t_lo = min(t_lo, __shfl_xor_sync(0xFFFFFFFFu, t_lo, o));
+    t_hi = max(t_hi, __shfl_xor_sync(0xFFFFFFFFu, t_hi, o));
+  }
   for (int q = warp; q < nq; q += kPostWarps) {
     const float* src = lg + (size_t)q * T;
-    for (int t = lane; t < T; t += 32) row[t] = __fdiv_rn(1.0f, __fadd_rn(1.0f, expf(-src[t])));
+    for (int t = t_lo + lane; t < t_hi; t += 32) row[t] = __frcp_rn(__fadd_rn(1.0f, expf(-src[t])));   // = 1 / (1 + e^-x)
     __syncwarp();
     float best = -INFINITY;
     int best_p = 0x7FFFFFFF;
     for (int p = lane; p < P; p += 32) {
-      const int t0 = phrase_ranges[2 * p], t1 = phrase_ranges[2 * p + 1];
+      const int t0 = pr[p].x, t1 = pr[p].y;
       float sum = 0.0f;
       for (int t = t0; t < t1; ++t) sum = __fadd_rn(sum, row[t]);
       if (sum > best || (sum != sum && best == best)) {   // NaN wins like torch.max, first occurrence kept
@@ -298,6 +324,7 @@ gdino_post_kernel(const float* __restrict__ logits, const float* __restrict__ bo
     __syncwarp();
   }
   __syncthreads();
+  post_stamp(trace, 1);
 
   // 2. candidates = queries above the box threshold, in stable decreasing score order
   for (int i = threadIdx.x; i < npad; i += kPostThreads) {
@@ -305,6 +332,7 @@ gdino_post_kernel(const float* __restrict__ logits, const float* __restrict__ bo
     s.keys[i] = ok ? ((uint64_t)score_key_desc(q_score[i]) << 32) | (uint32_t)i : kPadKey;
   }
   block_sort(s.keys, npad);
+  post_stamp(trace, 2);
   // number of candidates = first pad key (keys are sorted)
   int* n_cand = s.warp_tot + kPostWarps;
   if (threadIdx.x == 0) *n_cand = npad;
@@ -326,7 +354,9 @@ gdino_post_kernel(const float* __restrict__ logits, const float* __restrict__ bo
       s.sb[p] = make_float4(__fsub_rn(cx, hw), __fsub_rn(cy, hh), __fadd_rn(cx, hw), __fadd_rn(cy, hh));
     }
   }
+  post_stamp(trace, 3);
   block_greedy(s.sb, nullptr, s.alive, n, nms_thr, reinterpret_cast<uint32_t*>(s.warp_tot));
+  post_stamp(trace, 4);
 
   // 4. survivors in keep order
   float4* ob = reinterpret_cast<float4*>(out_boxes) + (size_t)b * nq;
@@ -499,27 +529,46 @@ box_class_nms_kernel(BoxCfg cfg, const float* __restrict__ probs, const float* _
 __global__ void __launch_bounds__(kPostThreads, 1)
 box_topk_kernel(BoxCfg cfg, const float* __restrict__ probs, const float* __restrict__ cand_boxes,
                 const int32_t* __restrict__ seg_offsets, int max_per_image, const int32_t* __restrict__ class_keep,
-                const int32_t* __restrict__ class_count, int npad, int cap, float* __restrict__ out_boxes,
+                const int32_t* __restrict__ class_count, int npad, int npad_small, int cap, float* __restrict__ out_boxes,
                 float* __restrict__ out_scores, int64_t* __restrict__ out_classes, int32_t* __restrict__ out_index,
                 float* __restrict__ out_scores_full, int32_t* __restrict__ out_count) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   uint64_t* keys = reinterpret_cast<uint64_t*>(smem_raw);            // [npad]
-  int* offs = reinterpret_cast<int*>(smem_raw + (size_t)npad * 8);   // [K + 1]
+  uint64_t* small = keys + npad;                                     // [npad_small]: the selected top-k keys
+  int* offs = reinterpret_cast<int*>(smem_raw + (size_t)(npad + npad_small) * 8);   // [K + 1]
   const int img = blockIdx.x, K = cfg.K;
   const int r0 = seg_offsets[img];
   const int len = min(seg_offsets[img + 1] - r0, max_per_image);
   const int per_class = cfg.topk >= 0 ? min(cfg.topk, max_per_image) : max_per_image;
-  if (threadIdx.x == 0) {
-    int acc = 0;
-    for (int k = 0; k < K; ++k) {
-      offs[k] = acc;
-      acc += len > 0 ? min(class_count[img * K + k], per_class) : 0;
+  int* wsum = offs + K + 1;                                          // [33]
+  {   // offs = exclusive scan over the classes of min(survivors, top-k): K <= 1024 = one value per thread
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int c = (threadIdx.x < K && len > 0) ? min(class_count[img * K + threadIdx.x], per_class) : 0;
+    int incl = c;
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+      if (lane >= o) incl += y;
     }
-    offs[K] = acc;
+    if (lane == 31) wsum[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+      const int v = wsum[lane];
+      int wi = v;
+      for (int o = 1; o < 32; o <<= 1) {
+        const int y = __shfl_up_sync(0xFFFFFFFFu, wi, o);
+        if (lane >= o) wi += y;
+      }
+      wsum[lane] = wi - v;
+      if (lane == 31) wsum[32] = wi;
+    }
+    __syncthreads();
+    if (threadIdx.x < K) offs[threadIdx.x] = wsum[warp] + incl - c;
+    if (threadIdx.x == 0) offs[K] = wsum[32];
   }
-  for (int i = threadIdx.x; i < npad; i += kPostThreads) keys[i] = kPadKey;
   __syncthreads();
   const int total = offs[K];
+  npad = min(npad, next_pow2(total));      // sort what is there, not the worst case the buffer was sized for
+  for (int i = total + threadIdx.x; i < npad; i += kPostThreads) keys[i] = kPadKey;
   // a class list is already in decreasing score order: only its first top-k entries can reach the image's top-k
   for (int k = threadIdx.x >> 5; k < K; k += kPostWarps) {
     const int c = offs[k + 1] - offs[k];
@@ -530,8 +579,68 @@ box_topk_kernel(BoxCfg cfg, const float* __restrict__ probs, const float* __rest
       keys[offs[k] + j] = ((uint64_t)score_key_desc(sc) << 32) | (uint32_t)(r * K + k);   // ties: (r, k) row-major,
     }                                                                                      // the order of nonzero()
   }
-  block_sort(keys, npad);
   const int n_out = cfg.topk >= 0 ? min(total, cfg.topk) : total;
+  if (n_out > 0 && n_out < total && next_pow2(n_out) <= npad_small) {
+    // Far more survivors than top-k (5000 against 100 at the shipped sizes): radix-select the top-k-th key, eight
+    // 8-bit passes over the unsorted keys with a 256-bin shared-memory histogram, then sort only the selected keys
+    // (sorting all 8192 slots took 84 us of the branch's 126).  Keys are unique, so exactly n_out keys are <= it.
+    uint32_t* hist = reinterpret_cast<uint32_t*>(wsum + 33);         // [256]
+    int* sel = reinterpret_cast<int*>(hist + 256);                   // [0] bin, [1] rank left inside the bin, [2] slot counter
+    uint64_t prefix = 0;
+    int want = n_out;
+    __syncthreads();
+    for (int shift = 56; shift >= 0; shift -= 8) {
+      for (int i = threadIdx.x; i < 256; i += kPostThreads) hist[i] = 0;
+      __syncthreads();
+      const uint64_t hi_mask = shift == 56 ? 0ull : (~0ull << (shift + 8));
+      for (int i = threadIdx.x; i < total; i += kPostThreads) {
+        const uint64_t k = keys[i];
+        if ((k & hi_mask) == prefix) atomicAdd(&hist[(uint32_t)(k >> shift) & 255u], 1u);
+      }
+      __syncthreads();
+      if (threadIdx.x < 32) {
+        const int lane = threadIdx.x;
+        uint32_t h[8], loc = 0;
+#pragma unroll
+        for (int b = 0; b < 8; ++b) {
+          h[b] = hist[lane * 8 + b];
+          loc += h[b];
+        }
+        uint32_t incl = loc;
+        for (int o = 1; o < 32; o <<= 1) {
+          const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+          if (lane >= o) incl += y;
+        }
+        uint32_t before = incl - loc;
+        if (before < (uint32_t)want && (uint32_t)want <= incl) {      // the crossing is inside this lane's 8 bins
+#pragma unroll
+          for (int b = 0; b < 8; ++b) {
+            if (before < (uint32_t)want && (uint32_t)want <= before + h[b]) {
+              sel[0] = lane * 8 + b;
+              sel[1] = want - (int)before;
+            }
+            before += h[b];
+          }
+        }
+      }
+      __syncthreads();
+      prefix |= (uint64_t)(uint32_t)sel[0] << shift;
+      want = sel[1];
+      __syncthreads();
+    }
+    const int np2 = next_pow2(n_out);
+    if (threadIdx.x == 0) sel[2] = 0;
+    for (int i = threadIdx.x; i < np2; i += kPostThreads) small[i] = kPadKey;
+    __syncthreads();
+    for (int i = threadIdx.x; i < total; i += kPostThreads) {
+      const uint64_t k = keys[i];
+      if (k <= prefix) small[atomicAdd(&sel[2], 1)] = k;
+    }
+    block_sort(small, np2);
+    keys = small;
+  } else {
+    block_sort(keys, npad);
+  }
   const int Kb = cfg.agnostic ? 1 : K;
   const float4* cb = reinterpret_cast<const float4*>(cand_boxes);
   for (int j = threadIdx.x; j < n_out; j += kPostThreads) {
@@ -559,6 +668,8 @@ int host_next_pow2(int n) {
 }
 
 }  // namespace
+
+void post_set_trace(unsigned long long* buf) { g_post_trace = buf; }
 
 int nms_launch(const float* boxes, const float* scores, const int64_t* classes, const int32_t* seg_offsets,
                int32_t num_segments, int32_t max_segment_len, double iou_threshold, int32_t mode, int32_t* keep,
@@ -604,7 +715,7 @@ int gdino_post_launch(const float* logits, const float* boxes_cxcywh, const int3
     return OVM_OK;
   }
   const int npad = host_next_pow2(nq);
-  const size_t smem = post_smem_bytes(npad) + (size_t)npad * 8 + (size_t)kPostWarps * T * 4;
+  const size_t smem = post_smem_bytes(npad) + (size_t)npad * 8 + (size_t)kPostWarps * T * 4 + (size_t)P * 8;
   OVM_REQUIRE(smem <= 227 * 1024, "ovm_gdino_post: %zu bytes of shared memory needed", smem);
   static size_t configured = 0;
   if (smem > configured) {
@@ -614,7 +725,7 @@ int gdino_post_launch(const float* logits, const float* boxes_cxcywh, const int3
   gdino_post_kernel<<<batch, kPostThreads, smem, stream>>>(logits, boxes_cxcywh, phrase_ranges, nq, T, P,
                                                            (float)image_width, (float)image_height, box_threshold,
                                                            nms_threshold, out_boxes, out_scores, out_classes,
-                                                           out_query, out_count);
+                                                           out_query, out_count, g_post_trace);
   OVM_LAUNCHED("gdino_post_kernel");
   return OVM_OK;
 }
@@ -681,14 +792,15 @@ int box_inference_launch(const ovm_box_inference_cfg_t* c, const float* logits, 
                                                                       ws->class_count);
   OVM_LAUNCHED("box_class_nms_kernel");
   const int npad = host_next_pow2((int)std::max<int64_t>(merged, 1));
-  const size_t smem_topk = (size_t)npad * 8 + (size_t)(K + 1) * 4;
+  const int npad_small = c->topk_per_image >= 0 && c->topk_per_image <= 2048 ? host_next_pow2(c->topk_per_image) : 0;
+  const size_t smem_topk = (size_t)(npad + npad_small) * 8 + (size_t)(K + 1 + 33 + 256 + 4) * 4;
   static size_t conf_topk = 0;
   if (smem_topk > conf_topk) {
     OVM_CUDA(cudaFuncSetAttribute(box_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_topk));
     conf_topk = smem_topk;
   }
   box_topk_kernel<<<N, kPostThreads, smem_topk, stream>>>(b, ws->probs, ws->cand_boxes, seg_offsets, max_per_image,
-                                                          ws->class_keep, ws->class_count, npad, cap, out_boxes,
+                                                          ws->class_keep, ws->class_count, npad, npad_small, cap, out_boxes,
                                                           out_scores, out_classes, out_index, out_scores_full,
                                                           out_count);
   OVM_LAUNCHED("box_topk_kernel");

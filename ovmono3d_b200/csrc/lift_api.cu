@@ -166,6 +166,11 @@ int ovm_head_set_trace(uint64_t* buf) {
   return OVM_OK;
 }
 
+int ovm_post_set_trace(uint64_t* buf) {
+  post_set_trace(reinterpret_cast<unsigned long long*>(buf));
+  return OVM_OK;
+}
+
 int ovm_bias_act(const float* in, int64_t ldi, const float* bias, int32_t relu, int32_t M, int32_t N, void* out,
                  int32_t out_dtype, int64_t ldo, void* stream) {
   return bias_act_launch(in, ldi, bias, relu, M, N, out, out_dtype, ldo, static_cast<cudaStream_t>(stream));

@@ -33,7 +33,7 @@ REC_CLASS = 46
 
 EXPORTS = ("ovm_abi_version", "ovm_last_error", "ovm_launch_count", "ovm_struct_size", "ovm_roi_align", "ovm_gemm_bf16",
            "ovm_bias_act", "ovm_cast_bf16", "ovm_head_decode", "ovm_lift_forward", "ovm_set_stage_events", "ovm_gemm_set_trace",
-           "ovm_roi_set_trace", "ovm_head_set_trace", "ovm_nms", "ovm_gdino_post", "ovm_box_inference")
+           "ovm_roi_set_trace", "ovm_head_set_trace", "ovm_nms", "ovm_gdino_post", "ovm_box_inference", "ovm_post_set_trace")
 NMS_MAX_SEGMENT = 4096
 NMS_AGNOSTIC, NMS_COORD_TRICK, NMS_PER_CLASS = 0, 1, 2
 
@@ -128,6 +128,7 @@ def load_library() -> C.CDLL:
     lib.ovm_gemm_set_trace.argtypes = [vp]
     lib.ovm_roi_set_trace.argtypes = [vp]
     lib.ovm_head_set_trace.argtypes = [vp]
+    lib.ovm_post_set_trace.argtypes = [vp]
     lib.ovm_set_stage_events.argtypes = [C.POINTER(C.c_void_p), i32]
     lib.ovm_nms.argtypes = [vp, vp, vp, vp, i32, i32, C.c_double, i32, vp, vp, vp]
     lib.ovm_box_inference.argtypes = [C.POINTER(ovm_box_inference_cfg_t), vp, i64, vp, i64, vp, vp, vp, i32, i32, i32,

@@ -24,6 +24,7 @@ def main() -> None:
     ap.add_argument("--queries", type=int, default=900)
     ap.add_argument("--batch", type=int, default=1)
     ap.add_argument("--iters", type=int, default=200)
+    ap.add_argument("--trace", action="store_true", help="per-phase %%globaltimer stamps of one call (ovm_post_set_trace)")
     a = ap.parse_args()
     dev = torch.device("cuda:0")
     case = gd.GdinoCase("bench", 5, a.queries, 256, gd.OMNI, (896, 1184))
@@ -61,6 +62,17 @@ def main() -> None:
     torch.cuda.synchronize()
     ref_us = (time.perf_counter() - t0) * 1e6 / n_ref
     assert kept == len(ref["scores"])
+    phases = None
+    if a.trace:
+        buf = torch.zeros(a.batch * 8, dtype=torch.int64, device=dev)
+        lib = ops.load_library()
+        lib.ovm_post_set_trace(buf.data_ptr())
+        ops.gdino_post(lg, bx, ranges, case.image_hw, 0.001, 0.5)
+        torch.cuda.synchronize()
+        lib.ovm_post_set_trace(None)
+        st = buf.view(a.batch, 8)[0].tolist()
+        names = ["query scores", "sort", "box staging", "suppression", "gather"]
+        phases = {nm: (st[i + 1] - st[i]) / 1e3 for i, nm in enumerate(names)}
     # NMS alone, 16 images x 1000 boxes per launch
     g = torch.Generator().manual_seed(1)
     n, S = 1000, 16
@@ -91,7 +103,7 @@ def main() -> None:
     print(json.dumps({
         "gdino_post": {"queries": a.queries, "batch": a.batch, "phrases": len(cap_list), "kept": kept,
                        "ours_us_device": ours_us, "ours_us_with_count_readback": ours_sync_us,
-                       "reference_sequence_us": ref_us, "speedup_vs_reference_sequence": ref_us / ours_sync_us},
+                       "reference_sequence_us": ref_us, "speedup_vs_reference_sequence": ref_us / ours_sync_us, "phase_us": phases},
         "nms_16x1000": {"ours_us": nms_us, "kept_mean": float(cnt.float().mean()),
                         "torchvision_cuda_nms_16_calls_us": tv_us, "speedup": tv_us / nms_us}}))
 
