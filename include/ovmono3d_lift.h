@@ -121,7 +121,8 @@ int ovm_roi_set_trace(uint64_t* buf);
 int ovm_head_set_trace(uint64_t* buf);
 
 /* Same for ovm_gdino_post (tools/gdino_post_bench.py --trace): [batch, 8] stamps of each CTA's thread 0 -- 0 entry,
- * 1 query scores done, 2 sorted, 3 boxes staged, 4 suppression done, 5 exit.  NULL switches it off.               */
+ * 1 query scores loaded, 2 sorted, 3 boxes staged, 4 suppression done, 5 exit, 6 / 7 SM cycles inside the suppression
+ * (pair tests << 32 | serial resolve; later positions).  NULL switches it off.               */
 int ovm_post_set_trace(uint64_t* buf);
 
 /* out[m, j] = act(in[m, j] + bias[j]) for j < N; in fp32 [M, ldi], out out_dtype [M, ldo]. */
@@ -226,7 +227,8 @@ int ovm_nms(const float* boxes, const float* scores, const int64_t* classes, con
             int32_t num_segments, int32_t max_segment_len, double iou_threshold, int32_t mode, int32_t* keep,
             int32_t* keep_count, void* stream);
 
-/* GroundingDINO outputs -> prompt boxes of the lift, one CTA per image, one launch.
+/* GroundingDINO outputs -> prompt boxes of the lift in two launches: query scores (a warp per query, all SMs), then
+ * one CTA per image for everything else.
  * logits [B, nq, T] fp32 raw `pred_logits` (sigmoid is applied here), boxes_cxcywh [B, nq, 4] fp32 `pred_boxes`
  * (normalised), phrase_ranges [P, 2] int32 (device): token columns [begin, end) of phrase p in the tokenised caption
  * (roi_heads_gdino.py:300-311).  A query survives when max_p sum_t sigmoid(logit[q, t in phrase p]) > box_threshold;

@@ -69,71 +69,121 @@ __device__ __forceinline__ float box_area(const float4& b) {
   return __fmul_rn(__fsub_rn(b.z, b.x), __fsub_rn(b.w, b.y));
 }
 
-__device__ __forceinline__ bool suppresses(const float4& a, float area_a, const float4& b, double thr) {
+struct IouThr {
+  double thr;     // the reference's threshold (compared in double, as torchvision's CPU kernel does)
+  float thr_f;    // (float)thr, for the one-product decision far from the threshold
+  bool fast;      // thr in a range where that decision is safe
+};
+__device__ __forceinline__ IouThr make_thr(double thr) {
+  IouThr t;
+  t.thr = thr;
+  t.thr_f = (float)thr;
+  t.fast = thr > 0.0 && thr < 1.0e6;
+  return t;
+}
+
+__device__ __forceinline__ bool suppresses(const float4& a, float area_a, const float4& b, float area_b,
+                                           const IouThr& t) {
   const float xx1 = fmaxf(a.x, b.x), yy1 = fmaxf(a.y, b.y);
   const float xx2 = fminf(a.z, b.z), yy2 = fminf(a.w, b.w);
   const float w = fmaxf(0.0f, __fsub_rn(xx2, xx1)), h = fmaxf(0.0f, __fsub_rn(yy2, yy1));
   const float inter = __fmul_rn(w, h);
-  if (inter <= 0.0f && thr >= 0.0) return false;   // 0 / union is 0 (or NaN for two empty boxes): never above thr
-  const float ovr = __fdiv_rn(inter, __fsub_rn(__fadd_rn(area_a, box_area(b)), inter));
-  return (double)ovr > thr;
+  if (inter <= 0.0f && t.thr >= 0.0) return false;   // 0 / union is 0 (or NaN for two empty boxes): never above thr
+  const float uni = __fsub_rn(__fadd_rn(area_a, area_b), inter);
+  // far from the threshold the quotient's rounding cannot matter (|error| < 1e-6 relative): decide with one product;
+  // only within 1e-4 of it, or for a degenerate union, do the reference's division and its comparison in double
+  const float tu = t.thr_f * uni;
+  if (t.fast && uni > 0.0f && tu > 1.0e-30f && tu < 3.0e38f) {
+    if (inter > tu * 1.0001f) return true;
+    if (inter < tu * 0.9999f) return false;
+  }
+  const float ovr = __fdiv_rn(inter, uni);
+  return (double)ovr > t.thr;
 }
 
 // Greedy suppression over boxes already in decreasing score order, 32 sorted positions per round.
 //   1. the 32 x 32 tests inside the round's block, one per thread (warp = candidate, lane = earlier candidate);
-//   2. warp 0 walks the block serially on the resulting bit rows: K = candidates of the block that are kept;
+//   2. warp 0 resolves the block on the resulting bit rows (fixed point, see below): K = its kept candidates;
 //   3. every thread tests its own later positions against the kept candidates only.
 // Three barriers per 32 positions whatever the number of survivors (a barrier per kept box costs 0.5 us each).
 // cls == nullptr: every pair competes.  alive[i] is 1 on entry for i < n.  blockDim.x must be kPostThreads.
 __device__ void block_greedy(const float4* sb, const int32_t* cls, volatile uint8_t* alive, int n, double thr,
-                             uint32_t* mrow /* [33] shared */) {
+                             uint32_t* mrow /* [33] shared */, unsigned long long* trace = nullptr) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  long long c1 = 0, c2 = 0, c3 = 0, t0 = 0, t1 = 0, t2 = 0;   // thread 0's cycles in the three steps (trace only)
+  const IouThr T = make_thr(thr);
   __syncthreads();
   for (int i0 = 0; i0 < n; i0 += 32) {
+    if (trace) t0 = clock64();
     {
       const int c = i0 + warp, e = i0 + lane;
       bool sup = false;
       if (lane < warp && c < n && (!cls || cls[c] == cls[e])) {
-        const float4 be = sb[e];
-        sup = suppresses(be, box_area(be), sb[c], thr);
+        const float4 be = sb[e], bc = sb[c];
+        sup = suppresses(be, box_area(be), bc, box_area(bc), T);
       }
       const uint32_t m = __ballot_sync(0xFFFFFFFFu, sup);
       if (lane == 0) mrow[warp] = m;
     }
     __syncthreads();
+    if (trace) t1 = clock64();
     if (warp == 0) {
+      // Greedy resolution of the block as a fixed point instead of a 32-step dependent chain (which, with the other
+      // 31 warps parked at the barrier and nothing to hide ALU latency, cost ~1000 cycles per round): a candidate is
+      // kept once every earlier candidate that overlaps it is dead, dead once one of them is kept.  The lowest
+      // undecided candidate is decided in every pass; typical depth is 2-4 passes of three ballots.
       const uint32_t m = mrow[lane];
-      const uint32_t abits = __ballot_sync(0xFFFFFFFFu, i0 + lane < n && alive[i0 + lane]);
+      const bool al = i0 + lane < n && alive[i0 + lane];
+      uint32_t dead = ~__ballot_sync(0xFFFFFFFFu, al);
       uint32_t K = 0;
-#pragma unroll
-      for (int c = 0; c < 32; ++c) {
-        const uint32_t mc = __shfl_sync(0xFFFFFFFFu, m, c);
-        if (((abits >> c) & 1u) && !(mc & K)) K |= 1u << c;
+      bool undecided = al;
+      while (true) {
+        const bool k_now = undecided && (m & ~dead) == 0u;
+        const bool d_now = undecided && (m & K) != 0u;
+        K |= __ballot_sync(0xFFFFFFFFu, k_now);
+        dead |= __ballot_sync(0xFFFFFFFFu, d_now);
+        undecided = undecided && !k_now && !d_now;
+        if (__ballot_sync(0xFFFFFFFFu, undecided) == 0u) break;
       }
       if (lane == 0) mrow[32] = K;
       if (i0 + lane < n) alive[i0 + lane] = (K >> lane) & 1u;
     }
     __syncthreads();
+    if (trace) t2 = clock64();
     const uint32_t K = mrow[32];
     if (K) {
       for (int j = i0 + 32 + threadIdx.x; j < n; j += kPostThreads) {
         if (!alive[j]) continue;
         const float4 bj = sb[j];
+        const float aj = box_area(bj);
         const int cj = cls ? cls[j] : 0;
         uint32_t k = K;
-        while (k) {
+        const int nk = __popc(K);
+        bool dead = false;      // no early exit: the tests are independent, so their latencies overlap
+#pragma unroll 4
+        for (int t = 0; t < nk; ++t) {
           const int c = i0 + __ffs(k) - 1;
           k &= k - 1;
-          if (cls && cls[c] != cj) continue;
           const float4 bc = sb[c];
-          if (suppresses(bc, box_area(bc), bj, thr)) {
-            alive[j] = 0;
-            break;
-          }
+          const bool same = !cls || cls[c] == cj;
+          // (a four-compare early-out for pairs that do not touch was measured: slower on clustered boxes, where
+          // some lane of most warps overlaps and the warp then runs both paths)
+          dead |= same && suppresses(bc, box_area(bc), bj, aj, T);
         }
+        if (dead) alive[j] = 0;
       }
     }
     __syncthreads();
+    if (trace) {
+      const long long t3 = clock64();
+      c1 += t1 - t0;
+      c2 += t2 - t1;
+      c3 += t3 - t2;
+    }
+  }
+  if (trace && threadIdx.x == 0) {     // slots 6, 7: cycles of steps 1+2 and of step 3, summed over the rounds
+    trace[blockIdx.x * 8 + 6] = (unsigned long long)(c1 << 32 | (c2 & 0xFFFFFFFFll));
+    trace[blockIdx.x * 8 + 7] = (unsigned long long)c3;
   }
 }
 
@@ -258,31 +308,26 @@ nms_kernel(const float* __restrict__ boxes, const float* __restrict__ scores, co
 // ---------------------------------------------------------------------------------------------------------------
 // ovm_gdino_post
 
-__global__ void __launch_bounds__(kPostThreads, 1)
-gdino_post_kernel(const float* __restrict__ logits, const float* __restrict__ boxes_cxcywh,
-                  const int32_t* __restrict__ phrase_ranges, int nq, int T, int P, float img_w, float img_h,
-                  float box_thr, double nms_thr, float* __restrict__ out_boxes, float* __restrict__ out_scores,
-                  int64_t* __restrict__ out_classes, int32_t* __restrict__ out_query,
-                  int32_t* __restrict__ out_count, unsigned long long* trace) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int b = blockIdx.x;
-  const int npad = next_pow2(nq);
-  PostSmem s = carve(smem_raw, npad);
-  float* q_score = reinterpret_cast<float*>(s.tail);                 // [npad]
-  int32_t* q_cls = reinterpret_cast<int32_t*>(s.tail + (size_t)npad * 4);   // [npad]
-  float* rows = reinterpret_cast<float*>(s.tail + (size_t)npad * 8);        // [kPostWarps][T]
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const float* lg = logits + (size_t)b * nq * T;
-  post_stamp(trace, 0);
+// Query scores (roi_heads_gdino.py:186-202, 296-317): one warp per query, spread over the whole GPU (one CTA doing all
+// 900 queries took 78 of the post-processing's 144 us).  sigmoid of the query's token logits into shared memory,
+// phrase sums over each phrase's token columns, max / first argmax.  Results go to q_score / q_cls [B, nq].
+constexpr int kScoreWarps = 8;
 
-  // 1. per query: sigmoid of its token logits, phrase sums, max / first argmax (roi_heads_gdino.py:186-202, 296-317)
-  float* row = rows + (size_t)warp * T;
-  // only the token columns some phrase covers are ever summed: [t_lo, t_hi) (GroundingDINO fills the columns past the
-  // caption with -inf, whose sigmoid would take the slow paths of expf and the reciprocal for nothing)
-  int2* pr = reinterpret_cast<int2*>(rows + (size_t)kPostWarps * T);          // [P] phrase ranges, clamped to [0, T]
-  for (int p = threadIdx.x; p < P; p += kPostThreads)
+__global__ void __launch_bounds__(kScoreWarps * 32)
+gdino_score_kernel(const float* __restrict__ logits, const int32_t* __restrict__ phrase_ranges, int nq, int T, int P,
+                   float* __restrict__ q_score, int64_t* __restrict__ q_cls) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  float* rows = reinterpret_cast<float*>(smem_raw);                           // [kScoreWarps][T]
+  int2* pr = reinterpret_cast<int2*>(rows + (size_t)kScoreWarps * T);         // [P] phrase ranges, clamped to [0, T]
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int b = blockIdx.y;
+  for (int p = threadIdx.x; p < P; p += blockDim.x)
     pr[p] = make_int2(min(max(phrase_ranges[2 * p], 0), T), min(max(phrase_ranges[2 * p + 1], 0), T));
   __syncthreads();
+  const int q = blockIdx.x * kScoreWarps + warp;
+  if (q >= nq) return;
+  // only the token columns some phrase covers are ever summed: [t_lo, t_hi) (GroundingDINO fills the columns past the
+  // caption with -inf, whose sigmoid would take the slow paths of expf and the reciprocal for nothing)
   int t_lo = T, t_hi = 0;
   for (int p = lane; p < P; p += 32) {
     t_lo = min(t_lo, pr[p].x);
@@ -292,36 +337,54 @@ gdino_post_kernel(const float* __restrict__ logits, const float* __restrict__ bo
     t_lo = min(t_lo, __shfl_xor_sync(0xFFFFFFFFu, t_lo, o));
     t_hi = max(t_hi, __shfl_xor_sync(0xFFFFFFFFu, t_hi, o));
   }
-  for (int q = warp; q < nq; q += kPostWarps) {
-    const float* src = lg + (size_t)q * T;
-    for (int t = t_lo + lane; t < t_hi; t += 32) row[t] = __frcp_rn(__fadd_rn(1.0f, expf(-src[t])));   // = 1 / (1 + e^-x)
-    __syncwarp();
-    float best = -INFINITY;
-    int best_p = 0x7FFFFFFF;
-    for (int p = lane; p < P; p += 32) {
-      const int t0 = pr[p].x, t1 = pr[p].y;
-      float sum = 0.0f;
-      for (int t = t0; t < t1; ++t) sum = __fadd_rn(sum, row[t]);
-      if (sum > best || (sum != sum && best == best)) {   // NaN wins like torch.max, first occurrence kept
-        best = sum;
-        best_p = p;
-      }
+  float* row = rows + (size_t)warp * T;
+  const float* src = logits + ((size_t)b * nq + q) * T;
+  for (int t = t_lo + lane; t < t_hi; t += 32) row[t] = __frcp_rn(__fadd_rn(1.0f, expf(-src[t])));   // = 1 / (1 + e^-x)
+  __syncwarp();
+  float best = -INFINITY;
+  int best_p = 0x7FFFFFFF;
+  for (int p = lane; p < P; p += 32) {
+    const int t0 = pr[p].x, t1 = pr[p].y;
+    float sum = 0.0f;
+    for (int t = t0; t < t1; ++t) sum = __fadd_rn(sum, row[t]);
+    if (sum > best || (sum != sum && best == best)) {   // NaN wins like torch.max, first occurrence kept
+      best = sum;
+      best_p = p;
     }
-    for (int o = 16; o > 0; o >>= 1) {
-      const float ob = __shfl_xor_sync(0xFFFFFFFFu, best, o);
-      const int op = __shfl_xor_sync(0xFFFFFFFFu, best_p, o);
-      const bool o_nan = ob != ob, m_nan = best != best;
-      const bool take = (o_nan && (!m_nan || op < best_p)) || (!m_nan && !o_nan && (ob > best || (ob == best && op < best_p)));
-      if (take) {
-        best = ob;
-        best_p = op;
-      }
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ob = __shfl_xor_sync(0xFFFFFFFFu, best, o);
+    const int op = __shfl_xor_sync(0xFFFFFFFFu, best_p, o);
+    const bool o_nan = ob != ob, m_nan = best != best;
+    const bool take = (o_nan && (!m_nan || op < best_p)) || (!m_nan && !o_nan && (ob > best || (ob == best && op < best_p)));
+    if (take) {
+      best = ob;
+      best_p = op;
     }
-    if (lane == 0) {
-      q_score[q] = best;
-      q_cls[q] = best_p;
-    }
-    __syncwarp();
+  }
+  if (lane == 0) {
+    q_score[(size_t)b * nq + q] = best;
+    q_cls[(size_t)b * nq + q] = best_p;
+  }
+}
+
+// The rest for one image per CTA.  out_scores / out_classes hold the query scores / classes of gdino_score_kernel on
+// entry (indexed by query); they are copied to shared memory first and then overwritten with the result (indexed by
+// keep rank).
+__global__ void __launch_bounds__(kPostThreads, 1)
+gdino_post_kernel(const float* __restrict__ boxes_cxcywh, int nq, float img_w, float img_h, float box_thr,
+                  double nms_thr, float* __restrict__ out_boxes, float* out_scores, int64_t* out_classes,
+                  int32_t* __restrict__ out_query, int32_t* __restrict__ out_count, unsigned long long* trace) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int b = blockIdx.x;
+  const int npad = next_pow2(nq);
+  PostSmem s = carve(smem_raw, npad);
+  float* q_score = reinterpret_cast<float*>(s.tail);                 // [npad]
+  int32_t* q_cls = reinterpret_cast<int32_t*>(s.tail + (size_t)npad * 4);   // [npad]
+  post_stamp(trace, 0);
+  for (int i = threadIdx.x; i < nq; i += kPostThreads) {
+    q_score[i] = out_scores[(size_t)b * nq + i];
+    q_cls[i] = (int32_t)out_classes[(size_t)b * nq + i];
   }
   __syncthreads();
   post_stamp(trace, 1);
@@ -355,7 +418,7 @@ gdino_post_kernel(const float* __restrict__ logits, const float* __restrict__ bo
     }
   }
   post_stamp(trace, 3);
-  block_greedy(s.sb, nullptr, s.alive, n, nms_thr, reinterpret_cast<uint32_t*>(s.warp_tot));
+  block_greedy(s.sb, nullptr, s.alive, n, nms_thr, reinterpret_cast<uint32_t*>(s.warp_tot), trace);
   post_stamp(trace, 4);
 
   // 4. survivors in keep order
@@ -373,6 +436,7 @@ gdino_post_kernel(const float* __restrict__ logits, const float* __restrict__ bo
     if (oq) oq[rank] = q;
   });
   if (threadIdx.x == 0) out_count[b] = cnt;
+  post_stamp(trace, 5);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -714,18 +778,26 @@ int gdino_post_launch(const float* logits, const float* boxes_cxcywh, const int3
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return OVM_OK;
   }
+  const size_t smem_score = (size_t)kScoreWarps * T * 4 + (size_t)P * 8;
+  OVM_REQUIRE(smem_score <= 200 * 1024, "ovm_gdino_post: %d phrases need %zu bytes of shared memory", P, smem_score);
+  static size_t conf_score = 0;
+  if (smem_score > conf_score) {
+    OVM_CUDA(cudaFuncSetAttribute(gdino_score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_score));
+    conf_score = smem_score;
+  }
+  gdino_score_kernel<<<dim3((nq + kScoreWarps - 1) / kScoreWarps, batch), kScoreWarps * 32, smem_score, stream>>>(
+      logits, phrase_ranges, nq, T, P, out_scores, out_classes);
+  OVM_LAUNCHED("gdino_score_kernel");
   const int npad = host_next_pow2(nq);
-  const size_t smem = post_smem_bytes(npad) + (size_t)npad * 8 + (size_t)kPostWarps * T * 4 + (size_t)P * 8;
-  OVM_REQUIRE(smem <= 227 * 1024, "ovm_gdino_post: %zu bytes of shared memory needed", smem);
+  const size_t smem = post_smem_bytes(npad) + (size_t)npad * 8;
   static size_t configured = 0;
   if (smem > configured) {
     OVM_CUDA(cudaFuncSetAttribute(gdino_post_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = smem;
   }
-  gdino_post_kernel<<<batch, kPostThreads, smem, stream>>>(logits, boxes_cxcywh, phrase_ranges, nq, T, P,
-                                                           (float)image_width, (float)image_height, box_threshold,
-                                                           nms_threshold, out_boxes, out_scores, out_classes,
-                                                           out_query, out_count, g_post_trace);
+  gdino_post_kernel<<<batch, kPostThreads, smem, stream>>>(boxes_cxcywh, nq, (float)image_width, (float)image_height,
+                                                           box_threshold, nms_threshold, out_boxes, out_scores,
+                                                           out_classes, out_query, out_count, g_post_trace);
   OVM_LAUNCHED("gdino_post_kernel");
   return OVM_OK;
 }

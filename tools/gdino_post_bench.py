@@ -71,8 +71,11 @@ def main() -> None:
         torch.cuda.synchronize()
         lib.ovm_post_set_trace(None)
         st = buf.view(a.batch, 8)[0].tolist()
-        names = ["query scores", "sort", "box staging", "suppression", "gather"]
+        names = ["load query scores", "sort", "box staging", "suppression", "gather"]
         phases = {nm: (st[i + 1] - st[i]) / 1e3 for i, nm in enumerate(names)}
+        phases["suppression_cycles_step1_pair_tests"] = st[6] >> 32
+        phases["suppression_cycles_step2_serial_resolve"] = st[6] & 0xFFFFFFFF
+        phases["suppression_cycles_step3_later_positions"] = st[7]
     # NMS alone, 16 images x 1000 boxes per launch
     g = torch.Generator().manual_seed(1)
     n, S = 1000, 16
