@@ -9,12 +9,16 @@
 // descending score | ascending row, which is the stable descending order torch's sort produces), the sorted boxes
 // stay in shared memory, and the greedy pass walks them 32 positions per round (three barriers).  Nothing goes back to the
 // host in between (torchvision's CUDA nms copies its n x n/64 mask to the host and scans it there).
+#include <cooperative_groups.h>
+
 #include <algorithm>
+#include <cstdlib>
 
 #include "common.cuh"
 
 namespace ovm {
 namespace {
+namespace cg = cooperative_groups;
 
 constexpr int kPostThreads = 1024;
 constexpr int kPostWarps = kPostThreads / 32;
@@ -26,7 +30,7 @@ __device__ __forceinline__ void post_stamp(unsigned long long* trace, int slot) 
   if (trace && threadIdx.x == 0) {
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    trace[blockIdx.x * 8 + slot] = t;
+    trace[slot] = t;
   }
 }
 
@@ -107,10 +111,22 @@ __device__ __forceinline__ bool suppresses(const float4& a, float area_a, const 
 //   3. every thread tests its own later positions against the kept candidates only.
 // Three barriers per 32 positions whatever the number of survivors (a barrier per kept box costs 0.5 us each).
 // cls == nullptr: every pair competes.  alive[i] is 1 on entry for i < n.  blockDim.x must be kPostThreads.
+//
+// C > 1: the CTA is one of a cluster of C that all hold the same sorted boxes.  Steps 1 and 2 run in every CTA (same
+// inputs, same K).  Step 3 is a per-thread chain of popc(K) dependent-latency tests (measured: splitting the
+// *positions* over the cluster does not shorten it), so the round's kept candidates are split instead: CTA r tests
+// every later position against the candidates c = r mod C only.  Each CTA's alive[] then holds a partial view; before
+// the next round every CTA publishes its view of the next block (one 32-bit word per CTA, stored into every CTA's
+// shared memory through DSMEM), one cluster barrier replaces the round's last CTA barrier, and step 2 ANDs the C
+// words.  A block's final state is the K every CTA computes for it, so each CTA ends with the complete result.
+template <int C>
 __device__ void block_greedy(const float4* sb, const int32_t* cls, volatile uint8_t* alive, int n, double thr,
-                             uint32_t* mrow /* [33] shared */, unsigned long long* trace = nullptr) {
+                             uint32_t* mrow /* [33] shared */, unsigned long long* trace = nullptr,
+                             uint32_t* xbits = nullptr /* C > 1: [2][C] shared words, each CTA's view of the next block */) {
+  static_assert(C == 1 || C == 8, "the candidate split below is written for clusters of 8");
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  long long c1 = 0, c2 = 0, c3 = 0, t0 = 0, t1 = 0, t2 = 0;   // thread 0's cycles in the three steps (trace only)
+  const int rank = C > 1 ? (int)cg::this_cluster().block_rank() : 0;
+  long long c1 = 0, c2 = 0, c3 = 0, c4 = 0, t0 = 0, t1 = 0, t2 = 0, t3c = 0;   // thread 0's cycles in the three steps (trace only)
   const IouThr T = make_thr(thr);
   __syncthreads();
   for (int i0 = 0; i0 < n; i0 += 32) {
@@ -133,7 +149,16 @@ __device__ void block_greedy(const float4* sb, const int32_t* cls, volatile uint
       // kept once every earlier candidate that overlaps it is dead, dead once one of them is kept.  The lowest
       // undecided candidate is decided in every pass; typical depth is 2-4 passes of three ballots.
       const uint32_t m = mrow[lane];
-      const bool al = i0 + lane < n && alive[i0 + lane];
+      // C > 1: the block is alive where every CTA of the cluster still has it alive
+      bool al;
+      if (C > 1 && i0 > 0) {
+        uint32_t merged = 0xFFFFFFFFu;
+#pragma unroll
+        for (int r = 0; r < C; ++r) merged &= xbits[((i0 >> 5) & 1) * C + r];
+        al = i0 + lane < n && ((merged >> lane) & 1u) != 0u;
+      } else {
+        al = i0 + lane < n && alive[i0 + lane] != 0;
+      }
       uint32_t dead = ~__ballot_sync(0xFFFFFFFFu, al);
       uint32_t K = 0;
       bool undecided = al;
@@ -151,39 +176,57 @@ __device__ void block_greedy(const float4* sb, const int32_t* cls, volatile uint
     __syncthreads();
     if (trace) t2 = clock64();
     const uint32_t K = mrow[32];
-    if (K) {
-      for (int j = i0 + 32 + threadIdx.x; j < n; j += kPostThreads) {
-        if (!alive[j]) continue;
-        const float4 bj = sb[j];
-        const float aj = box_area(bj);
-        const int cj = cls ? cls[j] : 0;
-        uint32_t k = K;
-        const int nk = __popc(K);
-        bool dead = false;      // no early exit: the tests are independent, so their latencies overlap
+    auto test_position = [&](int j, uint32_t Kuse) {
+      if (!alive[j]) return;
+      const float4 bj = sb[j];
+      const float aj = box_area(bj);
+      const int cj = cls ? cls[j] : 0;
+      uint32_t k = Kuse;
+      const int nk = __popc(Kuse);
+      bool dead = false;      // no early exit: the tests are independent, so their latencies overlap
 #pragma unroll 4
-        for (int t = 0; t < nk; ++t) {
-          const int c = i0 + __ffs(k) - 1;
-          k &= k - 1;
-          const float4 bc = sb[c];
-          const bool same = !cls || cls[c] == cj;
-          // (a four-compare early-out for pairs that do not touch was measured: slower on clustered boxes, where
-          // some lane of most warps overlaps and the warp then runs both paths)
-          dead |= same && suppresses(bc, box_area(bc), bj, aj, T);
-        }
-        if (dead) alive[j] = 0;
+      for (int t = 0; t < nk; ++t) {
+        const int c = i0 + __ffs(k) - 1;
+        k &= k - 1;
+        const float4 bc = sb[c];
+        const bool same = !cls || cls[c] == cj;
+        // (a four-compare early-out for pairs that do not touch was measured: slower on clustered boxes, where
+        // some lane of most warps overlaps and the warp then runs both paths)
+        dead |= same && suppresses(bc, box_area(bc), bj, aj, T);
       }
+      if (dead) alive[j] = 0;
+    };
+    if (C == 1) {
+      if (K)
+        for (int j = i0 + 32 + threadIdx.x; j < n; j += kPostThreads) test_position(j, K);
+      __syncthreads();
+    } else {
+      const uint32_t Kmine = K & (0x01010101u << rank);          // C == 8: candidates rank, rank + 8, rank + 16, rank + 24
+      if (Kmine)
+        for (int j = i0 + 32 + threadIdx.x; j < n; j += kPostThreads) test_position(j, Kmine);
+      if (warp == 0 && i0 + 32 < n) {
+        // this warp owns the next block's positions (j = i0 + 32 + lane): publish this CTA's view of them, lane r
+        // storing the word into CTA r's shared memory
+        __syncwarp();
+        const int j = i0 + 32 + lane;
+        const uint32_t bits = __ballot_sync(0xFFFFFFFFu, j < n && alive[j]);
+        // (two sets of words, alternating by round: a fast CTA may publish round r + 1 while a slow one still reads r)
+        if (lane < C) *cg::this_cluster().map_shared_rank(xbits + (((i0 >> 5) + 1) & 1) * C + rank, lane) = bits;
+      }
+      if (trace) t3c = clock64();
+      cg::this_cluster().sync();
     }
-    __syncthreads();
     if (trace) {
       const long long t3 = clock64();
       c1 += t1 - t0;
       c2 += t2 - t1;
       c3 += t3 - t2;
+      if (C > 1) c4 += t3 - t3c;      // of which: the cluster barrier
     }
   }
   if (trace && threadIdx.x == 0) {     // slots 6, 7: cycles of steps 1+2 and of step 3, summed over the rounds
-    trace[blockIdx.x * 8 + 6] = (unsigned long long)(c1 << 32 | (c2 & 0xFFFFFFFFll));
-    trace[blockIdx.x * 8 + 7] = (unsigned long long)c3;
+    trace[6] = (unsigned long long)(c1 << 32 | (c2 & 0xFFFFFFFFll));
+    trace[7] = (unsigned long long)(c4 << 32 | (c3 & 0xFFFFFFFFll));
   }
 }
 
@@ -243,12 +286,13 @@ size_t post_smem_bytes(int npad) { return (size_t)npad * 29 + 512; }
 // ---------------------------------------------------------------------------------------------------------------
 // ovm_nms
 
+template <int C>
 __global__ void __launch_bounds__(kPostThreads, 1)
 nms_kernel(const float* __restrict__ boxes, const float* __restrict__ scores, const int64_t* __restrict__ classes,
            const int32_t* __restrict__ seg_offsets, int max_len, double thr, int mode, int32_t* __restrict__ keep,
            int32_t* __restrict__ keep_count) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int seg = blockIdx.x;
+  const int seg = blockIdx.x / C;       // a cluster of C CTAs per segment
   const int r0 = seg_offsets[seg];
   const int n = seg_offsets[seg + 1] - r0;
   if (n <= 0 || n > max_len) {
@@ -297,8 +341,9 @@ nms_kernel(const float* __restrict__ boxes, const float* __restrict__ scores, co
     s.sb[p] = b;
     s.scls[p] = c;
   }
-  block_greedy(s.sb, mode == OVM_NMS_PER_CLASS ? s.scls : nullptr, s.alive, n, thr,
-               reinterpret_cast<uint32_t*>(s.warp_tot));
+  block_greedy<C>(s.sb, mode == OVM_NMS_PER_CLASS ? s.scls : nullptr, s.alive, n, thr,
+                  reinterpret_cast<uint32_t*>(s.warp_tot), nullptr, reinterpret_cast<uint32_t*>(s.red));
+  if (C > 1 && blockIdx.x % C != 0) return;     // every CTA has the result; the first of the cluster writes it
   int32_t* kout = keep + r0;
   const uint64_t* keys = s.keys;
   const int cnt = block_compact(s.alive, n, s.warp_tot, [&](int rank, int pos) { kout[rank] = (int32_t)(uint32_t)keys[pos]; });
@@ -371,12 +416,14 @@ gdino_score_kernel(const float* __restrict__ logits, const int32_t* __restrict__
 // The rest for one image per CTA.  out_scores / out_classes hold the query scores / classes of gdino_score_kernel on
 // entry (indexed by query); they are copied to shared memory first and then overwritten with the result (indexed by
 // keep rank).
+template <int C>
 __global__ void __launch_bounds__(kPostThreads, 1)
 gdino_post_kernel(const float* __restrict__ boxes_cxcywh, int nq, float img_w, float img_h, float box_thr,
                   double nms_thr, float* __restrict__ out_boxes, float* out_scores, int64_t* out_classes,
                   int32_t* __restrict__ out_query, int32_t* __restrict__ out_count, unsigned long long* trace) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int b = blockIdx.x;
+  const int b = blockIdx.x / C;         // a cluster of C CTAs per image
+  trace = (trace && blockIdx.x % C == 0) ? trace + b * 8 : nullptr;
   const int npad = next_pow2(nq);
   PostSmem s = carve(smem_raw, npad);
   float* q_score = reinterpret_cast<float*>(s.tail);                 // [npad]
@@ -386,6 +433,7 @@ gdino_post_kernel(const float* __restrict__ boxes_cxcywh, int nq, float img_w, f
     q_score[i] = out_scores[(size_t)b * nq + i];
     q_cls[i] = (int32_t)out_classes[(size_t)b * nq + i];
   }
+  if (C > 1) cg::this_cluster().sync();   // every CTA of the cluster has its copy before the first one overwrites the buffers
   __syncthreads();
   post_stamp(trace, 1);
 
@@ -418,8 +466,10 @@ gdino_post_kernel(const float* __restrict__ boxes_cxcywh, int nq, float img_w, f
     }
   }
   post_stamp(trace, 3);
-  block_greedy(s.sb, nullptr, s.alive, n, nms_thr, reinterpret_cast<uint32_t*>(s.warp_tot), trace);
+  block_greedy<C>(s.sb, nullptr, s.alive, n, nms_thr, reinterpret_cast<uint32_t*>(s.warp_tot), trace,
+                  reinterpret_cast<uint32_t*>(s.red));
   post_stamp(trace, 4);
+  if (C > 1 && blockIdx.x % C != 0) return;
 
   // 4. survivors in keep order
   float4* ob = reinterpret_cast<float4*>(out_boxes) + (size_t)b * nq;
@@ -584,7 +634,7 @@ box_class_nms_kernel(BoxCfg cfg, const float* __restrict__ probs, const float* _
       s.sb[p] = b;
     }
   }
-  block_greedy(s.sb, nullptr, s.alive, n, cfg.nms_thresh, reinterpret_cast<uint32_t*>(s.warp_tot));
+  block_greedy<1>(s.sb, nullptr, s.alive, n, cfg.nms_thresh, reinterpret_cast<uint32_t*>(s.warp_tot));
   const uint64_t* keys = s.keys;
   const int cnt = block_compact(s.alive, n, s.warp_tot, [&](int rank, int pos) { kout[rank] = (int32_t)(uint32_t)keys[pos]; });
   if (threadIdx.x == 0) class_count[img * K + k] = cnt;
@@ -725,6 +775,34 @@ box_topk_kernel(BoxCfg cfg, const float* __restrict__ probs, const float* __rest
   if (threadIdx.x == 0) out_count[img] = n_out;
 }
 
+// Cluster size for the per-image NMS kernels: 8 (portable maximum) unless OVM_NMS_CLUSTER=1 asks for single CTAs.
+int nms_cluster_size() {
+  static int c = -1;
+  if (c < 0) {
+    const char* e = std::getenv("OVM_NMS_CLUSTER");
+    c = (e && std::atoi(e) == 1) ? 1 : 8;
+  }
+  return c;
+}
+
+template <typename... KArgs, typename... Args>
+cudaError_t launch_cluster(void (*kernel)(KArgs...), int clusters, int csize, size_t smem, cudaStream_t stream,
+                           Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(clusters * csize);
+  cfg.blockDim = dim3(kPostThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = csize;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 int host_next_pow2(int n) {
   int p = 32;
   while (p < n) p <<= 1;
@@ -748,13 +826,15 @@ int nms_launch(const float* boxes, const float* scores, const int64_t* classes, 
               max_segment_len, OVM_NMS_MAX_SEGMENT);
   OVM_REQUIRE((reinterpret_cast<uintptr_t>(boxes) & 15) == 0, "ovm_nms: boxes must be 16-byte aligned");
   const size_t smem = post_smem_bytes(host_next_pow2(max_segment_len));
-  static size_t configured = 0;
-  if (smem > configured) {
-    OVM_CUDA(cudaFuncSetAttribute(nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
+  static size_t configured[2] = {0, 0};
+  const int csize = nms_cluster_size();
+  if (smem > configured[csize > 1]) {
+    OVM_CUDA(cudaFuncSetAttribute(csize > 1 ? nms_kernel<8> : nms_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)smem));
+    configured[csize > 1] = smem;
   }
-  nms_kernel<<<num_segments, kPostThreads, smem, stream>>>(boxes, scores, classes, seg_offsets, max_segment_len,
-                                                           iou_threshold, mode, keep, keep_count);
+  OVM_CUDA(launch_cluster(csize > 1 ? nms_kernel<8> : nms_kernel<1>, num_segments, csize, smem, stream, boxes, scores,
+                          classes, seg_offsets, max_segment_len, iou_threshold, mode, keep, keep_count));
   OVM_LAUNCHED("nms_kernel");
   return OVM_OK;
 }
@@ -790,14 +870,16 @@ int gdino_post_launch(const float* logits, const float* boxes_cxcywh, const int3
   OVM_LAUNCHED("gdino_score_kernel");
   const int npad = host_next_pow2(nq);
   const size_t smem = post_smem_bytes(npad) + (size_t)npad * 8;
-  static size_t configured = 0;
-  if (smem > configured) {
-    OVM_CUDA(cudaFuncSetAttribute(gdino_post_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
+  static size_t configured[2] = {0, 0};
+  const int csize = nms_cluster_size();
+  if (smem > configured[csize > 1]) {
+    OVM_CUDA(cudaFuncSetAttribute(csize > 1 ? gdino_post_kernel<8> : gdino_post_kernel<1>,
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured[csize > 1] = smem;
   }
-  gdino_post_kernel<<<batch, kPostThreads, smem, stream>>>(boxes_cxcywh, nq, (float)image_width, (float)image_height,
-                                                           box_threshold, nms_threshold, out_boxes, out_scores,
-                                                           out_classes, out_query, out_count, g_post_trace);
+  OVM_CUDA(launch_cluster(csize > 1 ? gdino_post_kernel<8> : gdino_post_kernel<1>, batch, csize, smem, stream,
+                          boxes_cxcywh, nq, (float)image_width, (float)image_height, box_threshold, nms_threshold,
+                          out_boxes, out_scores, out_classes, out_query, out_count, g_post_trace));
   OVM_LAUNCHED("gdino_post_kernel");
   return OVM_OK;
 }

@@ -75,7 +75,8 @@ def main() -> None:
         phases = {nm: (st[i + 1] - st[i]) / 1e3 for i, nm in enumerate(names)}
         phases["suppression_cycles_step1_pair_tests"] = st[6] >> 32
         phases["suppression_cycles_step2_serial_resolve"] = st[6] & 0xFFFFFFFF
-        phases["suppression_cycles_step3_later_positions"] = st[7]
+        phases["suppression_cycles_step3_later_positions"] = st[7] & 0xFFFFFFFF
+        phases["suppression_cycles_step3_of_which_cluster_barrier"] = st[7] >> 32
     # NMS alone, 16 images x 1000 boxes per launch
     g = torch.Generator().manual_seed(1)
     n, S = 1000, 16
