@@ -107,9 +107,9 @@ __device__ __forceinline__ bool suppresses(const float4& a, float area_a, const 
 
 // Greedy suppression over boxes already in decreasing score order, 32 sorted positions per round.
 //   1. the 32 x 32 tests inside the round's block, one per thread (warp = candidate, lane = earlier candidate);
-//   2. every warp resolves the block on the resulting bit rows (fixed point, see below): K = its kept candidates;
+//   2. warp 0 resolves the block on the resulting bit rows (fixed point, see below): K = its kept candidates;
 //   3. every thread tests its own later positions against the kept candidates only.
-// Two barriers per 32 positions whatever the number of survivors (a barrier per kept box costs 0.5 us each).
+// Three barriers per 32 positions whatever the number of survivors (a barrier per kept box costs 0.5 us each).
 // cls == nullptr: every pair competes.  alive[i] is 1 on entry for i < n.  blockDim.x must be kPostThreads.
 //
 // C > 1: the CTA is one of a cluster of C that all hold the same sorted boxes.  Steps 1 and 2 run in every CTA (same
@@ -143,8 +143,7 @@ __device__ void block_greedy(const float4* sb, const int32_t* cls, volatile uint
     }
     __syncthreads();
     if (trace) t1 = clock64();
-    uint32_t K = 0;
-    {   // in every warp, redundantly: no second barrier and no shared-memory round trip for K
+    if (warp == 0) {
       // Greedy resolution of the block as a fixed point instead of a 32-step dependent chain (which, with the other
       // 31 warps parked at the barrier and nothing to hide ALU latency, cost ~1000 cycles per round): a candidate is
       // kept once every earlier candidate that overlaps it is dead, dead once one of them is kept.  The lowest
@@ -161,6 +160,7 @@ __device__ void block_greedy(const float4* sb, const int32_t* cls, volatile uint
         al = i0 + lane < n && alive[i0 + lane] != 0;
       }
       uint32_t dead = ~__ballot_sync(0xFFFFFFFFu, al);
+      uint32_t K = 0;
       bool undecided = al;
       while (true) {
         const bool k_now = undecided && (m & ~dead) == 0u;
@@ -170,9 +170,12 @@ __device__ void block_greedy(const float4* sb, const int32_t* cls, volatile uint
         undecided = undecided && !k_now && !d_now;
         if (__ballot_sync(0xFFFFFFFFu, undecided) == 0u) break;
       }
-      if (warp == 0 && i0 + lane < n) alive[i0 + lane] = (K >> lane) & 1u;   // final state of the block
+      if (lane == 0) mrow[32] = K;
+      if (i0 + lane < n) alive[i0 + lane] = (K >> lane) & 1u;
     }
+    __syncthreads();
     if (trace) t2 = clock64();
+    const uint32_t K = mrow[32];
     auto test_position = [&](int j, uint32_t Kuse) {
       if (!alive[j]) return;
       const float4 bj = sb[j];
