@@ -34,6 +34,20 @@ __device__ __forceinline__ void post_stamp(unsigned long long* trace, int slot) 
   }
 }
 
+// Cluster barrier in its two halves and a 32-bit store into another CTA's shared memory.  (cooperative_groups'
+// cluster.sync() compiles to the same barrier plus MEMBAR.ALL.GPU and CCTL.IVALL; measured ~850 cycles per round.)
+__device__ __forceinline__ void cluster_arrive_release() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void cluster_wait_acquire() {
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void st_shared_cluster_u32(const void* local_smem, int cta_rank, uint32_t v) {
+  uint32_t remote;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(smem_u32(local_smem)), "r"(cta_rank));
+  asm volatile("st.shared::cluster.u32 [%0], %1;" ::"r"(remote), "r"(v) : "memory");
+}
+
 // fp32 -> 32-bit key whose unsigned ascending order is the descending order of the floats (-0 == +0)
 __device__ __forceinline__ uint32_t score_key_desc(float s) {
   if (s == 0.0f) s = 0.0f;
@@ -141,6 +155,7 @@ __device__ void block_greedy(const float4* sb, const int32_t* cls, volatile uint
       const uint32_t m = __ballot_sync(0xFFFFFFFFu, sup);
       if (lane == 0) mrow[warp] = m;
     }
+    if (C > 1 && i0 > 0) cluster_wait_acquire();   // the other CTAs' views of this block have landed (arrive: end of last round)
     __syncthreads();
     if (trace) t1 = clock64();
     if (warp == 0) {
@@ -211,10 +226,11 @@ __device__ void block_greedy(const float4* sb, const int32_t* cls, volatile uint
         const int j = i0 + 32 + lane;
         const uint32_t bits = __ballot_sync(0xFFFFFFFFu, j < n && alive[j]);
         // (two sets of words, alternating by round: a fast CTA may publish round r + 1 while a slow one still reads r)
-        if (lane < C) *cg::this_cluster().map_shared_rank(xbits + (((i0 >> 5) + 1) & 1) * C + rank, lane) = bits;
+        if (lane < C) st_shared_cluster_u32(xbits + (((i0 >> 5) + 1) & 1) * C + rank, lane, bits);
       }
       if (trace) t3c = clock64();
-      cg::this_cluster().sync();
+      // split barrier: arrive now, wait after the next round's pair tests (which need nothing from the other CTAs)
+      cluster_arrive_release();
     }
     if (trace) {
       const long long t3 = clock64();
@@ -224,6 +240,8 @@ __device__ void block_greedy(const float4* sb, const int32_t* cls, volatile uint
       if (C > 1) c4 += t3 - t3c;      // of which: the cluster barrier
     }
   }
+  if (C > 1 && n > 0) cluster_wait_acquire();   // pairs the last arrive: no CTA leaves while another may still store into it
+  if (C > 1) __syncthreads();
   if (trace && threadIdx.x == 0) {     // slots 6, 7: cycles of steps 1+2 and of step 3, summed over the rounds
     trace[6] = (unsigned long long)(c1 << 32 | (c2 & 0xFFFFFFFFll));
     trace[7] = (unsigned long long)(c4 << 32 | (c3 & 0xFFFFFFFFll));
