@@ -423,6 +423,10 @@ def kernel_breakdown(eng, dbs, flush, lift, K: int, peaks) -> Dict[str, object]:
     for k in kernels.values():
         if "peak" in k:
             k["frac"] = k["achieved"] / k["peak"]
+            # the same with the measured cost of an empty event-to-event interval taken off the stage: closer to the
+            # kernel's own duration (compare the ncu launch list in profiles/); `frac` stays the conservative figure
+            net = max(k["ms"] - event_pair_us * 1e-3, 1e-6)
+            k["frac_net_of_event_overhead"] = k["frac"] * k["ms"] / net
     top = max(("roi_align", "fc1", "fc2"), key=lambda s: ms[s])
     traffic = None
     tp = os.path.join(ROOT, "profiles", "traffic.json")   # dram bytes per launch from the committed ncu capture
