@@ -120,7 +120,7 @@ int ovm_roi_set_trace(uint64_t* buf);
  * 5 record written.  NULL switches it off.                                                                  */
 int ovm_head_set_trace(uint64_t* buf);
 
-/* Same for ovm_gdino_post (tools/gdino_post_bench.py --trace): [batch, 8] stamps of each CTA's thread 0 -- 0 entry,
+/* Same for ovm_gdino_post (tests/perf_gdino_post.py --trace): [batch, 8] stamps of each CTA's thread 0 -- 0 entry,
  * 1 query scores loaded, 2 sorted, 3 boxes staged, 4 suppression done, 5 exit, 6 / 7 SM cycles inside the suppression
  * (pair tests << 32 | serial resolve; later positions).  NULL switches it off.               */
 int ovm_post_set_trace(uint64_t* buf);

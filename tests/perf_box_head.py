@@ -2,7 +2,7 @@
 NMS, top-k) and the whole branch next to the reference's own call sequence run on the GPU through
 oracle/box_head_oracle.py (torch CUDA ops + torchvision CUDA batched_nms, fast_rcnn.py:57-116).  One JSON line.
 
-    python tools/box_head_bench.py [--images 2] [--proposals 1000] [--iters 100]
+    python tests/perf_box_head.py [--images 2] [--proposals 1000] [--iters 100]
 """
 import argparse
 import json
@@ -20,7 +20,7 @@ from ovmono3d_b200 import ops                       # noqa: E402
 from tests.golden import box_cases as bc            # noqa: E402
 
 
-def main() -> None:
+def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--images", type=int, default=2)
     ap.add_argument("--proposals", type=int, default=1000)
@@ -66,10 +66,12 @@ def main() -> None:
     same = all(int(out[5][i]) == len(w[1]) and out[2][i, :len(w[1])].tolist() == w[3].tolist()
                for i, w in enumerate(want))
     cands = [int((torch.softmax(lg[o:o + c], -1)[:, :-1] > case.score_thresh).sum()) for o, c in zip(off.tolist(), counts)]
-    print(json.dumps({"box_inference": {"images": a.images, "proposals_per_image": a.proposals, "classes": 50,
+    res = {"box_inference": {"images": a.images, "proposals_per_image": a.proposals, "classes": 50,
                                         "candidates_per_image": cands, "ours_us": ours_us,
                                         "reference_gpu_sequence_us": ref_us, "speedup": ref_us / ours_us,
-                                        "same_classes_as_reference_gpu_sequence": same}}))
+                                        "same_classes_as_reference_gpu_sequence": same}}
+    print(json.dumps(res))
+    return res
 
 
 if __name__ == "__main__":

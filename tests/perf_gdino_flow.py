@@ -4,7 +4,7 @@ lift, through `ROIHeads3DGDINOB200` with `GroundingDinoPostB200` as its detector
 on the same GPU (oracle post-processing with its `.cpu()` copies and host NMS, then the oracle lift on CUDA tensors).
 Wall clock per call with a device synchronisation at the end (the caller consumes the Instances).  One JSON line.
 
-    python tools/gdino_flow_bench.py [--iters 100]
+    python tests/perf_gdino_flow.py [--iters 100]
 """
 import argparse
 import json
@@ -23,7 +23,7 @@ from ovmono3d_b200 import gdino_post as gp, ops                 # noqa: E402
 from tests.golden import gdino_cases as gd                       # noqa: E402
 
 
-def main() -> None:
+def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--iters", type=int, default=100)
     a = ap.parse_args()
@@ -87,10 +87,12 @@ def main() -> None:
     assert len(out["scores"]) == n
     got, want = res[0].pred_center_cam.cpu(), r.pred_center_cam[0].cpu()
     assert float((got - want).abs().max() / want.abs().max()) <= 1e-2       # same answer (bf16-operand head)
-    print(json.dumps({"workload": "one image, 900 queries x 256 tokens, %d phrases -> %d prompt boxes -> lift "
+    res = {"workload": "one image, 900 queries x 256 tokens, %d phrases -> %d prompt boxes -> lift "
                                   "(DINOv2 SFP pyramid, head 12544-1024-1024-13)" % (len(cats), n),
                       "ours_ms_per_call": ours_ms, "reference_gpu_sequence_ms_per_call": ref_ms,
-                      "speedup": ref_ms / ours_ms}))
+                      "speedup": ref_ms / ours_ms}
+    print(json.dumps(res))
+    return res
 
 
 if __name__ == "__main__":

@@ -2,7 +2,7 @@
 (roi_heads_gdino.py:186-202, 269-275: CUDA sigmoid / gathers / max, three `.cpu()` copies, torchvision nms on the
 host) run through oracle/gdino_post_oracle.py on CUDA tensors.  Prints one JSON line.
 
-    python tools/gdino_post_bench.py [--queries 900] [--iters 200]
+    python tests/perf_gdino_post.py [--queries 900] [--iters 200]
 """
 import argparse
 import json
@@ -19,7 +19,7 @@ from ovmono3d_b200 import gdino_post as gp, ops     # noqa: E402
 from tests.golden import gdino_cases as gd          # noqa: E402
 
 
-def main() -> None:
+def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--queries", type=int, default=900)
     ap.add_argument("--batch", type=int, default=1)
@@ -104,12 +104,14 @@ def main() -> None:
             tv_nms(nb[i * n:(i + 1) * n], ns[i * n:(i + 1) * n], 0.5)
     torch.cuda.synchronize()
     tv_us = (time.perf_counter() - t0) * 1e6 / n_ref
-    print(json.dumps({
+    res = {
         "gdino_post": {"queries": a.queries, "batch": a.batch, "phrases": len(cap_list), "kept": kept,
                        "ours_us_device": ours_us, "ours_us_with_count_readback": ours_sync_us,
                        "reference_sequence_us": ref_us, "speedup_vs_reference_sequence": ref_us / ours_sync_us, "phase_us": phases},
         "nms_16x1000": {"ours_us": nms_us, "kept_mean": float(cnt.float().mean()),
-                        "torchvision_cuda_nms_16_calls_us": tv_us, "speedup": tv_us / nms_us}}))
+                        "torchvision_cuda_nms_16_calls_us": tv_us, "speedup": tv_us / nms_us}}
+    print(json.dumps(res))
+    return res
 
 
 if __name__ == "__main__":
