@@ -214,7 +214,8 @@ int ovm_set_stage_events(void* const* events, int32_t count);
 #define OVM_NMS_MAX_SEGMENT 4096  /* boxes of one segment that one CTA sorts and suppresses in shared memory */
 enum { OVM_NMS_AGNOSTIC = 0, OVM_NMS_COORD_TRICK = 1, OVM_NMS_PER_CLASS = 2 };
 
-/* Greedy NMS, one CTA per segment (image); no host round trip (torchvision's CUDA nms copies its mask to the host).
+/* Greedy NMS, one cluster of 8 CTAs per segment (image; single CTAs with OVM_NMS_CLUSTER=1 in the environment); no host
+ * round trip (torchvision's CUDA nms copies its mask to the host).
  * boxes [n,4] xyxy fp32, scores [n] fp32, classes [n] int64 (NULL with OVM_NMS_AGNOSTIC), seg_offsets [S+1] int32
  * (device): segment s = rows [seg_offsets[s], seg_offsets[s+1]), each at most max_segment_len (<= OVM_NMS_MAX_SEGMENT)
  * long.  Arithmetic is torchvision's CPU kernel (fp32 areas, inter / (a_i + a_j - inter) > threshold compared in
@@ -235,7 +236,8 @@ int ovm_nms(const float* boxes, const float* scores, const int64_t* classes, con
  * its score / class are that max / argmax (first on ties); boxes become xyxy pixels with image_width / image_height
  * (the padded network input, :269); class-agnostic NMS at nms_threshold; survivors are written in decreasing score
  * order: out_boxes [B, nq, 4], out_scores [B, nq], out_classes [B, nq] int64, out_query [B, nq] int32 (source query,
- * optional), out_count [B] int32.  Rows past out_count[b] are left untouched.  nq <= OVM_NMS_MAX_SEGMENT, T <= 512. */
+ * optional), out_count [B] int32.  Rows past out_count[b] are undefined (out_scores / out_classes carry the per-query
+ * scores between the two launches).  nq <= OVM_NMS_MAX_SEGMENT, T <= 512. */
 int ovm_gdino_post(const float* logits, const float* boxes_cxcywh, const int32_t* phrase_ranges, int32_t batch,
                    int32_t num_queries, int32_t num_tokens, int32_t num_phrases, int32_t image_height,
                    int32_t image_width, float box_threshold, double nms_threshold, float* out_boxes,
