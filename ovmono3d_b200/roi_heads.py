@@ -406,10 +406,13 @@ class ROIHeads3DB200(nn.Module):
             scores = stage_d[o_sc:o_sc + n] if with_scores else None
             classes = stage_d[o_cls:o_cls + 2 * n].view(torch.int64)
         else:
-            boxes = torch.cat([x.pred_boxes.tensor for x in instances]).to(device=device, dtype=torch.float32).contiguous()
-            classes = torch.cat([x.pred_classes for x in instances]).to(device=device, dtype=torch.int64).contiguous()
-            scores = (torch.cat([x.scores for x in instances]).to(device=device, dtype=torch.float32).contiguous()
-                      if with_scores else None)
+            def gather(ts, dt):   # one Instances (the GDINO flow) with the right dtype on the device: no copy at all
+                t = ts[0] if len(ts) == 1 else torch.cat(ts)
+                return t.to(device=device, dtype=dt).contiguous()
+
+            boxes = gather([x.pred_boxes.tensor for x in instances], torch.float32)
+            classes = gather([x.pred_classes for x in instances], torch.int64)
+            scores = gather([x.scores for x in instances], torch.float32) if with_scores else None
 
         eng = self._get_engine()
         eng.prepare(device, self.priors_dims_per_cat, self.priors_z_scales, getattr(self, "priors_z_stats", None))
@@ -421,6 +424,9 @@ class ROIHeads3DB200(nn.Module):
                   ("pred_dimensions", records[:, ops.REC_DIMENSIONS]), ("pred_pose", records[:, ops.REC_POSE].view(n, 3, 3)))
         for name, t in fields:
             # lengths match by construction: skip Instances.set()'s per-field len() assertion (96 of them per batch)
+            if N == 1:
+                instances[0]._fields[name] = t
+                continue
             for inst, part in zip(instances, t.split(num_boxes_per_image)):
                 inst._fields[name] = part
         self.last_records, self.last_raw = records, raw
@@ -467,7 +473,10 @@ class ROIHeads3DGDINOB200(ROIHeads3DB200):
             if self.groundingdino_model is None:
                 raise ops.LiftError("ROIHeads3DGDINOB200 needs a 2-D detector callable (GroundingDINO is not part of "
                                     "the lift path); pass detector=... or use ROIHeads3DB200 with given boxes")
-            ov = self.groundingdino_model(images[0][[2, 1, 0], :, :], filtered_texts)
+            # images[0][[2, 1, 0], :, :] of the reference (:141): for three channels that is a flip, one kernel and no
+            # index tensor to build and copy
+            img = images[0]
+            ov = self.groundingdino_model(img.flip(0) if img.shape[0] == 3 else img[[2, 1, 0], :, :], filtered_texts)
             if "pred_classes" in ov:     # GroundingDinoPostB200: indices into category_list, already on the device
                 target.pred_classes = ov["pred_classes"]
             else:
@@ -475,7 +484,8 @@ class ROIHeads3DGDINOB200(ROIHeads3DB200):
                                                    dtype=torch.int64)
             target.pred_boxes = Boxes(ov["bboxes"])
             target.scores = ov["scores"]
-            target = target.to(device=device)
+            if any(t.device != device for t in (target.pred_classes, target.pred_boxes.tensor, target.scores)):
+                target = target.to(device=device)
         pred_instances = [target]
         if self.loss_w_3d > 0:
             pred_instances = self._forward_cube(features, pred_instances, Ks, im_dims, im_scales_ratio)
