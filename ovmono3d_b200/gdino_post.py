@@ -41,6 +41,15 @@ def phrase_token_ranges(tokenizer: Any, cap_list: Sequence[str], caption: str) -
     return torch.tensor(ranges, dtype=torch.int32).reshape(-1, 2)
 
 
+def first_occurrence_lut(cap_list: Sequence[str]):
+    """None when every phrase is unique, else an int64 table phrase index -> index of its first occurrence: the class
+    the reference assigns through `filtered_texts.index([class_name])` (roi_heads_gdino.py:162)."""
+    first = [cap_list.index(c) for c in cap_list]
+    if first == list(range(len(cap_list))):
+        return None
+    return torch.tensor(first, dtype=torch.int64)
+
+
 class GroundingDinoPostB200:
     """Callable with the signature `ROIHeads3DGDINOB200` expects from its `detector`:
     `detector(image_bgr [3,H,W], text_prompt [[cat], ...]) -> {"labels", "bboxes", "scores", "pred_classes"}`.
@@ -79,6 +88,9 @@ class GroundingDinoPostB200:
         h, w = image.shape[1:]
         (boxes, scores, classes, _), = self.postprocess(outputs["pred_logits"][:1].float(),
                                                         outputs["pred_boxes"][:1].float(), ranges, (h, w))
+        lut = first_occurrence_lut(cap_list)
+        if lut is not None:      # a category listed twice: the reference's `filtered_texts.index([name])` (:162) finds the first
+            classes = lut.to(classes.device)[classes]
         return {"bboxes": boxes, "scores": scores, "pred_classes": classes,
                 "labels": _LazyLabels(cap_list, classes)}
 

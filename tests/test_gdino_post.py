@@ -65,6 +65,16 @@ def test_host_mirror_caption_and_phrase_columns():
         gp.phrase_token_ranges(BadTok(), ["a", "b"], "a . b .")
 
 
+def test_duplicate_categories_map_to_first_occurrence():
+    from ovmono3d_b200 import gdino_post as gp
+
+    assert gp.first_occurrence_lut(["chair", "table", "sofa"]) is None
+    lut = gp.first_occurrence_lut(["chair", "table", "chair", "sofa", "table"])
+    caps = ["chair", "table", "chair", "sofa", "table"]
+    assert lut.tolist() == [0, 1, 0, 3, 1]
+    assert lut.tolist() == [[[c] for c in caps].index([c]) for c in caps]       # roi_heads_gdino.py:162
+
+
 def test_detector_needs_cuda():
     from ovmono3d_b200 import gdino_post as gp, ops
 
