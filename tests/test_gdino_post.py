@@ -196,6 +196,29 @@ def test_batched_nms_matches_torchvision(n, classes):
 
 
 @pytest.mark.gpu
+def test_nms_randomized_sizes_repeated():
+    """80 random problems (sizes around the 32-position round and 1024-thread boundaries, dense and sparse overlap),
+    each run three times back to back in one batch of segments: the cluster exchange has no run-to-run freedom."""
+    from ovmono3d_b200 import ops
+
+    g = torch.Generator().manual_seed(2024)
+    lens = [int(x) for x in torch.randint(1, 1600, (80,), generator=g)]
+    lens[:12] = [31, 32, 33, 63, 64, 65, 1023, 1024, 1025, 1055, 1056, 1057]
+    boxes = torch.cat([_random_boxes(g, n, clusters=max(1, n // int(torch.randint(2, 40, (1,), generator=g)))) for n in lens])
+    scores = torch.rand(boxes.shape[0], generator=g)
+    off = torch.tensor([0] + list(np.cumsum(lens)), dtype=torch.int32)
+    for thr in (0.4, 0.5, 0.65):
+        want = [go.nms(boxes[a:b], scores[a:b], thr).tolist() for a, b in zip(off[:-1].tolist(), off[1:].tolist())]
+        for _ in range(3):
+            keep, cnt = ops.nms(boxes.to(_dev()), scores.to(_dev()), thr, seg_offsets=off.to(_dev()),
+                                max_segment_len=max(lens))
+            keep, cnt = keep.cpu(), cnt.cpu().tolist()
+            for s_, (a, w) in enumerate(zip(off[:-1].tolist(), want)):
+                assert cnt[s_] == len(w), (s_, lens[s_], thr)
+                assert keep[a:a + len(w)].long().tolist() == w, (s_, lens[s_], thr)
+
+
+@pytest.mark.gpu
 def test_nms_ragged_segments_and_errors():
     from ovmono3d_b200 import ops
 
