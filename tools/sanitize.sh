@@ -1,0 +1,21 @@
+#!/bin/bash
+# compute-sanitizer evidence (SURVEY.md section 5 "Race detection"; VERDICT r1 "missing" 6).  Run ON THE GPU BOX from
+# the repo root:   tools/sanitize.sh r02      -> gpurun_out/r02_sanitizer_*.log  (copy the summaries to profiles/)
+# Targets: the smoke (small lift + GroundingDINO post-processing), one C2 lift step, the NMS / box-inference tests.
+set -u
+tag=${1:-run}
+o=gpurun_out
+mkdir -p $o
+cs=/usr/local/cuda/bin/compute-sanitizer
+run() {  # name tool timeout command...
+  local name=$1 tool=$2 to=$3; shift 3
+  echo "=== $tool :: $*" > $o/${tag}_sanitizer_${tool}_${name}.log
+  timeout $to $cs --tool $tool --print-limit 20 --error-exitcode 0 "$@" >> $o/${tag}_sanitizer_${tool}_${name}.log 2>&1
+  echo "exit $?" >> $o/${tag}_sanitizer_${tool}_${name}.log
+  grep -E "ERROR SUMMARY|RACECHECK SUMMARY|exit |ok:|passed|failed" $o/${tag}_sanitizer_${tool}_${name}.log | tail -4
+}
+for tool in memcheck synccheck racecheck; do
+  run smoke $tool 600 python __graft_entry__.py smoke
+  run c2step $tool 900 python tools/one_step.py --steps 1
+  run post $tool 900 python -m pytest -q -x -m gpu tests/test_gdino_post.py tests/test_box_head.py -k "not random and not perf"
+done
