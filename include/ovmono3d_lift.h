@@ -15,8 +15,9 @@
  *   ovm_head_decode  the five linear heads, cube_head.py:158-164,176-204, the class/bin selection
  *                    roi_heads.py:433-477 and the whole decode roi_heads.py:378-419,480-549,795-843
  *                    with math_util.py:116-219,581-592,651-679,969-978.
+ *   ovm_fc_tail      the last nn.Linear of the FC stack, the heads and the decode fused (same lines as the two above).
  *   ovm_lift_forward the inference slice of ROIHeads3D._forward_cube, roi_heads.py:329-848:
- *                    the three kernels above on one stream.
+ *                    the kernels above on one stream.
  *   ovm_nms          torchvision.ops.nms / batched_nms as the reference calls them:
  *                    roi_heads_gdino.py:6,272 (class-agnostic, 0.5) and fast_rcnn.py:105 (per class).
  *   ovm_gdino_post   GroundingDINO post-processing, the step right before the lift:
@@ -36,7 +37,7 @@
 extern "C" {
 #endif
 
-#define OVM_ABI_VERSION 5
+#define OVM_ABI_VERSION 6
 #define OVM_MAX_LEVELS 8
 #define OVM_RECORD_WIDTH 48   /* floats per detection record, see ovm_head_decode */
 
@@ -48,7 +49,11 @@ enum {
 };
 
 enum { OVM_LAYOUT_NCHW = 0, OVM_LAYOUT_NHWC = 1 };
-enum { OVM_F32 = 0, OVM_BF16 = 1 };
+enum {
+  OVM_F32 = 0,
+  OVM_BF16 = 1,
+  OVM_TF32 = 2 /* fp32 storage, values rounded to TF32 (10 mantissa bits, nearest): operands of a kind::tf32 layer */
+};
 enum { OVM_Z_DIRECT = 0, OVM_Z_SIGMOID = 1, OVM_Z_LOG = 2, OVM_Z_CLUSTERS = 3 };
 enum { OVM_POSE_6D = 0, OVM_POSE_QUATERNION = 1, OVM_POSE_EULER = 2 };
 enum { OVM_DIMS_EXP = 0, OVM_DIMS_SIGMOID = 1 };
@@ -157,6 +162,9 @@ typedef struct {
  * classes [n] int64, scores [n] fp32 or NULL, batch_idx [n] int32.
  * cams [num_images, 12] fp32: K row-major (9), im_scales_ratio, H of the padded network input, 0
  * (roi_heads.py:378-400).
+ * A class id outside [0, num_classes) (only looked at with per-class heads / depth bins) or an image index outside
+ * [0, num_images) never indexes device memory: such a box gets a record whose decoded fields are NaN (the reference
+ * raises IndexError there); the plugin validates class ids on the host when it has them there.
  * records [n, 48] fp32: bbox3D 8x3 (0..23) | center_cam (24..26) | center_2D (27..28) |
  *   dimensions W,H,L (29..31) | pose 3x3 (32..40) | 2-D box (41..44) | score (45) | class (46) | 0.
  * raw (optional) [n,16] fp32: the selected head outputs before decode: deltas(2) z(1) dims(3)
@@ -172,6 +180,10 @@ typedef struct {
   const float* bias;    /* fp32 [N] */
   int32_t N, K;
   int64_t ldw;
+  const float* weight_tf32; /* optional: the same weight as fp32 [N, ldw_tf32] rounded to TF32 (ovm_round_tf32).  Used by the
+                               LAST layer of a stack that ends in ovm_fc_tail: the layer then runs as a kind::tf32 MMA on
+                               fp32 activations instead of bf16 x bf16 (see ovm_fc_tail) */
+  int64_t ldw_tf32;         /* elements, multiple of 4 */
 } ovm_fc_layer_t;
 
 typedef struct {
@@ -185,9 +197,10 @@ typedef struct {
   int64_t ld_pooled;
   float* acc;          /* fp32 [n, fc_dim] split-K accumulator: ZERO-FILLED by the caller once, when it is
                           allocated; ovm_lift_forward leaves it zero-filled again (no per-call memset) */
-  void* act_a;         /* bf16 [n, fc_dim] ping */
-  void* act_b;         /* bf16 [n, fc_dim] pong */
-  float* feats;        /* fp32 [n, num_groups * fc_dim] */
+  void* act_a;         /* [n, fc_dim] x 4 bytes: activations between FC layers, ping (bf16, or TF32 in fp32 storage) */
+  void* act_b;         /* same, pong */
+  float* feats;        /* fp32 [n, num_groups * fc_dim]: output of the last FC layer; not touched when the stack ends
+                          in the fused ovm_fc_tail (the last layer's output never leaves the SM) */
   int32_t* levels;     /* int32 [n] */
   int32_t* tile_counters;      /* optional int32 [num_tile_counters], ZERO-FILLED once like acc (left zeroed): with
                                   it the split-K FC layer finishes (bias, ReLU, cast) inside the GEMM launch; NULL:
@@ -196,7 +209,25 @@ typedef struct {
   int32_t _pad;
 } ovm_workspace_t;
 
-/* ROIAlign (bf16 out) -> FC stack -> heads + decode on `stream`. */
+/* Last FC layer + the five linear heads + the cube decode in ONE launch (cube_head.py:157-164 last Linear + heads,
+ * roi_heads.py:378-549,798-843): a cluster of N/128 CTAs per 128 boxes, the layer's output stays in tensor memory /
+ * registers, per-box head partial sums are exchanged through distributed shared memory, one thread decodes a box.
+ * A [n, lda]: the layer's input -- bf16 (a_dtype OVM_BF16) or fp32 values rounded to TF32 (OVM_TF32, e.g. written by
+ * ovm_gemm_bf16 with out_dtype OVM_TF32); W [N, ldw] the layer's weight in the SAME type (nn.Linear layout), bias [N]
+ * fp32.  Needs class-agnostic heads (DIMS_PRIORS_ENABLED off, CLUSTER_BINS 1), one shared FC stack and N in
+ * {128, 256, 512, 1024}; returns OVM_EUNSUPPORTED otherwise (use ovm_gemm_bf16 + ovm_head_decode).  The remaining
+ * arguments are those of ovm_head_decode.  Class ids are not used to index anything in this configuration.        */
+int ovm_fc_tail(const void* A, int64_t lda, int32_t a_dtype, const void* W, int64_t ldw, const float* bias, int32_t N,
+                int32_t K, const ovm_decode_cfg_t* cfg, const ovm_head_weights_t* w, const float* boxes,
+                const int64_t* classes, const float* scores, const int32_t* batch_idx, const float* cams,
+                int32_t num_images, int32_t n, float* records, float* raw, void* stream);
+
+/* x (fp32 [rows, ld_in]) -> fp32 [rows, ld_out] rounded to TF32 (nearest, ties away), columns >= cols zero-filled. */
+int ovm_round_tf32(const float* in, int64_t ld_in, int32_t rows, int32_t cols, float* out, int64_t ld_out, void* stream);
+
+/* ROIAlign (bf16 out) -> FC stack -> heads + decode on `stream`.  With one shared FC stack of >= 2 layers and
+ * class-agnostic heads the last layer, the heads and the decode run as one ovm_fc_tail launch (TF32 when the last
+ * layer carries weight_tf32, bf16 otherwise; OVM_FUSE_TAIL=0 in the environment selects the unfused sequence). */
 int ovm_lift_forward(const ovm_pooler_t* pooler, const ovm_fc_stack_t* fc, const ovm_decode_cfg_t* cfg,
                      const ovm_head_weights_t* heads, const float* boxes, const int64_t* classes,
                      const float* scores, const int32_t* batch_idx, const float* cams, int32_t n,

@@ -45,6 +45,24 @@ inline int check_cuda(cudaError_t e, const char* what) {
 
 constexpr int kNumSMs = 148;  // B200
 
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-device (per-context) property of a kernel: remember, per device,
+// the largest size already granted, so that a process driving several GPUs opts in on each of them and the
+// steady state costs one cudaGetDevice.  Racing host threads at worst both set the attribute.
+struct SmemOptIn {
+  static constexpr int kMaxDevices = 64;
+  std::atomic<int> granted[kMaxDevices];
+  template <typename F>
+  int ensure(F kernel, size_t bytes) {
+    int dev = 0;
+    OVM_CUDA(cudaGetDevice(&dev));
+    std::atomic<int>* slot = (dev >= 0 && dev < kMaxDevices) ? &granted[dev] : nullptr;
+    if (slot && (int)bytes <= slot->load(std::memory_order_relaxed)) return OVM_OK;
+    OVM_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    if (slot) slot->store((int)bytes, std::memory_order_relaxed);
+    return OVM_OK;
+  }
+};
+
 // Programmatic dependent launch: every kernel of the lift is launched with the programmatic-stream-serialization
 // attribute, tells the scheduler right away that its dependents may be launched (pdl_trigger), and waits for the
 // kernel before it in the stream (pdl_wait: full completion, memory visible) only where it first touches that
@@ -112,6 +130,14 @@ int head_decode_launch(const ovm_decode_cfg_t* cfg, const ovm_head_weights_t* w,
                        int64_t ld_feats, const float* boxes, const int64_t* classes, const float* scores,
                        const int32_t* batch_idx, const float* cams, int32_t num_images, int32_t n,
                        float* records, float* raw, cudaStream_t stream);
+// fc_tail.cu: last FC layer + heads + decode in one launch (class-agnostic heads, shared FC stack)
+bool fc_tail_supported(const ovm_decode_cfg_t* cfg, int32_t N, int32_t K);
+int fc_tail_launch(const void* A, int64_t lda, int32_t a_dtype, const void* W, int64_t ldw, const float* bias, int32_t N,
+                   int32_t K, const ovm_decode_cfg_t* cfg, const ovm_head_weights_t* w, const float* boxes,
+                   const int64_t* classes, const float* scores, const int32_t* batch_idx, const float* cams,
+                   int32_t num_images, int32_t n, float* records, float* raw, cudaStream_t stream);
+int round_tf32_launch(const float* in, int64_t ld_in, int32_t rows, int32_t cols, float* out, int64_t ld_out,
+                      cudaStream_t stream);
 
 // detect_post.cu
 int nms_launch(const float* boxes, const float* scores, const int64_t* classes, const int32_t* seg_offsets,

@@ -359,6 +359,13 @@ nms_kernel(const float* __restrict__ boxes, const float* __restrict__ scores, co
     s.sb[p] = b;
     s.scls[p] = c;
   }
+  if (C > 1) {
+    // block_greedy's first round already stores into the peer CTAs' exchange words, which alias s.red: every CTA of the
+    // cluster must have started (CUDA's rule for any distributed-shared-memory access) and be past its own reads of
+    // s.red in the coordinate-trick reduction above before a faster peer may do that
+    cluster_arrive_release();
+    cluster_wait_acquire();
+  }
   block_greedy<C>(s.sb, mode == OVM_NMS_PER_CLASS ? s.scls : nullptr, s.alive, n, thr,
                   reinterpret_cast<uint32_t*>(s.warp_tot), nullptr, reinterpret_cast<uint32_t*>(s.red));
   if (C > 1 && blockIdx.x % C != 0) return;     // every CTA has the result; the first of the cluster writes it
@@ -844,12 +851,11 @@ int nms_launch(const float* boxes, const float* scores, const int64_t* classes, 
               max_segment_len, OVM_NMS_MAX_SEGMENT);
   OVM_REQUIRE((reinterpret_cast<uintptr_t>(boxes) & 15) == 0, "ovm_nms: boxes must be 16-byte aligned");
   const size_t smem = post_smem_bytes(host_next_pow2(max_segment_len));
-  static size_t configured[2] = {0, 0};
+  static SmemOptIn opt[2];
   const int csize = nms_cluster_size();
-  if (smem > configured[csize > 1]) {
-    OVM_CUDA(cudaFuncSetAttribute(csize > 1 ? nms_kernel<8> : nms_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)smem));
-    configured[csize > 1] = smem;
+  {
+    int rc = csize > 1 ? opt[1].ensure(nms_kernel<8>, smem) : opt[0].ensure(nms_kernel<1>, smem);
+    if (rc != OVM_OK) return rc;
   }
   OVM_CUDA(launch_cluster(csize > 1 ? nms_kernel<8> : nms_kernel<1>, num_segments, csize, smem, stream, boxes, scores,
                           classes, seg_offsets, max_segment_len, iou_threshold, mode, keep, keep_count));
@@ -878,22 +884,21 @@ int gdino_post_launch(const float* logits, const float* boxes_cxcywh, const int3
   }
   const size_t smem_score = (size_t)kScoreWarps * T * 4 + (size_t)P * 8;
   OVM_REQUIRE(smem_score <= 200 * 1024, "ovm_gdino_post: %d phrases need %zu bytes of shared memory", P, smem_score);
-  static size_t conf_score = 0;
-  if (smem_score > conf_score) {
-    OVM_CUDA(cudaFuncSetAttribute(gdino_score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_score));
-    conf_score = smem_score;
+  static SmemOptIn opt_score;
+  {
+    int rc = opt_score.ensure(gdino_score_kernel, smem_score);
+    if (rc != OVM_OK) return rc;
   }
   gdino_score_kernel<<<dim3((nq + kScoreWarps - 1) / kScoreWarps, batch), kScoreWarps * 32, smem_score, stream>>>(
       logits, phrase_ranges, nq, T, P, out_scores, out_classes);
   OVM_LAUNCHED("gdino_score_kernel");
   const int npad = host_next_pow2(nq);
   const size_t smem = post_smem_bytes(npad) + (size_t)npad * 8;
-  static size_t configured[2] = {0, 0};
+  static SmemOptIn opt[2];
   const int csize = nms_cluster_size();
-  if (smem > configured[csize > 1]) {
-    OVM_CUDA(cudaFuncSetAttribute(csize > 1 ? gdino_post_kernel<8> : gdino_post_kernel<1>,
-                                  cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured[csize > 1] = smem;
+  {
+    int rc = csize > 1 ? opt[1].ensure(gdino_post_kernel<8>, smem) : opt[0].ensure(gdino_post_kernel<1>, smem);
+    if (rc != OVM_OK) return rc;
   }
   OVM_CUDA(launch_cluster(csize > 1 ? gdino_post_kernel<8> : gdino_post_kernel<1>, batch, csize, smem, stream,
                           boxes_cxcywh, nq, (float)image_width, (float)image_height, box_threshold, nms_threshold,
@@ -954,10 +959,10 @@ int box_inference_launch(const ovm_box_inference_cfg_t* c, const float* logits, 
                                                      image_sizes, N, R, ws->probs, ws->cand_boxes, ws->image_stats);
   OVM_LAUNCHED("box_predict_kernel");
   const size_t smem_nms = post_smem_bytes(host_next_pow2(max_per_image));
-  static size_t conf_nms = 0;
-  if (smem_nms > conf_nms) {
-    OVM_CUDA(cudaFuncSetAttribute(box_class_nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_nms));
-    conf_nms = smem_nms;
+  static SmemOptIn opt_nms;
+  {
+    int rc = opt_nms.ensure(box_class_nms_kernel, smem_nms);
+    if (rc != OVM_OK) return rc;
   }
   box_class_nms_kernel<<<dim3(K, N), kPostThreads, smem_nms, stream>>>(b, ws->probs, ws->cand_boxes, seg_offsets,
                                                                       ws->image_stats, max_per_image, ws->class_keep,
@@ -966,10 +971,10 @@ int box_inference_launch(const ovm_box_inference_cfg_t* c, const float* logits, 
   const int npad = host_next_pow2((int)std::max<int64_t>(merged, 1));
   const int npad_small = c->topk_per_image >= 0 && c->topk_per_image <= 2048 ? host_next_pow2(c->topk_per_image) : 0;
   const size_t smem_topk = (size_t)(npad + npad_small) * 8 + (size_t)(K + 1 + 33 + 256 + 4) * 4;
-  static size_t conf_topk = 0;
-  if (smem_topk > conf_topk) {
-    OVM_CUDA(cudaFuncSetAttribute(box_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_topk));
-    conf_topk = smem_topk;
+  static SmemOptIn opt_topk;
+  {
+    int rc = opt_topk.ensure(box_topk_kernel, smem_topk);
+    if (rc != OVM_OK) return rc;
   }
   box_topk_kernel<<<N, kPostThreads, smem_topk, stream>>>(b, ws->probs, ws->cand_boxes, seg_offsets, max_per_image,
                                                           ws->class_keep, ws->class_count, npad, npad_small, cap, out_boxes,

@@ -1,0 +1,447 @@
+// fc_tail_kernel: the last FC layer of CubeHead, its five linear heads and the whole cube decode in ONE launch.
+//
+//   h2 = ReLU(h1 . W2^T + b2)                reference cubercnn/modeling/roi_heads/cube_head.py:64-74,157 (last Linear)
+//   heads = h2 . Wh^T + bh  (<= 13 rows)     cube_head.py:158-164
+//   record = decode(heads, box, camera)      roi_heads.py:378-549,798-843 (decode_core.cuh)
+//
+// h2 never leaves the SM: the unfused sequence wrote it as fp32 [n, 1024] (6.5 MB at C2) from one kernel and read it
+// back in the next, with a launch and a serial dependency in between (34 us = 18 % of the C2 step in round 1).
+//
+// Decomposition: a cluster of CS = FC_DIM / 128 CTAs owns 128 boxes.  CTA r of the cluster computes the 128 x 128
+// block h2[:, 128 r : 128 r + 128] with tcgen05.mma (operands by TMA, 128-byte swizzle, fp32 accumulator in TMEM),
+// applies bias + ReLU on the way out of TMEM (thread = box row, tcgen05.ld), and multiplies the block straight into
+// its slice of the head rows (staged in shared memory, broadcast reads): 13 partial sums per box and CTA.  The
+// partials are exchanged through distributed shared memory -- box row i belongs to CTA i / (128 / CS), every CTA
+// stores its 13 partials of that row into the owner's buffer with st.shared::cluster -- one cluster barrier, then
+// each CTA sums the 2 CS contributions of its 128 / CS boxes in a fixed order (deterministic) and decodes them, one
+// thread per box.
+//
+// Precision: operands are either bf16 (kind::f16) or TF32 (kind::tf32: fp32 in shared memory, pre-rounded to 10
+// mantissa bits by the producer of h1 and by ovm_round_tf32 for W2).  fc2 is 7.5 % of the head's FLOPs; running it
+// at TF32 removes half of the bf16 head's pose / corner error (profiles/r02_bf16_attribution.json) for 2x the operand
+// bytes of this one small layer.
+#include <cuda.h>
+
+#include <cstdlib>
+
+#include "common.cuh"
+#include "decode_core.cuh"
+
+namespace ovm {
+
+namespace {
+
+constexpr int kTM = 128;               // boxes per cluster (UMMA M)
+constexpr int kTN = 128;               // fc2 output columns per CTA (UMMA N)
+constexpr int kRowBytes = 128;         // K bytes per operand row and stage = one 128-byte swizzle row
+constexpr int kTailStages = 5;
+constexpr int kTailABytes = kTM * kRowBytes;
+constexpr int kTailBBytes = kTN * kRowBytes;
+constexpr int kTailStageBytes = kTailABytes + kTailBBytes;
+constexpr int kTailEpiWarps = 8;       // two per TMEM lane quadrant, each takes 64 of the CTA's 128 columns
+constexpr int kTailThreads = (2 + kTailEpiWarps) * 32;
+constexpr int kHwStride = 16;          // head rows per column in shared memory (13 used)
+constexpr int kMaxCS = 8;
+constexpr int kPartFloats = 2 * kMaxCS * kMaxHeadRows * (kTM / kMaxCS);   // [2 CS contributors][13][128 / CS rows]
+constexpr size_t kTailSmemBytes = 1024 + (size_t)kTailStages * kTailStageBytes + 128 /* barriers, tmem slot */ +
+                                  (size_t)(kTN * kHwStride + kTN + 16 + kPartFloats) * 4;
+
+struct TailArgs {
+  DecodeArgs d;          // feats / ld_feats unused
+  int K;                 // input features of the layer
+  int N;                 // FC_DIM = CS * 128
+  int cs;                // cluster size
+  int kblocks;           // ceil(K * sizeof(element) / 128)
+  int elems_per_row;     // K elements per 128-byte row: 32 (tf32) or 64 (bf16)
+  const float* bias;     // [N]
+};
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done;
+  do {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t"
+        "}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+  } while (!done);
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
+      "l"(map), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tcgen05_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+template <bool TF32>
+__device__ __forceinline__ void umma(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  if (TF32) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+        "}" ::"r"(tmem_d),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+  } else {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+        "}" ::"r"(tmem_d),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+  }
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* v) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+// K-major operand, 128-byte swizzle, 1024 bytes between 8-row groups (see gemm_tcgen05.cu)
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ uint32_t mapa_shared(uint32_t addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void st_cluster_f32(uint32_t addr, float v) {
+  asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+// Row r of the class-agnostic head stack in decode order (deltas 0-1, dims 2-4, z 5, uncertainty 6 if any, pose after)
+__device__ __forceinline__ const float* agnostic_head_row(const ovm_head_weights_t& w, int r, int conf_rows, int K,
+                                                          float* bias) {
+  if (r < 2) { *bias = w.b_deltas[r]; return w.w_deltas + (long long)r * K; }
+  if (r < 5) { *bias = w.b_dims[r - 2]; return w.w_dims + (long long)(r - 2) * K; }
+  if (r == 5) { *bias = w.b_z[0]; return w.w_z; }
+  if (r == 6 && conf_rows) { *bias = w.b_uncert[0]; return w.w_uncert; }
+  *bias = w.b_pose[r - 6 - conf_rows];
+  return w.w_pose + (long long)(r - 6 - conf_rows) * K;
+}
+
+template <bool TF32>
+__global__ void __launch_bounds__(kTailThreads, 1)
+fc_tail_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TailArgs g) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  uint8_t* aligned = smem_raw + (base - raw);
+  const uint32_t smem_a = base;
+  const uint32_t smem_b = base + kTailStages * kTailABytes;
+  const uint32_t bars = base + kTailStages * kTailStageBytes;
+  const uint32_t full_bar = bars;                          // kTailStages
+  const uint32_t empty_bar = bars + 8 * kTailStages;       // kTailStages
+  const uint32_t tfull_bar = bars + 16 * kTailStages;      // 1
+  const uint32_t tmem_slot = tfull_bar + 16;
+  uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(aligned + kTailStages * kTailStageBytes + 16 * kTailStages + 16);
+  float* hw_t = reinterpret_cast<float*>(aligned + kTailStages * kTailStageBytes + 128);   // [128 columns][16 rows]
+  float* b2s = hw_t + kTN * kHwStride;                                                     // [128]
+  float* hbias = b2s + kTN;                                                                // [16]
+  float* part = hbias + 16;                                                                // [2 cs][13][rpc]
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int cs = g.cs;
+  const int rank = (int)cluster_ctarank();
+  const int m_tile = blockIdx.x / cs;
+  const int rpc = kTM / cs;                     // box rows this CTA decodes
+  const ovm_decode_cfg_t& cfg = g.d.cfg;
+  const int pose_n = cfg.pose_type == OVM_POSE_6D ? 6 : (cfg.pose_type == OVM_POSE_QUATERNION ? 4 : 3);
+  const int conf_rows = cfg.use_confidence ? 1 : 0;
+  const int nrows = 6 + conf_rows + pose_n;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < kTailStages; ++s) {
+      mbar_init(full_bar + 8 * s, 1);
+      mbar_init(empty_bar + 8 * s, 1);
+    }
+    mbar_init(tfull_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 2) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"((uint32_t)kTN) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  // parameters of the model (not results of the kernels before): staged while fc1 is still running
+  if (warp >= 2) {
+    const int e = threadIdx.x - 64;             // 0 .. 255
+    const int col0 = rank * kTN;
+    for (int i = e; i < kTN * kHwStride; i += kTailEpiWarps * 32) {
+      const int r = i / kTN, j = i - r * kTN;   // consecutive threads read consecutive columns of one head row
+      float v = 0.f;
+      if (r < nrows) {
+        float b;
+        const float* row = agnostic_head_row(g.d.w, r, conf_rows, g.N, &b);
+        v = __ldg(row + col0 + j);
+        if (j == 0) hbias[r] = b;
+      }
+      hw_t[j * kHwStride + r] = v;
+    }
+    if (e < kTN) b2s[e] = __ldg(g.bias + col0 + e);
+  }
+  // the boxes this CTA decodes are inputs of the call (complete before the chain's first kernel): loaded ahead of the wait
+  const int e = threadIdx.x - 64;
+  const int my_row = m_tile * kTM + rank * rpc + e;
+  const bool decoder = e >= 0 && e < rpc && my_row < g.d.n;
+  BoxIn in{};
+  if (decoder) in = load_box_in(g.d, my_row);
+
+  tcgen05_fence_before();
+  cluster_sync_all();        // barriers initialised, TMEM allocated, staging visible; every CTA of the cluster has started
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+  pdl_trigger();
+  pdl_wait();                // h1 comes from the FC layer before
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ===== TMA producer
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = 0; kb < g.kblocks; ++kb) {
+        mbar_wait(empty_bar + 8 * stage, phase ^ 1);
+        mbar_expect_tx(full_bar + 8 * stage, kTailStageBytes);
+        tma_load_2d(smem_a + stage * kTailABytes, &tmA, full_bar + 8 * stage, kb * g.elems_per_row, m_tile * kTM);
+        tma_load_2d(smem_b + stage * kTailBBytes, &tmB, full_bar + 8 * stage, kb * g.elems_per_row, rank * kTN);
+        if (++stage == kTailStages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // ===== MMA issuer: D[128 x 128] += A[128 x 32 B] . B[128 x 32 B]^T, four per stage
+      constexpr uint32_t fmt = TF32 ? 2u : 1u;
+      constexpr uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(kTN >> 3) << 17) | ((uint32_t)(kTM >> 4) << 24);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = 0; kb < g.kblocks; ++kb) {
+        mbar_wait(full_bar + 8 * stage, phase);
+        tcgen05_fence_after();
+        const uint64_t adesc = make_smem_desc(smem_a + stage * kTailABytes);
+        const uint64_t bdesc = make_smem_desc(smem_b + stage * kTailBBytes);
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          umma<TF32>(tmem_base, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (kb > 0 || k > 0) ? 1u : 0u);
+        tcgen05_commit(empty_bar + 8 * stage);
+        if (++stage == kTailStages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+      tcgen05_commit(tfull_bar);
+    }
+  } else {
+    // ===== epilogue: thread = box row of the tile (TMEM lane), 64 columns per warp
+    const int quad = warp & 3;
+    const int half = (warp - 2) >> 2;
+    const int row = quad * 32 + lane;
+    float p[kMaxHeadRows];
+#pragma unroll
+    for (int k = 0; k < kMaxHeadRows; ++k) p[k] = 0.f;
+    mbar_wait(tfull_bar, 0);
+    tcgen05_fence_after();
+#pragma unroll 1
+    for (int c = 0; c < 4; ++c) {
+      uint32_t v[16];
+      const int colb = half * 64 + c * 16;
+      tmem_ld16(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)colb, v);
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        float x = __uint_as_float(v[i]) + b2s[colb + i];
+        x = x < 0.f ? 0.f : x;                                  // torch.relu keeps NaN
+        const float4* w4 = reinterpret_cast<const float4*>(hw_t + (colb + i) * kHwStride);
+        const float4 w0 = w4[0], w1 = w4[1], w2 = w4[2], w3 = w4[3];
+        p[0] = fmaf(x, w0.x, p[0]); p[1] = fmaf(x, w0.y, p[1]); p[2] = fmaf(x, w0.z, p[2]); p[3] = fmaf(x, w0.w, p[3]);
+        p[4] = fmaf(x, w1.x, p[4]); p[5] = fmaf(x, w1.y, p[5]); p[6] = fmaf(x, w1.z, p[6]); p[7] = fmaf(x, w1.w, p[7]);
+        p[8] = fmaf(x, w2.x, p[8]); p[9] = fmaf(x, w2.y, p[9]); p[10] = fmaf(x, w2.z, p[10]); p[11] = fmaf(x, w2.w, p[11]);
+        p[12] = fmaf(x, w3.x, p[12]);
+      }
+    }
+    tcgen05_fence_before();
+    // partial sums of this row -> the CTA that decodes it
+    const int dst = row / rpc, t = row - dst * rpc;
+    const int contributor = rank * 2 + half;
+    const uint32_t remote = mapa_shared(smem_u32(part), (uint32_t)dst);
+#pragma unroll
+    for (int k = 0; k < kMaxHeadRows; ++k)
+      st_cluster_f32(remote + (uint32_t)(((contributor * kMaxHeadRows + k) * rpc + t) * 4), p[k]);
+  }
+  __syncwarp();
+  cluster_sync_all();        // every partial has landed (release / acquire at cluster scope)
+  if (warp == 2) {
+    tcgen05_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)kTN) : "memory");
+  }
+  if (decoder) {
+    float hv[kMaxHeadRows];
+#pragma unroll
+    for (int k = 0; k < kMaxHeadRows; ++k) {
+      float s = 0.f;
+      for (int c = 0; c < 2 * cs; ++c) s += part[(c * kMaxHeadRows + k) * rpc + e];   // fixed order: deterministic
+      hv[k] = s + hbias[k < nrows ? k : 0];
+    }
+    decode_record(g.d, my_row, in, 0, hv, true);
+  }
+}
+
+// [rows, cols] row-major with leading dimension ld (elements) -> 2-D map, box {128 bytes of K, 128 rows}, 128-byte
+// swizzle, out-of-bounds elements read as zero (row and K tails).
+int make_tail_map(CUtensorMap* map, const void* ptr, int64_t rows, int64_t cols, int64_t ld, bool tf32) {
+  EncodeTiledFn enc = tensormap_encode_fn();
+  if (!enc) {
+    set_error("cuTensorMapEncodeTiled not available from the driver");
+    return OVM_ECUDA;
+  }
+  const int esz = tf32 ? 4 : 2;
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * esz};
+  cuuint32_t box[2] = {(cuuint32_t)(kRowBytes / esz), 128};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(map, tf32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims,
+                   strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled (fc tail) failed with CUresult %d (rows=%lld cols=%lld ld=%lld)", (int)r, (long long)rows,
+              (long long)cols, (long long)ld);
+    return OVM_ECUDA;
+  }
+  return OVM_OK;
+}
+
+template <bool TF32>
+int launch_tail(const CUtensorMap& tmA, const CUtensorMap& tmB, const TailArgs& g, int grid, cudaStream_t stream) {
+  static SmemOptIn opt;
+  {
+    int rc = opt.ensure(fc_tail_kernel<TF32>, kTailSmemBytes);
+    if (rc != OVM_OK) return rc;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kTailThreads);
+  cfg.dynamicSmemBytes = kTailSmemBytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  attr[1].id = cudaLaunchAttributeClusterDimension;
+  attr[1].val.clusterDim.x = g.cs;
+  attr[1].val.clusterDim.y = 1;
+  attr[1].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 2;
+  OVM_CUDA(cudaLaunchKernelEx(&cfg, fc_tail_kernel<TF32>, tmA, tmB, g));
+  OVM_LAUNCHED("fc_tail_kernel");
+  return OVM_OK;
+}
+
+}  // namespace
+
+bool fc_tail_supported(const ovm_decode_cfg_t* cfg, int32_t N, int32_t K) {
+  static const bool enabled = [] { const char* v = getenv("OVM_FUSE_TAIL"); return !v || atoi(v) != 0; }();
+  if (!enabled || !cfg) return false;
+  if (cfg->dims_priors_enabled || cfg->cluster_bins != 1) return false;   // head rows depend on the box's class / bin
+  for (int i = 1; i < 5; ++i)
+    if (cfg->feat_offset[i] != cfg->feat_offset[0]) return false;         // one FC stack per head (SHARED_FC = False)
+  if (N != cfg->fc_dim || K <= 0) return false;
+  return N == 128 || N == 256 || N == 512 || N == 1024;
+}
+
+int fc_tail_launch(const void* A, int64_t lda, int32_t a_dtype, const void* W, int64_t ldw, const float* bias, int32_t N,
+                   int32_t K, const ovm_decode_cfg_t* cfg, const ovm_head_weights_t* w, const float* boxes,
+                   const int64_t* classes, const float* scores, const int32_t* batch_idx, const float* cams,
+                   int32_t num_images, int32_t n, float* records, float* raw, cudaStream_t stream) {
+  OVM_REQUIRE(cfg && w, "ovm_fc_tail: cfg / weights are NULL");
+  OVM_REQUIRE(a_dtype == OVM_BF16 || a_dtype == OVM_TF32, "ovm_fc_tail: operand dtype %d (OVM_BF16 or OVM_TF32)", a_dtype);
+  OVM_REQUIRE(cfg->z_type >= OVM_Z_DIRECT && cfg->z_type <= OVM_Z_CLUSTERS, "ovm_fc_tail: z_type %d", cfg->z_type);
+  OVM_REQUIRE(cfg->pose_type >= OVM_POSE_6D && cfg->pose_type <= OVM_POSE_EULER,
+              "Cuboid pose type %d is not recognized", cfg->pose_type);
+  if (!fc_tail_supported(cfg, N, K)) {
+    set_error("ovm_fc_tail: needs class-agnostic heads (DIMS_PRIORS_ENABLED off, CLUSTER_BINS 1), SHARED_FC and "
+              "FC_DIM in {128, 256, 512, 1024}; use ovm_gemm_bf16 + ovm_head_decode otherwise");
+    return OVM_EUNSUPPORTED;
+  }
+  OVM_REQUIRE(cfg->z_type != OVM_Z_CLUSTERS || w->priors_z_stats, "ovm_fc_tail: priors_z_stats needed for Z_TYPE clusters");
+  OVM_REQUIRE(w->w_deltas && w->b_deltas && w->w_dims && w->b_dims && w->w_pose && w->b_pose && w->w_z && w->b_z,
+              "ovm_fc_tail: a head weight is NULL");
+  OVM_REQUIRE(!cfg->use_confidence || (w->w_uncert && w->b_uncert), "ovm_fc_tail: uncertainty head is NULL");
+  if (n == 0) return OVM_OK;
+  const int esz = a_dtype == OVM_TF32 ? 4 : 2;
+  OVM_REQUIRE(n > 0 && A && W && bias && boxes && classes && batch_idx && cams && records && num_images > 0,
+              "ovm_fc_tail: NULL input with n=%d", n);
+  OVM_REQUIRE(lda >= K && ldw >= K && (lda * esz) % 16 == 0 && (ldw * esz) % 16 == 0 &&
+                  !(reinterpret_cast<uintptr_t>(A) & 15) && !(reinterpret_cast<uintptr_t>(W) & 15),
+              "ovm_fc_tail: operands must be 16-byte aligned with 16-byte row pitches >= K");
+  OVM_REQUIRE(!(reinterpret_cast<uintptr_t>(records) & 15) && (!raw || !(reinterpret_cast<uintptr_t>(raw) & 15)),
+              "ovm_fc_tail: records / raw must be 16-byte aligned");
+  TailArgs g{};
+  g.d.cfg = *cfg;
+  g.d.w = *w;
+  g.d.boxes = boxes;
+  g.d.classes = reinterpret_cast<const long long*>(classes);
+  g.d.scores = scores;
+  g.d.batch_idx = batch_idx;
+  g.d.cams = cams;
+  g.d.num_images = num_images;
+  g.d.n = n;
+  g.d.records = records;
+  g.d.raw = raw;
+  g.K = K;
+  g.N = N;
+  g.cs = N / kTN;
+  g.elems_per_row = kRowBytes / esz;
+  g.kblocks = (K + g.elems_per_row - 1) / g.elems_per_row;
+  g.bias = bias;
+  CUtensorMap tmA, tmB;
+  int rc = make_tail_map(&tmA, A, n, K, lda, a_dtype == OVM_TF32);
+  if (rc != OVM_OK) return rc;
+  rc = make_tail_map(&tmB, W, N, K, ldw, a_dtype == OVM_TF32);
+  if (rc != OVM_OK) return rc;
+  const int grid = g.cs * ((n + kTM - 1) / kTM);
+  return a_dtype == OVM_TF32 ? launch_tail<true>(tmA, tmB, g, grid, stream) : launch_tail<false>(tmA, tmB, g, grid, stream);
+}
+
+}  // namespace ovm

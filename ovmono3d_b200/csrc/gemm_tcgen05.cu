@@ -66,6 +66,7 @@ struct GemmArgs {
   void* fin_out;
   long long fin_ldo;
   int fin_bf16;
+  int round_tf32;        // fp32 outputs (DIRECT epilogue / fused finish) are rounded to TF32: the next layer is a kind::tf32 MMA
 };
 
 thread_local unsigned long long* g_gemm_trace = nullptr;
@@ -145,6 +146,15 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* v) {
       : "r"(taddr)
       : "memory");
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+// round-to-nearest (ties away) to TF32's 10 mantissa bits; the value stays an fp32 bit pattern
+__device__ __forceinline__ float round_tf32(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
+__device__ __forceinline__ float4 round_tf32(float4 v) {
+  return make_float4(round_tf32(v.x), round_tf32(v.y), round_tf32(v.z), round_tf32(v.w));
 }
 __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
@@ -372,6 +382,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             x.y = (relu && x.y < 0.f) ? 0.f : x.y;
             x.z = (relu && x.z < 0.f) ? 0.f : x.z;
             x.w = (relu && x.w < 0.f) ? 0.f : x.w;
+            if (MODE == kModeF32 && g.round_tf32) x = round_tf32(x);
           }
           const long long off = (long long)(row0 + r) * g.ldo + c;
           if (full) {
@@ -445,6 +456,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                   v.x = v.x < 0.f ? 0.f : v.x; v.y = v.y < 0.f ? 0.f : v.y;
                   v.z = v.z < 0.f ? 0.f : v.z; v.w = v.w < 0.f ? 0.f : v.w;
                 }
+                if (g.round_tf32) v = round_tf32(v);
                 const long long off = (long long)row * g.fin_ldo + c;
                 if (g.fin_bf16) {
                   __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
@@ -770,6 +782,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                   w.x = w.x < 0.f ? 0.f : w.x; w.y = w.y < 0.f ? 0.f : w.y;
                   w.z = w.z < 0.f ? 0.f : w.z; w.w = w.w < 0.f ? 0.f : w.w;
                 }
+                if (g.round_tf32) w = round_tf32(w);
                 const long long off = (long long)row * g.fin_ldo + c;
                 if (g.fin_bf16) {
                   __nv_bfloat162 lo = __floats2bfloat162_rn(w.x, w.y), hi = __floats2bfloat162_rn(w.z, w.w);
@@ -799,7 +812,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
 // ------------------------------------------------------------------ small elementwise kernels
 __global__ void bias_act_kernel(const float* in, long long ldi, const float* __restrict__ bias, int relu,
-                                int M, int N, void* out, int out_bf16, long long ldo, int clear_in) {
+                                int M, int N, void* out, int out_bf16, long long ldo, int clear_in, int tf32) {
   // one thread per 4 consecutive columns (N % 4 == 0 is required by the launcher)
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const int n4 = N >> 2;
@@ -817,6 +830,7 @@ __global__ void bias_act_kernel(const float* in, long long ldi, const float* __r
   if (relu) {   // torch.relu keeps NaN
     v.x = v.x < 0.f ? 0.f : v.x; v.y = v.y < 0.f ? 0.f : v.y; v.z = v.z < 0.f ? 0.f : v.z; v.w = v.w < 0.f ? 0.f : v.w;
   }
+  if (tf32) v = round_tf32(v);
   if (out_bf16) {
     __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y), b = __floats2bfloat162_rn(v.z, v.w);
     uint2 pk;
@@ -834,6 +848,15 @@ __global__ void cast_bf16_kernel(const float* __restrict__ in, long long ld_in, 
   if (idx >= (long long)rows * ld_out) return;
   const int r = (int)(idx / ld_out), c = (int)(idx - (long long)r * ld_out);
   out[idx] = __float2bfloat16_rn(c < cols ? in[(long long)r * ld_in + c] : 0.f);
+}
+
+// W (fp32) -> fp32 rounded to TF32, columns >= cols zero-filled up to ld_out: the weight operand of a kind::tf32 layer
+__global__ void round_tf32_kernel(const float* __restrict__ in, long long ld_in, int rows, int cols,
+                                  float* __restrict__ out, long long ld_out) {
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (long long)rows * ld_out) return;
+  const int r = (int)(idx / ld_out), c = (int)(idx - (long long)r * ld_out);
+  out[idx] = c < cols ? round_tf32(in[(long long)r * ld_in + c]) : 0.f;
 }
 
 // ------------------------------------------------------------------ host side
@@ -862,11 +885,10 @@ int make_map(CUtensorMap* map, const void* ptr, int64_t rows, int64_t cols, int6
 
 template <int BN, int MODE>
 int launch_gemm_mode(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& g, int grid, cudaStream_t stream) {
-  static bool attr_done = false;
-  if (!attr_done) {
-    OVM_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel<BN, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)GemmShape<BN>::kSmemBytes));
-    attr_done = true;
+  static SmemOptIn opt;
+  {
+    int rc = opt.ensure(gemm_bf16_kernel<BN, MODE>, GemmShape<BN>::kSmemBytes);
+    if (rc != OVM_OK) return rc;
   }
   OVM_CUDA(launch_pdl(gemm_bf16_kernel<BN, MODE>, dim3(grid), dim3(kGemmThreads), GemmShape<BN>::kSmemBytes, stream, tmA,
                       tmB, g));
@@ -892,7 +914,7 @@ int gemm_bf16_launch(const void* A, int64_t lda, const void* B, int64_t ldb, int
   OVM_REQUIRE(lda >= K && ldb >= K && lda % 8 == 0 && ldb % 8 == 0, "ovm_gemm_bf16: lda/ldb must be >= K and multiples of 8");
   OVM_REQUIRE(!(reinterpret_cast<uintptr_t>(A) & 15) && !(reinterpret_cast<uintptr_t>(B) & 15),
               "ovm_gemm_bf16: A and B must be 16-byte aligned");
-  OVM_REQUIRE(out_dtype == OVM_F32 || out_dtype == OVM_BF16, "ovm_gemm_bf16: out_dtype %d", out_dtype);
+  OVM_REQUIRE(out_dtype == OVM_F32 || out_dtype == OVM_BF16 || out_dtype == OVM_TF32, "ovm_gemm_bf16: out_dtype %d", out_dtype);
   OVM_REQUIRE(ldo >= N && ldo % 8 == 0 && !(reinterpret_cast<uintptr_t>(out) & 15),
               "ovm_gemm_bf16: ldo must be >= N, a multiple of 8, and out 16-byte aligned");
   OVM_REQUIRE(mode >= OVM_GEMM_AUTO && mode <= OVM_GEMM_STREAMK, "ovm_gemm_bf16: mode %d", mode);
@@ -931,6 +953,7 @@ int gemm_bf16_launch(const void* A, int64_t lda, const void* B, int64_t ldb, int
   g.streamk = mode == OVM_GEMM_STREAMK;
   g.relu = relu;
   g.out_bf16 = out_dtype == OVM_BF16;
+  g.round_tf32 = out_dtype == OVM_TF32;
   g.bias = bias;
   g.out = out;
   g.ldo = ldo;
@@ -945,6 +968,7 @@ int gemm_bf16_launch(const void* A, int64_t lda, const void* B, int64_t ldb, int
     g.fin_out = fin->out;
     g.fin_ldo = fin->ldo;
     g.fin_bf16 = fin->out_dtype == OVM_BF16;
+    g.round_tf32 = fin->out_dtype == OVM_TF32;
   }
   CUtensorMap tmA, tmB;
   int rc = make_map(&tmA, A, M, K, lda, BM);
@@ -957,11 +981,9 @@ int gemm_bf16_launch(const void* A, int64_t lda, const void* B, int64_t ldb, int
     const int num_pair_tiles = ((num_m_tiles + 1) / 2) * g.num_n_tiles;
     const long long total = (long long)num_pair_tiles * g.kb_per_tile;
     const int clusters = (int)(total < kNumSMs / 2 ? total : kNumSMs / 2);
-    static bool attr_done = false;
-    if (!attr_done) {
-      OVM_CUDA(cudaFuncSetAttribute(gemm_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPairSmemBytes));
-      attr_done = true;
-    }
+    static SmemOptIn opt;
+    rc = opt.ensure(gemm_pair_kernel, kPairSmemBytes);
+    if (rc != OVM_OK) return rc;
     OVM_CUDA(launch_pdl(gemm_pair_kernel, dim3(2 * clusters), dim3(kGemmThreads), kPairSmemBytes, stream, tmA, tmB, g,
                         num_pair_tiles));
     OVM_LAUNCHED("gemm_pair_kernel");
@@ -985,10 +1007,11 @@ int bias_act_launch(const float* in, int64_t ldi, const float* bias, int32_t rel
   if (M == 0) return OVM_OK;
   OVM_REQUIRE(in && out && M > 0 && N > 0, "ovm_bias_act: bad arguments");
   OVM_REQUIRE(N % 4 == 0 && ldi % 4 == 0 && ldo % 4 == 0, "ovm_bias_act: N, ldi, ldo must be multiples of 4");
-  OVM_REQUIRE(out_dtype == OVM_F32 || out_dtype == OVM_BF16, "ovm_bias_act: out_dtype %d", out_dtype);
+  OVM_REQUIRE(out_dtype == OVM_F32 || out_dtype == OVM_BF16 || out_dtype == OVM_TF32, "ovm_bias_act: out_dtype %d", out_dtype);
   const long long total = (long long)M * (N / 4);
   OVM_CUDA(launch_pdl(bias_act_kernel, dim3((unsigned)((total + 255) / 256)), dim3(256), 0, stream, in, (long long)ldi, bias,
-                      (int)relu, (int)M, (int)N, out, (int)(out_dtype == OVM_BF16), (long long)ldo, clear_in ? 1 : 0));
+                      (int)relu, (int)M, (int)N, out, (int)(out_dtype == OVM_BF16), (long long)ldo, clear_in ? 1 : 0,
+                      (int)(out_dtype == OVM_TF32)));
   OVM_LAUNCHED("bias_act_kernel");
   return OVM_OK;
 }
@@ -1001,6 +1024,16 @@ int cast_bf16_launch(const float* in, int64_t ld_in, int32_t rows, int32_t cols,
   cast_bf16_kernel<<<(unsigned)((total + 255) / 256), 256, 0, stream>>>(in, ld_in, rows, cols,
                                                                        reinterpret_cast<__nv_bfloat16*>(out), ld_out);
   OVM_LAUNCHED("cast_bf16_kernel");
+  return OVM_OK;
+}
+
+int round_tf32_launch(const float* in, int64_t ld_in, int32_t rows, int32_t cols, float* out, int64_t ld_out,
+                      cudaStream_t stream) {
+  if (rows == 0) return OVM_OK;
+  OVM_REQUIRE(in && out && rows > 0 && cols > 0 && ld_in >= cols && ld_out >= cols, "ovm_round_tf32: bad arguments");
+  const long long total = (long long)rows * ld_out;
+  round_tf32_kernel<<<(unsigned)((total + 255) / 256), 256, 0, stream>>>(in, ld_in, rows, cols, out, ld_out);
+  OVM_LAUNCHED("round_tf32_kernel");
   return OVM_OK;
 }
 

@@ -50,18 +50,22 @@ namespace {
 
 // One FC stack (cube_head.py:64-74): every layer is Linear + ReLU.  The last layer's output is the fp32
 // feature block `feats[:, col0 : col0 + N]`; earlier layers ping-pong through bf16 activations.
-int run_fc_group(const ovm_fc_layer_t* layers, int num_fc, const void* x, int64_t ldx, int32_t n,
-                 const ovm_workspace_t* ws, float* feats, int64_t ld_feats, cudaStream_t stream, int& stage) {
+// `mid_dtype`: storage of the activations between layers (OVM_BF16, or OVM_TF32 for a layer that feeds a kind::tf32
+// tail).  `num_fc` may stop short of the stack's last layer (fused tail): then every layer run here is a middle one
+// and *out_last / *ld_last describe the activations handed to the tail.
+int run_fc_group(const ovm_fc_layer_t* layers, int num_fc, bool ends_stack, int last_mid_dtype, const void* x, int64_t ldx,
+                 int32_t n, const ovm_workspace_t* ws, float* feats, int64_t ld_feats, cudaStream_t stream, int& stage,
+                 const void** out_last = nullptr, int64_t* ld_last = nullptr) {
   const void* in = x;
   int64_t ld_in = ldx;
   for (int k = 0; k < num_fc; ++k) {
     const ovm_fc_layer_t& L = layers[k];
-    const bool last = k == num_fc - 1;
+    const bool last = ends_stack && k == num_fc - 1;
     OVM_REQUIRE(L.weight && L.bias && L.N > 0 && L.K > 0, "ovm_lift_forward: FC layer %d is incomplete", k);
     OVM_REQUIRE(L.N % 8 == 0, "ovm_lift_forward: FC_DIM must be a multiple of 8 (got %d)", L.N);
     void* out = last ? static_cast<void*>(feats) : (k % 2 == 0 ? ws->act_a : ws->act_b);
     const int64_t ldo = last ? ld_feats : L.N;
-    const int out_dtype = last ? OVM_F32 : OVM_BF16;
+    const int out_dtype = last ? OVM_F32 : (k == num_fc - 1 ? last_mid_dtype : OVM_BF16);
     // Ask the GEMM which mode it would pick for a raw fp32 accumulation; a long-K layer whose tiles cannot fill
     // the SMs runs split-K into ws->acc and gets bias+ReLU from the small follow-up kernel.
     int mode = OVM_GEMM_DIRECT;
@@ -97,6 +101,8 @@ int run_fc_group(const ovm_fc_layer_t* layers, int num_fc, const void* x, int64_
     int rc = stage_mark(stage, stream);
     if (rc != OVM_OK) return rc;
   }
+  if (out_last) *out_last = in;
+  if (ld_last) *ld_last = ld_in;
   return OVM_OK;
 }
 
@@ -188,6 +194,18 @@ int ovm_head_decode(const ovm_decode_cfg_t* cfg, const ovm_head_weights_t* w, co
                             raw, static_cast<cudaStream_t>(stream));
 }
 
+int ovm_fc_tail(const void* A, int64_t lda, int32_t a_dtype, const void* W, int64_t ldw, const float* bias, int32_t N,
+                int32_t K, const ovm_decode_cfg_t* cfg, const ovm_head_weights_t* w, const float* boxes,
+                const int64_t* classes, const float* scores, const int32_t* batch_idx, const float* cams,
+                int32_t num_images, int32_t n, float* records, float* raw, void* stream) {
+  return fc_tail_launch(A, lda, a_dtype, W, ldw, bias, N, K, cfg, w, boxes, classes, scores, batch_idx, cams, num_images,
+                        n, records, raw, static_cast<cudaStream_t>(stream));
+}
+
+int ovm_round_tf32(const float* in, int64_t ld_in, int32_t rows, int32_t cols, float* out, int64_t ld_out, void* stream) {
+  return round_tf32_launch(in, ld_in, rows, cols, out, ld_out, static_cast<cudaStream_t>(stream));
+}
+
 int ovm_lift_forward(const ovm_pooler_t* pooler, const ovm_fc_stack_t* fc, const ovm_decode_cfg_t* cfg,
                      const ovm_head_weights_t* heads, const float* boxes, const int64_t* classes, const float* scores,
                      const int32_t* batch_idx, const float* cams, int32_t n, const ovm_workspace_t* ws,
@@ -212,13 +230,30 @@ int ovm_lift_forward(const ovm_pooler_t* pooler, const ovm_fc_stack_t* fc, const
   if (rc != OVM_OK) return rc;
   // fc1 reads only the first C*P*P columns of each pooled row (its TMA map is K wide), so the pad is never touched
   const int64_t ld_feats = (int64_t)fc->num_groups * cfg->fc_dim;
+  const ovm_fc_layer_t& tail = fc->layers[fc->num_fc - 1];
+  if (fc->num_groups == 1 && fc->num_fc >= 2 && fc_tail_supported(cfg, tail.N, tail.K) && tail.weight && tail.bias) {
+    // one shared stack, class-agnostic heads: [fc1 .. fc(k-1)] -> {fc k + heads + decode} in one launch
+    OVM_REQUIRE(fc->layers[0].K == k_in, "ovm_lift_forward: fc1 expects K=%d but the pooler produces %lld",
+                fc->layers[0].K, (long long)k_in);
+    const bool tf32 = tail.weight_tf32 != nullptr;
+    const void* h = nullptr;
+    int64_t ldh = 0;
+    rc = run_fc_group(fc->layers, fc->num_fc - 1, /*ends_stack=*/false, tf32 ? OVM_TF32 : OVM_BF16, ws->pooled,
+                      ws->ld_pooled, n, ws, nullptr, 0, stream, stage, &h, &ldh);
+    if (rc != OVM_OK) return rc;
+    rc = fc_tail_launch(h, ldh, tf32 ? OVM_TF32 : OVM_BF16, tf32 ? static_cast<const void*>(tail.weight_tf32) : tail.weight,
+                        tf32 ? tail.ldw_tf32 : tail.ldw, tail.bias, tail.N, tail.K, cfg, heads, boxes, classes, scores,
+                        batch_idx, cams, pooler->num_images, n, records, raw, stream);
+    if (rc != OVM_OK) return rc;
+    return stage_mark(stage, stream);
+  }
   for (int g = 0; g < fc->num_groups; ++g) {
     const ovm_fc_layer_t* layers = fc->layers + (size_t)g * fc->num_fc;
     OVM_REQUIRE(layers[0].K == k_in, "ovm_lift_forward: fc1 expects K=%d but the pooler produces %lld",
                 layers[0].K, (long long)k_in);
     OVM_REQUIRE(layers[fc->num_fc - 1].N == cfg->fc_dim, "ovm_lift_forward: last FC width != cfg.fc_dim");
-    rc = run_fc_group(layers, fc->num_fc, ws->pooled, ws->ld_pooled, n, ws, ws->feats + (size_t)g * cfg->fc_dim,
-                      ld_feats, stream, stage);
+    rc = run_fc_group(layers, fc->num_fc, /*ends_stack=*/true, OVM_BF16, ws->pooled, ws->ld_pooled, n, ws,
+                      ws->feats + (size_t)g * cfg->fc_dim, ld_feats, stream, stage);
     if (rc != OVM_OK) return rc;
   }
   rc = head_decode_launch(cfg, heads, ws->feats, ld_feats, boxes, classes, scores, batch_idx, cams,

@@ -1000,13 +1000,12 @@ int roi_align_launch(const ovm_pooler_t* p, const float* boxes, const int32_t* b
               8 + 8 * nitems);
   a.xalign_mask = tune.align8 ? ~7 : ~3;
   a.evict_first = tune.evict;
-  static bool attr_done = false;
+  static SmemOptIn optA, optB;
   auto kA = roi_align_kernel<12288, 6144, 0>;   // 48 KB ring, stages up to 24 KB: 69 KB of shared memory, 3 CTAs / SM
   auto kB = roi_align_kernel<9216, 4608, 4>;    // 36 KB ring, stages up to 18 KB, 64 registers: 4 CTAs / SM -- measured 125 vs 104 us (OVM_ROI_STAGES=3, tools/roi_bench.py)
-  if (!attr_done) {
-    OVM_CUDA(cudaFuncSetAttribute(kA, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)roi_smem_bytes(12288)));
-    OVM_CUDA(cudaFuncSetAttribute(kB, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)roi_smem_bytes(9216)));
-    attr_done = true;
+  {
+    int rc = tune.stages == 3 ? optB.ensure(kB, roi_smem_bytes(9216)) : optA.ensure(kA, roi_smem_bytes(12288));
+    if (rc != OVM_OK) return rc;
   }
   if (a.order) {
     OVM_CUDA(launch_pdl(roi_order_kernel, dim3(1), dim3(1024), 0, stream, a, p->order_ws));

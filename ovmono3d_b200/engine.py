@@ -7,6 +7,7 @@ Host side of the inference slice of `ROIHeads3D._forward_cube`
 from __future__ import annotations
 
 import ctypes as C
+import os
 from dataclasses import dataclass
 from typing import Dict, List, Optional, Sequence, Tuple
 
@@ -53,6 +54,11 @@ class LiftEngine:
             raise ValueError("Cuboid pose type {} is not recognized".format(settings.pose_type))
         if settings.z_type not in ops.Z_TYPES:
             raise ValueError("Z type {} is not recognized".format(settings.z_type))
+        # operand format of the stack's last FC layer when it runs fused with the heads and the decode (ovm_fc_tail):
+        # "tf32" (default; fp32 activations from the layer before, 10-bit mantissas) or "bf16"
+        self.tail_precision = os.environ.get("OVM_TAIL_PRECISION", "tf32").lower()
+        if self.tail_precision not in ("tf32", "bf16"):
+            raise ValueError("OVM_TAIL_PRECISION must be tf32 or bf16")
         self._weights_key = None
         self._params = None
         self._fc_weights: List[torch.Tensor] = []
@@ -101,11 +107,19 @@ class LiftEngine:
                     raise ops.LiftError("cube_head lives on %s but the features are on %s" % (w.device, device))
                 N, K = w.shape
                 ldw = _round_up(K, 8)
-                wb = ops.cast_bf16(w.float().contiguous(), ldw)            # [N, K] view of [N, ldw] bf16
+                wf = w.float().contiguous()
+                wb = ops.cast_bf16(wf, ldw)                                 # [N, K] view of [N, ldw] bf16
                 b = fc.bias.detach().float().contiguous()
                 self._fc_weights.append(wb)
                 keep.append(b)
-                layers.append(ops.ovm_fc_layer_t(wb.data_ptr(), b.data_ptr(), N, K, ldw))
+                w32, ld32 = None, 0
+                if fc is fcs[-1] and len(gens) == 1 and num_fc >= 2 and self.tail_precision == "tf32":
+                    # the stack's last layer may run fused with the heads and the decode (ovm_fc_tail) on TF32 operands
+                    ld32 = _round_up(K, 4)
+                    w32 = ops.round_tf32(wf, ld32)
+                    keep.append(w32)
+                layers.append(ops.ovm_fc_layer_t(wb.data_ptr(), b.data_ptr(), N, K, ldw,
+                                                 None if w32 is None else w32.data_ptr(), ld32))
         self._fc_layers = (ops.ovm_fc_layer_t * len(layers))(*layers)
         self._fc_stack = ops.ovm_fc_stack_t(len(gens), num_fc, self._fc_layers)
         self.fc_dim = layers[-1].N
@@ -145,6 +159,9 @@ class LiftEngine:
         for i in range(5):
             cfg.feat_offset[i] = 0 if shared else min(i, len(gens) - 1) * self.fc_dim
         self._cfg = cfg
+        # mirrors fc_tail_supported() (csrc/fc_tail.cu): does ovm_lift_forward end in the fused fc-last + heads + decode launch?
+        self.tail_fused = (shared and num_fc >= 2 and not cfg.dims_priors_enabled and cfg.cluster_bins == 1
+                           and self.fc_dim in (128, 256, 512, 1024) and os.environ.get("OVM_FUSE_TAIL", "1") != "0")
         self._keep = keep
         self._weights_key = key
         self._cap = 0  # workspace widths depend on the stack
@@ -159,8 +176,8 @@ class LiftEngine:
         t = dict(
             pooled=torch.empty((cap, ld_pooled), device=device, dtype=torch.bfloat16),
             acc=torch.zeros((cap, self.fc_dim), device=device, dtype=torch.float32),   # zero on entry / exit of every lift
-            act_a=torch.empty((cap, self.fc_dim), device=device, dtype=torch.bfloat16),
-            act_b=torch.empty((cap, self.fc_dim), device=device, dtype=torch.bfloat16),
+            act_a=torch.empty((cap, self.fc_dim), device=device, dtype=torch.float32),   # bf16 or TF32-in-fp32 activations
+            act_b=torch.empty((cap, self.fc_dim), device=device, dtype=torch.float32),
             feats=torch.empty((cap, groups * self.fc_dim), device=device, dtype=torch.float32),
             levels=torch.empty((cap,), device=device, dtype=torch.int32),
             counters=torch.zeros((_round_up(cap, 128) // 128 * (_round_up(self.fc_dim, 256) // 256),), device=device,

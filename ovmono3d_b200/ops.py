@@ -11,11 +11,11 @@ from typing import List, Optional, Sequence, Tuple
 
 import torch
 
-OVM_ABI_VERSION = 5
+OVM_ABI_VERSION = 6
 OVM_MAX_LEVELS = 8
 RECORD_WIDTH = 48
 LAYOUT_NCHW, LAYOUT_NHWC = 0, 1
-F32, BF16 = 0, 1
+F32, BF16, TF32 = 0, 1, 2
 Z_TYPES = {"direct": 0, "sigmoid": 1, "log": 2, "clusters": 3}
 POSE_TYPES = {"6d": 0, "quaternion": 1, "euler": 2}
 DIMS_FUNCS = {"exp": 0, "sigmoid": 1}
@@ -33,7 +33,8 @@ REC_CLASS = 46
 
 EXPORTS = ("ovm_abi_version", "ovm_last_error", "ovm_launch_count", "ovm_struct_size", "ovm_roi_align", "ovm_gemm_bf16",
            "ovm_bias_act", "ovm_cast_bf16", "ovm_head_decode", "ovm_lift_forward", "ovm_set_stage_events", "ovm_gemm_set_trace",
-           "ovm_roi_set_trace", "ovm_head_set_trace", "ovm_nms", "ovm_gdino_post", "ovm_box_inference", "ovm_post_set_trace")
+           "ovm_roi_set_trace", "ovm_head_set_trace", "ovm_nms", "ovm_gdino_post", "ovm_box_inference", "ovm_post_set_trace",
+           "ovm_fc_tail", "ovm_round_tf32")
 NMS_MAX_SEGMENT = 4096
 NMS_AGNOSTIC, NMS_COORD_TRICK, NMS_PER_CLASS = 0, 1, 2
 
@@ -68,7 +69,8 @@ class ovm_head_weights_t(C.Structure):
 
 
 class ovm_fc_layer_t(C.Structure):
-    _fields_ = [("weight", C.c_void_p), ("bias", C.c_void_p), ("N", C.c_int32), ("K", C.c_int32), ("ldw", C.c_int64)]
+    _fields_ = [("weight", C.c_void_p), ("bias", C.c_void_p), ("N", C.c_int32), ("K", C.c_int32), ("ldw", C.c_int64),
+                ("weight_tf32", C.c_void_p), ("ldw_tf32", C.c_int64)]
 
 
 class ovm_fc_stack_t(C.Structure):
@@ -125,6 +127,9 @@ def load_library() -> C.CDLL:
     lib.ovm_lift_forward.argtypes = [C.POINTER(ovm_pooler_t), C.POINTER(ovm_fc_stack_t), C.POINTER(ovm_decode_cfg_t),
                                      C.POINTER(ovm_head_weights_t), vp, vp, vp, vp, vp, i32,
                                      C.POINTER(ovm_workspace_t), vp, vp, vp]
+    lib.ovm_fc_tail.argtypes = [vp, i64, i32, vp, i64, vp, i32, i32, C.POINTER(ovm_decode_cfg_t),
+                                C.POINTER(ovm_head_weights_t), vp, vp, vp, vp, vp, i32, i32, vp, vp, vp]
+    lib.ovm_round_tf32.argtypes = [vp, i64, i32, i32, vp, i64, vp]
     lib.ovm_gemm_set_trace.argtypes = [vp]
     lib.ovm_roi_set_trace.argtypes = [vp]
     lib.ovm_head_set_trace.argtypes = [vp]
@@ -191,6 +196,20 @@ def dtype_code(dt: torch.dtype) -> int:
     raise LiftError("unsupported output dtype %s" % dt)
 
 
+def round_tf32(x: torch.Tensor, ld_out: Optional[int] = None) -> torch.Tensor:
+    """fp32 [rows, cols] -> fp32 [rows, ld_out] rounded to TF32 (zero-padded), returned as the [rows, cols] view: the
+    weight operand of a `kind::tf32` layer (`ovm_fc_tail`)."""
+    lib = load_library()
+    _need_cuda(x, "x", torch.float32)
+    rows, cols = x.shape
+    ld_out = ld_out or (cols + 3) // 4 * 4
+    out = torch.empty((rows, ld_out), device=x.device, dtype=torch.float32)
+    if rows:
+        _check(lib.ovm_round_tf32(x.data_ptr(), x.stride(0), rows, cols, out.data_ptr(), ld_out, _stream()),
+               "ovm_round_tf32")
+    return out[:, :cols]
+
+
 def order_ws_len(n: int) -> int:
     """OVM_ORDER_WS_LEN(n) of include/ovmono3d_lift.h."""
     return 24 * max(int(n), 1) + 4808
@@ -253,11 +272,12 @@ def roi_align(features: Sequence[torch.Tensor], scales: Sequence[float], boxes: 
 
 def gemm_bf16(A: torch.Tensor, B: torch.Tensor, bias: Optional[torch.Tensor] = None, relu: bool = False,
               out_dtype: torch.dtype = torch.float32, mode: int = GEMM_AUTO,
-              out: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, int]:
+              out: Optional[torch.Tensor] = None, tf32_out: bool = False) -> Tuple[torch.Tensor, int]:
     """act(A[M,K] @ B[N,K]^T + bias) with bf16 operands and fp32 accumulation.  Returns (out, mode used).
 
     In STREAMK mode (chosen by AUTO for long-K, few-tile shapes when no bias/relu is requested) `out` is the raw
-    fp32 accumulation and must start at zero (it is zeroed here when allocated here)."""
+    fp32 accumulation and must start at zero (it is zeroed here when allocated here).  `tf32_out`: fp32 results are
+    rounded to TF32 (the input format of a `kind::tf32` layer; DIRECT mode only)."""
     lib = load_library()
     _need_cuda(A, "A", torch.bfloat16)
     _need_cuda(B, "B", torch.bfloat16)
@@ -275,7 +295,8 @@ def gemm_bf16(A: torch.Tensor, B: torch.Tensor, bias: Optional[torch.Tensor] = N
     if bias is not None:
         _need_cuda(bias, "bias", torch.float32)
     _check(lib.ovm_gemm_bf16(A.data_ptr(), A.stride(0), B.data_ptr(), B.stride(0), M, N, K, _ptr(bias), int(relu),
-                             out.data_ptr(), dtype_code(out.dtype), ldo, mode, C.byref(used), _stream()),
+                             out.data_ptr(), TF32 if (tf32_out and out.dtype == torch.float32) else dtype_code(out.dtype),
+                             ldo, mode, C.byref(used), _stream()),
            "ovm_gemm_bf16")
     return out, used.value
 
@@ -301,6 +322,45 @@ def cast_bf16(x: torch.Tensor, ld_out: Optional[int] = None) -> torch.Tensor:
         _check(lib.ovm_cast_bf16(x.data_ptr(), x.stride(0), rows, cols, out.data_ptr(), ld_out, _stream()),
                "ovm_cast_bf16")
     return out[:, :cols]
+
+
+def head_decode(cfg: "ovm_decode_cfg_t", heads: "ovm_head_weights_t", feats: torch.Tensor, boxes: torch.Tensor,
+                classes: torch.Tensor, scores: Optional[torch.Tensor], batch_idx: torch.Tensor, cams: torch.Tensor,
+                want_raw: bool = False) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+    """`ovm_head_decode`: fp32 FC features [n, ld] -> (records [n, 48], raw [n, 16] or None)."""
+    lib = load_library()
+    _need_cuda(feats, "feats", torch.float32)
+    n = boxes.shape[0]
+    rec = torch.empty((n, RECORD_WIDTH), device=feats.device, dtype=torch.float32)
+    raw = torch.empty((n, 16), device=feats.device, dtype=torch.float32) if want_raw else None
+    _check(lib.ovm_head_decode(C.byref(cfg), C.byref(heads), feats.data_ptr(), feats.stride(0), boxes.data_ptr(),
+                               classes.data_ptr(), _ptr(scores), batch_idx.data_ptr(), cams.data_ptr(), cams.shape[0], n,
+                               rec.data_ptr(), _ptr(raw), _stream()), "ovm_head_decode")
+    return rec, raw
+
+
+def fc_tail(cfg: "ovm_decode_cfg_t", heads: "ovm_head_weights_t", A: torch.Tensor, W: torch.Tensor, bias: torch.Tensor,
+            boxes: torch.Tensor, classes: torch.Tensor, scores: Optional[torch.Tensor], batch_idx: torch.Tensor,
+            cams: torch.Tensor, want_raw: bool = False) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+    """`ovm_fc_tail`: last FC layer + heads + decode in one launch.  A [n, K] and W [N, K] are both bf16, or both fp32
+    holding TF32-rounded values (`round_tf32`, or `gemm_bf16(..., tf32_out=True)`)."""
+    lib = load_library()
+    if A.dtype != W.dtype or A.dtype not in (torch.float32, torch.bfloat16):
+        raise LiftError("fc_tail: A and W must both be bf16 or both be fp32 (TF32-rounded)")
+    _need_cuda(A, "A", A.dtype)
+    _need_cuda(W, "W", W.dtype)
+    _need_cuda(bias, "bias", torch.float32)
+    if A.dim() != 2 or W.dim() != 2 or A.shape[1] != W.shape[1] or A.stride(1) != 1 or W.stride(1) != 1:
+        raise LiftError("fc_tail: A [n,K] and W [N,K] must be row-major with the same K")
+    n, K = A.shape
+    N = W.shape[0]
+    rec = torch.empty((n, RECORD_WIDTH), device=A.device, dtype=torch.float32)
+    raw = torch.empty((n, 16), device=A.device, dtype=torch.float32) if want_raw else None
+    _check(lib.ovm_fc_tail(A.data_ptr(), A.stride(0), TF32 if A.dtype == torch.float32 else BF16, W.data_ptr(),
+                           W.stride(0), bias.data_ptr(), N, K, C.byref(cfg), C.byref(heads), boxes.data_ptr(),
+                           classes.data_ptr(), _ptr(scores), batch_idx.data_ptr(), cams.data_ptr(), cams.shape[0], n,
+                           rec.data_ptr(), _ptr(raw), _stream()), "ovm_fc_tail")
+    return rec, raw
 
 
 def nms(boxes: torch.Tensor, scores: torch.Tensor, iou_threshold: float, classes: Optional[torch.Tensor] = None,

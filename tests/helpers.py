@@ -29,25 +29,49 @@ def lift_config(case: gc.Case) -> lo.LiftConfig:
     )
 
 
-def _fc_stack_bf16_operands(w, prefix, x):
-    """`lift_oracle._fc_stack` with both operands of every Linear rounded to bf16 (round-to-nearest-even) and the
+def round_tf32(x: torch.Tensor) -> torch.Tensor:
+    """cvt.rna.tf32.f32 (nearest, ties away from zero, 10 mantissa bits) on an fp32 tensor."""
+    i = x.contiguous().view(torch.int32)
+    return ((i + 0x1000) & ~0x1FFF).view(torch.float32)
+
+
+def tail_is_tf32(case: gc.Case) -> bool:
+    """Does the product run this case's last FC layer fused with the heads and the decode on TF32 operands
+    (`ovm_fc_tail`, csrc/fc_tail.cu: shared FC stack, class-agnostic heads, FC_DIM a power of two in 128..1024)?"""
+    import os
+
+    cube = case.cube
+    return (cube.get("SHARED_FC", True) and not cube.get("DIMS_PRIORS_ENABLED", True) and cube.get("CLUSTER_BINS", 1) <= 1
+            and case.fc_dim in (128, 256, 512, 1024) and os.environ.get("OVM_FUSE_TAIL", "1") != "0"
+            and os.environ.get("OVM_TAIL_PRECISION", "tf32").lower() == "tf32")
+
+
+def fc_stack_product_operands(tail_tf32: bool):
+    """`lift_oracle._fc_stack` with the operands of every Linear rounded the way the product rounds them -- bf16
+    (round-to-nearest-even) everywhere, except TF32 for the last layer when it runs inside `ovm_fc_tail` -- and the
     products summed exactly (fp64), which is what the tcgen05 GEMMs compute up to fp32 summation order: the
-    kernel-correctness oracle for the bf16 head, separate from the error of the number format itself."""
+    kernel-correctness oracle for the head, separate from the error of the number formats themselves."""
     import torch.nn.functional as F
 
-    k = 1
-    while f"{prefix}.fc{k}.weight" in w:
-        a = x.bfloat16().double()
-        wt = w[f"{prefix}.fc{k}.weight"].bfloat16().double()
-        x = F.relu(F.linear(a, wt, w[f"{prefix}.fc{k}.bias"].double())).float()
-        k += 1
-    return x
+    def stack(w, prefix, x):
+        num = 0
+        while f"{prefix}.fc{num + 1}.weight" in w:
+            num += 1
+        for k in range(1, num + 1):
+            tf32 = tail_tf32 and k == num and num >= 2
+            rnd = round_tf32 if tf32 else (lambda t: t.bfloat16().float())
+            a = rnd(x).double()
+            wt = rnd(w[f"{prefix}.fc{k}.weight"]).double()
+            x = F.relu(F.linear(a, wt, w[f"{prefix}.fc{k}.bias"].double())).float()
+        return x
+
+    return stack
 
 
 def run_oracle(case: gc.Case, bf16_operands: bool = False):
     if bf16_operands:
         saved = lo._fc_stack
-        lo._fc_stack = _fc_stack_bf16_operands
+        lo._fc_stack = fc_stack_product_operands(tail_is_tf32(case))
         try:
             return run_oracle(case)
         finally:

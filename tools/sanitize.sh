@@ -14,8 +14,11 @@ run() {  # name tool timeout command...
   echo "exit $?" >> $o/${tag}_sanitizer_${tool}_${name}.log
   grep -E "ERROR SUMMARY|RACECHECK SUMMARY|exit |ok:|passed|failed" $o/${tag}_sanitizer_${tool}_${name}.log | tail -4
 }
+to=${SANITIZE_TIMEOUT:-240}
 for tool in memcheck synccheck racecheck; do
-  run smoke $tool 600 python __graft_entry__.py smoke
-  run c2step $tool 900 python tools/one_step.py --steps 1
-  run post $tool 900 python -m pytest -q -x -m gpu tests/test_gdino_post.py tests/test_box_head.py -k "not random and not perf"
+  run smoke $tool $to python __graft_entry__.py smoke
+  # racecheck tracks every shared-memory access: the full C2 step (2400 CTAs) does not finish in the budget, the smoke
+  # runs the same kernels on a small batch
+  [ $tool != racecheck ] && run c2step $tool $to python tools/one_step.py --steps 1
+  run post $tool $to python -m pytest -q -x -m gpu tests/test_gdino_post.py tests/test_box_head.py -k "not random and not perf"
 done
