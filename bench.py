@@ -468,6 +468,9 @@ def run_e2e(head, names, inputs, device, K: int, W: int, world: int, lift) -> Di
     rec_host = torch.empty((n, ops.RECORD_WIDTH), dtype=torch.float32).pin_memory()
 
     def instances_of(hb):
+        """The caller's per-image containers (the 2-D detector's output in the reference, roi_heads_gdino.py:157-167),
+        holding the pinned host tensors.  Built once per host batch: `_forward_cube` mutates them in place (it replaces
+        `scores` and adds the pred_* fields, roi_heads.py:817-843), so a step only puts the input scores back."""
         out = []
         for i in range(len(hb.boxes)):
             inst = Instances(hb.im_dims[i])
@@ -477,14 +480,20 @@ def run_e2e(head, names, inputs, device, K: int, W: int, world: int, lift) -> Di
             out.append(inst)
         return out
 
+    held = {id(hb): instances_of(hb) for hb in hbs}
+    feats = dict(zip(names, dev_feats))
+    stream = torch.cuda.current_stream()
+
     def step(hb, copy_features: bool):
         if copy_features:
             for d, h in zip(dev_feats, hb.features):
                 d.copy_(h, non_blocking=True)
-        feats = dict(zip(names, dev_feats))
-        head._forward_cube(feats, instances_of(hb), hb.Ks, hb.im_dims, hb.ratios)
+        insts = held[id(hb)]
+        for inst, sc in zip(insts, hb.scores):
+            inst._fields["scores"] = sc
+        head._forward_cube(feats, insts, hb.Ks, hb.im_dims, hb.ratios)
         rec_host.copy_(head.last_records, non_blocking=True)
-        torch.cuda.current_stream().synchronize()     # the caller reads the detections now
+        stream.synchronize()                          # the caller reads the detections now
         return rec_host
 
     def timed(copy_features: bool) -> float:

@@ -24,6 +24,8 @@
  *                    get_grounding_output roi_heads_gdino.py:186-202 (sigmoid, phrase logits :296-317, box
  *                    threshold, per-query max / argmax) + grounding_dino_inference_detector :269-275
  *                    (cxcywh -> xyxy in pixels :283-287, NMS 0.5, gather in keep order).
+ *   ovm_iou_box3d    box3d_overlap at evaluation: omni3d_evaluation.py:68-169 with pytorch3d's
+ *                    _C.iou_box3d.
  *   ovm_box_inference the inference tail of the 2-D box head: FastRCNNOutputLayers
  *                    predict_probs / predict_boxes (d2 Box2BoxTransform.apply_deltas) and
  *                    fast_rcnn_inference_single_image, fast_rcnn.py:57-116.
@@ -206,8 +208,16 @@ typedef struct {
                                   it the split-K FC layer finishes (bias, ReLU, cast) inside the GEMM launch; NULL:
                                   a separate bias/ReLU launch follows.  ceil(n/128) * ceil(fc_dim/256) are needed */
   int32_t num_tile_counters;
-  int32_t _pad;
+  int32_t splitk_flags_len;    /* int32 elements in splitk_flags */
+  float* splitk_slots;         /* optional fp32 [splitk_slots_len], 16-byte aligned: with it (and splitk_flags) the split-K
+                                  partial tiles of the first FC layer are exchanged through per-cluster slots with plain
+                                  stores and summed in a fixed order (bit-reproducible, no L2 atomics) instead of
+                                  red.global.add into acc.  OVM_SPLITK_SLOTS_LEN floats serve any n. */
+  int64_t splitk_slots_len;
+  int32_t* splitk_flags;       /* int32 [splitk_flags_len], ZERO-FILLED once (left zeroed); OVM_SPLITK_FLAGS_LEN */
 } ovm_workspace_t;
+#define OVM_SPLITK_SLOTS_LEN (74 * 2 * 128 * 256)
+#define OVM_SPLITK_FLAGS_LEN (74 * 2 * 8)
 
 /* Last FC layer + the five linear heads + the cube decode in ONE launch (cube_head.py:157-164 last Linear + heads,
  * roi_heads.py:378-549,798-843): a cluster of N/128 CTAs per 128 boxes, the layer's output stays in tensor memory /
@@ -307,6 +317,20 @@ int ovm_box_inference(const ovm_box_inference_cfg_t* cfg, const float* logits, i
                       const int32_t* image_sizes, int32_t num_images, int32_t num_proposals, int32_t max_per_image,
                       const ovm_box_inference_ws_t* ws, float* out_boxes, float* out_scores, int64_t* out_classes,
                       int32_t* out_index, float* out_scores_full, int32_t* out_count, void* stream);
+
+/* ---- evaluation side ---------------------------------------------------------------------- */
+
+/* Exact 3-D IoU of oriented cuboids: `box3d_overlap` of the reference's evaluator (cubercnn/evaluation/
+ * omni3d_evaluation.py:109-169) = pytorch3d `_C.iou_box3d` (:158, forced onto the CPU there by
+ * MAX_DTS_CROSS_GTS_FOR_IOU3D = 0, :65) + the `_check_coplanar` / `_check_nonzero` guards on the detections (:68-107).
+ * boxes_dt [N,8,3], boxes_gt [M,8,3] fp32 (device): the 8 corners in pytorch3d's order (the order of the docstring at
+ * :116-143; `get_cuboid_verts_faces` emits it).  iou [N,M] = vol / (vol_dt + vol_gt - vol); vol (optional) [N,M] the
+ * intersection volumes.  dt_flags (optional, device int32 [N]): when given, the guards run first -- flags[i] bit 0 =
+ * detection i fails the coplanarity test (eps_coplanar, reference default 1e-4), bit 1 = it has a face triangle of
+ * area <= eps_nonzero (1e-8) -- and the IoUs of flagged detections are zero, as in the reference (:160-167).
+ * One warp per pair, two launches.                                                                               */
+int ovm_iou_box3d(const float* boxes_dt, const float* boxes_gt, int32_t N, int32_t M, float eps_coplanar,
+                  float eps_nonzero, float* iou, float* vol, int32_t* dt_flags, void* stream);
 
 int ovm_abi_version(void);
 /* sizeof() of the ABI structs as this library was compiled, for binding self-checks:

@@ -114,6 +114,11 @@ struct GemmFinish {
   void* out;
   int32_t out_dtype;
   int64_t ldo;
+  // optional: deterministic split-K exchange (gemm_pair_kernel<true>), see ovm_workspace_t.splitk_slots
+  float* slots = nullptr;
+  int64_t slots_len = 0;
+  int32_t* slot_flags = nullptr;
+  int32_t flags_len = 0;
 };
 int gemm_bf16_launch(const void* A, int64_t lda, const void* B, int64_t ldb, int32_t M, int32_t N, int32_t K,
                      const float* bias, int32_t relu, void* out, int32_t out_dtype, int64_t ldo, int32_t mode,
@@ -121,6 +126,7 @@ int gemm_bf16_launch(const void* A, int64_t lda, const void* B, int64_t ldb, int
 void gemm_set_trace(unsigned long long* buf);
 void roi_set_trace(unsigned long long* buf);
 void head_set_trace(unsigned long long* buf);
+unsigned long long* head_get_trace();
 void post_set_trace(unsigned long long* buf);
 int bias_act_launch(const float* in, int64_t ldi, const float* bias, int32_t relu, int32_t M, int32_t N,
                     void* out, int32_t out_dtype, int64_t ldo, cudaStream_t stream, bool clear_in = false);
@@ -153,5 +159,9 @@ int box_inference_launch(const ovm_box_inference_cfg_t* cfg, const float* logits
                          const int32_t* image_sizes, int32_t N, int32_t R, int32_t max_per_image,
                          const ovm_box_inference_ws_t* ws, float* out_boxes, float* out_scores, int64_t* out_classes,
                          int32_t* out_index, float* out_scores_full, int32_t* out_count, cudaStream_t stream);
+
+// iou3d.cu
+int iou_box3d_launch(const float* boxes_dt, const float* boxes_gt, int32_t N, int32_t M, float eps_coplanar,
+                     float eps_nonzero, float* iou, float* vol, int32_t* dt_flags, cudaStream_t stream);
 
 }  // namespace ovm

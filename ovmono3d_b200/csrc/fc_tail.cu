@@ -85,6 +85,19 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
 __device__ __forceinline__ void tcgen05_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
+// the same arrive on the barrier at this offset in every CTA of `mask`
+__device__ __forceinline__ void tcgen05_commit_mc(uint32_t bar, uint16_t mask) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+               "h"(mask)
+               : "memory");
+}
+// TMA load delivered to the same shared-memory offset (and counted on the barrier at the same offset) in every CTA of `mask`
+__device__ __forceinline__ void tma_load_2d_mc(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, uint16_t mask) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%3, %4}], [%2], %5;" ::"r"(dst),
+      "l"(map), "r"(bar), "r"(c0), "r"(c1), "h"(mask)
+      : "memory");
+}
 __device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 template <bool TF32>
@@ -158,6 +171,17 @@ __device__ __forceinline__ const float* agnostic_head_row(const ovm_head_weights
   return w.w_pose + (long long)(r - 6 - conf_rows) * K;
 }
 
+// ovm_head_set_trace: [grid, 8] %globaltimer stamps per CTA -- 0 entry, 1 set-up + staging done (cluster barrier passed),
+// 2 the FC layer before has completed (programmatic-launch wait returned), 3 first operand stage landed, 4 accumulator
+// complete, 5 epilogue (bias, ReLU, head partials) done, 6 partials exchanged (cluster barrier), 7 records written
+__device__ __forceinline__ void tail_stamp(const TailArgs& g, int slot) {
+  if (g.d.trace) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    g.d.trace[(size_t)blockIdx.x * 8 + slot] = t;
+  }
+}
+
 template <bool TF32>
 __global__ void __launch_bounds__(kTailThreads, 1)
 fc_tail_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TailArgs g) {
@@ -179,6 +203,7 @@ fc_tail_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   float* part = hbias + 16;                                                                // [2 cs][13][rpc]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) tail_stamp(g, 0);
   const int cs = g.cs;
   const int rank = (int)cluster_ctarank();
   const int m_tile = blockIdx.x / cs;
@@ -195,7 +220,7 @@ fc_tail_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kTailStages; ++s) {
       mbar_init(full_bar + 8 * s, 1);
-      mbar_init(empty_bar + 8 * s, 1);
+      mbar_init(empty_bar + 8 * s, cs);      // a slot is free when every CTA of the cluster has consumed it (A is multicast)
     }
     mbar_init(tfull_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -232,18 +257,28 @@ fc_tail_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   cluster_sync_all();        // barriers initialised, TMEM allocated, staging visible; every CTA of the cluster has started
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
+  if (threadIdx.x == 0) tail_stamp(g, 1);
   pdl_trigger();
   pdl_wait();                // h1 comes from the FC layer before
+  if (threadIdx.x == 0) tail_stamp(g, 2);
 
   if (warp == 0) {
     if (lane == 0) {
-      // ===== TMA producer
+      // ===== TMA producer.  The 128 x 128-byte A block of a stage is the same for the whole cluster: every CTA fetches
+      // 128 / CS of its rows and multicasts them to all CS CTAs (each full barrier still sees 16 KB of A + 16 KB of B),
+      // which takes the A traffic out of L2 from CS x to 1 x (106 -> 60 MB per launch at C2 with TF32 operands).
       int stage = 0;
       uint32_t phase = 0;
+      const uint16_t mask = (uint16_t)((1u << cs) - 1u);
+      const int slice_rows = kTM / cs;
       for (int kb = 0; kb < g.kblocks; ++kb) {
         mbar_wait(empty_bar + 8 * stage, phase ^ 1);
         mbar_expect_tx(full_bar + 8 * stage, kTailStageBytes);
-        tma_load_2d(smem_a + stage * kTailABytes, &tmA, full_bar + 8 * stage, kb * g.elems_per_row, m_tile * kTM);
+        const uint32_t a_dst = smem_a + stage * kTailABytes + rank * slice_rows * kRowBytes;
+        if (cs > 1)
+          tma_load_2d_mc(a_dst, &tmA, full_bar + 8 * stage, kb * g.elems_per_row, m_tile * kTM + rank * slice_rows, mask);
+        else
+          tma_load_2d(a_dst, &tmA, full_bar + 8 * stage, kb * g.elems_per_row, m_tile * kTM);
         tma_load_2d(smem_b + stage * kTailBBytes, &tmB, full_bar + 8 * stage, kb * g.elems_per_row, rank * kTN);
         if (++stage == kTailStages) {
           stage = 0;
@@ -261,12 +296,14 @@ fc_tail_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       for (int kb = 0; kb < g.kblocks; ++kb) {
         mbar_wait(full_bar + 8 * stage, phase);
         tcgen05_fence_after();
+        if (kb == 0) tail_stamp(g, 3);
         const uint64_t adesc = make_smem_desc(smem_a + stage * kTailABytes);
         const uint64_t bdesc = make_smem_desc(smem_b + stage * kTailBBytes);
 #pragma unroll
         for (int k = 0; k < 4; ++k)
           umma<TF32>(tmem_base, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (kb > 0 || k > 0) ? 1u : 0u);
-        tcgen05_commit(empty_bar + 8 * stage);
+        if (cs > 1) tcgen05_commit_mc(empty_bar + 8 * stage, (uint16_t)((1u << cs) - 1u));   // frees the slot in every CTA
+        else tcgen05_commit(empty_bar + 8 * stage);
         if (++stage == kTailStages) {
           stage = 0;
           phase ^= 1;
@@ -284,6 +321,7 @@ fc_tail_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     for (int k = 0; k < kMaxHeadRows; ++k) p[k] = 0.f;
     mbar_wait(tfull_bar, 0);
     tcgen05_fence_after();
+    if (threadIdx.x == 64) tail_stamp(g, 4);
 #pragma unroll 1
     for (int c = 0; c < 4; ++c) {
       uint32_t v[16];
@@ -309,9 +347,11 @@ fc_tail_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
     for (int k = 0; k < kMaxHeadRows; ++k)
       st_cluster_f32(remote + (uint32_t)(((contributor * kMaxHeadRows + k) * rpc + t) * 4), p[k]);
+    if (threadIdx.x == 64) tail_stamp(g, 5);
   }
   __syncwarp();
   cluster_sync_all();        // every partial has landed (release / acquire at cluster scope)
+  if (threadIdx.x == 64) tail_stamp(g, 6);
   if (warp == 2) {
     tcgen05_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)kTN) : "memory");
@@ -326,11 +366,12 @@ fc_tail_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     decode_record(g.d, my_row, in, 0, hv, true);
   }
+  if (threadIdx.x == 64) tail_stamp(g, 7);
 }
 
-// [rows, cols] row-major with leading dimension ld (elements) -> 2-D map, box {128 bytes of K, 128 rows}, 128-byte
+// [rows, cols] row-major with leading dimension ld (elements) -> 2-D map, box {128 bytes of K, box_rows rows}, 128-byte
 // swizzle, out-of-bounds elements read as zero (row and K tails).
-int make_tail_map(CUtensorMap* map, const void* ptr, int64_t rows, int64_t cols, int64_t ld, bool tf32) {
+int make_tail_map(CUtensorMap* map, const void* ptr, int64_t rows, int64_t cols, int64_t ld, bool tf32, int box_rows) {
   EncodeTiledFn enc = tensormap_encode_fn();
   if (!enc) {
     set_error("cuTensorMapEncodeTiled not available from the driver");
@@ -339,7 +380,7 @@ int make_tail_map(CUtensorMap* map, const void* ptr, int64_t rows, int64_t cols,
   const int esz = tf32 ? 4 : 2;
   cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
   cuuint64_t strides[1] = {(cuuint64_t)ld * esz};
-  cuuint32_t box[2] = {(cuuint32_t)(kRowBytes / esz), 128};
+  cuuint32_t box[2] = {(cuuint32_t)(kRowBytes / esz), (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = enc(map, tf32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims,
                    strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
@@ -429,6 +470,7 @@ int fc_tail_launch(const void* A, int64_t lda, int32_t a_dtype, const void* W, i
   g.d.n = n;
   g.d.records = records;
   g.d.raw = raw;
+  g.d.trace = head_get_trace();
   g.K = K;
   g.N = N;
   g.cs = N / kTN;
@@ -436,9 +478,9 @@ int fc_tail_launch(const void* A, int64_t lda, int32_t a_dtype, const void* W, i
   g.kblocks = (K + g.elems_per_row - 1) / g.elems_per_row;
   g.bias = bias;
   CUtensorMap tmA, tmB;
-  int rc = make_tail_map(&tmA, A, n, K, lda, a_dtype == OVM_TF32);
+  int rc = make_tail_map(&tmA, A, n, K, lda, a_dtype == OVM_TF32, kTM / g.cs);   // each CTA multicasts its slice of the rows
   if (rc != OVM_OK) return rc;
-  rc = make_tail_map(&tmB, W, N, K, ldw, a_dtype == OVM_TF32);
+  rc = make_tail_map(&tmB, W, N, K, ldw, a_dtype == OVM_TF32, kTN);
   if (rc != OVM_OK) return rc;
   const int grid = g.cs * ((n + kTM - 1) / kTM);
   return a_dtype == OVM_TF32 ? launch_tail<true>(tmA, tmB, g, grid, stream) : launch_tail<false>(tmA, tmB, g, grid, stream);

@@ -67,6 +67,9 @@ struct GemmArgs {
   long long fin_ldo;
   int fin_bf16;
   int round_tf32;        // fp32 outputs (DIRECT epilogue / fused finish) are rounded to TF32: the next layer is a kind::tf32 MMA
+  // gemm_pair_kernel<true>: split-K partials meet in per-cluster slots (plain stores) instead of L2 atomics
+  float* slots;          // [clusters][2 CTAs][128 rows][256 columns] fp32
+  int* slot_flags;       // [clusters][2 CTAs][8 epilogue warps], zero between launches
 };
 
 thread_local unsigned long long* g_gemm_trace = nullptr;
@@ -573,6 +576,26 @@ struct PairIter {
   }
 };
 
+__device__ __forceinline__ int ld_acquire_gpu(const int* p) {
+  int v;
+  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_gpu(int* p, int v) {
+  asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// SLOTS = false: partial tiles meet in the zeroed fp32 accumulator through red.global.add, the CTA that completes a tile
+//   (per-tile counter) reads it back and finishes it (round 1).
+// SLOTS = true: deterministic, no atomics.  In the flat (tile, K block) order a cluster's range starts inside at most
+//   one tile: that first segment (k0 > 0) is a PARTIAL -- its raw fp32 accumulator is stored to the cluster's slot with
+//   plain 16-byte stores and published with one release flag per epilogue warp.  Every later segment of the cluster
+//   starts a tile (k0 == 0): the cluster OWNS that tile, keeps its own accumulator in tensor memory, and on the way out
+//   adds the slots of the clusters whose ranges start inside the tile (cluster + 1, + 2, ...; the host guarantees at most
+//   kMaxPartials of them) in a fixed order, then bias / ReLU / cast -> the layer's output.  The partials a cluster
+//   produces are the first thing it does, so an owner never waits on anything that waits on it.
+constexpr int kMaxPartials = 4;
+template <bool SLOTS>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
 gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmArgs g,
                  const int num_pair_tiles) {
@@ -704,6 +727,134 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const int m_tile = s.m_pair * 2 + (int)rank;
       const int row0 = m_tile * BM + quad * 32;
       const bool rows_full = row0 + 32 <= g.M;
+      if (SLOTS) {
+        const int cluster = blockIdx.x >> 1, nclusters = gridDim.x >> 1;
+        const bool cta_valid = m_tile * BM < g.M;       // the odd last row tile of a pair may not exist (CTA-uniform)
+        const int widx = warp - 2;
+        if (s.k0 > 0) {
+          // ---- partial: raw accumulator -> this cluster's slot
+          float* slot = g.slots + ((size_t)cluster * 2 + rank) * (size_t)(BM * BN) + (size_t)(quad * 32) * BN;
+          if (cta_valid) {
+#pragma unroll 1
+            for (int ci = 0; ci < kChunksPerWarp; ++ci) {
+              const int ch = half * kChunksPerWarp + ci;
+              uint32_t v[kChunk];
+              __syncwarp();
+              tmem_ld16(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN + ch * kChunk), v);
+              float4* wr = reinterpret_cast<float4*>(stg + lane * kChunk);
+              const int sw = (lane >> 1) & 3;
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                wr[k ^ sw] = make_float4(__uint_as_float(v[4 * k]), __uint_as_float(v[4 * k + 1]),
+                                         __uint_as_float(v[4 * k + 2]), __uint_as_float(v[4 * k + 3]));
+              __syncwarp();
+#pragma unroll
+              for (int rr = 0; rr < 32; rr += 8) {
+                const int r = rr + q;
+                const float4 x = reinterpret_cast<const float4*>(stg + r * kChunk)[l4 ^ ((r >> 1) & 3)];
+                *reinterpret_cast<float4*>(slot + (size_t)r * BN + ch * kChunk + 4 * l4) = x;
+              }
+            }
+          }
+          tcgen05_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_remote(tempty_leader + 8 * acc);
+          if (cta_valid) {
+            __threadfence();      // every lane: its slot stores are visible GPU-wide before the flag
+            __syncwarp();
+            if (lane == 0) st_release_gpu(g.slot_flags + ((size_t)cluster * 2 + rank) * kEpiWarps + widx, 1);
+          }
+        } else {
+          // ---- owner: own accumulator + the slots of the clusters that start inside this tile -> finished output
+          const long long total = (long long)num_pair_tiles * g.kb_per_tile;
+          const long long tile_end = (long long)(s.m_pair * g.num_n_tiles + s.n_tile + 1) * g.kb_per_tile;
+          int P = 0;
+          if (s.k1 < g.kb_per_tile)
+            while (P < kMaxPartials && cluster + 1 + P < nclusters && total * (cluster + 1 + P) / nclusters < tile_end) ++P;
+          const float* src[kMaxPartials];
+#pragma unroll
+          for (int p = 0; p < kMaxPartials; ++p)
+            src[p] = g.slots + ((size_t)(cluster + 1 + (p < P ? p : 0)) * 2 + rank) * (size_t)(BM * BN) + (size_t)(quad * 32) * BN;
+          if (cta_valid) {
+#pragma unroll
+            for (int p = 0; p < kMaxPartials; ++p)
+              if (p < P) {
+                const int* f = g.slot_flags + ((size_t)(cluster + 1 + p) * 2 + rank) * kEpiWarps + widx;
+                while (ld_acquire_gpu(f) == 0) {
+                }
+              }
+            if (threadIdx.x == 64) {
+              trace_stamp(g, 8);                                   // every partial of the tile has been published
+              if (g.trace) g.trace[(size_t)blockIdx.x * 16 + 11] = (unsigned long long)P;
+            }
+#pragma unroll 1
+            for (int ci = 0; ci < kChunksPerWarp; ++ci) {
+              if (threadIdx.x == 64 && ci == 1) trace_stamp(g, 9);   // first chunk merged and stored
+              const int ch = half * kChunksPerWarp + ci;
+              const int col0 = s.n_tile * BN + ch * kChunk;
+              // the partials of this chunk first: their L2 round trips overlap the TMEM read and the transpose
+              float4 pv[kMaxPartials][4];
+#pragma unroll
+              for (int p = 0; p < kMaxPartials; ++p)
+#pragma unroll
+                for (int rr = 0; rr < 4; ++rr)
+                  pv[p][rr] = p < P ? __ldcg(reinterpret_cast<const float4*>(src[p] + (size_t)(rr * 8 + q) * BN + ch * kChunk + 4 * l4))
+                                    : make_float4(0.f, 0.f, 0.f, 0.f);
+              uint32_t v[kChunk];
+              __syncwarp();
+              tmem_ld16(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN + ch * kChunk), v);
+              if (row0 >= g.M || col0 >= g.N) continue;   // warp-uniform
+              float4* wr = reinterpret_cast<float4*>(stg + lane * kChunk);
+              const int sw = (lane >> 1) & 3;
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                wr[k ^ sw] = make_float4(__uint_as_float(v[4 * k]), __uint_as_float(v[4 * k + 1]),
+                                         __uint_as_float(v[4 * k + 2]), __uint_as_float(v[4 * k + 3]));
+              __syncwarp();
+              const int c = col0 + 4 * l4;
+              float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+              if (g.bias && c + 3 < g.N) bv = __ldg(reinterpret_cast<const float4*>(g.bias + c));
+#pragma unroll
+              for (int rr = 0; rr < 4; ++rr) {
+                const int r = rr * 8 + q;
+                float4 x = reinterpret_cast<const float4*>(stg + r * kChunk)[l4 ^ ((r >> 1) & 3)];
+#pragma unroll
+                for (int p = 0; p < kMaxPartials; ++p) {   // fixed order: bit-reproducible
+                  x.x += pv[p][rr].x; x.y += pv[p][rr].y; x.z += pv[p][rr].z; x.w += pv[p][rr].w;
+                }
+                x.x += bv.x; x.y += bv.y; x.z += bv.z; x.w += bv.w;
+                if (g.relu) {   // torch.relu keeps NaN
+                  x.x = x.x < 0.f ? 0.f : x.x; x.y = x.y < 0.f ? 0.f : x.y;
+                  x.z = x.z < 0.f ? 0.f : x.z; x.w = x.w < 0.f ? 0.f : x.w;
+                }
+                if (g.round_tf32) x = round_tf32(x);
+                if (row0 + r >= g.M || c + 3 >= g.N) continue;     // N % 4 == 0 (checked by the launcher)
+                const long long off = (long long)(row0 + r) * g.fin_ldo + c;
+                if (g.fin_bf16) {
+                  __nv_bfloat162 lo = __floats2bfloat162_rn(x.x, x.y), hi = __floats2bfloat162_rn(x.z, x.w);
+                  uint2 pk;
+                  pk.x = *reinterpret_cast<uint32_t*>(&lo);
+                  pk.y = *reinterpret_cast<uint32_t*>(&hi);
+                  *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(g.fin_out) + off) = pk;
+                } else {
+                  *reinterpret_cast<float4*>(reinterpret_cast<float*>(g.fin_out) + off) = x;
+                }
+              }
+            }
+            if (threadIdx.x == 64) trace_stamp(g, 10);              // last chunk merged and stored
+            __syncwarp();
+            if (lane == 0)   // consumed: hand the flags back cleared for the next launch
+              for (int p = 0; p < P; ++p) g.slot_flags[((size_t)(cluster + 1 + p) * 2 + rank) * kEpiWarps + widx] = 0;
+          }
+          tcgen05_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_remote(tempty_leader + 8 * acc);
+        }
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1;
+        if (threadIdx.x == 64) trace_stamp(g, 7);
+        continue;
+      }
 #pragma unroll 1
       for (int ci = 0; ci < kChunksPerWarp; ++ci) {
         const int ch = half * kChunksPerWarp + ci;
@@ -981,11 +1132,27 @@ int gemm_bf16_launch(const void* A, int64_t lda, const void* B, int64_t ldb, int
     const int num_pair_tiles = ((num_m_tiles + 1) / 2) * g.num_n_tiles;
     const long long total = (long long)num_pair_tiles * g.kb_per_tile;
     const int clusters = (int)(total < kNumSMs / 2 ? total : kNumSMs / 2);
-    static SmemOptIn opt;
-    rc = opt.ensure(gemm_pair_kernel, kPairSmemBytes);
-    if (rc != OVM_OK) return rc;
-    OVM_CUDA(launch_pdl(gemm_pair_kernel, dim3(2 * clusters), dim3(kGemmThreads), kPairSmemBytes, stream, tmA, tmB, g,
-                        num_pair_tiles));
+    // deterministic slot exchange when the workspace has the slots and no tile is shared by more than kMaxPartials + 1 clusters
+    static const bool slots_ok = [] { const char* v = getenv("OVM_GEMM_SLOTS"); return !v || atoi(v) != 0; }();
+    const long long starts_per_tile = ((long long)g.kb_per_tile * clusters + total - 1) / total;   // cluster ranges starting in one tile, at most
+    const bool use_slots = slots_ok && fin->slots && fin->slot_flags && starts_per_tile <= kMaxPartials &&
+                           fin->slots_len >= (long long)clusters * 2 * BM * kPairBN && fin->flags_len >= clusters * 2 * kEpiWarps &&
+                           !(reinterpret_cast<uintptr_t>(fin->slots) & 15);
+    if (use_slots) {
+      g.slots = fin->slots;
+      g.slot_flags = fin->slot_flags;
+      static SmemOptIn opt;
+      rc = opt.ensure(gemm_pair_kernel<true>, kPairSmemBytes);
+      if (rc != OVM_OK) return rc;
+      OVM_CUDA(launch_pdl(gemm_pair_kernel<true>, dim3(2 * clusters), dim3(kGemmThreads), kPairSmemBytes, stream, tmA, tmB, g,
+                          num_pair_tiles));
+    } else {
+      static SmemOptIn opt;
+      rc = opt.ensure(gemm_pair_kernel<false>, kPairSmemBytes);
+      if (rc != OVM_OK) return rc;
+      OVM_CUDA(launch_pdl(gemm_pair_kernel<false>, dim3(2 * clusters), dim3(kGemmThreads), kPairSmemBytes, stream, tmA, tmB, g,
+                          num_pair_tiles));
+    }
     OVM_LAUNCHED("gemm_pair_kernel");
     return OVM_OK;
   }

@@ -332,6 +332,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) head_decode_kernel(const 
 }  // namespace
 
 void head_set_trace(unsigned long long* buf) { g_head_trace = buf; }
+unsigned long long* head_get_trace() { return g_head_trace; }
 
 int head_decode_launch(const ovm_decode_cfg_t* cfg, const ovm_head_weights_t* w, const float* feats, int64_t ld_feats,
                        const float* boxes, const int64_t* classes, const float* scores, const int32_t* batch_idx,

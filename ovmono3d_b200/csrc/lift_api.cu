@@ -80,7 +80,8 @@ int run_fc_group(const ovm_fc_layer_t* layers, int num_fc, bool ends_stack, int 
       // ws->acc (and the tile counters) are zero on entry (workspace contract) and handed back zeroed
       if (ws->tile_counters && ws->num_tile_counters >= ((n + 127) / 128) * ((L.N + 255) / 256)) {
         // one launch: the CTA that completes a tile applies bias + ReLU and writes the layer's output
-        const GemmFinish fin{ws->tile_counters, ws->num_tile_counters, L.bias, 1, out, out_dtype, ldo};
+        const GemmFinish fin{ws->tile_counters, ws->num_tile_counters, L.bias, 1, out, out_dtype, ldo,
+                             ws->splitk_slots, ws->splitk_slots_len, ws->splitk_flags, ws->splitk_flags_len};
         int rc = gemm_bf16_launch(in, ld_in, L.weight, L.ldw, n, L.N, L.K, nullptr, 0, ws->acc, OVM_F32, L.N,
                                   OVM_GEMM_STREAMK, nullptr, stream, &fin);
         if (rc != OVM_OK) return rc;
@@ -286,6 +287,12 @@ int ovm_box_inference(const ovm_box_inference_cfg_t* cfg, const float* logits, i
   return box_inference_launch(cfg, logits, ld_logits, deltas, ld_deltas, proposals, seg_offsets, image_sizes,
                               num_images, num_proposals, max_per_image, ws, out_boxes, out_scores, out_classes,
                               out_index, out_scores_full, out_count, static_cast<cudaStream_t>(stream));
+}
+
+int ovm_iou_box3d(const float* boxes_dt, const float* boxes_gt, int32_t N, int32_t M, float eps_coplanar,
+                  float eps_nonzero, float* iou, float* vol, int32_t* dt_flags, void* stream) {
+  return iou_box3d_launch(boxes_dt, boxes_gt, N, M, eps_coplanar, eps_nonzero, iou, vol, dt_flags,
+                          static_cast<cudaStream_t>(stream));
 }
 
 }  // extern "C"

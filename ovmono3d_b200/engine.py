@@ -69,6 +69,7 @@ class LiftEngine:
         self._cap = 0
         self._ws_tensors: Dict[str, torch.Tensor] = {}
         self._ws = None
+        self._pooler_cache: Dict[tuple, tuple] = {}
 
     # ------------------------------------------------------------------ weights
     def _generators(self) -> List[nn.Module]:
@@ -85,6 +86,13 @@ class LiftEngine:
             self._params = list(self.cube_head.parameters())
         ts = self._params + [p for p in priors if p is not None]
         return tuple((t.data_ptr(), t._version) for t in ts)
+
+    def invalidate(self) -> None:
+        """Forget the bf16 / TF32 copies of the FC weights: the next `prepare` rebuilds them.  `prepare` notices
+        re-assigned parameters and in-place updates that bump the tensor version (`load_state_dict`, `copy_`, optimiser
+        steps); writes through `param.data` or raw pointers do not bump it -- call this after such an update (the
+        plugin does so from a `load_state_dict` post-hook)."""
+        self._weights_key = None
 
     def prepare(self, device: torch.device, priors_dims_per_cat: Optional[torch.Tensor],
                 priors_z_scales: Optional[torch.Tensor], priors_z_stats: Optional[torch.Tensor]) -> None:
@@ -183,10 +191,14 @@ class LiftEngine:
             counters=torch.zeros((_round_up(cap, 128) // 128 * (_round_up(self.fc_dim, 256) // 256),), device=device,
                                  dtype=torch.int32),   # split-K tile counters: zero on entry / exit
             order=torch.empty((ops.order_ws_len(cap),), device=device, dtype=torch.int32),
+            # split-K exchange of the first FC layer: per-cluster partial tiles + their flags (zero between calls)
+            slots=torch.empty((ops.SPLITK_SLOTS_LEN,), device=device, dtype=torch.float32),
+            flags=torch.zeros((ops.SPLITK_FLAGS_LEN,), device=device, dtype=torch.int32),
         )
         ws = ops.ovm_workspace_t(t["pooled"].data_ptr(), ld_pooled, t["acc"].data_ptr(), t["act_a"].data_ptr(),
                                  t["act_b"].data_ptr(), t["feats"].data_ptr(), t["levels"].data_ptr(),
-                                 t["counters"].data_ptr(), t["counters"].numel(), 0)
+                                 t["counters"].data_ptr(), t["counters"].numel(), t["flags"].numel(),
+                                 t["slots"].data_ptr(), t["slots"].numel(), t["flags"].data_ptr())
         self._ws_tensors, self._ws, self._cap = t, ws, cap
         return ws
 
@@ -209,11 +221,24 @@ class LiftEngine:
         raw = torch.empty((n, 16), device=device, dtype=torch.float32) if want_raw else None
         if n == 0:
             return records, raw
-        pooler, keep = ops.make_pooler(features, self.scales, self.P, self.sampling_ratio, self.canonical_box_size,
-                                       self.canonical_level, self.settings.scale_roi_boxes)
-        if pooler.channels * self.P * self.P != self.in_dim:
-            raise ops.LiftError("fc1 expects %d inputs but the pyramid gives C*P*P = %d"
-                                % (self.in_dim, pooler.channels * self.P * self.P))
+        # the pyramid descriptor depends only on the maps' addresses, shapes and layouts: a steady-state caller (the same
+        # backbone output buffers call after call) re-describes nothing
+        pkey = tuple((f.data_ptr(), f.shape, f.stride()) for f in features)
+        cached = self._pooler_cache.get(pkey)
+        if cached is None:
+            cached = ops.make_pooler(features, self.scales, self.P, self.sampling_ratio, self.canonical_box_size,
+                                     self.canonical_level, self.settings.scale_roi_boxes)
+            if cached[0].channels * self.P * self.P != self.in_dim:
+                raise ops.LiftError("fc1 expects %d inputs but the pyramid gives C*P*P = %d"
+                                    % (self.in_dim, cached[0].channels * self.P * self.P))
+            if any(k is not f for k, f in zip(cached[1], features)):
+                cached = (cached[0], cached[1], False)     # a level was copied to make it contiguous: do not cache the copy
+            else:
+                cached = (cached[0], None, True)           # (do not keep the caller's tensors alive)
+                if len(self._pooler_cache) >= 8:
+                    self._pooler_cache.clear()
+                self._pooler_cache[pkey] = cached
+        pooler, keep = cached[0], cached[1]
         ws = self._workspace(n, device)
         pooler.order_ws = self._ws_tensors["order"].data_ptr()
         pooler.order_ws_len = self._ws_tensors["order"].numel()

@@ -1,0 +1,163 @@
+"""3-D IoU at evaluation: `ovm_iou_box3d` / `evaluation.box3d_overlap` against
+`oracle/iou3d_oracle.py` (the reference's `box3d_overlap`, omni3d_evaluation.py:68-169, over the published
+pytorch3d algorithm) and the oracle itself against analytic answers and an independent exact construction (qhull).
+
+The reference has no tests for this function and pytorch3d's source is not in the tree: parity is pinned by the known
+answers below, not by reference vectors.
+"""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import iou3d_oracle as io
+
+I3 = np.eye(3)
+
+
+def _rot(axis, deg):
+    a = math.radians(deg)
+    c, s = math.cos(a), math.sin(a)
+    return {"x": np.array([[1, 0, 0], [0, c, -s], [0, s, c]]), "y": np.array([[c, 0, s], [0, 1, 0], [-s, 0, c]]),
+            "z": np.array([[c, -s, 0], [s, c, 0], [0, 0, 1]])}[axis]
+
+
+def _random_rotation(rng):
+    q = rng.normal(size=4)
+    q /= np.linalg.norm(q)
+    w, x, y, z = q
+    return np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w)],
+                     [2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w)],
+                     [2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)]])
+
+
+UNIT = io.make_box([0, 0, 0], [1, 1, 1], I3)
+# (second box, expected IoU with the unit cube at the origin)
+KNOWN = [
+    ("identical", UNIT, 1.0),
+    ("disjoint", io.make_box([3, 0, 0], [1, 1, 1], I3), 0.0),
+    ("face touching", io.make_box([1, 0, 0], [1, 1, 1], I3), 0.0),
+    ("edge touching", io.make_box([1, 1, 0], [1, 1, 1], I3), 0.0),
+    ("half overlap along x", io.make_box([0.5, 0, 0], [1, 1, 1], I3), 1.0 / 3.0),
+    ("quarter overlap along x and y", io.make_box([0.5, 0.5, 0], [1, 1, 1], I3), 0.25 / 1.75),
+    ("nested half-size", io.make_box([0.1, 0, 0], [0.5, 0.5, 0.5], I3), 0.125),
+    ("nested sharing a face plane", io.make_box([0.25, 0, 0], [0.5, 0.5, 0.5], I3), 0.125),
+    ("slab through the cube", io.make_box([0, 0, 0], [3, 0.5, 0.5], I3), 0.25 / (1 + 0.75 - 0.25)),
+    ("rotated 45 deg about z", io.make_box([0, 0, 0], [1, 1, 1], _rot("z", 45)), 1.0 / math.sqrt(2.0)),
+    ("rotated 45 deg about x", io.make_box([0, 0, 0], [1, 1, 1], _rot("x", 45)), 1.0 / math.sqrt(2.0)),
+    ("rotated 90 deg about y", io.make_box([0, 0, 0], [1, 1, 1], _rot("y", 90)), 1.0),
+    ("far from the origin", None, 1.0 / 3.0),
+]
+
+
+def _known_pairs():
+    a, b, want = [], [], []
+    for name, box, iou in KNOWN:
+        if box is None:       # the half-overlap pair 40 m away: fp32 cancellation check
+            a.append(UNIT + np.array([12.0, -7.0, 40.0]))
+            b.append(io.make_box([12.5, -7.0, 40.0], [1, 1, 1], I3))
+        else:
+            a.append(UNIT)
+            b.append(box)
+        want.append(iou)
+    return np.stack(a), np.stack(b), np.array(want)
+
+
+def _random_boxes(n, seed, spread=0.8):
+    rng = np.random.default_rng(seed)
+    return np.stack([io.make_box(rng.normal(size=3) * spread + [0, 0, 8], rng.uniform(0.4, 2.5, 3), _random_rotation(rng))
+                     for _ in range(n)])
+
+
+# --------------------------------------------------------------------------- the oracle itself (CPU)
+def test_oracle_known_answers():
+    a, b, want = _known_pairs()
+    for k, (name, _, _) in enumerate(KNOWN):
+        vol, iou = io.iou_box3d_pair(a[k], b[k])
+        assert abs(iou - want[k]) <= 1e-9, name
+
+
+def test_oracle_matches_qhull_on_random_oriented_boxes():
+    a, b = _random_boxes(40, 1), _random_boxes(40, 2)
+    nonzero = 0
+    for k in range(40):
+        v1, i1 = io.iou_box3d_pair(a[k], b[k])
+        v2, i2 = io.iou_box3d_qhull(a[k], b[k])
+        assert abs(i1 - i2) <= 1e-9 and abs(v1 - v2) <= 1e-9 * max(1.0, v2)
+        nonzero += i2 > 0
+    assert nonzero >= 20
+    # symmetry
+    assert abs(io.iou_box3d_pair(a[0], b[0])[1] - io.iou_box3d_pair(b[0], a[0])[1]) <= 1e-12
+
+
+def test_oracle_guards_match_the_reference_formulas():
+    boxes = torch.from_numpy(_random_boxes(6, 3)).float()
+    assert io.check_coplanar(boxes).all() and io.check_nonzero(boxes).all()
+    bad = boxes.clone()
+    bad[1, 6] += torch.tensor([0.0, 0.0, 0.3])          # one corner pulled off its faces
+    bad[4, 4:] = bad[4, :4]                               # flat box: zero-area side triangles
+    assert io.check_coplanar(bad).tolist() == [True, False, True, True, True, True]
+    assert io.check_nonzero(bad).tolist() == [True, True, True, True, False, True]
+    iou = io.box3d_overlap(bad, boxes[:3])
+    assert float(iou[1].abs().max()) == 0.0 and float(iou[4].abs().max()) == 0.0 and float(iou[0, 0]) > 0.99
+
+
+# --------------------------------------------------------------------------- the kernel (GPU)
+@pytest.mark.gpu
+def test_kernel_known_answers():
+    from ovmono3d_b200 import ops
+
+    a, b, want = _known_pairs()
+    dev = torch.device("cuda:0")
+    iou, flags, vol = ops.iou_box3d(torch.from_numpy(a).float().to(dev), torch.from_numpy(b).float().to(dev), want_vol=True)
+    got = iou.diagonal().cpu().numpy()
+    assert int(flags.abs().sum()) == 0
+    for k, (name, _, _) in enumerate(KNOWN):
+        assert abs(got[k] - want[k]) <= 1e-4, "%s: %.6f vs %.6f" % (name, got[k], want[k])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("N,M,seed", [(1, 1, 0), (7, 5, 1), (40, 33, 2), (100, 16, 3)])
+def test_kernel_matches_oracle_on_random_oriented_boxes(N, M, seed):
+    from ovmono3d_b200 import ops
+
+    a, b = _random_boxes(N, 10 + seed), _random_boxes(M, 20 + seed)
+    ta, tb = torch.from_numpy(a).float(), torch.from_numpy(b).float()
+    want_vol, want = io.iou_box3d(ta, tb)           # from the fp32-rounded corners, float64 arithmetic
+    dev = torch.device("cuda:0")
+    iou, flags, vol = ops.iou_box3d(ta.to(dev), tb.to(dev), want_vol=True)
+    assert int(flags.abs().sum()) == 0
+    assert float((iou.cpu() - want).abs().max()) <= 1e-4
+    assert float((vol.cpu() - want_vol).abs().max()) <= 1e-4 * float(want_vol.max().clamp_min(1.0))
+    assert float((want > 0).float().mean()) > 0.2     # the comparison is not vacuous
+    # IoU is symmetric
+    iou_t, _, _ = ops.iou_box3d(tb.to(dev), ta.to(dev))
+    assert float((iou_t.t() - iou).abs().max()) <= 2e-5
+
+
+@pytest.mark.gpu
+def test_box3d_overlap_guards_and_lift_corner_order(capsys):
+    """`evaluation.box3d_overlap` = the reference's function: flagged detections get zero rows and a warning; the
+    corners `get_cuboid_verts_faces` emits (the lift's `pred_bbox3D`) are in the order the IoU expects."""
+    from oracle import lift_oracle as lo
+    from ovmono3d_b200 import evaluation
+
+    dev = torch.device("cuda:0")
+    boxes = torch.from_numpy(_random_boxes(6, 3)).float()
+    bad = boxes.clone()
+    bad[1, 6] += torch.tensor([0.0, 0.0, 0.3])
+    bad[4, 4:] = bad[4, :4]
+    want = io.box3d_overlap(bad.clone(), boxes[:3])
+    got = evaluation.box3d_overlap(bad.to(dev), boxes[:3].to(dev)).cpu()
+    out = capsys.readouterr().out
+    assert "skipping 1 non-coplanar boxes" in out and "skipping 1 zero volume boxes" in out
+    assert float((got - want).abs().max()) <= 1e-4 and float(got[1].abs().max()) == 0.0 and float(got[4].abs().max()) == 0.0
+    # a cuboid from the lift's own corner generator against itself and against a shifted copy
+    b3d = torch.tensor([[0.3, -0.2, 6.0, 1.2, 0.8, 2.0]])          # X Y Z W H L
+    R = torch.from_numpy(_rot("y", 30)).float().unsqueeze(0)
+    v = lo.get_cuboid_verts(b3d, R)
+    v2 = lo.get_cuboid_verts(b3d + torch.tensor([[0.0, 0.4, 0.0, 0, 0, 0]]), R)
+    iou = evaluation.box3d_overlap(torch.cat([v, v2]).to(dev), v.to(dev)).cpu()
+    assert abs(float(iou[0, 0]) - 1.0) <= 1e-4
+    assert abs(float(iou[1, 0]) - 0.4 / 1.2) <= 1e-4           # shifted by half of H = 0.8 along y: (1/2) / (3/2)

@@ -65,7 +65,9 @@ def pipeline():
         eng.forward(db.features, db.boxes, db.classes, db.scores, db.batch_idx, db.cams)
     lib.ovm_gemm_set_trace(None)
     torch.cuda.synchronize()
-    t = trace.cpu().numpy().reshape(-1, 16)[104:148]    # fc2 (104 CTAs) overwrote rows 0..103: fc1's CTAs 104..147
+    t = trace.cpu().numpy().reshape(-1, 16)
+    if not eng.tail_fused:
+        t = t[104:148]    # fc2 (104 CTAs) overwrote rows 0..103: fc1's CTAs 104..147
     t = t[t[:, 0] > 0].astype(np.float64)
     names = ["entry", "setup", "last_tma", "prev_done", "last_mma", "acc_ready", "epi_done", "partial_added"]
     t0 = t[:, 0].min()
@@ -80,6 +82,16 @@ def pipeline():
                   ("partial add (acc_ready -> added)", d(7, 5)), ("finish (added -> epi_done)", d(6, 7))):
         print("  %-36s min %6.2f  median %6.2f  p90 %6.2f  max %6.2f   sorted: %s" % (
             nm, v.min(), np.median(v), np.percentile(v, 90), v.max(), " ".join("%.1f" % x for x in np.sort(v)[::4])))
+    own = t[:, 8] > 0       # slot exchange (gemm_pair_kernel<true>): CTAs whose last segment owns a tile
+    if own.any():
+        o = t[own]
+        print("  owners of a tile (last segment): %d CTAs; partial sources per tile %s" % (
+            len(o), np.bincount(o[:, 11].astype(int)).tolist()))
+        for nm, v in (("acc_ready -> all partials published", (o[:, 8] - o[:, 5]) / 1e3),
+                      ("published -> first chunk merged", (o[:, 9] - o[:, 8]) / 1e3),
+                      ("first chunk -> last chunk merged", (o[:, 10] - o[:, 9]) / 1e3)):
+            v = v[np.isfinite(v)]
+            print("    %-38s min %6.2f  median %6.2f  p90 %6.2f  max %6.2f" % (nm, v.min(), np.median(v), np.percentile(v, 90), v.max()))
 
 
 if __name__ == "__main__":
