@@ -54,6 +54,35 @@ POOL = 7
 L2_FLUSH_BYTES = 256 << 20   # > 126 MB L2
 WORKLOAD = ("C2: OVMono3D_dinov2_SFP lift, 16 images x 100 boxes per rank-step, SFP p2-p4 256ch "
             "@128/64/32 (896px, strides 7/14/28) fp32 NCHW, head 12544-1024-1024-13 bf16 operands / fp32 accumulate")
+_C2_WORKLOAD = WORKLOAD
+CONFIG = "C2"
+SEED = 1235
+STREAM = False      # C4: the steps are consecutive batches of one stream (no L2 flush between them, one event pair)
+
+
+def set_workload(name: str) -> None:
+    """Select one of BASELINE.json's configs (ovmono3d_b200/workloads.py) for every arm of this file.  The default, C2,
+    is the configuration the metric is quoted on; C4 is the C2 batch streamed 20 000 images deep."""
+    global NUM_IMAGES, BOXES_PER_IMAGE, STRIDES, CANVAS, CHANNELS, FC_DIM, WORKLOAD, CONFIG, SEED, STREAM
+    from ovmono3d_b200 import workloads
+
+    STREAM = name == "C4"
+    w = workloads.get("C2" if STREAM else name)
+    NUM_IMAGES, BOXES_PER_IMAGE, STRIDES, CANVAS, CHANNELS, FC_DIM = (w.num_images, w.boxes_per_image, tuple(w.strides),
+                                                                     w.canvas, w.channels, w.fc_dim)
+    CONFIG, SEED = name, w.seed
+    if STREAM:
+        WORKLOAD = ("C4: Omni3D-test-scale synthetic stream, 20 000 images x 100 boxes in batches of 16 per rank-step "
+                    "(C2 shapes), images sharded contiguously by rank, detections exchanged once at the end")
+    elif name != "C2":
+        WORKLOAD = w.describe()
+    else:
+        WORKLOAD = _C2_WORKLOAD
+
+
+def config_dict(n: int) -> Dict[str, object]:
+    """`config` of the JSON line: the workload only, identical in both arms (what is arm-specific goes to `method`)."""
+    return {"workload": WORKLOAD, "name": CONFIG, "images_per_step_per_gpu": NUM_IMAGES, "boxes_per_step_per_gpu": n}
 
 
 def _peaks() -> Dict[str, float]:
@@ -169,7 +198,9 @@ class ClockSampler:
 def make_batch(seed: int):
     from ovmono3d_b200 import synth
 
-    return synth.make_inputs(seed, NUM_IMAGES, BOXES_PER_IMAGE, strides=STRIDES, canvas=CANVAS, channels=CHANNELS)
+    content = 512 if CONFIG == "C1" else None
+    return synth.make_inputs(seed, NUM_IMAGES, BOXES_PER_IMAGE, strides=STRIDES, canvas=CANVAS, content=content,
+                             channels=CHANNELS)
 
 
 def make_weights():
@@ -184,7 +215,7 @@ def build_head(device: torch.device):
     from ovmono3d_b200.config import get_cfg
     from ovmono3d_b200.roi_heads import build_roi_heads
 
-    names = ["p2", "p3", "p4"]
+    names = ["p%d" % (2 + i) for i in range(len(STRIDES))]
     c = get_cfg()
     c.MODEL.ROI_HEADS.NAME = "ROIHeads3DB200"
     c.MODEL.ROI_HEADS.IN_FEATURES = names
@@ -290,7 +321,7 @@ def run_ours(args) -> Dict[str, object]:
 
     head, names = build_head(device)
     num_sets = 3   # 3 x 352 MB of pyramids: the steps rotate over inputs larger than L2
-    inputs = [make_batch(1235 + 1000 * rank + i) for i in range(num_sets)]
+    inputs = [make_batch(SEED + 1000 * rank + i) for i in range(num_sets)]
     dbs = [DeviceBatch(x, device) for x in inputs]
     n = dbs[0].n
     eng = head._get_engine()
@@ -298,8 +329,9 @@ def run_ours(args) -> Dict[str, object]:
     flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=device)
     records_all = torch.empty((K, n, ops.RECORD_WIDTH), device=device, dtype=torch.float32)
 
-    def lift(db, out=None):
-        return eng.forward(db.features, db.boxes, db.classes, db.scores, db.batch_idx, db.cams, out=out)[0]
+    def lift(db, out=None, peers=None):
+        return eng.forward(db.features, db.boxes, db.classes, db.scores, db.batch_idx, db.cams, out=out,
+                           peer_ptrs=peers)[0]
 
     def barrier():
         if world > 1:
@@ -310,10 +342,21 @@ def run_ours(args) -> Dict[str, object]:
     for i in range(W):
         flush.zero_()
         lift(dbs[i % num_sets])
-    if world > 1:   # the communicator and the gather's buffers are set up before the timed region
+    exchange, transport = None, "single GPU"
+    if world > 1:   # the communicator and the exchange's buffers are set up before the timed region
         from ovmono3d_b200 import shard
 
-        shard.gather_records(records_all.view(-1, ops.RECORD_WIDTH))
+        transport = os.environ.get("OVM_GATHER", "peer")
+        try:
+            exchange = shard.RecordExchange(K * n, device, transport=transport)
+        except Exception as ex:       # symmetric memory not available on this box: the one-collective NCCL path
+            sys.stderr.write("RecordExchange(%s) unavailable (%s); using nccl\n" % (transport, ex))
+            transport = "nccl"
+            exchange = shard.RecordExchange(K * n, device, transport=transport)
+        records_all = exchange.local.view(K, n, ops.RECORD_WIDTH)    # the lift writes straight into the send block
+        for i in range(min(W, K)):
+            lift(dbs[i % num_sets], out=records_all[i], peers=exchange.peer_ptrs(i * n))
+        exchange.finish(K * n)
     barrier()
     starts = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
     stops = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
@@ -323,10 +366,16 @@ def run_ours(args) -> Dict[str, object]:
     launches0 = ops.launch_count()
     t_wall0 = time.perf_counter()
     for i in range(K):
-        flush.zero_()
-        starts[i].record()
-        lift(dbs[i % num_sets], out=records_all[i])
-        stops[i].record()
+        if not STREAM:
+            flush.zero_()
+            starts[i].record()
+        elif i == 0:
+            starts[0].record()
+        lift(dbs[i % num_sets], out=records_all[i], peers=exchange.peer_ptrs(i * n) if exchange is not None else None)
+        if not STREAM:
+            stops[i].record()
+        elif i == K - 1:
+            stops[0].record()
     g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     gathered = None
     if world > 1:
@@ -335,16 +384,19 @@ def run_ours(args) -> Dict[str, object]:
         barrier()
     g0.record()
     if world > 1:   # the path's one exchange: detections gathered once at the end (omni3d_evaluation.py:717-720)
-        from ovmono3d_b200 import shard
-
-        gathered, counts, _ = shard.gather_records(records_all.view(-1, ops.RECORD_WIDTH))
+        gathered, counts = exchange.finish(K * n)
     g1.record()
     if world > 1:
-        assert int(counts.cpu().sum()) == world * K * n and gathered.shape[0] == world * K * n
+        assert counts.cpu().tolist() == [K * n] * world and tuple(gathered.shape) == (world, K * n, ops.RECORD_WIDTH)
+        assert torch.isfinite(gathered[:, :, :47]).all(), "non-finite gathered records"
     barrier()
     loop_wall_ms = (time.perf_counter() - t_wall0) * 1e3
     launches = ops.launch_count() - launches0
-    step_ms = [s.elapsed_time(e) for s, e in zip(starts, stops)]
+    if STREAM:      # one event pair around the whole stream
+        loop_ms = starts[0].elapsed_time(stops[0])
+        step_ms = [loop_ms / K] * K
+    else:
+        step_ms = [s.elapsed_time(e) for s, e in zip(starts, stops)]
     gather_ms = g0.elapsed_time(g1) if world > 1 else 0.0
     total_ms = _max_over_ranks(sum(step_ms) + gather_ms, world, device)
     time.sleep(0.15)
@@ -357,16 +409,21 @@ def run_ours(args) -> Dict[str, object]:
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "bf16", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "images_per_step_per_gpu": NUM_IMAGES, "boxes_per_step_per_gpu": n,
-                   "sharding": "images sharded by rank, no data-path collective; one NCCL all-gather of the "
-                               "detection records after the last step, inside the timed total" if world > 1 else
-                               "single GPU",
-                   "l2": "256 MiB memset between steps (outside the per-step event pairs) and steps rotate over "
-                         "3 input batches of 352 MB each",
-                   "timing": "sum of per-step CUDA-event pairs on the launching stream (+ gather), max over ranks"},
+        "config": config_dict(n),
+        "method": {"sharding": ("images sharded by rank, no data-path collective; detection records exchanged inside the "
+                                "timed total: " + ("the decode stores every record into every rank's symmetric-memory "
+                                                   "block over NVLink (ovm_lift_forward_peers), one signal-pad barrier after "
+                                                   "the last step" if transport == "peer" else
+                                                   "one NCCL all-gather of fixed-capacity blocks after the last step"))
+                   if world > 1 else "single GPU",
+                   "l2": ("no flush: consecutive batches of one stream, rotating over 3 input batches larger than L2"
+                          if STREAM else "256 MiB memset between steps (outside the per-step event pairs) and steps rotate "
+                          "over 3 input batches of %d MB each" % (sum(f.numel() * 4 for f in dbs[0].features) // 1000000)),
+                   "timing": ("one CUDA-event pair around the whole stream (+ exchange), max over ranks" if STREAM else
+                              "sum of per-step CUDA-event pairs on the launching stream (+ exchange), max over ranks")},
         "clocks": clocks, "gpu_launches": int(launches),
         "step_ms_min_median_max": [min(step_ms), float(np.median(step_ms)), max(step_ms)],
-        "gather_ms_total": gather_ms, "loop_wall_ms_incl_flush": loop_wall_ms,
+        "gather_ms_total": gather_ms, "gather_transport": transport, "loop_wall_ms_incl_flush": loop_wall_ms,
     }
     if rank == 0:
         out.update(kernel_breakdown(eng, dbs, flush, lift, K, peaks))
@@ -568,8 +625,9 @@ def cpu_baseline(inp, budget_s: float) -> Dict[str, object]:
         times.append(time.perf_counter() - t0)
     best = min(times)
     return {"value": n / best, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": "%d whole C2 batches (16 images x 100 boxes, fp32) after 1 warm-up, best batch %.1f ms, "
-                      "mean %.1f ms" % (len(times), best * 1e3, float(np.mean(times)) * 1e3)}
+            "sample": "%d whole %s batches (%d images x %d boxes, fp32) after 1 warm-up, best batch %.1f ms, "
+                      "mean %.1f ms" % (len(times), CONFIG, NUM_IMAGES, BOXES_PER_IMAGE, best * 1e3,
+                                        float(np.mean(times)) * 1e3)}
 
 
 def run_reference(args) -> Optional[Dict[str, object]]:
@@ -580,7 +638,7 @@ def run_reference(args) -> Optional[Dict[str, object]]:
         return None
     K, W = args.steps, max(args.warmup, 1)
     cores, cfg, weights = _oracle_setup()
-    inputs = [make_batch(1235 + i) for i in range(2)]
+    inputs = [make_batch(SEED + i) for i in range(2)]
     n = sum(len(b) for b in inputs[0].boxes)
     for i in range(W):
         _oracle_step(inputs[i % 2], weights, cfg)
@@ -589,12 +647,14 @@ def run_reference(args) -> Optional[Dict[str, object]]:
         _oracle_step(inputs[i % 2], weights, cfg)
     dt = time.perf_counter() - t0
     value = n * K / dt
-    sample = "each step = one whole C2 batch (16 images x 100 boxes) on %d host threads" % cores
+    sample = "each step = one whole %s batch (%d images x %d boxes) on %d host threads" % (
+        CONFIG, NUM_IMAGES, BOXES_PER_IMAGE, cores)
     return {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": K,
         "warmup": W, "ms_per_step": dt / K * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "device": "cpu",
+        "config": config_dict(n),
+        "method": {"device": "cpu",
                    "note": "the reference (pure Python on detectron2 + pytorch3d, both un-vendored) cannot be installed "
                            "here; this arm runs oracle/, its op-for-op CPU restatement pinned to vectors written by the "
                            "reference's own code (tests/golden/make_golden.py)"},
@@ -611,11 +671,17 @@ def main() -> None:
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--config", default="C2",
+                    help="BASELINE.json config to run (default C2, the one the metric is quoted on): C1, C2, C3-1x2000, "
+                         "C3-8x2000, C3-8x300, C4 (the C2 batch streamed, no L2 flush), C5-sfp4, C5-dla, C5-c128, C5-c512")
     args = ap.parse_args()
+    set_workload(args.config)
     # exactly one JSON line on stdout: libraries that print there (NCCL's version banner under NCCL_DEBUG) go to stderr
     sys.stdout.flush()
     real_stdout = os.dup(1)
     os.dup2(2, 1)
+    if STREAM and args.steps == 50 and args.impl != "reference":
+        args.steps = max(20000 // (NUM_IMAGES * max(args.gpus, 1)), 1)     # the whole 20 000-image stream
     if args.impl == "reference":
         if args.steps == 50 and args.warmup == 5:
             args.steps, args.warmup = 10, 2

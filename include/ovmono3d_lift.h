@@ -62,7 +62,7 @@ enum { OVM_DIMS_EXP = 0, OVM_DIMS_SIGMOID = 1 };
 enum { OVM_GEMM_AUTO = 0, OVM_GEMM_DIRECT = 1, OVM_GEMM_STREAMK = 2 };
 
 /* int32 elements of ovm_pooler_t.order_ws that are always enough for n boxes */
-#define OVM_ORDER_WS_LEN(n) (24 * (int64_t)(n) + 4808)
+#define OVM_ORDER_WS_LEN(n) (48 * (int64_t)(n) + 2048)
 
 /* One pyramid level: fp32 feature map of N images, C channels, contiguous in `layout`. */
 typedef struct {
@@ -83,10 +83,11 @@ typedef struct {
   int32_t canonical_level;       /* d2 default 4 */
   float scale_roi_boxes;         /* SCALE_ROI_BOXES; <= 0 disables (roi_heads.py:310-327) */
   int32_t order_ws_len;          /* int32 elements in order_ws; OVM_ORDER_WS_LEN(n) is enough for n boxes */
-  int32_t* order_ws;             /* optional device scratch (16-byte aligned): when given, one extra tiny launch turns the boxes into
-                                    work items (large footprints are cut along the channels, largest item first)
-                                    so that no single CTA sets the kernel time; NULL = one CTA per box in input
-                                    order */
+  int32_t* order_ws;             /* optional device scratch (16-byte aligned): when given, two small launches ahead of the
+                                    pooling kernel plan every box once (level, sampling geometry, bin ranges, stage
+                                    geometry: a warp per box) and turn the boxes into work items (large footprints are
+                                    cut along the channels, largest item first) so that no single CTA sets the kernel
+                                    time; NULL = one CTA per box in input order, planning its box itself */
 } ovm_pooler_t;
 
 /* Multi-level ROIAlignV2.  boxes [n,4] xyxy fp32, batch_idx [n] int32 (image of each box), both
@@ -243,6 +244,25 @@ int ovm_lift_forward(const ovm_pooler_t* pooler, const ovm_fc_stack_t* fc, const
                      const float* scores, const int32_t* batch_idx, const float* cams, int32_t n,
                      const ovm_workspace_t* ws, float* records, float* raw, void* stream);
 
+/* The same, with the cross-rank exchange of the detections fused into the decode (SURVEY.md sections 5 / 8e; the
+ * reference gathers pickled per-image lists over Gloo once per dataset, omni3d_evaluation.py:717-720).
+ * peers->records[p] (p < num_peers <= OVM_MAX_PEERS) are device-visible addresses -- NVLink peer mappings of the other
+ * ranks' exchange buffers (CUDA IPC / torch symmetric memory), each already offset to the row where THIS call's first
+ * record belongs; the decode stores every 192-byte record to `records` and to each of them.  The caller completes the
+ * exchange with one barrier across the ranks after its last call (a kernel boundary orders the posted writes).  16-byte
+ * aligned pointers; NULL or num_peers == 0 = ovm_lift_forward.                                                      */
+#define OVM_MAX_PEERS 8
+typedef struct {
+  int32_t num_peers;
+  int32_t _pad;
+  float* records[OVM_MAX_PEERS];
+} ovm_peer_records_t;
+int ovm_lift_forward_peers(const ovm_pooler_t* pooler, const ovm_fc_stack_t* fc, const ovm_decode_cfg_t* cfg,
+                           const ovm_head_weights_t* heads, const float* boxes, const int64_t* classes,
+                           const float* scores, const int32_t* batch_idx, const float* cams, int32_t n,
+                           const ovm_workspace_t* ws, float* records, float* raw, const ovm_peer_records_t* peers,
+                           void* stream);
+
 /* Measurement hook (bench.py): while set, ovm_lift_forward records events[0] before its first launch and the
  * next event after each stage -- ROIAlign, every FC layer in issue order (memset + split-K GEMM + bias/ReLU
  * count as one layer), heads+decode -- on the stream it was given, up to `count` events.  Events are
@@ -335,8 +355,8 @@ int ovm_iou_box3d(const float* boxes_dt, const float* boxes_gt, int32_t N, int32
 int ovm_abi_version(void);
 /* sizeof() of the ABI structs as this library was compiled, for binding self-checks:
  * 0 ovm_level_t, 1 ovm_pooler_t, 2 ovm_decode_cfg_t, 3 ovm_head_weights_t, 4 ovm_fc_layer_t,
- * 5 ovm_fc_stack_t, 6 ovm_workspace_t, 7 ovm_box_inference_cfg_t, 8 ovm_box_inference_ws_t; -1 for any other
- * index. */
+ * 5 ovm_fc_stack_t, 6 ovm_workspace_t, 7 ovm_box_inference_cfg_t, 8 ovm_box_inference_ws_t, 9 ovm_peer_records_t;
+ * -1 for any other index. */
 int ovm_struct_size(int which);
 const char* ovm_last_error(void);
 /* Number of kernel launches (incl. memsets) the library has issued in this process. */

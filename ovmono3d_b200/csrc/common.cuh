@@ -135,13 +135,14 @@ int cast_bf16_launch(const float* in, int64_t ld_in, int32_t rows, int32_t cols,
 int head_decode_launch(const ovm_decode_cfg_t* cfg, const ovm_head_weights_t* w, const float* feats,
                        int64_t ld_feats, const float* boxes, const int64_t* classes, const float* scores,
                        const int32_t* batch_idx, const float* cams, int32_t num_images, int32_t n,
-                       float* records, float* raw, cudaStream_t stream);
+                       float* records, float* raw, cudaStream_t stream, const ovm_peer_records_t* peers = nullptr);
 // fc_tail.cu: last FC layer + heads + decode in one launch (class-agnostic heads, shared FC stack)
 bool fc_tail_supported(const ovm_decode_cfg_t* cfg, int32_t N, int32_t K);
 int fc_tail_launch(const void* A, int64_t lda, int32_t a_dtype, const void* W, int64_t ldw, const float* bias, int32_t N,
                    int32_t K, const ovm_decode_cfg_t* cfg, const ovm_head_weights_t* w, const float* boxes,
                    const int64_t* classes, const float* scores, const int32_t* batch_idx, const float* cams,
-                   int32_t num_images, int32_t n, float* records, float* raw, cudaStream_t stream);
+                   int32_t num_images, int32_t n, float* records, float* raw, cudaStream_t stream,
+                   const ovm_peer_records_t* peers = nullptr);
 int round_tf32_launch(const float* in, int64_t ld_in, int32_t rows, int32_t cols, float* out, int64_t ld_out,
                       cudaStream_t stream);
 

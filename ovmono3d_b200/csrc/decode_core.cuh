@@ -37,6 +37,10 @@ struct DecodeArgs {
   float* raw;
   unsigned long long* trace;   // optional [grid, 8] %globaltimer stamps of warp 0 (ovm_head_set_trace), else NULL
   int* error_flag;             // optional device int: set to 1 when a class id / image index is out of range
+  // fused gather (ovm_lift_forward_peers): every record is also stored into these buffers -- the gather slots of this
+  // rank in every rank's exchange buffer, mapped into this device's address space (NVLink peer mappings)
+  float* peer_records[OVM_MAX_PEERS];
+  int num_peers;
 };
 
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + expf(-x)); }
@@ -255,6 +259,11 @@ __device__ __forceinline__ void decode_record(const DecodeArgs& a, const int box
   float4* out = reinterpret_cast<float4*>(a.records + (long long)box * OVM_RECORD_WIDTH);
 #pragma unroll
   for (int i = 0; i < OVM_RECORD_WIDTH / 4; ++i) out[i] = make_float4(rec[4 * i], rec[4 * i + 1], rec[4 * i + 2], rec[4 * i + 3]);
+  for (int p = 0; p < a.num_peers; ++p) {   // the exchange: 192 bytes per box and peer, posted writes over NVLink
+    float4* po = reinterpret_cast<float4*>(a.peer_records[p] + (long long)box * OVM_RECORD_WIDTH);
+#pragma unroll
+    for (int i = 0; i < OVM_RECORD_WIDTH / 4; ++i) po[i] = make_float4(rec[4 * i], rec[4 * i + 1], rec[4 * i + 2], rec[4 * i + 3]);
+  }
   if (a.raw) {
     float4* ro = reinterpret_cast<float4*>(a.raw + (long long)box * 16);
     ro[0] = make_float4(deltas[0], deltas[1], z_raw, dims_raw[0]);

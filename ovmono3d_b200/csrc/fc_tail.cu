@@ -434,7 +434,8 @@ bool fc_tail_supported(const ovm_decode_cfg_t* cfg, int32_t N, int32_t K) {
 int fc_tail_launch(const void* A, int64_t lda, int32_t a_dtype, const void* W, int64_t ldw, const float* bias, int32_t N,
                    int32_t K, const ovm_decode_cfg_t* cfg, const ovm_head_weights_t* w, const float* boxes,
                    const int64_t* classes, const float* scores, const int32_t* batch_idx, const float* cams,
-                   int32_t num_images, int32_t n, float* records, float* raw, cudaStream_t stream) {
+                   int32_t num_images, int32_t n, float* records, float* raw, cudaStream_t stream,
+                   const ovm_peer_records_t* peers) {
   OVM_REQUIRE(cfg && w, "ovm_fc_tail: cfg / weights are NULL");
   OVM_REQUIRE(a_dtype == OVM_BF16 || a_dtype == OVM_TF32, "ovm_fc_tail: operand dtype %d (OVM_BF16 or OVM_TF32)", a_dtype);
   OVM_REQUIRE(cfg->z_type >= OVM_Z_DIRECT && cfg->z_type <= OVM_Z_CLUSTERS, "ovm_fc_tail: z_type %d", cfg->z_type);
@@ -471,6 +472,15 @@ int fc_tail_launch(const void* A, int64_t lda, int32_t a_dtype, const void* W, i
   g.d.records = records;
   g.d.raw = raw;
   g.d.trace = head_get_trace();
+  if (peers) {
+    OVM_REQUIRE(peers->num_peers >= 0 && peers->num_peers <= OVM_MAX_PEERS, "ovm_lift_forward_peers: num_peers %d", peers->num_peers);
+    for (int p = 0; p < peers->num_peers; ++p) {
+      OVM_REQUIRE(peers->records[p] && !(reinterpret_cast<uintptr_t>(peers->records[p]) & 15),
+                  "ovm_lift_forward_peers: peer buffer %d is NULL or not 16-byte aligned", p);
+      g.d.peer_records[p] = peers->records[p];
+    }
+    g.d.num_peers = peers->num_peers;
+  }
   g.K = K;
   g.N = N;
   g.cs = N / kTN;

@@ -337,7 +337,7 @@ unsigned long long* head_get_trace() { return g_head_trace; }
 int head_decode_launch(const ovm_decode_cfg_t* cfg, const ovm_head_weights_t* w, const float* feats, int64_t ld_feats,
                        const float* boxes, const int64_t* classes, const float* scores, const int32_t* batch_idx,
                        const float* cams, int32_t num_images, int32_t n, float* records, float* raw,
-                       cudaStream_t stream) {
+                       cudaStream_t stream, const ovm_peer_records_t* peers) {
   OVM_REQUIRE(cfg && w, "ovm_head_decode: cfg / weights are NULL");
   OVM_REQUIRE(cfg->z_type >= OVM_Z_DIRECT && cfg->z_type <= OVM_Z_CLUSTERS, "ovm_head_decode: z_type %d", cfg->z_type);
   OVM_REQUIRE(cfg->pose_type >= OVM_POSE_6D && cfg->pose_type <= OVM_POSE_EULER,
@@ -381,6 +381,16 @@ int head_decode_launch(const ovm_decode_cfg_t* cfg, const ovm_head_weights_t* w,
   a.raw = raw;
   a.trace = g_head_trace;
   a.error_flag = nullptr;
+  a.num_peers = 0;
+  if (peers) {
+    OVM_REQUIRE(peers->num_peers >= 0 && peers->num_peers <= OVM_MAX_PEERS, "ovm_lift_forward_peers: num_peers %d", peers->num_peers);
+    for (int p = 0; p < peers->num_peers; ++p) {
+      OVM_REQUIRE(peers->records[p] && !(reinterpret_cast<uintptr_t>(peers->records[p]) & 15),
+                  "ovm_lift_forward_peers: peer buffer %d is NULL or not 16-byte aligned", p);
+      a.peer_records[p] = peers->records[p];
+    }
+    a.num_peers = peers->num_peers;
+  }
   const int pose_n = cfg->pose_type == OVM_POSE_6D ? 6 : (cfg->pose_type == OVM_POSE_QUATERNION ? 4 : 3);
   const int stage_rows = 6 + (cfg->use_confidence ? 1 : 0) + pose_n;
   const size_t stage_bytes = ((size_t)stage_rows * cfg->fc_dim + 16) * sizeof(float);   // rows, then their biases

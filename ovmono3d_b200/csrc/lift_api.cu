@@ -130,6 +130,7 @@ int ovm_struct_size(int which) {
     case 6: return (int)sizeof(ovm_workspace_t);
     case 7: return (int)sizeof(ovm_box_inference_cfg_t);
     case 8: return (int)sizeof(ovm_box_inference_ws_t);
+    case 9: return (int)sizeof(ovm_peer_records_t);
     default: return -1;
   }
 }
@@ -211,7 +212,17 @@ int ovm_lift_forward(const ovm_pooler_t* pooler, const ovm_fc_stack_t* fc, const
                      const ovm_head_weights_t* heads, const float* boxes, const int64_t* classes, const float* scores,
                      const int32_t* batch_idx, const float* cams, int32_t n, const ovm_workspace_t* ws,
                      float* records, float* raw, void* stream_) {
+  return ovm_lift_forward_peers(pooler, fc, cfg, heads, boxes, classes, scores, batch_idx, cams, n, ws, records, raw,
+                                nullptr, stream_);
+}
+
+int ovm_lift_forward_peers(const ovm_pooler_t* pooler, const ovm_fc_stack_t* fc, const ovm_decode_cfg_t* cfg,
+                           const ovm_head_weights_t* heads, const float* boxes, const int64_t* classes,
+                           const float* scores, const int32_t* batch_idx, const float* cams, int32_t n,
+                           const ovm_workspace_t* ws, float* records, float* raw, const ovm_peer_records_t* peers,
+                           void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (peers && peers->num_peers == 0) peers = nullptr;
   OVM_REQUIRE(pooler && fc && cfg && heads && ws, "ovm_lift_forward: NULL descriptor");
   OVM_REQUIRE(fc->num_groups >= 1 && fc->num_groups <= 5 && fc->num_fc >= 1 && fc->layers,
               "ovm_lift_forward: bad FC stack (%d groups x %d layers)", fc->num_groups, fc->num_fc);
@@ -244,7 +255,7 @@ int ovm_lift_forward(const ovm_pooler_t* pooler, const ovm_fc_stack_t* fc, const
     if (rc != OVM_OK) return rc;
     rc = fc_tail_launch(h, ldh, tf32 ? OVM_TF32 : OVM_BF16, tf32 ? static_cast<const void*>(tail.weight_tf32) : tail.weight,
                         tf32 ? tail.ldw_tf32 : tail.ldw, tail.bias, tail.N, tail.K, cfg, heads, boxes, classes, scores,
-                        batch_idx, cams, pooler->num_images, n, records, raw, stream);
+                        batch_idx, cams, pooler->num_images, n, records, raw, stream, peers);
     if (rc != OVM_OK) return rc;
     return stage_mark(stage, stream);
   }
@@ -258,7 +269,7 @@ int ovm_lift_forward(const ovm_pooler_t* pooler, const ovm_fc_stack_t* fc, const
     if (rc != OVM_OK) return rc;
   }
   rc = head_decode_launch(cfg, heads, ws->feats, ld_feats, boxes, classes, scores, batch_idx, cams,
-                          pooler->num_images, n, records, raw, stream);
+                          pooler->num_images, n, records, raw, stream, peers);
   if (rc != OVM_OK) return rc;
   return stage_mark(stage, stream);
 }

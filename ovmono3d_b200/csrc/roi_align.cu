@@ -49,7 +49,7 @@ constexpr int kMaxRows = 64;               // rows one output bin-row may touch
 constexpr int kWxFloats = kMaxW * 8;
 constexpr int kWyFloats = kP * kMaxRows;
 constexpr int kOutFloats = 32 * kP * kP;   // one chunk of results
-constexpr int kMetaInts = 64;
+constexpr int kMetaInts = 72;              // 32 spare + the work item's header (kHdrInts)
 constexpr int kMaxSlots = 8;               // ring slots (a slot is as large as the box's stage, not kStageFloats)
 constexpr size_t roi_smem_bytes(int ring_floats) {
   return 1024 + (size_t)ring_floats * 4 + (size_t)(2 * kOutFloats + kWxFloats + kWyFloats) * 4 + kMetaInts * 4 + 2 * kMaxSlots * 8;
@@ -84,8 +84,22 @@ struct RoiArgs {
   float split_factor;           // roi_order_kernel: an item may cost this many average boxes before the box is cut
   int xalign_mask;              // footprint start column is rounded down to this mask (~3 or ~7)
   int evict_first;              // feature loads carry the L2 evict_first policy (OVM_ROI_EVICT)
+  int ring_floats, stage_floats;   // shared-memory ring / largest stage of the pooling kernel that will run (plan_box needs them)
+  const int* box_hdr;              // [n][kHdrInts] per-box headers written by roi_plan_kernel (with `order`)
   unsigned long long* trace;    // optional [grid, 16] %globaltimer stamps (ovm_roi_set_trace), else NULL
 };
+
+// Everything a pooling CTA needs to know about its box before it can issue its first TMA load, computed ONCE per box by
+// roi_plan_kernel (a warp per box, all SMs) instead of by every CTA that works on a piece of the box: round 1's pooling
+// CTAs spent 3 of their 4.6 us prologue on this (sqrt / divisions of the level assignment, 28 sample taps for the bin
+// ranges, the stage-geometry search), 2408 times per C2 batch, with two or three threads active.
+constexpr int kHdrInts = 40;      // 160 bytes = 10 x int4 per work item
+enum {
+  H_BOX = 0, H_CHUNKS, H_LEVEL, H_IMAGE, H_FLAGS, H_WSEL, H_G, H_RMAX, H_X0, H_FW, H_YLO, H_ROWS, H_GW, H_GH, H_NYMAX, H_PAD0,
+  H_START_W, H_START_H, H_BIN_W, H_BIN_H, H_COUNT, H_COST, H_PAD1, H_PAD2, H_META   // H_META .. H_META + 13: 28 x int16
+};
+enum { HF_DIRECT = 1, HF_EMPTY = 2 };
+constexpr int kMetaNone = 0x7fff;   // int16 encoding of "no valid sample" for a bin's low end (high end: -1)
 
 thread_local unsigned long long* g_roi_trace = nullptr;
 
@@ -355,13 +369,158 @@ __device__ __forceinline__ void consume_tile(const float* __restrict__ slab0, in
   }
 }
 
-// Work items for a grid of CTAs with very different run times.  One CTA turns the boxes into items
-// (box, first chunk, chunks) so that no item is much more expensive than the average box -- a box whose footprint
+// One warp plans one box: level, sampling geometry, the pixel range of every bin, the stage geometry (tile width, row
+// groups) of the TMA pipeline, and the footprint area the work-item planner balances by -> the 40-int header `h`
+// (warp-private).  Lanes 0..27 each take one end sample of one bin; everything else is computed redundantly.
+__device__ void plan_box_warp(const RoiArgs& a, float x1, float y1, float x2, float y2, int image, int box, int lane, int* h) {
+  const BoxGeom g = box_geometry_xy(a, x1, y1, x2, y2, image);
+  short* meta16 = reinterpret_cast<short*>(h + H_META);
+  bool direct = (a.P != kP) || g.level < 0 || g.gw <= 0 || g.gh <= 0;
+  if (!direct) direct = !a.tma_ok[g.level];
+  int flags = 0, wsel = -1, G = kP, rmax = 0, x0 = 0, fw = 0, y_lo = 0, rows_total = 0, ny_max = 0;
+  float cost = 1.f;
+  if (g.level >= 0) {
+    const RoiLevel lv = a.lv[g.level];
+    // pixel rows x columns of the footprint, clipped to the map
+    const float w = fminf(fmaxf(g.bin_w * (float)a.P, 0.f), (float)lv.W) + 2.f;
+    const float hgt = fminf(fmaxf(g.bin_h * (float)a.P, 0.f), (float)lv.H) + 2.f;
+    const float area = w * hgt;
+    cost = (area == area) ? area : 1.f;
+  }
+  if (!direct) {   // warp-uniform
+    const RoiLevel lv = a.lv[g.level];
+    const int H = lv.H, W = lv.W;
+    // ---- pixel range of every bin.  The sample coordinate is monotone in the sample index (every rounding step of
+    // make_tap is), so a bin's range is [lo of its first valid sample, hi of its last valid one]; only a bin whose end
+    // sample is off the map scans.
+    if (lane < 4 * kP) {
+      const int k = lane / kP, p = lane - k * kP;
+      const bool is_x = !(k & 1), from_end = k >= 2;
+      const float start = is_x ? g.start_w : g.start_h, bin = is_x ? g.bin_w : g.bin_h;
+      const int grid = is_x ? g.gw : g.gh, size = is_x ? W : H;
+      int v = from_end ? -1 : kMetaNone;
+      if (bin >= 0.f) {
+        for (int i = 0; i < grid; ++i) {
+          const Tap t = make_tap(start, bin, grid, p, from_end ? grid - 1 - i : i, size);
+          if (t.valid) {
+            v = from_end ? t.hi : t.lo;
+            break;
+          }
+        }
+      } else {   // inverted box with a fixed sampling ratio: coordinates decrease, every sample is looked at
+        for (int i = 0; i < grid; ++i) {
+          const Tap t = make_tap(start, bin, grid, p, i, size);
+          if (t.valid) v = from_end ? max(v, t.hi) : min(v, t.lo);
+        }
+      }
+      meta16[(is_x ? 0 : 14) + (from_end ? 7 : 0) + p] = (short)min(v, kMetaNone);
+    }
+    __syncwarp();
+    int x_lo = kMetaNone, x_hi = -1, yl = kMetaNone, y_hi = -1;
+#pragma unroll
+    for (int p = 0; p < kP; ++p) {
+      x_lo = min(x_lo, (int)meta16[p]);
+      x_hi = max(x_hi, (int)meta16[7 + p]);
+      yl = min(yl, (int)meta16[14 + p]);
+      y_hi = max(y_hi, (int)meta16[21 + p]);
+      ny_max = max(ny_max, (int)meta16[21 + p] - (int)meta16[14 + p] + 1);
+    }
+    if (x_hi < 0 || y_hi < 0) {
+      flags |= HF_EMPTY;   // every sample out of range: the reference's sum is empty
+    } else {
+      // ---- column tiling: the innermost TMA coordinate must be a multiple of 16 bytes (measured: anything else
+      // faults), so the footprint starts at the 4-float boundary at or below its first column
+      y_lo = yl;
+      x0 = x_lo & a.xalign_mask;
+      fw = x_hi - x0 + 1;
+      rows_total = y_hi - y_lo + 1;
+      // Row groups: a stage holds the pixel rows of G consecutive bin-rows (G = 7: the whole footprint; 4, 2, 1: tall
+      // footprints are walked group by group).  Pick the largest G -- and for it the tile width with the least padding,
+      // wider on ties -- whose stage fits the largest stage and leaves at least a.min_slots ring slots; if nothing gives
+      // that depth, the largest G that fits at all.
+      int best_pad = INT_MAX;
+      auto try_cfg = [&](int gcand, int need_slots) {
+        int rm = rows_total;
+        if (gcand != kP) {
+          rm = 0;
+          for (int hh = 0; hh * gcand < kP; ++hh) {
+            int lo = INT_MAX, hi = -1;
+            for (int p = hh * gcand; p < min(kP, (hh + 1) * gcand); ++p) {
+              if (meta16[21 + p] >= meta16[14 + p]) {
+                lo = min(lo, (int)meta16[14 + p]);
+                hi = max(hi, (int)meta16[21 + p]);
+              }
+            }
+            rm = max(rm, hi < lo ? 1 : hi - lo + 1);
+          }
+        }
+        int ws = -1, bp = INT_MAX;
+#pragma unroll
+        for (int k = kWidths - 1; k >= 0; --k) {
+          const int wt = 8 << k;
+          const int pad = (fw + wt - 1) / wt * wt;
+          const int stage = rm * wt * 32;
+          if (stage <= a.stage_floats && stage * need_slots <= a.ring_floats && pad < bp) {
+            bp = pad;
+            ws = k;
+          }
+        }
+        if (ws < 0) return false;
+        wsel = ws; best_pad = bp; G = gcand; rmax = rm;
+        return true;
+      };
+      const int gs[4] = {7, 4, 2, 1};
+      bool ok = false;
+#pragma unroll
+      for (int i = 0; i < 4 && !ok; ++i) ok = try_cfg(gs[i], a.min_slots);
+#pragma unroll
+      for (int i = 0; i < 4 && !ok; ++i) ok = try_cfg(gs[i], 1);
+      if (wsel < 0 || best_pad > kMaxW || ny_max > kMaxRows) direct = true;
+    }
+  }
+  __syncwarp();
+  if (lane == 0) {
+    if (direct) flags = HF_DIRECT;
+    h[H_BOX] = box; h[H_CHUNKS] = 0; h[H_LEVEL] = g.level; h[H_IMAGE] = image; h[H_FLAGS] = flags;
+    h[H_WSEL] = wsel; h[H_G] = G; h[H_RMAX] = rmax; h[H_X0] = x0; h[H_FW] = fw; h[H_YLO] = y_lo; h[H_ROWS] = rows_total;
+    h[H_GW] = g.level >= 0 ? g.gw : 0; h[H_GH] = g.level >= 0 ? g.gh : 0; h[H_NYMAX] = ny_max; h[H_PAD0] = 0;
+    h[H_START_W] = __float_as_int(g.level >= 0 ? g.start_w : 0.f); h[H_START_H] = __float_as_int(g.level >= 0 ? g.start_h : 0.f);
+    h[H_BIN_W] = __float_as_int(g.level >= 0 ? g.bin_w : 0.f); h[H_BIN_H] = __float_as_int(g.level >= 0 ? g.bin_h : 0.f);
+    h[H_COUNT] = __float_as_int(g.level >= 0 ? g.count : 1.f); h[H_COST] = __float_as_int(cost);
+    h[H_PAD1] = 0; h[H_PAD2] = 0;
+  }
+  __syncwarp();
+}
+
+// First kernel of the lift: one warp per box, 32 boxes per CTA, spread over the SMs.  Writes the per-box headers
+// (hdr [n][kHdrInts]) and the level of every box.
+__global__ void __launch_bounds__(1024) roi_plan_kernel(const RoiArgs a, int* __restrict__ hdr) {
+  __shared__ __align__(16) int h[32][kHdrInts];
+  // Everything the caller's stream did before the call is complete and visible once this wait returns, and the trigger
+  // comes after it -- so no later kernel of the chain can start before that point, and they may read the call's inputs
+  // (boxes, classes, cameras, weights) ahead of their own wait.  It also covers the workspace, which the ROIAlign
+  // kernel of the previous call may still be reading.
+  pdl_wait();
+  pdl_trigger();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int box = blockIdx.x * 32 + warp;
+  if (box >= a.n) return;
+  const float x1 = a.boxes[4 * box + 0], y1 = a.boxes[4 * box + 1], x2 = a.boxes[4 * box + 2], y2 = a.boxes[4 * box + 3];
+  const int image = a.batch_idx[box];
+  plan_box_warp(a, x1, y1, x2, y2, image, box, lane, h[warp]);
+  if (lane < kHdrInts / 4)
+    reinterpret_cast<int4*>(hdr + (size_t)box * kHdrInts)[lane] = reinterpret_cast<const int4*>(h[warp])[lane];
+  if (lane == 0 && a.level_out) a.level_out[box] = h[warp][H_LEVEL];
+}
+
+// Work items for a grid of CTAs with very different run times.  One CTA turns the planned boxes into items
+// (header, first chunk, chunks) so that no item is much more expensive than the average box -- a box whose footprint
 // is k times the mean is cut into up to k pieces along the channel chunks (otherwise the largest box alone, walked
 // by one CTA, sets the kernel time: measured 89 us for a 34 x 34 pixel footprint) -- and orders the items by
 // cost, largest first, with a counting sort in shared memory.  ws layout: [0] item count, [1..7] unused, then
-// 8 int32 per item: box, first chunk | chunks << 16, x1, y1, x2, y2 (fp32 bits), image, 0.   At most max(3, splits) * n items (see roi_align_launch).
-__global__ void __launch_bounds__(1024) roi_order_kernel(const RoiArgs a, int* __restrict__ ws) {
+// 2 int32 per item: box, first chunk | chunks << 16.
+// At most max(3, splits) * n items (see roi_align_launch).
+__global__ void __launch_bounds__(1024) roi_order_kernel(const RoiArgs a, int* __restrict__ ws, const int* __restrict__ hdr) {
   // one histogram per warp ([bucket][warp], rows padded to 33 words): boxes crowd into a few cost buckets, and a
   // single shared histogram serialised ~n atomics on the same word, twice
   __shared__ int hist[64 * 33];
@@ -369,43 +528,19 @@ __global__ void __launch_bounds__(1024) roi_order_kernel(const RoiArgs a, int* _
   __shared__ float warp_sum[32];
   __shared__ float mean_area;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  // First kernel of the lift: everything the caller's stream did before the call is complete and visible once this
-  // wait returns, and the trigger comes after it -- so no later kernel of the chain can start before that point, and
-  // they may read the call's inputs (boxes, classes, cameras, weights) ahead of their own wait.  It also covers ws,
-  // which the ROIAlign kernel of the previous call may still be reading.
-  pdl_wait();
   pdl_trigger();
   for (int i = tid; i < 64 * 33; i += 1024) hist[i] = 0;
-  auto area_of = [&](const float4 b) {
-    const BoxGeom g = box_geometry_xy(a, b.x, b.y, b.z, b.w, 0);
-    if (g.level < 0) return 1.f;
-    const RoiLevel lv = a.lv[g.level];
-    // pixel rows x columns of the footprint, clipped to the map
-    const float w = fminf(fmaxf(g.bin_w * (float)a.P, 0.f), (float)lv.W) + 2.f;
-    const float h = fminf(fmaxf(g.bin_h * (float)a.P, 0.f), (float)lv.H) + 2.f;
-    const float area = w * h;
-    return (area == area) ? area : 1.f;
-  };
-  auto load_box = [&](int box) {
-    return make_float4(a.boxes[4 * box + 0], a.boxes[4 * box + 1], a.boxes[4 * box + 2], a.boxes[4 * box + 3]);
-  };
-  constexpr int kKeep = 4;   // the first 4096 boxes (and their areas) stay in registers between the passes
-  float4 bx[kKeep];
-  int img[kKeep];
+  pdl_wait();      // the per-box headers come from roi_plan_kernel
+  auto cost_of = [&](int box) { return __int_as_float(hdr[(size_t)box * kHdrInts + H_COST]); };
+  constexpr int kKeep = 4;   // the costs of the first 4096 boxes stay in registers between the passes
   float areas[kKeep];
   float sum = 0.f;
 #pragma unroll
-  for (int k = 0; k < kKeep; ++k) {   // all loads of the pass in flight together (cold: they come from DRAM)
-    const int box = tid + k * 1024;
-    bx[k] = box < a.n ? load_box(box) : make_float4(0.f, 0.f, 0.f, 0.f);
-    img[k] = box < a.n ? a.batch_idx[box] : 0;
-  }
-#pragma unroll
   for (int k = 0; k < kKeep; ++k) {
-    areas[k] = tid + k * 1024 < a.n ? area_of(bx[k]) : 0.f;
+    areas[k] = tid + k * 1024 < a.n ? cost_of(tid + k * 1024) : 0.f;
     sum += areas[k];
   }
-  for (int box = tid + kKeep * 1024; box < a.n; box += 1024) sum += area_of(load_box(box));
+  for (int box = tid + kKeep * 1024; box < a.n; box += 1024) sum += cost_of(box);
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
   if (lane == 0) warp_sum[warp] = sum;
@@ -440,7 +575,7 @@ __global__ void __launch_bounds__(1024) roi_order_kernel(const RoiArgs a, int* _
     }
   }
   for (int box = tid + kKeep * 1024; box < a.n; box += 1024) {
-    const float ar = area_of(load_box(box));
+    const float ar = cost_of(box);
     const int cpi = cpi_of(ar);
     atomicAdd(&hist[slot_of(ar, cpi)], (chunks + cpi - 1) / cpi);
   }
@@ -477,24 +612,19 @@ __global__ void __launch_bounds__(1024) roi_order_kernel(const RoiArgs a, int* _
     hist[i1] = before + h0;
   }
   __syncthreads();
-  auto emit = [&](int box, const float4 b, int image, float ar) {
+  // an item = (box, first chunk | chunks << 16): the pooling CTA reads it, then the box's header (roi_plan_kernel).
+  // (Copying the 160-byte header into every item made this one CTA move 0.6 MB: 28 us instead of 13 for the stage.)
+  auto emit = [&](int box, float ar) {
     const int cpi = cpi_of(ar);
     const int pieces = (chunks + cpi - 1) / cpi;
     const int at = atomicAdd(&hist[slot_of(ar, cpi)], pieces);
-    for (int j = 0; j < pieces; ++j) {
-      // 32-byte item: box, first chunk | chunks << 16, the box itself and its image -- the pooling CTA needs one load
-      int4* it = reinterpret_cast<int4*>(ws + 8 + 8 * (at + j));
-      it[0] = make_int4(box, (j * cpi) | (min(cpi, chunks - j * cpi) << 16), __float_as_int(b.x), __float_as_int(b.y));
-      it[1] = make_int4(__float_as_int(b.z), __float_as_int(b.w), image, 0);
-    }
+    for (int j = 0; j < pieces; ++j)
+      reinterpret_cast<int2*>(ws + 8)[at + j] = make_int2(box, (j * cpi) | (min(cpi, chunks - j * cpi) << 16));
   };
 #pragma unroll
   for (int k = 0; k < kKeep; ++k)
-    if (tid + k * 1024 < a.n) emit(tid + k * 1024, bx[k], img[k], areas[k]);
-  for (int box = tid + kKeep * 1024; box < a.n; box += 1024) {
-    const float4 b = load_box(box);
-    emit(box, b, a.batch_idx[box], area_of(b));
-  }
+    if (tid + k * 1024 < a.n) emit(tid + k * 1024, areas[k]);
+  for (int box = tid + kKeep * 1024; box < a.n; box += 1024) emit(box, cost_of(box));
 }
 
 // meta layout (ints): [0..6] x bin lo, [7..13] x bin hi, [14..20] y bin lo, [21..27] y bin hi (lo > hi: no valid sample)
@@ -513,68 +643,13 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) roi_align_kernel(const _
   int* meta = reinterpret_cast<int*>(Wy + kWyFloats);
   const uint32_t bars = smem_u32(meta + kMetaInts);                  // full[kStages], empty[kStages]
 
-  pdl_trigger();
-  pdl_wait();      // the work items come from roi_order_kernel
-  int box, chunk_begin, chunk_end, bb = 0;
-  float bx1 = 0.f, by1 = 0.f, bx2 = 0.f, by2 = 0.f;
-  if (a.order) {   // work items of roi_order_kernel; the grid is an upper bound of their number
-    const int count = a.order[0];                       // the two loads are independent: one round trip
-    const int4* itp = reinterpret_cast<const int4*>(a.order + 8 + 8 * blockIdx.x);
-    const int4 i0 = itp[0], i1 = itp[1];
-    if ((int)blockIdx.x >= count) return;
-    box = i0.x;
-    chunk_begin = i0.y & 0xffff;
-    chunk_end = chunk_begin + (i0.y >> 16);
-    bx1 = __int_as_float(i0.z); by1 = __int_as_float(i0.w);
-    bx2 = __int_as_float(i1.x); by2 = __int_as_float(i1.y);
-    bb = i1.z;
-  } else {
-    box = (int)(blockIdx.x / a.splits);
-    chunk_begin = (int)(blockIdx.x % a.splits) * a.chunks_per_split;
-    chunk_end = min((a.C + 31) / 32, chunk_begin + a.chunks_per_split);
-  }
+  int* hdr = meta + 32;                                              // kHdrInts ints, 16-byte aligned
+  const short* meta16 = reinterpret_cast<const short*>(hdr + H_META);
+  auto mt = [&](int i) { return (int)meta16[i]; };                   // bin ranges (see the layout comment above)
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int c_begin = chunk_begin * 32;
-  const int c_end = min(a.C, chunk_end * 32);
 
-  if (tid == 0) trace_stamp(a, 0);
-  const BoxGeom g = a.order ? box_geometry_xy(a, bx1, by1, bx2, by2, bb) : box_geometry(a, box);
-  if (chunk_begin == 0 && tid == 0 && a.level_out) a.level_out[box] = g.level;
-
-  bool direct = (a.P != kP) || g.level < 0 || g.gw <= 0 || g.gh <= 0;
-  if (!direct) direct = !a.tma_ok[g.level];
-  if (direct) {  // block-uniform
-    direct_path(a, g, box, c_begin, c_end);
-    return;
-  }
-  const RoiLevel lv = a.lv[g.level];
-  const int H = lv.H, W = lv.W;
-
-  // ---- pass A: pixel range of every bin.  The sample coordinate is monotone in the sample index (every rounding
-  // step of make_tap is), so a bin's range is [lo of its first valid sample, hi of its last valid one]: warps 0/1
-  // take the first sample of the x / y bins, warps 2/3 the last; only a bin whose end sample is off the map scans.
-  if (lane < kP && warp < 4) {
-    const bool is_x = !(warp & 1), from_end = warp >= 2;
-    const float start = is_x ? g.start_w : g.start_h, bin = is_x ? g.bin_w : g.bin_h;
-    const int grid = is_x ? g.gw : g.gh, size = is_x ? W : H;
-    int v = from_end ? -1 : INT_MAX;
-    if (bin >= 0.f) {
-      for (int k = 0; k < grid; ++k) {
-        const Tap t = make_tap(start, bin, grid, lane, from_end ? grid - 1 - k : k, size);
-        if (t.valid) {
-          v = from_end ? t.hi : t.lo;
-          break;
-        }
-      }
-    } else {   // inverted box with a fixed sampling ratio: coordinates decrease, every sample is looked at
-      for (int i = 0; i < grid; ++i) {
-        const Tap t = make_tap(start, bin, grid, lane, i, size);
-        if (t.valid) v = from_end ? max(v, t.hi) : min(v, t.lo);
-      }
-    }
-    meta[(is_x ? 0 : 14) + (from_end ? 7 : 0) + lane] = v;
-  }
-  // the tap tables are cleared here, by everybody, while the 14 range threads above are still busy
+  pdl_trigger();
+  // shared-memory set-up that depends on nothing: the tap tables are cleared, the ring's barriers initialised
   for (int i = tid; i < (kWxFloats + kWyFloats) / 4; i += kThreads)
     reinterpret_cast<float4*>(Wx)[i] = make_float4(0.f, 0.f, 0.f, 0.f);   // Wy follows Wx
   if (tid == 0) {
@@ -584,90 +659,74 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) roi_align_kernel(const _
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
+  pdl_wait();      // the work items come from roi_order_kernel
+  if (tid == 0) trace_stamp(a, 0);
+  if (a.order) {   // work items of roi_order_kernel; the grid is an upper bound of their number
+    if ((int)blockIdx.x >= a.order[0]) return;
+    if (tid < kHdrInts / 4) {
+      const int2 item = reinterpret_cast<const int2*>(a.order + 8)[blockIdx.x];
+      int4 v = reinterpret_cast<const int4*>(a.box_hdr + (size_t)kHdrInts * item.x)[tid];
+      if (tid == 0) v.y = item.y;      // H_CHUNKS
+      reinterpret_cast<int4*>(hdr)[tid] = v;
+    }
+  } else if (warp == 0) {   // no planner: one CTA per (box, split) in input order, its first warp plans the box
+    const int bx = (int)(blockIdx.x / a.splits);
+    plan_box_warp(a, a.boxes[4 * bx + 0], a.boxes[4 * bx + 1], a.boxes[4 * bx + 2], a.boxes[4 * bx + 3], a.batch_idx[bx], bx,
+                  lane, hdr);
+    if (lane == 0) {
+      const int cb = (int)(blockIdx.x % a.splits) * a.chunks_per_split;
+      hdr[H_CHUNKS] = cb | ((min((a.C + 31) / 32, cb + a.chunks_per_split) - cb) << 16);
+      if (cb == 0 && a.level_out) a.level_out[bx] = hdr[H_LEVEL];
+    }
+  }
   __syncthreads();
   if (tid == 0) trace_stamp(a, 1);
-  int x_lo = INT_MAX, x_hi = -1, y_lo = INT_MAX, y_hi = -1, ny_max = 0;
-#pragma unroll
-  for (int p = 0; p < kP; ++p) {
-    x_lo = min(x_lo, meta[p]);
-    x_hi = max(x_hi, meta[7 + p]);
-    y_lo = min(y_lo, meta[14 + p]);
-    y_hi = max(y_hi, meta[21 + p]);
-    ny_max = max(ny_max, meta[21 + p] - meta[14 + p] + 1);
-  }
+  const int box = hdr[H_BOX];
+  const int chunk_begin = hdr[H_CHUNKS] & 0xffff, chunk_end = chunk_begin + (hdr[H_CHUNKS] >> 16);
+  const int c_begin = chunk_begin * 32;
+  const int c_end = min(a.C, chunk_end * 32);
+  BoxGeom g;
+  g.level = hdr[H_LEVEL];
+  g.b = hdr[H_IMAGE];
+  g.start_w = __int_as_float(hdr[H_START_W]); g.start_h = __int_as_float(hdr[H_START_H]);
+  g.bin_w = __int_as_float(hdr[H_BIN_W]); g.bin_h = __int_as_float(hdr[H_BIN_H]);
+  g.gw = hdr[H_GW]; g.gh = hdr[H_GH];
+  g.count = __int_as_float(hdr[H_COUNT]);
+  const int flags = hdr[H_FLAGS];
   const long long out_row = (long long)box * a.out_ld;
-  if (x_hi < 0 || y_hi < 0) {  // every sample out of range: the reference's sum is empty
+  if (flags & HF_DIRECT) {  // block-uniform: what TMA cannot address or a stage cannot hold
+    direct_path(a, g, box, c_begin, c_end);
+    return;
+  }
+  if (flags & HF_EMPTY) {   // every sample out of range: the reference's sum is empty
     for (int o = tid; o < (c_end - c_begin) * kP * kP; o += kThreads)
       store_out(a, out_row + (long long)c_begin * kP * kP + o, 0.f);
     return;
   }
-  // ---- column tiling: the tile width with the least padding that lets all footprint rows sit in one stage
-  // the innermost TMA coordinate must be a multiple of 16 bytes (measured: anything else faults), so the footprint
-  // starts at the 4-float boundary at or below its first column
-  const int x0 = x_lo & a.xalign_mask;
-  const int fw = x_hi - x0 + 1, rows_total = y_hi - y_lo + 1;
-  // Row groups: a stage holds the pixel rows of G consecutive bin-rows (G = 7: the whole footprint; 4, 2, 1: tall
-  // footprints are walked group by group, each consumer warp working only in its own group's stages).  Pick the
-  // largest G -- and for it the tile width with the least padding, wider on ties -- whose stage fits kStageFloats and
-  // leaves at least a.min_slots ring slots; if nothing gives that depth, the largest G that fits at all.
-  auto group_span = [&](int G, int h, int& gy, int& rows) {   // pixel rows of group h (one dummy row if it has no sample)
-    if (G == kP) {   // the common case: the whole footprint in one stage
+  const RoiLevel lv = a.lv[g.level];
+  const int H = lv.H, W = lv.W;
+  const int wsel = hdr[H_WSEL], G = hdr[H_G], rmax = hdr[H_RMAX];
+  const int x0 = hdr[H_X0], fw = hdr[H_FW], y_lo = hdr[H_YLO], rows_total = hdr[H_ROWS];
+  auto group_span = [&](int Gs, int h, int& gy, int& rows) {   // pixel rows of group h (one dummy row if it has no sample)
+    if (Gs == kP) {   // the common case: the whole footprint in one stage
       gy = y_lo;
       rows = rows_total;
       return;
     }
     int lo = INT_MAX, hi = -1;
-    for (int p = h * G; p < min(kP, (h + 1) * G); ++p) {
-      if (meta[21 + p] >= meta[14 + p]) {
-        lo = min(lo, meta[14 + p]);
-        hi = max(hi, meta[21 + p]);
+    for (int p = h * Gs; p < min(kP, (h + 1) * Gs); ++p) {
+      if (mt(21 + p) >= mt(14 + p)) {
+        lo = min(lo, mt(14 + p));
+        hi = max(hi, mt(21 + p));
       }
     }
     if (hi < lo) lo = hi = y_lo;
     gy = lo;
     rows = hi - lo + 1;
   };
-  int wsel = -1, best_pad = INT_MAX, G = kP, rmax = rows_total;
-  auto try_cfg = [&](int g, int need_slots) {
-    int rm = rows_total;
-    if (g != kP) {
-      rm = 0;
-      for (int h = 0; h * g < kP; ++h) {
-        int gy, rows;
-        group_span(g, h, gy, rows);
-        rm = max(rm, rows);
-      }
-    }
-    int ws = -1, bp = INT_MAX;
-#pragma unroll
-    for (int k = kWidths - 1; k >= 0; --k) {
-      const int wt = 8 << k;
-      const int pad = (fw + wt - 1) / wt * wt;
-      const int stage = rm * wt * 32;
-      if (stage <= kStageFloats && stage * need_slots <= kRingFloats && pad < bp) {
-        bp = pad;
-        ws = k;
-      }
-    }
-    if (ws < 0) return false;
-    wsel = ws; best_pad = bp; G = g; rmax = rm;
-    return true;
-  };
-  {
-    const int gs[4] = {7, 4, 2, 1};
-    bool ok = false;
-#pragma unroll
-    for (int i = 0; i < 4 && !ok; ++i) ok = try_cfg(gs[i], a.min_slots);
-#pragma unroll
-    for (int i = 0; i < 4 && !ok; ++i) ok = try_cfg(gs[i], 1);
-  }
-  if (wsel < 0 || best_pad > kMaxW || ny_max > kMaxRows) {
-    direct_path(a, g, box, c_begin, c_end);
-    return;
-  }
   const int ngroups = (kP + G - 1) / G;
   const int Wt = 8 << wsel;
-  const int ntiles = best_pad / Wt;
+  const int ntiles = ((fw + Wt - 1) / Wt * Wt) / Wt;
   const int slab_floats = 32 * Wt;               // one footprint row of one chunk: [32 channels][Wt]
   // The ring is cut into slots of this box's stage size: small footprints get up to kMaxSlots stages in flight.
   const int slot_floats = rmax * slab_floats;
@@ -726,7 +785,7 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) roi_align_kernel(const _
     const bool is_x = warp == 0;
     const float start = is_x ? g.start_w : g.start_h, bin = is_x ? g.bin_w : g.bin_h;
     const int grid = is_x ? g.gw : g.gh, size = is_x ? W : H;
-    const int y_first = meta[14 + lane];
+    const int y_first = mt(14 + lane);
     for (int i = 0; i < grid; ++i) {
       Tap t = make_tap(start, bin, grid, lane, i, size);
       if (!t.valid) continue;
@@ -755,8 +814,8 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) roi_align_kernel(const _
   const int my_grp = ph / G;
   int my_gy, my_rows;
   group_span(G, my_grp, my_gy, my_rows);
-  const int ys = meta[14 + ph];
-  const int ny = meta[21 + ph] - ys + 1;          // <= 0: bin-row has no valid sample
+  const int ys = mt(14 + ph);
+  const int ny = mt(21 + ph) - ys + 1;          // <= 0: bin-row has no valid sample
   const float* wy = Wy + ph * kMaxRows;
   const float inv_count = 1.f / g.count;
   // 16-byte unit j of lane c's row sits at unit j ^ sw (the TMA swizzle of the slab, see the header comment)
@@ -995,9 +1054,12 @@ int roi_align_launch(const ovm_pooler_t* p, const float* boxes, const int32_t* b
   a.split_factor = 0.01f * (float)(tune.split_pct < 100 ? 100 : tune.split_pct);   // < 1 would break the item bound
   // with work items: a box yields at most max(splits, 2 area / (split_factor mean area)) of them
   const long long nitems = (long long)n * a.splits + (a.order ? (long long)(2.0 * n / a.split_factor) + 8 : 0);
-  OVM_REQUIRE(!a.order || (8 + 8 * nitems <= (long long)p->order_ws_len && !(reinterpret_cast<uintptr_t>(a.order) & 15)),
+  // workspace: [0] item count, [1..7] unused, nitems 8-byte work items, then the n per-box headers
+  const long long ws_items = (8 + 2 * nitems + 3) / 4 * 4;       // count + 8-byte items, rounded to 16 bytes
+  const long long ws_need = ws_items + (long long)kHdrInts * n;
+  OVM_REQUIRE(!a.order || (ws_need <= (long long)p->order_ws_len && !(reinterpret_cast<uintptr_t>(a.order) & 15)),
               "ovm_roi_align: order_ws holds %d int32, %lld needed (OVM_ORDER_WS_LEN), 16-byte aligned", p->order_ws_len,
-              8 + 8 * nitems);
+              ws_need);
   a.xalign_mask = tune.align8 ? ~7 : ~3;
   a.evict_first = tune.evict;
   static SmemOptIn optA, optB;
@@ -1007,8 +1069,14 @@ int roi_align_launch(const ovm_pooler_t* p, const float* boxes, const int32_t* b
     int rc = tune.stages == 3 ? optB.ensure(kB, roi_smem_bytes(9216)) : optA.ensure(kA, roi_smem_bytes(12288));
     if (rc != OVM_OK) return rc;
   }
+  a.ring_floats = tune.stages == 3 ? 9216 : 12288;
+  a.stage_floats = tune.stages == 3 ? 4608 : 6144;
   if (a.order) {
-    OVM_CUDA(launch_pdl(roi_order_kernel, dim3(1), dim3(1024), 0, stream, a, p->order_ws));
+    int* box_hdr = p->order_ws + ws_items;
+    a.box_hdr = box_hdr;
+    OVM_CUDA(launch_pdl(roi_plan_kernel, dim3((unsigned)((n + 31) / 32)), dim3(1024), 0, stream, a, box_hdr));
+    OVM_LAUNCHED("roi_plan_kernel");
+    OVM_CUDA(launch_pdl(roi_order_kernel, dim3(1), dim3(1024), 0, stream, a, p->order_ws, static_cast<const int*>(box_hdr)));
     OVM_LAUNCHED("roi_order_kernel");
   }
   if (stage_idx) {

@@ -205,10 +205,12 @@ class LiftEngine:
     # ------------------------------------------------------------------ forward
     def forward(self, features: Sequence[torch.Tensor], boxes: torch.Tensor, classes: torch.Tensor,
                 scores: Optional[torch.Tensor], batch_idx: torch.Tensor, cams: torch.Tensor,
-                want_raw: bool = False, out: Optional[torch.Tensor] = None
-                ) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+                want_raw: bool = False, out: Optional[torch.Tensor] = None,
+                peer_ptrs: Optional[Sequence[int]] = None) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
         """-> (records [n, 48] fp32, raw [n, 16] or None).  `prepare` must have been called.  `out` (optional,
-        contiguous fp32 [n, 48] on the same device) receives the records instead of a fresh tensor."""
+        contiguous fp32 [n, 48] on the same device) receives the records instead of a fresh tensor.  `peer_ptrs`
+        (optional): device-visible addresses of other ranks' gather slots for THIS call's records (shard.RecordExchange);
+        the decode stores every record there as well (`ovm_lift_forward_peers`)."""
         lib = ops.load_library()
         n = boxes.shape[0]
         device = boxes.device
@@ -248,9 +250,18 @@ class LiftEngine:
         ops._need_cuda(cams, "cams", torch.float32)
         if scores is not None:
             ops._need_cuda(scores, "scores", torch.float32)
-        rc = lib.ovm_lift_forward(C.byref(pooler), C.byref(self._fc_stack), C.byref(self._cfg), C.byref(self._heads),
-                                  boxes.data_ptr(), classes.data_ptr(), ops._ptr(scores), batch_idx.data_ptr(),
-                                  cams.data_ptr(), n, C.byref(ws), records.data_ptr(), ops._ptr(raw), ops._stream())
+        if peer_ptrs:
+            if len(peer_ptrs) > ops.OVM_MAX_PEERS:
+                raise ops.LiftError("at most %d peers" % ops.OVM_MAX_PEERS)
+            peers = ops.ovm_peer_records_t(len(peer_ptrs), 0, (C.c_void_p * ops.OVM_MAX_PEERS)(*peer_ptrs))
+            rc = lib.ovm_lift_forward_peers(C.byref(pooler), C.byref(self._fc_stack), C.byref(self._cfg),
+                                            C.byref(self._heads), boxes.data_ptr(), classes.data_ptr(), ops._ptr(scores),
+                                            batch_idx.data_ptr(), cams.data_ptr(), n, C.byref(ws), records.data_ptr(),
+                                            ops._ptr(raw), C.byref(peers), ops._stream())
+        else:
+            rc = lib.ovm_lift_forward(C.byref(pooler), C.byref(self._fc_stack), C.byref(self._cfg), C.byref(self._heads),
+                                      boxes.data_ptr(), classes.data_ptr(), ops._ptr(scores), batch_idx.data_ptr(),
+                                      cams.data_ptr(), n, C.byref(ws), records.data_ptr(), ops._ptr(raw), ops._stream())
         ops._check(rc, "ovm_lift_forward")
         del keep
         return records, raw

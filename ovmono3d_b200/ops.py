@@ -34,7 +34,7 @@ REC_CLASS = 46
 EXPORTS = ("ovm_abi_version", "ovm_last_error", "ovm_launch_count", "ovm_struct_size", "ovm_roi_align", "ovm_gemm_bf16",
            "ovm_bias_act", "ovm_cast_bf16", "ovm_head_decode", "ovm_lift_forward", "ovm_set_stage_events", "ovm_gemm_set_trace",
            "ovm_roi_set_trace", "ovm_head_set_trace", "ovm_nms", "ovm_gdino_post", "ovm_box_inference", "ovm_post_set_trace",
-           "ovm_fc_tail", "ovm_round_tf32", "ovm_iou_box3d")
+           "ovm_fc_tail", "ovm_round_tf32", "ovm_iou_box3d", "ovm_lift_forward_peers")
 NMS_MAX_SEGMENT = 4096
 SPLITK_SLOTS_LEN = 74 * 2 * 128 * 256      # OVM_SPLITK_SLOTS_LEN / OVM_SPLITK_FLAGS_LEN of the header
 SPLITK_FLAGS_LEN = 74 * 2 * 8
@@ -96,8 +96,15 @@ class ovm_box_inference_ws_t(C.Structure):
     _fields_ = [(k, C.c_void_p) for k in ("probs", "cand_boxes", "class_keep", "class_count", "image_stats")]
 
 
+OVM_MAX_PEERS = 8
+
+
+class ovm_peer_records_t(C.Structure):
+    _fields_ = [("num_peers", C.c_int32), ("_pad", C.c_int32), ("records", C.c_void_p * OVM_MAX_PEERS)]
+
+
 ABI_STRUCTS = (ovm_level_t, ovm_pooler_t, ovm_decode_cfg_t, ovm_head_weights_t, ovm_fc_layer_t, ovm_fc_stack_t,
-               ovm_workspace_t, ovm_box_inference_cfg_t, ovm_box_inference_ws_t)
+               ovm_workspace_t, ovm_box_inference_cfg_t, ovm_box_inference_ws_t, ovm_peer_records_t)
 _LIB: Optional[C.CDLL] = None
 LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libovmono3d_lift.so")
 
@@ -130,6 +137,9 @@ def load_library() -> C.CDLL:
     lib.ovm_lift_forward.argtypes = [C.POINTER(ovm_pooler_t), C.POINTER(ovm_fc_stack_t), C.POINTER(ovm_decode_cfg_t),
                                      C.POINTER(ovm_head_weights_t), vp, vp, vp, vp, vp, i32,
                                      C.POINTER(ovm_workspace_t), vp, vp, vp]
+    lib.ovm_lift_forward_peers.argtypes = [C.POINTER(ovm_pooler_t), C.POINTER(ovm_fc_stack_t), C.POINTER(ovm_decode_cfg_t),
+                                           C.POINTER(ovm_head_weights_t), vp, vp, vp, vp, vp, i32,
+                                           C.POINTER(ovm_workspace_t), vp, vp, C.POINTER(ovm_peer_records_t), vp]
     lib.ovm_fc_tail.argtypes = [vp, i64, i32, vp, i64, vp, i32, i32, C.POINTER(ovm_decode_cfg_t),
                                 C.POINTER(ovm_head_weights_t), vp, vp, vp, vp, vp, i32, i32, vp, vp, vp]
     lib.ovm_round_tf32.argtypes = [vp, i64, i32, i32, vp, i64, vp]
@@ -218,7 +228,7 @@ def round_tf32(x: torch.Tensor, ld_out: Optional[int] = None) -> torch.Tensor:
 
 def order_ws_len(n: int) -> int:
     """OVM_ORDER_WS_LEN(n) of include/ovmono3d_lift.h."""
-    return 24 * max(int(n), 1) + 4808
+    return 48 * max(int(n), 1) + 2048
 
 
 def make_pooler(features: Sequence[torch.Tensor], scales: Sequence[float], output_size: int, sampling_ratio: int,

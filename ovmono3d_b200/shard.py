@@ -81,6 +81,86 @@ def gather_records(records: torch.Tensor, image_index: Optional[torch.Tensor] = 
     return flat[:, :RECORD_WIDTH].contiguous(), counts, idx
 
 
+class RecordExchange:
+    """Fixed-capacity all-gather of detection records without a host round trip.
+
+    Every rank owns a block of `cap` rows x 48 floats; `local` is where its lift calls write (`out=` of
+    `LiftEngine.forward`, row by row as the batches come).  `finish(count)` completes the exchange and returns
+    (`blocks` [world, cap, 48], `counts` [world] int64 on the device) -- rows past `counts[r]` of block r are undefined.
+    No `.item()`, no zero-filled staging block, no compaction pass: `compact()` does that lazily where a consumer
+    wants one dense [n_total, 48] tensor.  Two transports:
+
+      * "nccl"  (and gloo for CPU tensors): ONE `all_gather_into_tensor` of the [cap, 48] blocks; the count rides in the
+        pad column (47) of the block's first row.
+      * "peer": no data collective at all.  The blocks live in symmetric memory (torch.distributed._symmetric_memory:
+        every rank's buffer is mapped into every other rank's address space over NVLink); `peer_ptrs(row)` gives
+        `LiftEngine.forward(peer_ptrs=...)` the addresses of this rank's slot in all the OTHER ranks' buffers, so the
+        decode epilogue stores each 192-byte record straight into its final place on every GPU while the lift is still
+        running (`ovm_lift_forward_peers`); `finish` is one barrier on the symmetric-memory signal pads.
+
+    The reference's exchange is `comm.gather` of pickled per-image lists over a Gloo side group, once per dataset
+    (cubercnn/evaluation/omni3d_evaluation.py:717-720)."""
+
+    def __init__(self, cap: int, device: torch.device, transport: str = "nccl", group: Optional[dist.ProcessGroup] = None):
+        self.cap, self.device, self.group = int(cap), torch.device(device), group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.transport = transport if self.world > 1 else "local"
+        self._hdl = None
+        if self.transport == "peer":
+            import torch.distributed._symmetric_memory as symm_mem
+
+            if self.device.type != "cuda":
+                raise ValueError("the peer transport needs CUDA tensors")
+            # rows: [world, cap + 1, 48]; the extra last row of every block carries that rank's count
+            self._buf = symm_mem.empty((self.world, self.cap + 1, RECORD_WIDTH), dtype=torch.float32, device=self.device)
+            self._hdl = symm_mem.rendezvous(self._buf, dist.group.WORLD if group is None else group)
+            self.blocks = self._buf[:, : self.cap]
+            self.local = self._buf[self.rank, : self.cap]
+            self._peer_views = [self._hdl.get_buffer(r, (self.world, self.cap + 1, RECORD_WIDTH), torch.float32)
+                                for r in range(self.world)]
+            self._slot_bytes = (self.cap + 1) * RECORD_WIDTH * 4
+        else:
+            self.blocks = torch.empty((self.world, self.cap, RECORD_WIDTH), dtype=torch.float32, device=self.device)
+            # the send block is the rank's own row of the result: no copy before the collective, none after
+            self.local = self.blocks[self.rank]
+
+    def peer_ptrs(self, row: int) -> Optional[List[int]]:
+        """Addresses (valid on this device) of row `row` of this rank's block in every other rank's buffer."""
+        if self.transport != "peer":
+            return None
+        off = self.rank * self._slot_bytes + row * RECORD_WIDTH * 4
+        return [int(p) + off for r, p in enumerate(self._hdl.buffer_ptrs) if r != self.rank]
+
+    def finish(self, count: int) -> Tuple[torch.Tensor, torch.Tensor]:
+        if count > self.cap:
+            raise ValueError("%d records exceed the exchange capacity %d" % (count, self.cap))
+        if self.transport == "local":
+            return self.blocks, torch.tensor([count], dtype=torch.int64, device=self.device)
+        if self.transport == "peer":
+            for r in range(self.world):      # 4-byte posted writes: this rank's count into every rank's buffer
+                self._peer_views[r][self.rank, self.cap, 0].fill_(float(count))
+            self._hdl.barrier(channel=0)     # every rank's records and counts have landed everywhere
+            counts = self._buf[:, self.cap, 0].to(torch.int64)
+            return self.blocks, counts
+        if self.cap:
+            self.local[0, RECORD_WIDTH - 1].fill_(float(count))     # the record's pad column carries the count
+        dist.all_gather_into_tensor(self.blocks.view(self.world * self.cap, RECORD_WIDTH), self.local, group=self.group)
+        counts = self.blocks[:, 0, RECORD_WIDTH - 1].to(torch.int64) if self.cap else torch.zeros(
+            self.world, dtype=torch.int64, device=self.device)
+        return self.blocks, counts
+
+    @staticmethod
+    def compact(blocks: torch.Tensor, counts: torch.Tensor) -> torch.Tensor:
+        """[world, cap, 48] + counts -> dense [n_total, 48] in rank order (this is where the host learns the sizes)."""
+        world, cap, _ = blocks.shape
+        keep = torch.arange(cap, device=blocks.device).unsqueeze(0) < counts.unsqueeze(1)
+        out = blocks[keep].clone()
+        if cap:     # the pad column is zero in every record; row 0 of a block carried the count on the nccl transport
+            out[:, RECORD_WIDTH - 1] = 0
+        return out
+
+
 def split_by_image(records: torch.Tensor, image_index: torch.Tensor, num_images: int) -> List[torch.Tensor]:
     """Per-image record lists in global image order (what the reference's evaluator consumes per image)."""
     order = torch.argsort(image_index, stable=True)

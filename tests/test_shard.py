@@ -74,3 +74,49 @@ def test_gather_records_single_process_is_identity():
     assert out is rec and counts.tolist() == [5] and idx is None
     with pytest.raises(ValueError):
         shard.gather_records(torch.zeros(3, 7))
+
+
+def _exchange_worker(rank, world, port, counts, cap, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        ex = shard.RecordExchange(cap, torch.device("cpu"), transport="nccl")     # "nccl" = the one-collective path (gloo here)
+        g = torch.Generator().manual_seed(100)
+        full = [torch.randn(c, shard.RECORD_WIDTH, generator=g) for c in counts]   # same on every rank
+        for f in full:
+            f[:, shard.RECORD_WIDTH - 1] = 0                                       # the pad column of a record is zero
+        ok = ex.peer_ptrs(0) is None and ex.local.shape == (cap, shard.RECORD_WIDTH)
+        ok = ok and ex.local.data_ptr() == ex.blocks[rank].data_ptr()              # written in place: no staging copy
+        ex.local[: counts[rank]] = full[rank]
+        blocks, cnt = ex.finish(counts[rank])
+        ok = ok and cnt.tolist() == list(counts) and blocks.shape == (world, cap, shard.RECORD_WIDTH)
+        dense = shard.RecordExchange.compact(blocks, cnt)
+        ok = ok and torch.equal(dense, torch.cat(full))
+        q.put((rank, bool(ok), cnt.tolist()))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("counts,cap", [((5, 3), 8), ((0, 4), 4), ((6, 6), 6)])
+def test_record_exchange_world_size_2_gloo(counts, cap):
+    world, port = 2, _free_port()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_exchange_worker, args=(r, world, port, counts, cap, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert all(ok for _, ok, _ in results), results
+
+
+def test_record_exchange_single_process():
+    ex = shard.RecordExchange(4, torch.device("cpu"))
+    ex.local[:3] = 1.0
+    blocks, cnt = ex.finish(3)
+    assert cnt.tolist() == [3] and shard.RecordExchange.compact(blocks, cnt).shape == (3, shard.RECORD_WIDTH)
+    with pytest.raises(ValueError):
+        ex.finish(5)
