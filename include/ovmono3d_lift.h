@@ -338,6 +338,18 @@ int ovm_box_inference(const ovm_box_inference_cfg_t* cfg, const float* logits, i
                       const ovm_box_inference_ws_t* ws, float* out_boxes, float* out_scores, int64_t* out_classes,
                       int32_t* out_index, float* out_scores_full, int32_t* out_count, void* stream);
 
+/* Detection records -> the rows of the reference's result file: d2 detector_postprocess as
+ * GeneralizedRCNN._postprocess runs it (cubercnn/modeling/meta_arch/rcnn3d.py:113-115: 2-D boxes scaled from the network
+ * resolution to the original image, clipped, empty ones dropped) and the XYXY -> XYWH conversion of
+ * Omni3DEvaluator.instances_to_coco_json (cubercnn/evaluation/omni3d_evaluation.py:1218-1219).
+ * records [n,48] (ovm_head_decode layout), offsets [N+1] int32 (records of image i are rows [offsets[i], offsets[i+1])),
+ * geom [N,4] fp32: scale_x = out_w / net_w and scale_y = out_h / net_h (computed in double, rounded to fp32, as torch
+ * does for a Python-float factor), out_w, out_h.  out [n,48] (must not alias records): the surviving rows of image i,
+ * in order, from row offsets[i]; columns 41..44 hold x, y, w, h in original-resolution pixels, the rest is copied.
+ * out_count [N] int32.  One CTA per image, one launch; bit-identical to the reference's fp32 arithmetic.         */
+int ovm_records_postprocess(const float* records, const int32_t* offsets, const float* geom, int32_t num_images,
+                            float* out, int32_t* out_count, void* stream);
+
 /* ---- evaluation side ---------------------------------------------------------------------- */
 
 /* Exact 3-D IoU of oriented cuboids: `box3d_overlap` of the reference's evaluator (cubercnn/evaluation/

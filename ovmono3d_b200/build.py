@@ -18,7 +18,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 BUILD = os.path.join(CSRC, "build")
 LIB_PATH = os.path.join(HERE, "libovmono3d_lift.so")
-SOURCES = ["roi_align.cu", "gemm_tcgen05.cu", "head_decode.cu", "fc_tail.cu", "detect_post.cu", "iou3d.cu", "lift_api.cu"]
+SOURCES = ["roi_align.cu", "gemm_tcgen05.cu", "head_decode.cu", "fc_tail.cu", "detect_post.cu", "iou3d.cu", "records.cu", "lift_api.cu"]
 HEADERS = [os.path.join(CSRC, "common.cuh"), os.path.join(CSRC, "decode_core.cuh"), os.path.join(os.path.dirname(HERE), "include", "ovmono3d_lift.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden", "--fmad=true"]

@@ -161,6 +161,9 @@ int box_inference_launch(const ovm_box_inference_cfg_t* cfg, const float* logits
                          const ovm_box_inference_ws_t* ws, float* out_boxes, float* out_scores, int64_t* out_classes,
                          int32_t* out_index, float* out_scores_full, int32_t* out_count, cudaStream_t stream);
 
+// records.cu
+int records_post_launch(const float* records, const int32_t* offsets, const float* geom, int32_t num_images, float* out,
+                        int32_t* out_count, cudaStream_t stream);
 // iou3d.cu
 int iou_box3d_launch(const float* boxes_dt, const float* boxes_gt, int32_t N, int32_t M, float eps_coplanar,
                      float eps_nonzero, float* iou, float* vol, int32_t* dt_flags, cudaStream_t stream);

@@ -101,7 +101,8 @@ __device__ __forceinline__ BoxIn load_box_in(const DecodeArgs& a, int box) {
 // (roi_heads.py:436-444; 0 when CLUSTER_BINS == 1).  Every calling thread computes everything; the record (and the
 // optional raw head outputs) are written only when `write` is set.
 __device__ __forceinline__ void decode_record(const DecodeArgs& a, const int box, const BoxIn& in, const int bin,
-                                              const float (&hv)[kMaxHeadRows], const bool write) {
+                                              const float (&hv)[kMaxHeadRows], const bool write,
+                                              const bool store_peers = true) {
   const ovm_decode_cfg_t& cfg = a.cfg;
   const bool per_class = cfg.dims_priors_enabled != 0;
   const int cls = in.valid ? in.cls : 0;
@@ -259,7 +260,7 @@ __device__ __forceinline__ void decode_record(const DecodeArgs& a, const int box
   float4* out = reinterpret_cast<float4*>(a.records + (long long)box * OVM_RECORD_WIDTH);
 #pragma unroll
   for (int i = 0; i < OVM_RECORD_WIDTH / 4; ++i) out[i] = make_float4(rec[4 * i], rec[4 * i + 1], rec[4 * i + 2], rec[4 * i + 3]);
-  for (int p = 0; p < a.num_peers; ++p) {   // the exchange: 192 bytes per box and peer, posted writes over NVLink
+  for (int p = 0; store_peers && p < a.num_peers; ++p) {   // the exchange: 192 bytes per box and peer, posted writes over NVLink
     float4* po = reinterpret_cast<float4*>(a.peer_records[p] + (long long)box * OVM_RECORD_WIDTH);
 #pragma unroll
     for (int i = 0; i < OVM_RECORD_WIDTH / 4; ++i) po[i] = make_float4(rec[4 * i], rec[4 * i + 1], rec[4 * i + 2], rec[4 * i + 3]);

@@ -364,7 +364,22 @@ fc_tail_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       for (int c = 0; c < 2 * cs; ++c) s += part[(c * kMaxHeadRows + k) * rpc + e];   // fixed order: deterministic
       hv[k] = s + hbias[k < nrows ? k : 0];
     }
-    decode_record(g.d, my_row, in, 0, hv, true);
+    decode_record(g.d, my_row, in, 0, hv, true, /*store_peers=*/false);
+  }
+  if (g.d.num_peers > 0) {
+    // fused gather: the CTA's records (contiguous rows) go to every peer rank with all threads, 16 bytes each, instead
+    // of 12 x peers dependent stores at the end of each decoding thread's chain
+    __syncthreads();          // the decoding threads' record stores are visible to the block
+    const int row0 = m_tile * kTM + rank * rpc;
+    const int rows = min(rpc, g.d.n - row0);
+    if (rows > 0) {
+      const int per_peer = rows * (OVM_RECORD_WIDTH / 4);
+      const float4* src = reinterpret_cast<const float4*>(g.d.records + (long long)row0 * OVM_RECORD_WIDTH);
+      for (int i = threadIdx.x; i < per_peer * g.d.num_peers; i += kTailThreads) {
+        const int p = i / per_peer, j = i - p * per_peer;
+        reinterpret_cast<float4*>(g.d.peer_records[p] + (long long)row0 * OVM_RECORD_WIDTH)[j] = src[j];
+      }
+    }
   }
   if (threadIdx.x == 64) tail_stamp(g, 7);
 }

@@ -300,6 +300,11 @@ int ovm_box_inference(const ovm_box_inference_cfg_t* cfg, const float* logits, i
                               out_index, out_scores_full, out_count, static_cast<cudaStream_t>(stream));
 }
 
+int ovm_records_postprocess(const float* records, const int32_t* offsets, const float* geom, int32_t num_images,
+                            float* out, int32_t* out_count, void* stream) {
+  return records_post_launch(records, offsets, geom, num_images, out, out_count, static_cast<cudaStream_t>(stream));
+}
+
 int ovm_iou_box3d(const float* boxes_dt, const float* boxes_gt, int32_t N, int32_t M, float eps_coplanar,
                   float eps_nonzero, float* iou, float* vol, int32_t* dt_flags, void* stream) {
   return iou_box3d_launch(boxes_dt, boxes_gt, N, M, eps_coplanar, eps_nonzero, iou, vol, dt_flags,

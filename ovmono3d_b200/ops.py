@@ -34,7 +34,8 @@ REC_CLASS = 46
 EXPORTS = ("ovm_abi_version", "ovm_last_error", "ovm_launch_count", "ovm_struct_size", "ovm_roi_align", "ovm_gemm_bf16",
            "ovm_bias_act", "ovm_cast_bf16", "ovm_head_decode", "ovm_lift_forward", "ovm_set_stage_events", "ovm_gemm_set_trace",
            "ovm_roi_set_trace", "ovm_head_set_trace", "ovm_nms", "ovm_gdino_post", "ovm_box_inference", "ovm_post_set_trace",
-           "ovm_fc_tail", "ovm_round_tf32", "ovm_iou_box3d", "ovm_lift_forward_peers")
+           "ovm_fc_tail", "ovm_round_tf32", "ovm_iou_box3d", "ovm_lift_forward_peers",
+           "ovm_records_postprocess")
 NMS_MAX_SEGMENT = 4096
 SPLITK_SLOTS_LEN = 74 * 2 * 128 * 256      # OVM_SPLITK_SLOTS_LEN / OVM_SPLITK_FLAGS_LEN of the header
 SPLITK_FLAGS_LEN = 74 * 2 * 8
@@ -144,6 +145,7 @@ def load_library() -> C.CDLL:
                                 C.POINTER(ovm_head_weights_t), vp, vp, vp, vp, vp, i32, i32, vp, vp, vp]
     lib.ovm_round_tf32.argtypes = [vp, i64, i32, i32, vp, i64, vp]
     lib.ovm_iou_box3d.argtypes = [vp, vp, i32, i32, C.c_float, C.c_float, vp, vp, vp, vp]
+    lib.ovm_records_postprocess.argtypes = [vp, vp, vp, i32, vp, vp, vp]
     lib.ovm_gemm_set_trace.argtypes = [vp]
     lib.ovm_roi_set_trace.argtypes = [vp]
     lib.ovm_head_set_trace.argtypes = [vp]
@@ -377,6 +379,25 @@ def fc_tail(cfg: "ovm_decode_cfg_t", heads: "ovm_head_weights_t", A: torch.Tenso
                            classes.data_ptr(), _ptr(scores), batch_idx.data_ptr(), cams.data_ptr(), cams.shape[0], n,
                            rec.data_ptr(), _ptr(raw), _stream()), "ovm_fc_tail")
     return rec, raw
+
+
+def records_postprocess(records: torch.Tensor, offsets: torch.Tensor, geom: torch.Tensor):
+    """`ovm_records_postprocess`: records [n,48], offsets [N+1] int32, geom [N,4] (scale_x, scale_y, out_w, out_h), all
+    CUDA -> (out [n,48] with image i's surviving rows compacted from offsets[i], XYWH boxes; count [N] int32)."""
+    lib = load_library()
+    _need_cuda(records, "records", torch.float32)
+    _need_cuda(offsets, "offsets", torch.int32)
+    _need_cuda(geom, "geom", torch.float32)
+    if records.dim() != 2 or records.shape[1] != RECORD_WIDTH or not records.is_contiguous():
+        raise LiftError("records must be a contiguous [n, %d] tensor" % RECORD_WIDTH)
+    N = offsets.numel() - 1
+    if geom.shape != (N, 4) or not geom.is_contiguous():
+        raise LiftError("geom must be a contiguous [N, 4] tensor")
+    out = torch.empty_like(records)
+    count = torch.zeros((max(N, 1),), dtype=torch.int32, device=records.device)
+    _check(lib.ovm_records_postprocess(_ptr(records), _ptr(offsets), _ptr(geom), N, _ptr(out), _ptr(count), _stream()),
+           "ovm_records_postprocess")
+    return out, count[:N]
 
 
 def iou_box3d(boxes_dt: torch.Tensor, boxes_gt: torch.Tensor, eps_coplanar: float = 1e-4, eps_nonzero: float = 1e-8,
