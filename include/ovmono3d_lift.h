@@ -83,11 +83,13 @@ typedef struct {
   int32_t canonical_level;       /* d2 default 4 */
   float scale_roi_boxes;         /* SCALE_ROI_BOXES; <= 0 disables (roi_heads.py:310-327) */
   int32_t order_ws_len;          /* int32 elements in order_ws; OVM_ORDER_WS_LEN(n) is enough for n boxes */
-  int32_t* order_ws;             /* optional device scratch (16-byte aligned): when given, two small launches ahead of the
-                                    pooling kernel plan every box once (level, sampling geometry, bin ranges, stage
-                                    geometry: a warp per box) and turn the boxes into work items (large footprints are
-                                    cut along the channels, largest item first) so that no single CTA sets the kernel
-                                    time; NULL = one CTA per box in input order, planning its box itself */
+  int32_t* order_ws;             /* optional device scratch (16-byte aligned), ZERO-FILLED by the caller once when it is
+                                    allocated (word 1 is a ticket counter that every call hands back cleared): when
+                                    given, one small launch ahead of the pooling kernel plans every box once (level,
+                                    sampling geometry, bin ranges, stage geometry: a warp per box, all SMs) and its last
+                                    CTA turns the boxes into work items (large footprints are cut along the channels,
+                                    largest item first) so that no single CTA sets the kernel time; NULL = one CTA per
+                                    box in input order, planning its box itself */
 } ovm_pooler_t;
 
 /* Multi-level ROIAlignV2.  boxes [n,4] xyxy fp32, batch_idx [n] int32 (image of each box), both
@@ -262,6 +264,10 @@ int ovm_lift_forward_peers(const ovm_pooler_t* pooler, const ovm_fc_stack_t* fc,
                            const float* scores, const int32_t* batch_idx, const float* cams, int32_t n,
                            const ovm_workspace_t* ws, float* records, float* raw, const ovm_peer_records_t* peers,
                            void* stream);
+
+/* Stores `value` to n <= OVM_MAX_PEERS device-visible addresses (host array of pointers) in one launch: how a rank
+ * announces its record count to every rank of the fused exchange (shard.RecordExchange, "peer" transport). */
+int ovm_peer_store_f32(float* const* ptrs, int32_t n, float value, void* stream);
 
 /* Measurement hook (bench.py): while set, ovm_lift_forward records events[0] before its first launch and the
  * next event after each stage -- ROIAlign, every FC layer in issue order (memset + split-K GEMM + bias/ReLU

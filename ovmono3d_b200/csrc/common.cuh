@@ -164,6 +164,7 @@ int box_inference_launch(const ovm_box_inference_cfg_t* cfg, const float* logits
 // records.cu
 int records_post_launch(const float* records, const int32_t* offsets, const float* geom, int32_t num_images, float* out,
                         int32_t* out_count, cudaStream_t stream);
+int peer_store_launch(float* const* ptrs, int32_t n, float value, cudaStream_t stream);
 // iou3d.cu
 int iou_box3d_launch(const float* boxes_dt, const float* boxes_gt, int32_t N, int32_t M, float eps_coplanar,
                      float eps_nonzero, float* iou, float* vol, int32_t* dt_flags, cudaStream_t stream);

@@ -305,6 +305,10 @@ int ovm_records_postprocess(const float* records, const int32_t* offsets, const 
   return records_post_launch(records, offsets, geom, num_images, out, out_count, static_cast<cudaStream_t>(stream));
 }
 
+int ovm_peer_store_f32(float* const* ptrs, int32_t n, float value, void* stream) {
+  return peer_store_launch(ptrs, n, value, static_cast<cudaStream_t>(stream));
+}
+
 int ovm_iou_box3d(const float* boxes_dt, const float* boxes_gt, int32_t N, int32_t M, float eps_coplanar,
                   float eps_nonzero, float* iou, float* vol, int32_t* dt_flags, void* stream) {
   return iou_box3d_launch(boxes_dt, boxes_gt, N, M, eps_coplanar, eps_nonzero, iou, vol, dt_flags,

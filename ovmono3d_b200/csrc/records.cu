@@ -72,7 +72,31 @@ records_post_kernel(const float* __restrict__ rec, const int* __restrict__ offse
   if (threadIdx.x == 0) out_count[img] = base;
 }
 
+// one value -> up to OVM_MAX_PEERS addresses (peer mappings): a rank announces its record count to every rank in one launch
+struct PeerPtrs {
+  float* p[OVM_MAX_PEERS];
+};
+__global__ void peer_store_kernel(const PeerPtrs ptrs, int n, float value) {
+  if ((int)threadIdx.x < n) {
+    *ptrs.p[threadIdx.x] = value;
+    __threadfence_system();
+  }
+}
+
 }  // namespace
+
+int peer_store_launch(float* const* ptrs, int32_t n, float value, cudaStream_t stream) {
+  OVM_REQUIRE(n >= 0 && n <= OVM_MAX_PEERS && (n == 0 || ptrs), "ovm_peer_store_f32: n=%d", n);
+  if (n == 0) return OVM_OK;
+  PeerPtrs pp{};
+  for (int i = 0; i < n; ++i) {
+    OVM_REQUIRE(ptrs[i] && !(reinterpret_cast<uintptr_t>(ptrs[i]) & 3), "ovm_peer_store_f32: bad pointer %d", i);
+    pp.p[i] = ptrs[i];
+  }
+  peer_store_kernel<<<1, 32, 0, stream>>>(pp, n, value);
+  OVM_LAUNCHED("peer_store_kernel");
+  return OVM_OK;
+}
 
 int records_post_launch(const float* records, const int32_t* offsets, const float* geom, int32_t num_images, float* out,
                         int32_t* out_count, cudaStream_t stream) {

@@ -268,10 +268,6 @@ __device__ __forceinline__ BoxGeom box_geometry_xy(const RoiArgs& a, float x1, f
   g.count = (float)max(g.gh * g.gw, 1);
   return g;
 }
-__device__ __forceinline__ BoxGeom box_geometry(const RoiArgs& a, int box) {
-  return box_geometry_xy(a, a.boxes[4 * box + 0], a.boxes[4 * box + 1], a.boxes[4 * box + 2], a.boxes[4 * box + 3],
-                         a.batch_idx[box]);
-}
 
 __device__ __forceinline__ void store_out(const RoiArgs& a, long long idx, float v) {
   if (a.out_bf16)
@@ -492,9 +488,11 @@ __device__ void plan_box_warp(const RoiArgs& a, float x1, float y1, float x2, fl
   __syncwarp();
 }
 
+__device__ void sort_items(const RoiArgs& a, int* __restrict__ ws, const int* hdr);
+
 // First kernel of the lift: one warp per box, 32 boxes per CTA, spread over the SMs.  Writes the per-box headers
-// (hdr [n][kHdrInts]) and the level of every box.
-__global__ void __launch_bounds__(1024) roi_plan_kernel(const RoiArgs a, int* __restrict__ hdr) {
+// (hdr [n][kHdrInts]) and the level of every box; the last CTA to finish then sorts the work items (sort_items).
+__global__ void __launch_bounds__(1024) roi_plan_kernel(const RoiArgs a, int* __restrict__ hdr, int* __restrict__ ws) {
   __shared__ __align__(16) int h[32][kHdrInts];
   // Everything the caller's stream did before the call is complete and visible once this wait returns, and the trigger
   // comes after it -- so no later kernel of the chain can start before that point, and they may read the call's inputs
@@ -504,13 +502,25 @@ __global__ void __launch_bounds__(1024) roi_plan_kernel(const RoiArgs a, int* __
   pdl_trigger();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int box = blockIdx.x * 32 + warp;
-  if (box >= a.n) return;
-  const float x1 = a.boxes[4 * box + 0], y1 = a.boxes[4 * box + 1], x2 = a.boxes[4 * box + 2], y2 = a.boxes[4 * box + 3];
-  const int image = a.batch_idx[box];
-  plan_box_warp(a, x1, y1, x2, y2, image, box, lane, h[warp]);
-  if (lane < kHdrInts / 4)
-    reinterpret_cast<int4*>(hdr + (size_t)box * kHdrInts)[lane] = reinterpret_cast<const int4*>(h[warp])[lane];
-  if (lane == 0 && a.level_out) a.level_out[box] = h[warp][H_LEVEL];
+  if (box < a.n) {
+    const float x1 = a.boxes[4 * box + 0], y1 = a.boxes[4 * box + 1], x2 = a.boxes[4 * box + 2], y2 = a.boxes[4 * box + 3];
+    const int image = a.batch_idx[box];
+    plan_box_warp(a, x1, y1, x2, y2, image, box, lane, h[warp]);
+    if (lane < kHdrInts / 4)
+      reinterpret_cast<int4*>(hdr + (size_t)box * kHdrInts)[lane] = reinterpret_cast<const int4*>(h[warp])[lane];
+    if (lane == 0 && a.level_out) a.level_out[box] = h[warp][H_LEVEL];
+  }
+  if (!ws) return;     // headers only
+  // ---- the last CTA to finish turns the planned boxes into the sorted work items (threadfence-reduction pattern; the
+  // ticket word ws[1] is zero between launches: the sorting CTA hands it back cleared)
+  __shared__ int last;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) last = atomicAdd(ws + 1, 1) == (int)gridDim.x - 1;
+  __syncthreads();
+  if (!last) return;
+  __threadfence();
+  sort_items(a, ws, hdr);
 }
 
 // Work items for a grid of CTAs with very different run times.  One CTA turns the planned boxes into items
@@ -520,7 +530,7 @@ __global__ void __launch_bounds__(1024) roi_plan_kernel(const RoiArgs a, int* __
 // cost, largest first, with a counting sort in shared memory.  ws layout: [0] item count, [1..7] unused, then
 // 2 int32 per item: box, first chunk | chunks << 16.
 // At most max(3, splits) * n items (see roi_align_launch).
-__global__ void __launch_bounds__(1024) roi_order_kernel(const RoiArgs a, int* __restrict__ ws, const int* __restrict__ hdr) {
+__device__ void sort_items(const RoiArgs& a, int* __restrict__ ws, const int* hdr) {
   // one histogram per warp ([bucket][warp], rows padded to 33 words): boxes crowd into a few cost buckets, and a
   // single shared histogram serialised ~n atomics on the same word, twice
   __shared__ int hist[64 * 33];
@@ -528,10 +538,10 @@ __global__ void __launch_bounds__(1024) roi_order_kernel(const RoiArgs a, int* _
   __shared__ float warp_sum[32];
   __shared__ float mean_area;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  pdl_trigger();
   for (int i = tid; i < 64 * 33; i += 1024) hist[i] = 0;
-  pdl_wait();      // the per-box headers come from roi_plan_kernel
-  auto cost_of = [&](int box) { return __int_as_float(hdr[(size_t)box * kHdrInts + H_COST]); };
+  __syncthreads();
+  // (other CTAs wrote the headers: L2 loads)
+  auto cost_of = [&](int box) { return __int_as_float(__ldcg(hdr + (size_t)box * kHdrInts + H_COST)); };
   constexpr int kKeep = 4;   // the costs of the first 4096 boxes stay in registers between the passes
   float areas[kKeep];
   float sum = 0.f;
@@ -1074,10 +1084,8 @@ int roi_align_launch(const ovm_pooler_t* p, const float* boxes, const int32_t* b
   if (a.order) {
     int* box_hdr = p->order_ws + ws_items;
     a.box_hdr = box_hdr;
-    OVM_CUDA(launch_pdl(roi_plan_kernel, dim3((unsigned)((n + 31) / 32)), dim3(1024), 0, stream, a, box_hdr));
+    OVM_CUDA(launch_pdl(roi_plan_kernel, dim3((unsigned)((n + 31) / 32)), dim3(1024), 0, stream, a, box_hdr, p->order_ws));
     OVM_LAUNCHED("roi_plan_kernel");
-    OVM_CUDA(launch_pdl(roi_order_kernel, dim3(1), dim3(1024), 0, stream, a, p->order_ws, static_cast<const int*>(box_hdr)));
-    OVM_LAUNCHED("roi_order_kernel");
   }
   if (stage_idx) {
     int rc = stage_mark(*stage_idx, stream);

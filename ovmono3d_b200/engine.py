@@ -190,7 +190,7 @@ class LiftEngine:
             levels=torch.empty((cap,), device=device, dtype=torch.int32),
             counters=torch.zeros((_round_up(cap, 128) // 128 * (_round_up(self.fc_dim, 256) // 256),), device=device,
                                  dtype=torch.int32),   # split-K tile counters: zero on entry / exit
-            order=torch.empty((ops.order_ws_len(cap),), device=device, dtype=torch.int32),
+            order=torch.zeros((ops.order_ws_len(cap),), device=device, dtype=torch.int32),   # zero once: ticket word
             # split-K exchange of the first FC layer: per-cluster partial tiles + their flags (zero between calls)
             slots=torch.empty((ops.SPLITK_SLOTS_LEN,), device=device, dtype=torch.float32),
             flags=torch.zeros((ops.SPLITK_FLAGS_LEN,), device=device, dtype=torch.int32),

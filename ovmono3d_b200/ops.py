@@ -35,7 +35,7 @@ EXPORTS = ("ovm_abi_version", "ovm_last_error", "ovm_launch_count", "ovm_struct_
            "ovm_bias_act", "ovm_cast_bf16", "ovm_head_decode", "ovm_lift_forward", "ovm_set_stage_events", "ovm_gemm_set_trace",
            "ovm_roi_set_trace", "ovm_head_set_trace", "ovm_nms", "ovm_gdino_post", "ovm_box_inference", "ovm_post_set_trace",
            "ovm_fc_tail", "ovm_round_tf32", "ovm_iou_box3d", "ovm_lift_forward_peers",
-           "ovm_records_postprocess")
+           "ovm_records_postprocess", "ovm_peer_store_f32")
 NMS_MAX_SEGMENT = 4096
 SPLITK_SLOTS_LEN = 74 * 2 * 128 * 256      # OVM_SPLITK_SLOTS_LEN / OVM_SPLITK_FLAGS_LEN of the header
 SPLITK_FLAGS_LEN = 74 * 2 * 8
@@ -146,6 +146,7 @@ def load_library() -> C.CDLL:
     lib.ovm_round_tf32.argtypes = [vp, i64, i32, i32, vp, i64, vp]
     lib.ovm_iou_box3d.argtypes = [vp, vp, i32, i32, C.c_float, C.c_float, vp, vp, vp, vp]
     lib.ovm_records_postprocess.argtypes = [vp, vp, vp, i32, vp, vp, vp]
+    lib.ovm_peer_store_f32.argtypes = [C.POINTER(C.c_void_p), i32, C.c_float, vp]
     lib.ovm_gemm_set_trace.argtypes = [vp]
     lib.ovm_roi_set_trace.argtypes = [vp]
     lib.ovm_head_set_trace.argtypes = [vp]
@@ -279,7 +280,7 @@ def roi_align(features: Sequence[torch.Tensor], scales: Sequence[float], boxes: 
     Cc, P = pooler.channels, output_size
     out = torch.empty((n, Cc, P, P), device=boxes.device, dtype=out_dtype)
     levels = torch.empty((n,), device=boxes.device, dtype=torch.int32)
-    order = torch.empty((order_ws_len(n),), device=boxes.device, dtype=torch.int32)
+    order = torch.zeros((order_ws_len(n),), device=boxes.device, dtype=torch.int32)     # zero-filled once (ticket word)
     pooler.order_ws, pooler.order_ws_len = order.data_ptr(), order.numel()
     if n:
         _check(lib.ovm_roi_align(C.byref(pooler), boxes.data_ptr(), batch_idx.data_ptr(), n, out.data_ptr(),
@@ -381,6 +382,13 @@ def fc_tail(cfg: "ovm_decode_cfg_t", heads: "ovm_head_weights_t", A: torch.Tenso
     return rec, raw
 
 
+def peer_store_f32(ptrs: Sequence[int], value: float) -> None:
+    """`ovm_peer_store_f32`: one fp32 value to each of the (peer-mapped) addresses, one launch on the current stream."""
+    lib = load_library()
+    arr = (C.c_void_p * len(ptrs))(*ptrs)
+    _check(lib.ovm_peer_store_f32(arr, len(ptrs), float(value), _stream()), "ovm_peer_store_f32")
+
+
 def records_postprocess(records: torch.Tensor, offsets: torch.Tensor, geom: torch.Tensor):
     """`ovm_records_postprocess`: records [n,48], offsets [N+1] int32, geom [N,4] (scale_x, scale_y, out_w, out_h), all
     CUDA -> (out [n,48] with image i's surviving rows compacted from offsets[i], XYWH boxes; count [N] int32)."""
@@ -396,7 +404,7 @@ def records_postprocess(records: torch.Tensor, offsets: torch.Tensor, geom: torc
     out = torch.empty_like(records)
     count = torch.zeros((max(N, 1),), dtype=torch.int32, device=records.device)
     _check(lib.ovm_records_postprocess(_ptr(records), _ptr(offsets), _ptr(geom), N, _ptr(out), _ptr(count), _stream()),
-           "ovm_records_postprocess")
+           "ovm_records_postprocess", "ovm_peer_store_f32")
     return out, count[:N]
 
 

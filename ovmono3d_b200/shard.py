@@ -117,9 +117,9 @@ class RecordExchange:
             self._hdl = symm_mem.rendezvous(self._buf, dist.group.WORLD if group is None else group)
             self.blocks = self._buf[:, : self.cap]
             self.local = self._buf[self.rank, : self.cap]
-            self._peer_views = [self._hdl.get_buffer(r, (self.world, self.cap + 1, RECORD_WIDTH), torch.float32)
-                                for r in range(self.world)]
             self._slot_bytes = (self.cap + 1) * RECORD_WIDTH * 4
+            self._count_ptrs = [int(p) + self.rank * self._slot_bytes + self.cap * RECORD_WIDTH * 4
+                                for p in self._hdl.buffer_ptrs]
         else:
             self.blocks = torch.empty((self.world, self.cap, RECORD_WIDTH), dtype=torch.float32, device=self.device)
             # the send block is the rank's own row of the result: no copy before the collective, none after
@@ -138,9 +138,12 @@ class RecordExchange:
         if self.transport == "local":
             return self.blocks, torch.tensor([count], dtype=torch.int64, device=self.device)
         if self.transport == "peer":
-            for r in range(self.world):      # 4-byte posted writes: this rank's count into every rank's buffer
-                self._peer_views[r][self.rank, self.cap, 0].fill_(float(count))
-            self._hdl.barrier(channel=0)     # every rank's records and counts have landed everywhere
+            from . import ops
+
+            # this rank's count into every rank's buffer (4-byte posted writes, one launch), then one barrier on the
+            # signal pads: every rank's records and counts have landed everywhere
+            ops.peer_store_f32(self._count_ptrs, float(count))
+            self._hdl.barrier(channel=0)
             counts = self._buf[:, self.cap, 0].to(torch.int64)
             return self.blocks, counts
         if self.cap:
