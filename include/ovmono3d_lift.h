@@ -54,7 +54,8 @@ enum { OVM_LAYOUT_NCHW = 0, OVM_LAYOUT_NHWC = 1 };
 enum {
   OVM_F32 = 0,
   OVM_BF16 = 1,
-  OVM_TF32 = 2 /* fp32 storage, values rounded to TF32 (10 mantissa bits, nearest): operands of a kind::tf32 layer */
+  OVM_TF32 = 2, /* fp32 storage, values rounded to TF32 (10 mantissa bits, nearest): operands of a kind::tf32 layer */
+  OVM_F16 = 3   /* IEEE fp16, saturated to +-65504 when produced here: TF32's mantissa in bf16's bytes (ovm_fc_tail) */
 };
 enum { OVM_Z_DIRECT = 0, OVM_Z_SIGMOID = 1, OVM_Z_LOG = 2, OVM_Z_CLUSTERS = 3 };
 enum { OVM_POSE_6D = 0, OVM_POSE_QUATERNION = 1, OVM_POSE_EULER = 2 };
@@ -185,10 +186,13 @@ typedef struct {
   const float* bias;    /* fp32 [N] */
   int32_t N, K;
   int64_t ldw;
-  const float* weight_tf32; /* optional: the same weight as fp32 [N, ldw_tf32] rounded to TF32 (ovm_round_tf32).  Used by the
-                               LAST layer of a stack that ends in ovm_fc_tail: the layer then runs as a kind::tf32 MMA on
-                               fp32 activations instead of bf16 x bf16 (see ovm_fc_tail) */
-  int64_t ldw_tf32;         /* elements, multiple of 4 */
+  const void* weight_alt;   /* optional: the same weight in another operand format -- fp16 [N, ldw_alt] (ovm_cast_f16) or fp32
+                               rounded to TF32 (ovm_round_tf32).  Used by the LAST layer of a stack that ends in
+                               ovm_fc_tail: the layer then runs on that format, and the layer before writes its
+                               activations in it, instead of bf16 x bf16 (see ovm_fc_tail) */
+  int64_t ldw_alt;          /* elements; the row pitch in bytes must be a multiple of 16 */
+  int32_t alt_dtype;        /* OVM_F16 or OVM_TF32 (ignored when weight_alt is NULL) */
+  int32_t _pad;
 } ovm_fc_layer_t;
 
 typedef struct {
@@ -225,9 +229,9 @@ typedef struct {
 /* Last FC layer + the five linear heads + the cube decode in ONE launch (cube_head.py:157-164 last Linear + heads,
  * roi_heads.py:378-549,798-843): a cluster of N/128 CTAs per 128 boxes, the layer's output stays in tensor memory /
  * registers, per-box head partial sums are exchanged through distributed shared memory, one thread decodes a box.
- * A [n, lda]: the layer's input -- bf16 (a_dtype OVM_BF16) or fp32 values rounded to TF32 (OVM_TF32, e.g. written by
- * ovm_gemm_bf16 with out_dtype OVM_TF32); W [N, ldw] the layer's weight in the SAME type (nn.Linear layout), bias [N]
- * fp32.  Needs class-agnostic heads (DIMS_PRIORS_ENABLED off, CLUSTER_BINS 1), one shared FC stack and N in
+ * A [n, lda]: the layer's input -- bf16 (a_dtype OVM_BF16), fp16 (OVM_F16) or fp32 values rounded to TF32 (OVM_TF32), e.g.
+ * written by ovm_gemm_bf16 with that out_dtype; W [N, ldw] the layer's weight in the SAME type (nn.Linear layout), bias
+ * [N] fp32.  Needs class-agnostic heads (DIMS_PRIORS_ENABLED off, CLUSTER_BINS 1), one shared FC stack and N in
  * {128, 256, 512, 1024}; returns OVM_EUNSUPPORTED otherwise (use ovm_gemm_bf16 + ovm_head_decode).  The remaining
  * arguments are those of ovm_head_decode.  Class ids are not used to index anything in this configuration.        */
 int ovm_fc_tail(const void* A, int64_t lda, int32_t a_dtype, const void* W, int64_t ldw, const float* bias, int32_t N,
@@ -235,12 +239,16 @@ int ovm_fc_tail(const void* A, int64_t lda, int32_t a_dtype, const void* W, int6
                 const int64_t* classes, const float* scores, const int32_t* batch_idx, const float* cams,
                 int32_t num_images, int32_t n, float* records, float* raw, void* stream);
 
+/* x (fp32 [rows, ld_in]) -> fp16 [rows, ld_out] (nearest even, saturated to +-65504), columns >= cols zero-filled. */
+int ovm_cast_f16(const float* in, int64_t ld_in, int32_t rows, int32_t cols, void* out, int64_t ld_out, void* stream);
+
 /* x (fp32 [rows, ld_in]) -> fp32 [rows, ld_out] rounded to TF32 (nearest, ties away), columns >= cols zero-filled. */
 int ovm_round_tf32(const float* in, int64_t ld_in, int32_t rows, int32_t cols, float* out, int64_t ld_out, void* stream);
 
 /* ROIAlign (bf16 out) -> FC stack -> heads + decode on `stream`.  With one shared FC stack of >= 2 layers and
- * class-agnostic heads the last layer, the heads and the decode run as one ovm_fc_tail launch (TF32 when the last
- * layer carries weight_tf32, bf16 otherwise; OVM_FUSE_TAIL=0 in the environment selects the unfused sequence). */
+ * class-agnostic heads the last layer, the heads and the decode run as one ovm_fc_tail launch (in the format of the
+ * last layer's weight_alt -- fp16 or TF32 --, bf16 without one; OVM_FUSE_TAIL=0 in the environment selects the unfused
+ * sequence). */
 int ovm_lift_forward(const ovm_pooler_t* pooler, const ovm_fc_stack_t* fc, const ovm_decode_cfg_t* cfg,
                      const ovm_head_weights_t* heads, const float* boxes, const int64_t* classes,
                      const float* scores, const int32_t* batch_idx, const float* cams, int32_t n,

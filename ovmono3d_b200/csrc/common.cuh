@@ -143,6 +143,7 @@ int fc_tail_launch(const void* A, int64_t lda, int32_t a_dtype, const void* W, i
                    const int64_t* classes, const float* scores, const int32_t* batch_idx, const float* cams,
                    int32_t num_images, int32_t n, float* records, float* raw, cudaStream_t stream,
                    const ovm_peer_records_t* peers = nullptr);
+int cast_f16_launch(const float* in, int64_t ld_in, int32_t rows, int32_t cols, void* out, int64_t ld_out, cudaStream_t stream);
 int round_tf32_launch(const float* in, int64_t ld_in, int32_t rows, int32_t cols, float* out, int64_t ld_out,
                       cudaStream_t stream);
 

@@ -16,10 +16,12 @@
 // each CTA sums the 2 CS contributions of its 128 / CS boxes in a fixed order (deterministic) and decodes them, one
 // thread per box.
 //
-// Precision: operands are either bf16 (kind::f16) or TF32 (kind::tf32: fp32 in shared memory, pre-rounded to 10
-// mantissa bits by the producer of h1 and by ovm_round_tf32 for W2).  fc2 is 7.5 % of the head's FLOPs; running it
-// at TF32 removes half of the bf16 head's pose / corner error (profiles/r02_bf16_attribution.json) for 2x the operand
-// bytes of this one small layer.
+// Precision: operands are bf16, fp16 (both kind::f16) or TF32 (kind::tf32: fp32 in shared memory, pre-rounded to 10
+// mantissa bits).  fp16 is the default of the lift: it carries TF32's 10 mantissa bits in bf16's two bytes -- post-ReLU
+// activations and Xavier-scale weights sit well inside its range (the producer saturates at +-65504 instead of making
+// infinities) -- so fc2 gets TF32's accuracy (profiles/r02_bf16_attribution.json: the two are indistinguishable, and
+// remove the fc2 half of the bf16 head's pose / corner error) at bf16's operand traffic: 4.6 us of main loop at C2
+// instead of TF32's 9.2 (the layer is bound by operand bytes per SM, not by the tensor pipe).
 #include <cuda.h>
 
 #include <cstdlib>
@@ -100,9 +102,10 @@ __device__ __forceinline__ void tma_load_2d_mc(uint32_t dst, const CUtensorMap* 
 }
 __device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-template <bool TF32>
+enum { kFmtF16 = 0, kFmtBF16 = 1, kFmtTF32 = 2 };   // UMMA a_format / b_format codes of kind::f16 / kind::tf32
+template <int FMT>
 __device__ __forceinline__ void umma(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
-  if (TF32) {
+  if (FMT == kFmtTF32) {
     asm volatile(
         "{\n\t"
         ".reg .pred p;\n\t"
@@ -182,7 +185,7 @@ __device__ __forceinline__ void tail_stamp(const TailArgs& g, int slot) {
   }
 }
 
-template <bool TF32>
+template <int FMT>
 __global__ void __launch_bounds__(kTailThreads, 1)
 fc_tail_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TailArgs g) {
   extern __shared__ uint8_t smem_raw[];
@@ -289,7 +292,7 @@ fc_tail_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   } else if (warp == 1) {
     if (lane == 0) {
       // ===== MMA issuer: D[128 x 128] += A[128 x 32 B] . B[128 x 32 B]^T, four per stage
-      constexpr uint32_t fmt = TF32 ? 2u : 1u;
+      constexpr uint32_t fmt = (uint32_t)FMT;
       constexpr uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(kTN >> 3) << 17) | ((uint32_t)(kTM >> 4) << 24);
       int stage = 0;
       uint32_t phase = 0;
@@ -301,7 +304,7 @@ fc_tail_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const uint64_t bdesc = make_smem_desc(smem_b + stage * kTailBBytes);
 #pragma unroll
         for (int k = 0; k < 4; ++k)
-          umma<TF32>(tmem_base, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (kb > 0 || k > 0) ? 1u : 0u);
+          umma<FMT>(tmem_base, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (kb > 0 || k > 0) ? 1u : 0u);
         if (cs > 1) tcgen05_commit_mc(empty_bar + 8 * stage, (uint16_t)((1u << cs) - 1u));   // frees the slot in every CTA
         else tcgen05_commit(empty_bar + 8 * stage);
         if (++stage == kTailStages) {
@@ -386,18 +389,18 @@ fc_tail_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
 // [rows, cols] row-major with leading dimension ld (elements) -> 2-D map, box {128 bytes of K, box_rows rows}, 128-byte
 // swizzle, out-of-bounds elements read as zero (row and K tails).
-int make_tail_map(CUtensorMap* map, const void* ptr, int64_t rows, int64_t cols, int64_t ld, bool tf32, int box_rows) {
+int make_tail_map(CUtensorMap* map, const void* ptr, int64_t rows, int64_t cols, int64_t ld, int dtype, int box_rows) {
   EncodeTiledFn enc = tensormap_encode_fn();
   if (!enc) {
     set_error("cuTensorMapEncodeTiled not available from the driver");
     return OVM_ECUDA;
   }
-  const int esz = tf32 ? 4 : 2;
+  const int esz = dtype == OVM_TF32 ? 4 : 2;
   cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
   cuuint64_t strides[1] = {(cuuint64_t)ld * esz};
   cuuint32_t box[2] = {(cuuint32_t)(kRowBytes / esz), (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = enc(map, tf32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims,
+  CUresult r = enc(map, dtype == OVM_TF32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : (dtype == OVM_F16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16), 2, const_cast<void*>(ptr), dims,
                    strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
@@ -408,11 +411,11 @@ int make_tail_map(CUtensorMap* map, const void* ptr, int64_t rows, int64_t cols,
   return OVM_OK;
 }
 
-template <bool TF32>
+template <int FMT>
 int launch_tail(const CUtensorMap& tmA, const CUtensorMap& tmB, const TailArgs& g, int grid, cudaStream_t stream) {
   static SmemOptIn opt;
   {
-    int rc = opt.ensure(fc_tail_kernel<TF32>, kTailSmemBytes);
+    int rc = opt.ensure(fc_tail_kernel<FMT>, kTailSmemBytes);
     if (rc != OVM_OK) return rc;
   }
   cudaLaunchConfig_t cfg = {};
@@ -429,7 +432,7 @@ int launch_tail(const CUtensorMap& tmA, const CUtensorMap& tmB, const TailArgs& 
   attr[1].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 2;
-  OVM_CUDA(cudaLaunchKernelEx(&cfg, fc_tail_kernel<TF32>, tmA, tmB, g));
+  OVM_CUDA(cudaLaunchKernelEx(&cfg, fc_tail_kernel<FMT>, tmA, tmB, g));
   OVM_LAUNCHED("fc_tail_kernel");
   return OVM_OK;
 }
@@ -452,7 +455,8 @@ int fc_tail_launch(const void* A, int64_t lda, int32_t a_dtype, const void* W, i
                    int32_t num_images, int32_t n, float* records, float* raw, cudaStream_t stream,
                    const ovm_peer_records_t* peers) {
   OVM_REQUIRE(cfg && w, "ovm_fc_tail: cfg / weights are NULL");
-  OVM_REQUIRE(a_dtype == OVM_BF16 || a_dtype == OVM_TF32, "ovm_fc_tail: operand dtype %d (OVM_BF16 or OVM_TF32)", a_dtype);
+  OVM_REQUIRE(a_dtype == OVM_BF16 || a_dtype == OVM_TF32 || a_dtype == OVM_F16,
+              "ovm_fc_tail: operand dtype %d (OVM_BF16, OVM_F16 or OVM_TF32)", a_dtype);
   OVM_REQUIRE(cfg->z_type >= OVM_Z_DIRECT && cfg->z_type <= OVM_Z_CLUSTERS, "ovm_fc_tail: z_type %d", cfg->z_type);
   OVM_REQUIRE(cfg->pose_type >= OVM_POSE_6D && cfg->pose_type <= OVM_POSE_EULER,
               "Cuboid pose type %d is not recognized", cfg->pose_type);
@@ -503,12 +507,14 @@ int fc_tail_launch(const void* A, int64_t lda, int32_t a_dtype, const void* W, i
   g.kblocks = (K + g.elems_per_row - 1) / g.elems_per_row;
   g.bias = bias;
   CUtensorMap tmA, tmB;
-  int rc = make_tail_map(&tmA, A, n, K, lda, a_dtype == OVM_TF32, kTM / g.cs);   // each CTA multicasts its slice of the rows
+  int rc = make_tail_map(&tmA, A, n, K, lda, a_dtype, kTM / g.cs);   // each CTA multicasts its slice of the rows
   if (rc != OVM_OK) return rc;
-  rc = make_tail_map(&tmB, W, N, K, ldw, a_dtype == OVM_TF32, kTN);
+  rc = make_tail_map(&tmB, W, N, K, ldw, a_dtype, kTN);
   if (rc != OVM_OK) return rc;
   const int grid = g.cs * ((n + kTM - 1) / kTM);
-  return a_dtype == OVM_TF32 ? launch_tail<true>(tmA, tmB, g, grid, stream) : launch_tail<false>(tmA, tmB, g, grid, stream);
+  if (a_dtype == OVM_TF32) return launch_tail<kFmtTF32>(tmA, tmB, g, grid, stream);
+  if (a_dtype == OVM_F16) return launch_tail<kFmtF16>(tmA, tmB, g, grid, stream);
+  return launch_tail<kFmtBF16>(tmA, tmB, g, grid, stream);
 }
 
 }  // namespace ovm

@@ -18,6 +18,7 @@
 // (bias/ReLU then run in bias_act_kernel).  fc1 of the lift (M = 1600, N = 1024, K = 12544) has only 52-104
 // tiles for 148 SMs, which is why it needs the K split.
 #include <cuda.h>
+#include <cuda_fp16.h>
 
 #include <cstdlib>
 #include <cstring>
@@ -66,6 +67,7 @@ struct GemmArgs {
   void* fin_out;
   long long fin_ldo;
   int fin_bf16;
+  int f16;               // 16-bit outputs (DIRECT epilogue / fused finish) are fp16 instead of bf16
   int round_tf32;        // fp32 outputs (DIRECT epilogue / fused finish) are rounded to TF32: the next layer is a kind::tf32 MMA
   // gemm_pair_kernel<true>: split-K partials meet in per-cluster slots (plain stores) instead of L2 atomics
   float* slots;          // [clusters][2 CTAs][128 rows][256 columns] fp32
@@ -158,6 +160,23 @@ __device__ __forceinline__ float round_tf32(float x) {
 }
 __device__ __forceinline__ float4 round_tf32(float4 v) {
   return make_float4(round_tf32(v.x), round_tf32(v.y), round_tf32(v.z), round_tf32(v.w));
+}
+// four fp32 -> four 16-bit values: bf16 (round to nearest even) or fp16 (the same, saturated to +-65504 so that no
+// infinity is made; NaN stays NaN).  fp16 carries TF32's 10 mantissa bits in bf16's 2 bytes: the format of the
+// activations handed to a kind::f16 tail layer (fc_tail.cu).
+__device__ __forceinline__ float sat_f16(float x) { return x > 65504.f ? 65504.f : (x < -65504.f ? -65504.f : x); }
+__device__ __forceinline__ uint2 pack16(float4 v, int f16) {
+  uint2 pk;
+  if (f16) {
+    __half2 lo = __floats2half2_rn(sat_f16(v.x), sat_f16(v.y)), hi = __floats2half2_rn(sat_f16(v.z), sat_f16(v.w));
+    pk.x = *reinterpret_cast<uint32_t*>(&lo);
+    pk.y = *reinterpret_cast<uint32_t*>(&hi);
+  } else {
+    __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+    pk.x = *reinterpret_cast<uint32_t*>(&lo);
+    pk.y = *reinterpret_cast<uint32_t*>(&hi);
+  }
+  return pk;
 }
 __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
@@ -394,11 +413,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             } else if (MODE == kModeF32) {
               *reinterpret_cast<float4*>(reinterpret_cast<float*>(g.out) + off) = x;
             } else {
-              __nv_bfloat162 lo = __floats2bfloat162_rn(x.x, x.y), hi = __floats2bfloat162_rn(x.z, x.w);
-              uint2 pk;
-              pk.x = *reinterpret_cast<uint32_t*>(&lo);
-              pk.y = *reinterpret_cast<uint32_t*>(&hi);
-              *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(g.out) + off) = pk;
+              *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(g.out) + off) = pack16(x, g.f16);
             }
           } else if (row0 + r < g.M) {   // tile edge: element-wise
             const float xs[4] = {x.x, x.y, x.z, x.w};
@@ -407,6 +422,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               if (c + e >= g.N) continue;
               if (MODE == kModeStreamK) atomicAdd(reinterpret_cast<float*>(g.out) + off + e, xs[e]);
               else if (MODE == kModeF32) reinterpret_cast<float*>(g.out)[off + e] = xs[e];
+              else if (g.f16) reinterpret_cast<__half*>(g.out)[off + e] = __float2half_rn(sat_f16(xs[e]));
               else reinterpret_cast<__nv_bfloat16*>(g.out)[off + e] = __float2bfloat16_rn(xs[e]);
             }
           }
@@ -462,11 +478,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 if (g.round_tf32) v = round_tf32(v);
                 const long long off = (long long)row * g.fin_ldo + c;
                 if (g.fin_bf16) {
-                  __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
-                  uint2 pk;
-                  pk.x = *reinterpret_cast<uint32_t*>(&lo);
-                  pk.y = *reinterpret_cast<uint32_t*>(&hi);
-                  *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(g.fin_out) + off) = pk;
+                  *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(g.fin_out) + off) = pack16(v, g.f16);
                 } else {
                   *reinterpret_cast<float4*>(reinterpret_cast<float*>(g.fin_out) + off) = v;
                 }
@@ -831,11 +843,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 if (row0 + r >= g.M || c + 3 >= g.N) continue;     // N % 4 == 0 (checked by the launcher)
                 const long long off = (long long)(row0 + r) * g.fin_ldo + c;
                 if (g.fin_bf16) {
-                  __nv_bfloat162 lo = __floats2bfloat162_rn(x.x, x.y), hi = __floats2bfloat162_rn(x.z, x.w);
-                  uint2 pk;
-                  pk.x = *reinterpret_cast<uint32_t*>(&lo);
-                  pk.y = *reinterpret_cast<uint32_t*>(&hi);
-                  *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(g.fin_out) + off) = pk;
+                  *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(g.fin_out) + off) = pack16(x, g.f16);
                 } else {
                   *reinterpret_cast<float4*>(reinterpret_cast<float*>(g.fin_out) + off) = x;
                 }
@@ -936,11 +944,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 if (g.round_tf32) w = round_tf32(w);
                 const long long off = (long long)row * g.fin_ldo + c;
                 if (g.fin_bf16) {
-                  __nv_bfloat162 lo = __floats2bfloat162_rn(w.x, w.y), hi = __floats2bfloat162_rn(w.z, w.w);
-                  uint2 pk;
-                  pk.x = *reinterpret_cast<uint32_t*>(&lo);
-                  pk.y = *reinterpret_cast<uint32_t*>(&hi);
-                  *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(g.fin_out) + off) = pk;
+                  *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(g.fin_out) + off) = pack16(w, g.f16);
                 } else {
                   *reinterpret_cast<float4*>(reinterpret_cast<float*>(g.fin_out) + off) = w;
                 }
@@ -963,7 +967,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
 // ------------------------------------------------------------------ small elementwise kernels
 __global__ void bias_act_kernel(const float* in, long long ldi, const float* __restrict__ bias, int relu,
-                                int M, int N, void* out, int out_bf16, long long ldo, int clear_in, int tf32) {
+                                int M, int N, void* out, int out_bf16, long long ldo, int clear_in, int tf32, int f16) {
   // one thread per 4 consecutive columns (N % 4 == 0 is required by the launcher)
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const int n4 = N >> 2;
@@ -983,11 +987,7 @@ __global__ void bias_act_kernel(const float* in, long long ldi, const float* __r
   }
   if (tf32) v = round_tf32(v);
   if (out_bf16) {
-    __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y), b = __floats2bfloat162_rn(v.z, v.w);
-    uint2 pk;
-    pk.x = *reinterpret_cast<uint32_t*>(&a);
-    pk.y = *reinterpret_cast<uint32_t*>(&b);
-    *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(out) + (long long)m * ldo + j) = pk;
+    *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(out) + (long long)m * ldo + j) = pack16(v, f16);
   } else {
     *reinterpret_cast<float4*>(reinterpret_cast<float*>(out) + (long long)m * ldo + j) = v;
   }
@@ -999,6 +999,15 @@ __global__ void cast_bf16_kernel(const float* __restrict__ in, long long ld_in, 
   if (idx >= (long long)rows * ld_out) return;
   const int r = (int)(idx / ld_out), c = (int)(idx - (long long)r * ld_out);
   out[idx] = __float2bfloat16_rn(c < cols ? in[(long long)r * ld_in + c] : 0.f);
+}
+
+// x (fp32) -> fp16 (saturated), columns >= cols zero-filled up to ld_out: the weight operand of a kind::f16 tail layer
+__global__ void cast_f16_kernel(const float* __restrict__ in, long long ld_in, int rows, int cols,
+                                __half* __restrict__ out, long long ld_out) {
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (long long)rows * ld_out) return;
+  const int r = (int)(idx / ld_out), c = (int)(idx - (long long)r * ld_out);
+  out[idx] = __float2half_rn(c < cols ? sat_f16(in[(long long)r * ld_in + c]) : 0.f);
 }
 
 // W (fp32) -> fp32 rounded to TF32, columns >= cols zero-filled up to ld_out: the weight operand of a kind::tf32 layer
@@ -1065,7 +1074,8 @@ int gemm_bf16_launch(const void* A, int64_t lda, const void* B, int64_t ldb, int
   OVM_REQUIRE(lda >= K && ldb >= K && lda % 8 == 0 && ldb % 8 == 0, "ovm_gemm_bf16: lda/ldb must be >= K and multiples of 8");
   OVM_REQUIRE(!(reinterpret_cast<uintptr_t>(A) & 15) && !(reinterpret_cast<uintptr_t>(B) & 15),
               "ovm_gemm_bf16: A and B must be 16-byte aligned");
-  OVM_REQUIRE(out_dtype == OVM_F32 || out_dtype == OVM_BF16 || out_dtype == OVM_TF32, "ovm_gemm_bf16: out_dtype %d", out_dtype);
+  OVM_REQUIRE(out_dtype == OVM_F32 || out_dtype == OVM_BF16 || out_dtype == OVM_TF32 || out_dtype == OVM_F16,
+              "ovm_gemm_bf16: out_dtype %d", out_dtype);
   OVM_REQUIRE(ldo >= N && ldo % 8 == 0 && !(reinterpret_cast<uintptr_t>(out) & 15),
               "ovm_gemm_bf16: ldo must be >= N, a multiple of 8, and out 16-byte aligned");
   OVM_REQUIRE(mode >= OVM_GEMM_AUTO && mode <= OVM_GEMM_STREAMK, "ovm_gemm_bf16: mode %d", mode);
@@ -1103,7 +1113,8 @@ int gemm_bf16_launch(const void* A, int64_t lda, const void* B, int64_t ldb, int
   if (mode_used) *mode_used = mode;
   g.streamk = mode == OVM_GEMM_STREAMK;
   g.relu = relu;
-  g.out_bf16 = out_dtype == OVM_BF16;
+  g.out_bf16 = out_dtype == OVM_BF16 || out_dtype == OVM_F16;     // 16-bit store path
+  g.f16 = out_dtype == OVM_F16;
   g.round_tf32 = out_dtype == OVM_TF32;
   g.bias = bias;
   g.out = out;
@@ -1118,7 +1129,8 @@ int gemm_bf16_launch(const void* A, int64_t lda, const void* B, int64_t ldb, int
     g.relu = fin->relu;
     g.fin_out = fin->out;
     g.fin_ldo = fin->ldo;
-    g.fin_bf16 = fin->out_dtype == OVM_BF16;
+    g.fin_bf16 = fin->out_dtype == OVM_BF16 || fin->out_dtype == OVM_F16;
+    g.f16 = fin->out_dtype == OVM_F16;
     g.round_tf32 = fin->out_dtype == OVM_TF32;
   }
   CUtensorMap tmA, tmB;
@@ -1174,11 +1186,12 @@ int bias_act_launch(const float* in, int64_t ldi, const float* bias, int32_t rel
   if (M == 0) return OVM_OK;
   OVM_REQUIRE(in && out && M > 0 && N > 0, "ovm_bias_act: bad arguments");
   OVM_REQUIRE(N % 4 == 0 && ldi % 4 == 0 && ldo % 4 == 0, "ovm_bias_act: N, ldi, ldo must be multiples of 4");
-  OVM_REQUIRE(out_dtype == OVM_F32 || out_dtype == OVM_BF16 || out_dtype == OVM_TF32, "ovm_bias_act: out_dtype %d", out_dtype);
+  OVM_REQUIRE(out_dtype == OVM_F32 || out_dtype == OVM_BF16 || out_dtype == OVM_TF32 || out_dtype == OVM_F16,
+              "ovm_bias_act: out_dtype %d", out_dtype);
   const long long total = (long long)M * (N / 4);
   OVM_CUDA(launch_pdl(bias_act_kernel, dim3((unsigned)((total + 255) / 256)), dim3(256), 0, stream, in, (long long)ldi, bias,
-                      (int)relu, (int)M, (int)N, out, (int)(out_dtype == OVM_BF16), (long long)ldo, clear_in ? 1 : 0,
-                      (int)(out_dtype == OVM_TF32)));
+                      (int)relu, (int)M, (int)N, out, (int)(out_dtype == OVM_BF16 || out_dtype == OVM_F16), (long long)ldo,
+                      clear_in ? 1 : 0, (int)(out_dtype == OVM_TF32), (int)(out_dtype == OVM_F16)));
   OVM_LAUNCHED("bias_act_kernel");
   return OVM_OK;
 }
@@ -1191,6 +1204,15 @@ int cast_bf16_launch(const float* in, int64_t ld_in, int32_t rows, int32_t cols,
   cast_bf16_kernel<<<(unsigned)((total + 255) / 256), 256, 0, stream>>>(in, ld_in, rows, cols,
                                                                        reinterpret_cast<__nv_bfloat16*>(out), ld_out);
   OVM_LAUNCHED("cast_bf16_kernel");
+  return OVM_OK;
+}
+
+int cast_f16_launch(const float* in, int64_t ld_in, int32_t rows, int32_t cols, void* out, int64_t ld_out, cudaStream_t stream) {
+  if (rows == 0) return OVM_OK;
+  OVM_REQUIRE(in && out && rows > 0 && cols > 0 && ld_in >= cols && ld_out >= cols, "ovm_cast_f16: bad arguments");
+  const long long total = (long long)rows * ld_out;
+  cast_f16_kernel<<<(unsigned)((total + 255) / 256), 256, 0, stream>>>(in, ld_in, rows, cols, reinterpret_cast<__half*>(out), ld_out);
+  OVM_LAUNCHED("cast_f16_kernel");
   return OVM_OK;
 }
 

@@ -204,6 +204,10 @@ int ovm_fc_tail(const void* A, int64_t lda, int32_t a_dtype, const void* W, int6
                         n, records, raw, static_cast<cudaStream_t>(stream));
 }
 
+int ovm_cast_f16(const float* in, int64_t ld_in, int32_t rows, int32_t cols, void* out, int64_t ld_out, void* stream) {
+  return cast_f16_launch(in, ld_in, rows, cols, out, ld_out, static_cast<cudaStream_t>(stream));
+}
+
 int ovm_round_tf32(const float* in, int64_t ld_in, int32_t rows, int32_t cols, float* out, int64_t ld_out, void* stream) {
   return round_tf32_launch(in, ld_in, rows, cols, out, ld_out, static_cast<cudaStream_t>(stream));
 }
@@ -247,15 +251,18 @@ int ovm_lift_forward_peers(const ovm_pooler_t* pooler, const ovm_fc_stack_t* fc,
     // one shared stack, class-agnostic heads: [fc1 .. fc(k-1)] -> {fc k + heads + decode} in one launch
     OVM_REQUIRE(fc->layers[0].K == k_in, "ovm_lift_forward: fc1 expects K=%d but the pooler produces %lld",
                 fc->layers[0].K, (long long)k_in);
-    const bool tf32 = tail.weight_tf32 != nullptr;
+    const bool alt = tail.weight_alt != nullptr;
+    OVM_REQUIRE(!alt || tail.alt_dtype == OVM_F16 || tail.alt_dtype == OVM_TF32,
+                "ovm_lift_forward: weight_alt must be OVM_F16 or OVM_TF32 (got %d)", tail.alt_dtype);
+    const int fmt = alt ? tail.alt_dtype : OVM_BF16;
     const void* h = nullptr;
     int64_t ldh = 0;
-    rc = run_fc_group(fc->layers, fc->num_fc - 1, /*ends_stack=*/false, tf32 ? OVM_TF32 : OVM_BF16, ws->pooled,
-                      ws->ld_pooled, n, ws, nullptr, 0, stream, stage, &h, &ldh);
+    rc = run_fc_group(fc->layers, fc->num_fc - 1, /*ends_stack=*/false, fmt, ws->pooled, ws->ld_pooled, n, ws, nullptr, 0,
+                      stream, stage, &h, &ldh);
     if (rc != OVM_OK) return rc;
-    rc = fc_tail_launch(h, ldh, tf32 ? OVM_TF32 : OVM_BF16, tf32 ? static_cast<const void*>(tail.weight_tf32) : tail.weight,
-                        tf32 ? tail.ldw_tf32 : tail.ldw, tail.bias, tail.N, tail.K, cfg, heads, boxes, classes, scores,
-                        batch_idx, cams, pooler->num_images, n, records, raw, stream, peers);
+    rc = fc_tail_launch(h, ldh, fmt, alt ? tail.weight_alt : tail.weight, alt ? tail.ldw_alt : tail.ldw, tail.bias, tail.N,
+                        tail.K, cfg, heads, boxes, classes, scores, batch_idx, cams, pooler->num_images, n, records, raw,
+                        stream, peers);
     if (rc != OVM_OK) return rc;
     return stage_mark(stage, stream);
   }

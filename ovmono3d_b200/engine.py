@@ -55,10 +55,10 @@ class LiftEngine:
         if settings.z_type not in ops.Z_TYPES:
             raise ValueError("Z type {} is not recognized".format(settings.z_type))
         # operand format of the stack's last FC layer when it runs fused with the heads and the decode (ovm_fc_tail):
-        # "tf32" (default; fp32 activations from the layer before, 10-bit mantissas) or "bf16"
-        self.tail_precision = os.environ.get("OVM_TAIL_PRECISION", "tf32").lower()
-        if self.tail_precision not in ("tf32", "bf16"):
-            raise ValueError("OVM_TAIL_PRECISION must be tf32 or bf16")
+        # "f16" (default: TF32's 10-bit mantissa in two bytes), "tf32" (fp32 storage) or "bf16"
+        self.tail_precision = os.environ.get("OVM_TAIL_PRECISION", "f16").lower()
+        if self.tail_precision not in ("f16", "tf32", "bf16"):
+            raise ValueError("OVM_TAIL_PRECISION must be f16, tf32 or bf16")
         self._weights_key = None
         self._params = None
         self._fc_weights: List[torch.Tensor] = []
@@ -120,14 +120,18 @@ class LiftEngine:
                 b = fc.bias.detach().float().contiguous()
                 self._fc_weights.append(wb)
                 keep.append(b)
-                w32, ld32 = None, 0
-                if fc is fcs[-1] and len(gens) == 1 and num_fc >= 2 and self.tail_precision == "tf32":
-                    # the stack's last layer may run fused with the heads and the decode (ovm_fc_tail) on TF32 operands
-                    ld32 = _round_up(K, 4)
-                    w32 = ops.round_tf32(wf, ld32)
-                    keep.append(w32)
+                walt, ldalt, alt_dtype = None, 0, 0
+                if fc is fcs[-1] and len(gens) == 1 and num_fc >= 2 and self.tail_precision != "bf16":
+                    # the stack's last layer may run fused with the heads and the decode (ovm_fc_tail) on fp16 / TF32 operands
+                    if self.tail_precision == "f16":
+                        ldalt, alt_dtype = _round_up(K, 8), ops.F16
+                        walt = ops.cast_f16(wf, ldalt)
+                    else:
+                        ldalt, alt_dtype = _round_up(K, 4), ops.TF32
+                        walt = ops.round_tf32(wf, ldalt)
+                    keep.append(walt)
                 layers.append(ops.ovm_fc_layer_t(wb.data_ptr(), b.data_ptr(), N, K, ldw,
-                                                 None if w32 is None else w32.data_ptr(), ld32))
+                                                 None if walt is None else walt.data_ptr(), ldalt, alt_dtype, 0))
         self._fc_layers = (ops.ovm_fc_layer_t * len(layers))(*layers)
         self._fc_stack = ops.ovm_fc_stack_t(len(gens), num_fc, self._fc_layers)
         self.fc_dim = layers[-1].N

@@ -15,7 +15,7 @@ OVM_ABI_VERSION = 6
 OVM_MAX_LEVELS = 8
 RECORD_WIDTH = 48
 LAYOUT_NCHW, LAYOUT_NHWC = 0, 1
-F32, BF16, TF32 = 0, 1, 2
+F32, BF16, TF32, F16 = 0, 1, 2, 3
 Z_TYPES = {"direct": 0, "sigmoid": 1, "log": 2, "clusters": 3}
 POSE_TYPES = {"6d": 0, "quaternion": 1, "euler": 2}
 DIMS_FUNCS = {"exp": 0, "sigmoid": 1}
@@ -35,7 +35,7 @@ EXPORTS = ("ovm_abi_version", "ovm_last_error", "ovm_launch_count", "ovm_struct_
            "ovm_bias_act", "ovm_cast_bf16", "ovm_head_decode", "ovm_lift_forward", "ovm_set_stage_events", "ovm_gemm_set_trace",
            "ovm_roi_set_trace", "ovm_head_set_trace", "ovm_nms", "ovm_gdino_post", "ovm_box_inference", "ovm_post_set_trace",
            "ovm_fc_tail", "ovm_round_tf32", "ovm_iou_box3d", "ovm_lift_forward_peers",
-           "ovm_records_postprocess", "ovm_peer_store_f32")
+           "ovm_records_postprocess", "ovm_peer_store_f32", "ovm_cast_f16")
 NMS_MAX_SEGMENT = 4096
 SPLITK_SLOTS_LEN = 74 * 2 * 128 * 256      # OVM_SPLITK_SLOTS_LEN / OVM_SPLITK_FLAGS_LEN of the header
 SPLITK_FLAGS_LEN = 74 * 2 * 8
@@ -73,7 +73,7 @@ class ovm_head_weights_t(C.Structure):
 
 class ovm_fc_layer_t(C.Structure):
     _fields_ = [("weight", C.c_void_p), ("bias", C.c_void_p), ("N", C.c_int32), ("K", C.c_int32), ("ldw", C.c_int64),
-                ("weight_tf32", C.c_void_p), ("ldw_tf32", C.c_int64)]
+                ("weight_alt", C.c_void_p), ("ldw_alt", C.c_int64), ("alt_dtype", C.c_int32), ("_pad", C.c_int32)]
 
 
 class ovm_fc_stack_t(C.Structure):
@@ -144,6 +144,7 @@ def load_library() -> C.CDLL:
     lib.ovm_fc_tail.argtypes = [vp, i64, i32, vp, i64, vp, i32, i32, C.POINTER(ovm_decode_cfg_t),
                                 C.POINTER(ovm_head_weights_t), vp, vp, vp, vp, vp, i32, i32, vp, vp, vp]
     lib.ovm_round_tf32.argtypes = [vp, i64, i32, i32, vp, i64, vp]
+    lib.ovm_cast_f16.argtypes = [vp, i64, i32, i32, vp, i64, vp]
     lib.ovm_iou_box3d.argtypes = [vp, vp, i32, i32, C.c_float, C.c_float, vp, vp, vp, vp]
     lib.ovm_records_postprocess.argtypes = [vp, vp, vp, i32, vp, vp, vp]
     lib.ovm_peer_store_f32.argtypes = [C.POINTER(C.c_void_p), i32, C.c_float, vp]
@@ -212,7 +213,21 @@ def dtype_code(dt: torch.dtype) -> int:
         return F32
     if dt == torch.bfloat16:
         return BF16
+    if dt == torch.float16:
+        return F16
     raise LiftError("unsupported output dtype %s" % dt)
+
+
+def cast_f16(x: torch.Tensor, ld_out: Optional[int] = None) -> torch.Tensor:
+    """fp32 [rows, cols] -> fp16 [rows, ld_out] (saturated, zero-padded), returned as the [rows, cols] view."""
+    lib = load_library()
+    _need_cuda(x, "x", torch.float32)
+    rows, cols = x.shape
+    ld_out = ld_out or (cols + 7) // 8 * 8
+    out = torch.empty((rows, ld_out), device=x.device, dtype=torch.float16)
+    if rows:
+        _check(lib.ovm_cast_f16(x.data_ptr(), x.stride(0), rows, cols, out.data_ptr(), ld_out, _stream()), "ovm_cast_f16")
+    return out[:, :cols]
 
 
 def round_tf32(x: torch.Tensor, ld_out: Optional[int] = None) -> torch.Tensor:
@@ -361,11 +376,11 @@ def head_decode(cfg: "ovm_decode_cfg_t", heads: "ovm_head_weights_t", feats: tor
 def fc_tail(cfg: "ovm_decode_cfg_t", heads: "ovm_head_weights_t", A: torch.Tensor, W: torch.Tensor, bias: torch.Tensor,
             boxes: torch.Tensor, classes: torch.Tensor, scores: Optional[torch.Tensor], batch_idx: torch.Tensor,
             cams: torch.Tensor, want_raw: bool = False) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
-    """`ovm_fc_tail`: last FC layer + heads + decode in one launch.  A [n, K] and W [N, K] are both bf16, or both fp32
-    holding TF32-rounded values (`round_tf32`, or `gemm_bf16(..., tf32_out=True)`)."""
+    """`ovm_fc_tail`: last FC layer + heads + decode in one launch.  A [n, K] and W [N, K] are both bf16, both fp16
+    (`cast_f16`), or both fp32 holding TF32-rounded values (`round_tf32`, or `gemm_bf16(..., tf32_out=True)`)."""
     lib = load_library()
-    if A.dtype != W.dtype or A.dtype not in (torch.float32, torch.bfloat16):
-        raise LiftError("fc_tail: A and W must both be bf16 or both be fp32 (TF32-rounded)")
+    if A.dtype != W.dtype or A.dtype not in (torch.float32, torch.bfloat16, torch.float16):
+        raise LiftError("fc_tail: A and W must both be bf16, both fp16, or both fp32 (TF32-rounded)")
     _need_cuda(A, "A", A.dtype)
     _need_cuda(W, "W", W.dtype)
     _need_cuda(bias, "bias", torch.float32)
@@ -375,7 +390,8 @@ def fc_tail(cfg: "ovm_decode_cfg_t", heads: "ovm_head_weights_t", A: torch.Tenso
     N = W.shape[0]
     rec = torch.empty((n, RECORD_WIDTH), device=A.device, dtype=torch.float32)
     raw = torch.empty((n, 16), device=A.device, dtype=torch.float32) if want_raw else None
-    _check(lib.ovm_fc_tail(A.data_ptr(), A.stride(0), TF32 if A.dtype == torch.float32 else BF16, W.data_ptr(),
+    _check(lib.ovm_fc_tail(A.data_ptr(), A.stride(0), {torch.float32: TF32, torch.float16: F16, torch.bfloat16: BF16}[A.dtype],
+                           W.data_ptr(),
                            W.stride(0), bias.data_ptr(), N, K, C.byref(cfg), C.byref(heads), boxes.data_ptr(),
                            classes.data_ptr(), _ptr(scores), batch_idx.data_ptr(), cams.data_ptr(), cams.shape[0], n,
                            rec.data_ptr(), _ptr(raw), _stream()), "ovm_fc_tail")
@@ -404,7 +420,7 @@ def records_postprocess(records: torch.Tensor, offsets: torch.Tensor, geom: torc
     out = torch.empty_like(records)
     count = torch.zeros((max(N, 1),), dtype=torch.int32, device=records.device)
     _check(lib.ovm_records_postprocess(_ptr(records), _ptr(offsets), _ptr(geom), N, _ptr(out), _ptr(count), _stream()),
-           "ovm_records_postprocess", "ovm_peer_store_f32")
+           "ovm_records_postprocess")
     return out, count[:N]
 
 

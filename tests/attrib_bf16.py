@@ -38,6 +38,8 @@ def _round(x: torch.Tensor, how: str) -> torch.Tensor:
         i = x.contiguous().view(torch.int32)
         r = ((i + 0x0FFF + ((i >> 13) & 1)) & ~0x1FFF)
         return r.view(torch.float32)
+    if how == "f16":       # 10 explicit mantissa bits like TF32, 5 exponent bits: saturating round-to-nearest-even
+        return x.clamp(-65504.0, 65504.0).half().float()
     if how == "bf16x2":    # hi + lo bf16 pair: what a 3-term split product carries (16 mantissa bits)
         hi = x.bfloat16().float()
         return hi + (x - hi).bfloat16().float()
@@ -107,7 +109,8 @@ VARIANTS = [
     ("fc2_bf16 (h1+W2)", {(2, "a"): "bf16", (2, "w"): "bf16"}),
     ("all_bf16 (round 1 product)", {(1, "a"): "bf16", (1, "w"): "bf16", (2, "a"): "bf16", (2, "w"): "bf16"}),
     ("fc1_bf16 + fc2_tf32", {(1, "a"): "bf16", (1, "w"): "bf16", (2, "a"): "tf32", (2, "w"): "tf32"}),
-    ("fc1_bf16 + fc2_bf16x2 split (this round's product)", {(1, "a"): "bf16", (1, "w"): "bf16", (2, "a"): "bf16x2", (2, "w"): "bf16x2"}),
+    ("fc1_bf16 + fc2_f16 (this round's product)", {(1, "a"): "bf16", (1, "w"): "bf16", (2, "a"): "f16", (2, "w"): "f16"}),
+    ("fc1_bf16 + fc2_bf16x2 split", {(1, "a"): "bf16", (1, "w"): "bf16", (2, "a"): "bf16x2", (2, "w"): "bf16x2"}),
     ("fc1 pooled_bf16x2 W1_bf16 + fc2 split", {(1, "a"): "bf16x2", (1, "w"): "bf16", (2, "a"): "bf16x2", (2, "w"): "bf16x2"}),
     ("fc1 split both + fc2 split", {(1, "a"): "bf16x2", (1, "w"): "bf16x2", (2, "a"): "bf16x2", (2, "w"): "bf16x2"}),
 ]

@@ -35,20 +35,26 @@ def round_tf32(x: torch.Tensor) -> torch.Tensor:
     return ((i + 0x1000) & ~0x1FFF).view(torch.float32)
 
 
-def tail_is_tf32(case: gc.Case) -> bool:
-    """Does the product run this case's last FC layer fused with the heads and the decode on TF32 operands
-    (`ovm_fc_tail`, csrc/fc_tail.cu: shared FC stack, class-agnostic heads, FC_DIM a power of two in 128..1024)?"""
+def round_f16(x: torch.Tensor) -> torch.Tensor:
+    """fp32 -> fp16 -> fp32 as the kernels do it: round to nearest even, saturated to +-65504 (NaN stays NaN)."""
+    return torch.where(x == x, x.clamp(-65504.0, 65504.0), x).half().float()
+
+
+def tail_format(case: gc.Case) -> str:
+    """Operand format of this case's last FC layer in the product: "f16" / "tf32" when it runs fused with the heads and
+    the decode (`ovm_fc_tail`, csrc/fc_tail.cu: shared FC stack, class-agnostic heads, FC_DIM a power of two in
+    128..1024; the format is OVM_TAIL_PRECISION, default f16), else "bf16"."""
     import os
 
     cube = case.cube
-    return (cube.get("SHARED_FC", True) and not cube.get("DIMS_PRIORS_ENABLED", True) and cube.get("CLUSTER_BINS", 1) <= 1
-            and case.fc_dim in (128, 256, 512, 1024) and os.environ.get("OVM_FUSE_TAIL", "1") != "0"
-            and os.environ.get("OVM_TAIL_PRECISION", "tf32").lower() == "tf32")
+    fused = (cube.get("SHARED_FC", True) and not cube.get("DIMS_PRIORS_ENABLED", True) and cube.get("CLUSTER_BINS", 1) <= 1
+             and case.fc_dim in (128, 256, 512, 1024) and os.environ.get("OVM_FUSE_TAIL", "1") != "0")
+    return os.environ.get("OVM_TAIL_PRECISION", "f16").lower() if fused else "bf16"
 
 
-def fc_stack_product_operands(tail_tf32: bool):
+def fc_stack_product_operands(tail: str):
     """`lift_oracle._fc_stack` with the operands of every Linear rounded the way the product rounds them -- bf16
-    (round-to-nearest-even) everywhere, except TF32 for the last layer when it runs inside `ovm_fc_tail` -- and the
+    (round-to-nearest-even) everywhere, except fp16 (or TF32) for the last layer when it runs inside `ovm_fc_tail` -- and the
     products summed exactly (fp64), which is what the tcgen05 GEMMs compute up to fp32 summation order: the
     kernel-correctness oracle for the head, separate from the error of the number formats themselves."""
     import torch.nn.functional as F
@@ -58,8 +64,8 @@ def fc_stack_product_operands(tail_tf32: bool):
         while f"{prefix}.fc{num + 1}.weight" in w:
             num += 1
         for k in range(1, num + 1):
-            tf32 = tail_tf32 and k == num and num >= 2
-            rnd = round_tf32 if tf32 else (lambda t: t.bfloat16().float())
+            fmt = tail if (k == num and num >= 2) else "bf16"
+            rnd = {"tf32": round_tf32, "f16": round_f16, "bf16": lambda t: t.bfloat16().float()}[fmt]
             a = rnd(x).double()
             wt = rnd(w[f"{prefix}.fc{k}.weight"]).double()
             x = F.relu(F.linear(a, wt, w[f"{prefix}.fc{k}.bias"].double())).float()
@@ -71,7 +77,7 @@ def fc_stack_product_operands(tail_tf32: bool):
 def run_oracle(case: gc.Case, bf16_operands: bool = False):
     if bf16_operands:
         saved = lo._fc_stack
-        lo._fc_stack = fc_stack_product_operands(tail_is_tf32(case))
+        lo._fc_stack = fc_stack_product_operands(tail_format(case))
         try:
             return run_oracle(case)
         finally:

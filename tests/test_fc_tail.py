@@ -60,7 +60,7 @@ def _inputs(n, num_images, dev, seed):
 
 
 @pytest.mark.parametrize("fc_dim", [128, 256, 512, 1024])
-@pytest.mark.parametrize("fmt", ["tf32", "bf16"])
+@pytest.mark.parametrize("fmt", ["f16", "tf32", "bf16"])
 @pytest.mark.parametrize("n,K", [(1, 1024), (128, 64), (300, 200), (1600, 1024)])
 def test_fc_tail_matches_unfused_sequence(fc_dim, fmt, n, K):
     ops, eng, dev = _setup(fc_dim)
@@ -72,6 +72,12 @@ def test_fc_tail_matches_unfused_sequence(fc_dim, fmt, n, K):
     if fmt == "tf32":
         A, W = _tf32(h1), ops.round_tf32(W2.contiguous())
         assert torch.equal(W, _tf32(W2)), "ovm_round_tf32 differs from cvt.rna emulation"
+    elif fmt == "f16":
+        ld = (K + 7) // 8 * 8
+        A = torch.zeros(n, ld, device=dev, dtype=torch.float16)[:, :K]
+        A.copy_(h1)
+        W = ops.cast_f16(W2.contiguous())
+        assert torch.equal(W, W2.half()), "ovm_cast_f16 differs from torch's fp16 rounding"
     else:
         ld = (K + 7) // 8 * 8
         A = torch.zeros(n, ld, device=dev, dtype=torch.bfloat16)[:, :K]

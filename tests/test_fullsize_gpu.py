@@ -5,7 +5,7 @@ Per workload, all through the C ABI and compared with `oracle.lift_oracle.forwar
   * box-to-level assignment: bit-exact;
   * pooled features (fp32 `ovm_roi_align`): 1e-3 per box;
   * every record field of `ovm_lift_forward` against the oracle with the product's operand rounding (bf16 fc1,
-    TF32 fc2 -- helpers.fc_stack_product_operands): 1e-3 (kernel correctness);
+    fp16 fc2 -- helpers.fc_stack_product_operands): 1e-3 (kernel correctness);
   * against the all-fp32 oracle (format error of the bf16 head): north_star's 1e-2 on 3-D centres, dimensions,
     2-D centres, scores and on the 13 raw head outputs; pose and corners -- a Gram-Schmidt of six of those raw numbers
     -- per box against the raw error times the conditioning of the box's 6-D vector, plus relative L2 and the
@@ -56,7 +56,7 @@ def _oracle(w, inp, weights, product_operands):
 
     lo.tp.rotation_6d_to_matrix = capture
     if product_operands:
-        lo._fc_stack = helpers.fc_stack_product_operands(tail_tf32=True)
+        lo._fc_stack = helpers.fc_stack_product_operands("f16")
     try:
         with torch.no_grad():
             out = lo.forward_cube(inp.features, inp.boxes, inp.classes, inp.scores, inp.Ks, inp.im_dims,
@@ -156,7 +156,7 @@ def test_fullsize_parity(name):
     head = head.to(dev).eval()
     eng = head._get_engine()
     eng.prepare(dev, head.priors_dims_per_cat, head.priors_z_scales, getattr(head, "priors_z_stats", None))
-    assert eng.tail_fused and eng.tail_precision == "tf32", "the full-size workloads run the fused TF32 tail"
+    assert eng.tail_fused and eng.tail_precision == "f16", "the full-size workloads run the fused fp16 tail"
 
     feats = [f.to(dev) for f in inp.features]
     boxes = torch.cat(inp.boxes).to(dev)
