@@ -216,10 +216,11 @@ typedef struct {
                                   a separate bias/ReLU launch follows.  ceil(n/128) * ceil(fc_dim/256) are needed */
   int32_t num_tile_counters;
   int32_t splitk_flags_len;    /* int32 elements in splitk_flags */
-  float* splitk_slots;         /* optional fp32 [splitk_slots_len], 16-byte aligned: with it (and splitk_flags) the split-K
-                                  partial tiles of the first FC layer are exchanged through per-cluster slots with plain
-                                  stores and summed in a fixed order (bit-reproducible, no L2 atomics) instead of
-                                  red.global.add into acc.  OVM_SPLITK_SLOTS_LEN floats serve any n. */
+  float* splitk_slots;         /* optional fp32 [splitk_slots_len], 16-byte aligned: with it (and splitk_flags), and
+                                  OVM_GEMM_SLOTS=1 in the environment, the split-K partial tiles of the first FC layer are
+                                  exchanged through per-cluster slots with plain stores and summed in a fixed order
+                                  (bit-reproducible, no L2 atomics) instead of red.global.add into acc; measured 5 us
+                                  slower at C2, hence opt-in.  OVM_SPLITK_SLOTS_LEN floats serve any n. */
   int64_t splitk_slots_len;
   int32_t* splitk_flags;       /* int32 [splitk_flags_len], ZERO-FILLED once (left zeroed); OVM_SPLITK_FLAGS_LEN */
 } ovm_workspace_t;

@@ -1145,7 +1145,11 @@ int gemm_bf16_launch(const void* A, int64_t lda, const void* B, int64_t ldb, int
     const long long total = (long long)num_pair_tiles * g.kb_per_tile;
     const int clusters = (int)(total < kNumSMs / 2 ? total : kNumSMs / 2);
     // deterministic slot exchange when the workspace has the slots and no tile is shared by more than kMaxPartials + 1 clusters
-    static const bool slots_ok = [] { const char* v = getenv("OVM_GEMM_SLOTS"); return !v || atoi(v) != 0; }();
+    // Opt-in (OVM_GEMM_SLOTS=1): measured at C2, the slot exchange costs 56.4 us against 51.6 us for red.global.add --
+    // the owners' merge reads (2.6 partial tiles of 128 KB per CTA, ~1 us per L2 round trip on lines other SMs have just
+    // written, 12 loads in flight per lane) are slower than the L2's atomic units; prefetching the next chunk's partials
+    // needs registers the epilogue does not have (spills: 69 us).  What it buys is a bit-reproducible layer.
+    static const bool slots_ok = [] { const char* v = getenv("OVM_GEMM_SLOTS"); return v && atoi(v) != 0; }();
     const long long starts_per_tile = ((long long)g.kb_per_tile * clusters + total - 1) / total;   // cluster ranges starting in one tile, at most
     const bool use_slots = slots_ok && fin->slots && fin->slot_flags && starts_per_tile <= kMaxPartials &&
                            fin->slots_len >= (long long)clusters * 2 * BM * kPairBN && fin->flags_len >= clusters * 2 * kEpiWarps &&

@@ -174,8 +174,14 @@ def test_fullsize_parity(name):
     pooled, levels = ops.roi_align(feats, _cfg(w).scales, boxes, bidx, 7, 0, torch.float32)
     torch.cuda.synchronize()
     rec, raw, pooled, levels = rec.cpu(), raw.cpu(), pooled.cpu(), levels.cpu()
-    # no atomics anywhere on the path (fc1's split-K partials are summed from slots in a fixed order): bit-reproducible
-    assert torch.equal(rec, rec2.cpu()), "a repeated call must reproduce the records bit for bit"
+    import os
+    if os.environ.get("OVM_GEMM_SLOTS", "0") != "0":
+        # fc1's split-K partials are summed from per-cluster slots in a fixed order: no atomics anywhere, bit-reproducible
+        assert torch.equal(rec, rec2.cpu()), "a repeated call must reproduce the records bit for bit"
+    else:
+        # default: fc1's split-K partial sums meet in L2 atomics (red.global.add), whose order -- hence the last bits of
+        # h1 -- varies from run to run
+        assert float((rec - rec2.cpu()).abs().max()) <= 1e-4 * float(rec.abs().max()), "a repeated call must reproduce the records"
 
     ref, ref_raw6 = _oracle(w, inp, weights, False)
     # ---- levels: bit-exact, both from the stand-alone call and from inside the lift
