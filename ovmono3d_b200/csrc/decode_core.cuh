@@ -96,43 +96,32 @@ __device__ __forceinline__ BoxIn load_box_in(const DecodeArgs& a, int box) {
   return b;
 }
 
-// Decode one box.  hv = the selected head outputs (bias added) in the row order
-// deltas 0-1, dims 2-4, z 5, uncertainty 6 (if USE_CONFIDENCE), pose after that; `bin` = the box's depth bin
-// (roi_heads.py:436-444; 0 when CLUSTER_BINS == 1).  Every calling thread computes everything; the record (and the
-// optional raw head outputs) are written only when `write` is set.
-__device__ __forceinline__ void decode_record(const DecodeArgs& a, const int box, const BoxIn& in, const int bin,
-                                              const float (&hv)[kMaxHeadRows], const bool write,
-                                              const bool store_peers = true) {
+// ---- the decode in three parts, so that fc_tail_kernel can run the two independent chains of a box on two threads.
+// decode_record (below) runs them in sequence on one thread: the arithmetic is the same either way.
+
+struct BoxCam {   // derived from the call's inputs only (roi_heads.py:378-419): computed before the wait on the FC layer
+  float src_w, src_h, ctr_x, ctr_y, fx, fy, px, py, virtual_to_real;
+};
+__device__ __forceinline__ BoxCam box_camera(const ovm_decode_cfg_t& cfg, const BoxIn& in) {
+  BoxCam c;
+  // roi_heads.py:414-419
+  c.src_w = in.x2 - in.x1; c.src_h = in.y2 - in.y1;
+  c.ctr_x = in.x1 + 0.5f * c.src_w; c.ctr_y = in.y1 + 0.5f * c.src_h;
+  // roi_heads.py:378-408: K / ratio with [2,2] forced to 1; focal is the un-scaled K[1,1]
+  const float ratio = in.ratio, h_cur = in.h_cur;
+  c.fx = in.k00 / ratio; c.fy = in.k11 / ratio; c.px = in.k02 / ratio; c.py = in.k12 / ratio;
+  const float focal = in.k11;
+  const float h_orig = h_cur * ratio;
+  c.virtual_to_real = cfg.virtual_depth ? (h_cur * focal) / (cfg.virtual_focal * h_orig) : 1.f;
+  return c;
+}
+
+// Chain A: raw pose -> view rotation R (rows; cube_head.py:176-186) and raw dims -> dims (roi_heads.py:483-507).
+__device__ __forceinline__ void decode_pose_dims(const DecodeArgs& a, const BoxIn& in, const float (&pose_raw)[6],
+                                                 const float (&dims_raw)[3], float (&R)[9], float (&dims)[3]) {
   const ovm_decode_cfg_t& cfg = a.cfg;
   const bool per_class = cfg.dims_priors_enabled != 0;
   const int cls = in.valid ? in.cls : 0;
-
-  const float x1 = in.x1, y1 = in.y1, x2 = in.x2, y2 = in.y2;
-  // roi_heads.py:414-419
-  const float src_w = x2 - x1, src_h = y2 - y1;
-  const float ctr_x = x1 + 0.5f * src_w, ctr_y = y1 + 0.5f * src_h;
-
-  // roi_heads.py:378-408: K / ratio with [2,2] forced to 1; focal is the un-scaled K[1,1]
-  const float ratio = in.ratio, h_cur = in.h_cur;
-  const float fx = in.k00 / ratio, fy = in.k11 / ratio, px = in.k02 / ratio, py = in.k12 / ratio;
-  const float focal = in.k11;
-  const float h_orig = h_cur * ratio;
-  const float virtual_to_real = cfg.virtual_depth ? (h_cur * focal) / (cfg.virtual_focal * h_orig) : 1.f;
-
-  const int pose_n = cfg.pose_type == OVM_POSE_6D ? 6 : (cfg.pose_type == OVM_POSE_QUATERNION ? 4 : 3);
-  const int conf_rows = cfg.use_confidence ? 1 : 0;
-
-  const float deltas[2] = {hv[0], hv[1]};
-  const float dims_raw[3] = {hv[2], hv[3], hv[4]};
-  const float z_raw = hv[5];
-  float uncert = 0.f;
-  if (conf_rows) uncert = clip_min(hv[6], 0.01f);  // .clip(0.01), cube_head.py:164
-  float pose_raw[6];
-#pragma unroll
-  for (int j = 0; j < 6; ++j) pose_raw[j] = j < pose_n ? (conf_rows ? hv[7 + j] : hv[6 + j]) : 0.f;
-
-  // ---- pose -> R (rows), cube_head.py:176-186
-  float R[9];
   if (cfg.pose_type == OVM_POSE_6D) {
     const float a1x = pose_raw[0], a1y = pose_raw[1], a1z = pose_raw[2];
     const float a2x = pose_raw[3], a2y = pose_raw[4], a2z = pose_raw[5];
@@ -165,11 +154,6 @@ __device__ __forceinline__ void decode_record(const DecodeArgs& a, const int box
     matmul3(Rx, Ry, T);
     matmul3(T, Rz, R);
   }
-
-  // ---- xy and dims (roi_heads.py:480-507)
-  const float u = ctr_x + src_w * deltas[0];
-  const float v = ctr_y + src_h * deltas[1];
-  float dims[3];
 #pragma unroll
   for (int j = 0; j < 3; ++j) {
     if (per_class) {
@@ -185,10 +169,27 @@ __device__ __forceinline__ void decode_record(const DecodeArgs& a, const int box
       dims[j] = expf(dims_raw[j] > 5.f ? 5.f : dims_raw[j]);
     }
   }
+}
 
+// Chain B: deltas -> projected centre, allocentric rotation M (math_util.py:657-679; has_m false: the view rotation is
+// kept), z (roi_heads.py:515-549), back-projection, confidence and score (roi_heads.py:802-829).
+struct CentreOut {
+  float M[9];
+  int has_m;
+  float X, Y, z, u_out, v_out, score;
+};
+__device__ __forceinline__ CentreOut decode_centre(const DecodeArgs& a, const BoxIn& in, const BoxCam& c, const int bin,
+                                                   const float dx, const float dy, const float z_raw, const float uncert) {
+  const ovm_decode_cfg_t& cfg = a.cfg;
+  const int cls = in.valid ? in.cls : 0;
+  CentreOut o;
+  // ---- xy (roi_heads.py:480-481)
+  const float u = c.ctr_x + c.src_w * dx;
+  const float v = c.ctr_y + c.src_h * dy;
   // ---- allocentric -> egocentric (math_util.py:657-679)
+  o.has_m = 0;
   if (cfg.allocentric_pose) {
-    float rx = (u - px) / fx, ry = (v - py) / fy, rz = 1.f;
+    float rx = (u - c.px) / c.fx, ry = (v - c.py) / c.fy, rz = 1.f;
     const float rn = sqrtf(rx * rx + ry * ry + rz * rz);
     rx /= rn; ry /= rn; rz /= rn;
     const float angle = acosf(rz);
@@ -200,14 +201,10 @@ __device__ __forceinline__ void decode_record(const DecodeArgs& a, const int box
       const float angles = sqrtf(vx * vx + vy * vy + vz * vz);
       const float half = angles * 0.5f;
       const float s = fabsf(angles) < 1e-6f ? 0.5f - (angles * angles) / 48.f : sinf(half) / angles;
-      float M[9], T[9];
-      quat_to_matrix(cosf(half), vx * s, vy * s, vz * s, M);
-      matmul3(M, R, T);
-#pragma unroll
-      for (int i = 0; i < 9; ++i) R[i] = T[i];
+      quat_to_matrix(cosf(half), vx * s, vy * s, vz * s, o.M);
+      o.has_m = 1;
     }
   }
-
   // ---- z (roi_heads.py:515-549)
   float z = z_raw;
   if (cfg.z_type == OVM_Z_SIGMOID) {
@@ -219,17 +216,24 @@ __device__ __forceinline__ void decode_record(const DecodeArgs& a, const int box
     const float zlo = clip_min(st[0] - 3.f * st[1], 0.f), zhi = st[0] + 3.f * st[1];
     z = zlo + (zhi - zlo) * sigmoidf_(z);
   }
-  if (cfg.virtual_depth) z = z * virtual_to_real;
-
+  if (cfg.virtual_depth) z = z * c.virtual_to_real;
   // ---- back-projection, confidence, score (roi_heads.py:802-829)
-  const float X = z * (u - px) / fx;
-  const float Y = z * (v - py) / fy;
-  const float u_out = u * ratio, v_out = v * ratio;
-  const float last = cfg.use_confidence ? expf(-uncert) : v_out;  // cube_3D[:, -1]
-  const float score = a.scores ? sqrtf(in.score * last) : last;
+  o.X = z * (u - c.px) / c.fx;
+  o.Y = z * (v - c.py) / c.fy;
+  o.z = z;
+  o.u_out = u * in.ratio;
+  o.v_out = v * in.ratio;
+  const float last = cfg.use_confidence ? expf(-uncert) : o.v_out;  // cube_3D[:, -1]
+  o.score = a.scores ? sqrtf(in.score * last) : last;
+  return o;
+}
 
-  if (!write) return;
-  // ---- corners (math_util.py:172-193): x <-> L, y <-> H, z <-> W; box order is X,Y,Z,W,H,L
+// Corners (math_util.py:172-193: x <-> L, y <-> H, z <-> W; box order is X,Y,Z,W,H,L), the 48-float record, the optional
+// raw head outputs, the optional peer copies.
+__device__ __forceinline__ void write_record(const DecodeArgs& a, const int box, const BoxIn& in, const float (&R)[9],
+                                             const float (&dims)[3], const float X, const float Y, const float z,
+                                             const float u_out, const float v_out, const float score,
+                                             const float (&raw13)[13], const bool store_peers) {
   const float hw = dims[0] / 2.f, hh = dims[1] / 2.f, hl = dims[2] / 2.f;
   float rec[OVM_RECORD_WIDTH];
 #pragma unroll
@@ -246,7 +250,7 @@ __device__ __forceinline__ void decode_record(const DecodeArgs& a, const int box
   rec[29] = dims[0]; rec[30] = dims[1]; rec[31] = dims[2];
 #pragma unroll
   for (int i = 0; i < 9; ++i) rec[32 + i] = R[i];
-  rec[41] = x1; rec[42] = y1; rec[43] = x2; rec[44] = y2;
+  rec[41] = in.x1; rec[42] = in.y1; rec[43] = in.x2; rec[44] = in.y2;
   rec[45] = score;
   rec[46] = (float)in.cls;
   rec[47] = 0.f;
@@ -265,13 +269,53 @@ __device__ __forceinline__ void decode_record(const DecodeArgs& a, const int box
 #pragma unroll
     for (int i = 0; i < OVM_RECORD_WIDTH / 4; ++i) po[i] = make_float4(rec[4 * i], rec[4 * i + 1], rec[4 * i + 2], rec[4 * i + 3]);
   }
-  if (a.raw) {
+  if (a.raw) {   // deltas 2, z, dims 3, uncertainty (clipped), pose <= 6
     float4* ro = reinterpret_cast<float4*>(a.raw + (long long)box * 16);
-    ro[0] = make_float4(deltas[0], deltas[1], z_raw, dims_raw[0]);
-    ro[1] = make_float4(dims_raw[1], dims_raw[2], uncert, pose_raw[0]);
-    ro[2] = make_float4(pose_raw[1], pose_raw[2], pose_raw[3], pose_raw[4]);
-    ro[3] = make_float4(pose_raw[5], 0.f, 0.f, 0.f);
+    ro[0] = make_float4(raw13[0], raw13[1], raw13[2], raw13[3]);
+    ro[1] = make_float4(raw13[4], raw13[5], raw13[6], raw13[7]);
+    ro[2] = make_float4(raw13[8], raw13[9], raw13[10], raw13[11]);
+    ro[3] = make_float4(raw13[12], 0.f, 0.f, 0.f);
   }
+}
+
+// hv = the selected head outputs (bias added) in the row order deltas 0-1, dims 2-4, z 5, uncertainty 6 (if
+// USE_CONFIDENCE), pose after that  ->  the pieces the chains take
+struct HeadOut {
+  float deltas[2], dims_raw[3], z_raw, uncert, pose_raw[6];
+};
+__device__ __forceinline__ HeadOut split_heads(const ovm_decode_cfg_t& cfg, const float (&hv)[kMaxHeadRows]) {
+  const int pose_n = cfg.pose_type == OVM_POSE_6D ? 6 : (cfg.pose_type == OVM_POSE_QUATERNION ? 4 : 3);
+  const int conf_rows = cfg.use_confidence ? 1 : 0;
+  HeadOut h;
+  h.deltas[0] = hv[0]; h.deltas[1] = hv[1];
+  h.dims_raw[0] = hv[2]; h.dims_raw[1] = hv[3]; h.dims_raw[2] = hv[4];
+  h.z_raw = hv[5];
+  h.uncert = conf_rows ? clip_min(hv[6], 0.01f) : 0.f;   // .clip(0.01), cube_head.py:164
+#pragma unroll
+  for (int j = 0; j < 6; ++j) h.pose_raw[j] = j < pose_n ? (conf_rows ? hv[7 + j] : hv[6 + j]) : 0.f;
+  return h;
+}
+
+// Decode one box on one thread.  `bin` = the box's depth bin (roi_heads.py:436-444; 0 when CLUSTER_BINS == 1).  Every
+// calling thread computes everything; the record (and the optional raw head outputs) are written only when `write`.
+__device__ __forceinline__ void decode_record(const DecodeArgs& a, const int box, const BoxIn& in, const int bin,
+                                              const float (&hv)[kMaxHeadRows], const bool write,
+                                              const bool store_peers = true) {
+  const HeadOut h = split_heads(a.cfg, hv);
+  const BoxCam c = box_camera(a.cfg, in);
+  float R[9], dims[3];
+  decode_pose_dims(a, in, h.pose_raw, h.dims_raw, R, dims);
+  const CentreOut o = decode_centre(a, in, c, bin, h.deltas[0], h.deltas[1], h.z_raw, h.uncert);
+  if (o.has_m) {
+    float T[9];
+    matmul3(o.M, R, T);
+#pragma unroll
+    for (int i = 0; i < 9; ++i) R[i] = T[i];
+  }
+  if (!write) return;
+  const float raw13[13] = {h.deltas[0], h.deltas[1], h.z_raw, h.dims_raw[0], h.dims_raw[1], h.dims_raw[2], h.uncert,
+                           h.pose_raw[0], h.pose_raw[1], h.pose_raw[2], h.pose_raw[3], h.pose_raw[4], h.pose_raw[5]};
+  write_record(a, box, in, R, dims, o.X, o.Y, o.z, o.u_out, o.v_out, o.score, raw13, store_peers);
 }
 
 }  // namespace ovm

@@ -45,8 +45,9 @@ constexpr int kTailThreads = (2 + kTailEpiWarps) * 32;
 constexpr int kHwStride = 16;          // head rows per column in shared memory (13 used)
 constexpr int kMaxCS = 8;
 constexpr int kPartFloats = 2 * kMaxCS * kMaxHeadRows * (kTM / kMaxCS);   // [2 CS contributors][13][128 / CS rows]
+constexpr int kXchStride = 20;         // floats one box's two decoding threads exchange (M 9, has_m, X Y z u v score, 3 raw)
 constexpr size_t kTailSmemBytes = 1024 + (size_t)kTailStages * kTailStageBytes + 128 /* barriers, tmem slot */ +
-                                  (size_t)(kTN * kHwStride + kTN + 16 + kPartFloats) * 4;
+                                  (size_t)(kTN * kHwStride + kTN + 16 + kPartFloats + kTM * kXchStride) * 4;
 
 struct TailArgs {
   DecodeArgs d;          // feats / ld_feats unused
@@ -204,6 +205,7 @@ fc_tail_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   float* b2s = hw_t + kTN * kHwStride;                                                     // [128]
   float* hbias = b2s + kTN;                                                                // [16]
   float* part = hbias + 16;                                                                // [2 cs][13][rpc]
+  float* xch = part + kPartFloats;                                                         // [rpc][kXchStride]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) tail_stamp(g, 0);
@@ -250,11 +252,19 @@ fc_tail_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (e < kTN) b2s[e] = __ldg(g.bias + col0 + e);
   }
   // the boxes this CTA decodes are inputs of the call (complete before the chain's first kernel): loaded ahead of the wait
+  // Two threads per box: role 0 takes the pose / dims chain and writes the record, role 1 the centre chain (projected
+  // centre, allocentric rotation, depth, back-projection, score).  On one thread the decode is a ~1100-instruction
+  // dependent chain at ~10 cycles per instruction (5.9 us); the two chains are independent until the last matrix product.
   const int e = threadIdx.x - 64;
-  const int my_row = m_tile * kTM + rank * rpc + e;
-  const bool decoder = e >= 0 && e < rpc && my_row < g.d.n;
+  const int role = e >= rpc ? 1 : 0, t = e - role * rpc;
+  const int my_row = m_tile * kTM + rank * rpc + t;
+  const bool decoder = e >= 0 && e < 2 * rpc && my_row < g.d.n;
   BoxIn in{};
-  if (decoder) in = load_box_in(g.d, my_row);
+  BoxCam cam{};
+  if (decoder) {
+    in = load_box_in(g.d, my_row);
+    cam = box_camera(cfg, in);
+  }
 
   tcgen05_fence_before();
   cluster_sync_all();        // barriers initialised, TMEM allocated, staging visible; every CTA of the cluster has started
@@ -359,15 +369,46 @@ fc_tail_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     tcgen05_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)kTN) : "memory");
   }
+  float hv[kMaxHeadRows];
+#pragma unroll
+  for (int k = 0; k < kMaxHeadRows; ++k) hv[k] = 0.f;
   if (decoder) {
-    float hv[kMaxHeadRows];
 #pragma unroll
     for (int k = 0; k < kMaxHeadRows; ++k) {
+      // role 1 needs deltas (0, 1), z (5) and the uncertainty (6); role 0 dims (2..4) and the pose rows
+      const bool centre_row = k < 2 || k == 5 || (conf_rows && k == 6);
       float s = 0.f;
-      for (int c = 0; c < 2 * cs; ++c) s += part[(c * kMaxHeadRows + k) * rpc + e];   // fixed order: deterministic
+      if (centre_row == (role == 1))
+        for (int c = 0; c < 2 * cs; ++c) s += part[(c * kMaxHeadRows + k) * rpc + t];   // fixed order: deterministic
       hv[k] = s + hbias[k < nrows ? k : 0];
     }
-    decode_record(g.d, my_row, in, 0, hv, true, /*store_peers=*/false);
+  }
+  const HeadOut h = split_heads(cfg, hv);
+  float R[9], dims[3];
+  if (decoder && role == 0) decode_pose_dims(g.d, in, h.pose_raw, h.dims_raw, R, dims);
+  if (decoder && role == 1) {
+    const CentreOut o = decode_centre(g.d, in, cam, 0, h.deltas[0], h.deltas[1], h.z_raw, h.uncert);
+    float* x = xch + t * kXchStride;
+#pragma unroll
+    for (int i = 0; i < 9; ++i) x[i] = o.M[i];
+    x[9] = __int_as_float(o.has_m);
+    x[10] = o.X; x[11] = o.Y; x[12] = o.z; x[13] = o.u_out; x[14] = o.v_out; x[15] = o.score;
+    x[16] = h.deltas[0]; x[17] = h.deltas[1]; x[18] = h.z_raw; x[19] = h.uncert;
+  }
+  __syncthreads();
+  if (decoder && role == 0) {
+    const float* x = xch + t * kXchStride;
+    if (__float_as_int(x[9])) {
+      float M[9], T[9];
+#pragma unroll
+      for (int i = 0; i < 9; ++i) M[i] = x[i];
+      matmul3(M, R, T);
+#pragma unroll
+      for (int i = 0; i < 9; ++i) R[i] = T[i];
+    }
+    const float raw13[13] = {x[16], x[17], x[18], h.dims_raw[0], h.dims_raw[1], h.dims_raw[2], x[19],
+                             h.pose_raw[0], h.pose_raw[1], h.pose_raw[2], h.pose_raw[3], h.pose_raw[4], h.pose_raw[5]};
+    write_record(g.d, my_row, in, R, dims, x[10], x[11], x[12], x[13], x[14], x[15], raw13, /*store_peers=*/false);
   }
   if (g.d.num_peers > 0) {
     // fused gather: the CTA's records (contiguous rows) go to every peer rank with all threads, 16 bytes each, instead

@@ -16,6 +16,16 @@ SCORE_RTOL = 2e-6
 BOX_RTOL, BOX_ATOL = 1e-5, 1e-4
 
 
+@pytest.fixture(autouse=True)
+def _cpu_oracle_nms_rule(monkeypatch):
+    """The oracle is torchvision's CPU batched_nms, which leaves the coordinate trick above 1000 candidates (CUDA: 5000,
+    the plugin's default): run the plugin with the CPU rule so that both sides take the same arithmetic."""
+    from ovmono3d_b200.box_head import BoxBranchB200
+
+    monkeypatch.setattr(BoxBranchB200, "COORD_TRICK_MAX", 1000)
+
+
+
 def _oracle(case):
     logits, deltas, props = bc.build_case(case)
     boxes, probs = bo.predict(logits, deltas, props, bc.REG_WEIGHTS)
