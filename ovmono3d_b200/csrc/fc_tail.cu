@@ -373,15 +373,15 @@ fc_tail_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
   for (int k = 0; k < kMaxHeadRows; ++k) hv[k] = 0.f;
   if (decoder) {
+    // contributions outermost: 13 independent load + add chains per step (the other nesting ran one 16-long dependent
+    // chain per row, 13 times in a row: 3.7 of the decode's 5.9 us).  Fixed order: deterministic.
+    for (int c = 0; c < 2 * cs; ++c) {
+      const float* pc = part + (size_t)c * kMaxHeadRows * rpc + t;
 #pragma unroll
-    for (int k = 0; k < kMaxHeadRows; ++k) {
-      // role 1 needs deltas (0, 1), z (5) and the uncertainty (6); role 0 dims (2..4) and the pose rows
-      const bool centre_row = k < 2 || k == 5 || (conf_rows && k == 6);
-      float s = 0.f;
-      if (centre_row == (role == 1))
-        for (int c = 0; c < 2 * cs; ++c) s += part[(c * kMaxHeadRows + k) * rpc + t];   // fixed order: deterministic
-      hv[k] = s + hbias[k < nrows ? k : 0];
+      for (int k = 0; k < kMaxHeadRows; ++k) hv[k] += pc[k * rpc];
     }
+#pragma unroll
+    for (int k = 0; k < kMaxHeadRows; ++k) hv[k] += hbias[k < nrows ? k : 0];
   }
   const HeadOut h = split_heads(cfg, hv);
   float R[9], dims[3];
