@@ -69,6 +69,7 @@ struct GemmArgs {
   int fin_bf16;
   int f16;               // 16-bit outputs (DIRECT epilogue / fused finish) are fp16 instead of bf16
   int round_tf32;        // fp32 outputs (DIRECT epilogue / fused finish) are rounded to TF32: the next layer is a kind::tf32 MMA
+  int grid_finish;       // gemm_pair_kernel<false>: all CTAs finish 1/grid of the output after a grid-wide barrier
   // gemm_pair_kernel<true>: split-K partials meet in per-cluster slots (plain stores) instead of L2 atomics
   float* slots;          // [clusters][2 CTAs][128 rows][256 columns] fp32
   int* slot_flags;       // [clusters][2 CTAs][8 epilogue warps], zero between launches
@@ -903,7 +904,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1;
       if (threadIdx.x == 64) trace_stamp(g, 7);   // (last) partial tile added to the accumulator
-      if (g.tile_counters && m_tile * BM < g.M) {   // CTA-uniform; the odd last row tile of a pair may not exist
+      if (g.tile_counters && !g.grid_finish && m_tile * BM < g.M) {   // CTA-uniform; the odd last row tile of a pair may not exist
         // ---- fused finish of this CTA's 128-row tile (see gemm_bf16_kernel)
         __threadfence();
         asm volatile("bar.sync 2, %0;" ::"n"(kEpiWarps * 32) : "memory");
@@ -952,6 +953,66 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             }
           }
         }
+      }
+    }
+    if (!SLOTS && g.tile_counters && g.grid_finish) {
+      // ---- finish by everybody.  With per-tile counters the 52 CTAs that happen to complete a tile each read 128 KB
+      // back behind the other CTAs' atomics (5-8 us at the very end of the kernel, 96 SMs idle).  Here every CTA waits
+      // until ALL partials have been added (the grid is one wave: every CTA is resident, so the barrier cannot
+      // deadlock) and then finishes 1/grid of the output: 44 KB per CTA, every load in flight at once.
+      int* cnt = g.tile_counters;        // [0] arrivals, [1] departures; zero between launches
+      __threadfence();
+      asm volatile("bar.sync 2, %0;" ::"n"(kEpiWarps * 32) : "memory");
+      if (threadIdx.x == 64) {
+        atomicAdd(cnt, 1);
+        while (ld_acquire_gpu(cnt) < (int)gridDim.x) {
+        }
+      }
+      asm volatile("bar.sync 2, %0;" ::"n"(kEpiWarps * 32) : "memory");
+      if (threadIdx.x == 64) trace_stamp(g, 8);     // every partial of every tile has been added
+      const int n4 = g.N >> 2;
+      const long long total4 = (long long)g.M * n4;
+      const int et = threadIdx.x - 64;              // 0 .. 255
+      constexpr int kInFlight = 4;
+      for (long long i0 = (long long)blockIdx.x * (kEpiWarps * 32) + et; i0 < total4;
+           i0 += (long long)gridDim.x * (kEpiWarps * 32) * kInFlight) {
+        float4 x[kInFlight];
+        long long idx[kInFlight];
+#pragma unroll
+        for (int u = 0; u < kInFlight; ++u) {
+          idx[u] = i0 + (long long)u * gridDim.x * (kEpiWarps * 32);
+          if (idx[u] < total4) {
+            const int row = (int)(idx[u] / n4), c = (int)(idx[u] - (long long)row * n4) * 4;
+            x[u] = __ldcg(reinterpret_cast<const float4*>(accp + (long long)row * g.ldo + c));
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < kInFlight; ++u) {
+          if (idx[u] >= total4) continue;
+          const int row = (int)(idx[u] / n4), c = (int)(idx[u] - (long long)row * n4) * 4;
+          __stcg(reinterpret_cast<float4*>(accp + (long long)row * g.ldo + c), make_float4(0.f, 0.f, 0.f, 0.f));
+          float4 w = x[u];
+          if (g.bias) {
+            const float4 bv = __ldg(reinterpret_cast<const float4*>(g.bias + c));
+            w.x += bv.x; w.y += bv.y; w.z += bv.z; w.w += bv.w;
+          }
+          if (g.relu) {   // torch.relu keeps NaN
+            w.x = w.x < 0.f ? 0.f : w.x; w.y = w.y < 0.f ? 0.f : w.y;
+            w.z = w.z < 0.f ? 0.f : w.z; w.w = w.w < 0.f ? 0.f : w.w;
+          }
+          if (g.round_tf32) w = round_tf32(w);
+          const long long off = (long long)row * g.fin_ldo + c;
+          if (g.fin_bf16) {
+            *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(g.fin_out) + off) = pack16(w, g.f16);
+          } else {
+            *reinterpret_cast<float4*>(reinterpret_cast<float*>(g.fin_out) + off) = w;
+          }
+        }
+      }
+      asm volatile("bar.sync 2, %0;" ::"n"(kEpiWarps * 32) : "memory");
+      if (threadIdx.x == 64 && atomicAdd(cnt + 1, 1) == (int)gridDim.x - 1) {   // the last one out clears the barrier
+        cnt[0] = 0;
+        cnt[1] = 0;
       }
     }
   }
@@ -1154,6 +1215,11 @@ int gemm_bf16_launch(const void* A, int64_t lda, const void* B, int64_t ldb, int
     const bool use_slots = slots_ok && fin->slots && fin->slot_flags && starts_per_tile <= kMaxPartials &&
                            fin->slots_len >= (long long)clusters * 2 * BM * kPairBN && fin->flags_len >= clusters * 2 * kEpiWarps &&
                            !(reinterpret_cast<uintptr_t>(fin->slots) & 15);
+    // Opt-in (OVM_GEMM_GRIDFIN=1).  Measured at C2: the fc1 stage alone 53.4 -> 51.7 us, but the step 0.168 -> 0.172 ms:
+    // with every fc1 CTA held to the end, the next kernel's CTAs (resident 13 us early on the SMs of fc1 CTAs that finish
+    // first, staging their head weights) lose their head start.
+    static const bool gridfin = [] { const char* v = getenv("OVM_GEMM_GRIDFIN"); return v && atoi(v) != 0; }();
+    g.grid_finish = gridfin && !use_slots && fin->num_counters >= 2 && 2 * clusters <= kNumSMs;
     if (use_slots) {
       g.slots = fin->slots;
       g.slot_flags = fin->slot_flags;
