@@ -277,17 +277,17 @@ __device__ __forceinline__ void store_out(const RoiArgs& a, long long idx, float
 }
 
 // Direct path: thread per output scalar, global-memory sampling (any geometry, any P, NCHW or NHWC).
-__device__ void direct_path(const RoiArgs& a, const BoxGeom& g, int box, int c_begin, int c_end) {
+__device__ void direct_path(const RoiArgs& a, const BoxGeom& g, int box, int c_begin, int c_end, int tid, int nthreads) {
   const int PP = a.P * a.P;
   const int total = (c_end - c_begin) * PP;
   const long long out_row = (long long)box * a.out_ld;
   if (g.level < 0 || g.gw <= 0 || g.gh <= 0) {
-    for (int o = threadIdx.x; o < total; o += blockDim.x) store_out(a, out_row + (long long)c_begin * PP + o, 0.f);
+    for (int o = tid; o < total; o += nthreads) store_out(a, out_row + (long long)c_begin * PP + o, 0.f);
     return;
   }
   const RoiLevel lv = a.lv[g.level];
   const int H = lv.H, W = lv.W, C = a.C;
-  for (int o = threadIdx.x; o < total; o += blockDim.x) {
+  for (int o = tid; o < total; o += nthreads) {
     const int c = c_begin + o / PP;
     const int r = o % PP;
     const int ph = r / a.P, pw = r % a.P;
@@ -639,6 +639,44 @@ __device__ void sort_items(const RoiArgs& a, int* __restrict__ ws, const int* hd
   for (int box = tid + kKeep * 1024; box < a.n; box += 1024) emit(box, cost_of(box));
 }
 
+// One chunk's 32 x 49 staged results -> the box's output row (contiguous run), by the kConsumers pooling threads.
+__device__ __forceinline__ void write_chunk(const RoiArgs& a, const float* ob, long long out_row, int chunk, int tid) {
+  const int c0 = chunk * 32;
+  const int nvals = min(32, a.C - c0) * kP * kP;
+  const long long o0 = out_row + (long long)c0 * kP * kP;
+  if (a.out_bf16) {
+    __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(a.out) + o0;  // o0 is even: c0 % 32 == 0, out_ld is even
+    if (!(reinterpret_cast<uintptr_t>(out) & 15) && !(nvals & 7)) {
+      for (int i = tid; i < (nvals >> 3); i += kConsumers) {   // 8 values -> one 16-byte store
+        const float4 lo = *reinterpret_cast<const float4*>(ob + 8 * i);
+        const float4 hi = *reinterpret_cast<const float4*>(ob + 8 * i + 4);
+        __nv_bfloat162 b0 = __floats2bfloat162_rn(lo.x, lo.y), b1 = __floats2bfloat162_rn(lo.z, lo.w);
+        __nv_bfloat162 b2 = __floats2bfloat162_rn(hi.x, hi.y), b3 = __floats2bfloat162_rn(hi.z, hi.w);
+        uint4 pk;
+        pk.x = *reinterpret_cast<uint32_t*>(&b0);
+        pk.y = *reinterpret_cast<uint32_t*>(&b1);
+        pk.z = *reinterpret_cast<uint32_t*>(&b2);
+        pk.w = *reinterpret_cast<uint32_t*>(&b3);
+        *reinterpret_cast<uint4*>(out + 8 * i) = pk;
+      }
+    } else {
+      for (int i = tid; i < (nvals >> 1); i += kConsumers) {
+        const float2 v = *reinterpret_cast<const float2*>(ob + 2 * i);
+        *reinterpret_cast<__nv_bfloat162*>(out + 2 * i) = __floats2bfloat162_rn(v.x, v.y);
+      }
+      if ((nvals & 1) && tid == 0) out[nvals - 1] = __float2bfloat16_rn(ob[nvals - 1]);
+    }
+  } else {
+    float* out = reinterpret_cast<float*>(a.out) + o0;
+    if (!(reinterpret_cast<uintptr_t>(out) & 15) && !(nvals & 3)) {
+      for (int i = tid; i < (nvals >> 2); i += kConsumers)
+        *reinterpret_cast<float4*>(out + 4 * i) = *reinterpret_cast<const float4*>(ob + 4 * i);
+    } else {
+      for (int i = tid; i < nvals; i += kConsumers) out[i] = ob[i];
+    }
+  }
+}
+
 // meta layout (ints): [0..6] x bin lo, [7..13] x bin hi, [14..20] y bin lo, [21..27] y bin hi (lo > hi: no valid sample)
 // kRingFloats: shared-memory ring of footprint stages; kStageFloats: largest stage (rows x Wt x 32 channels) the TMA
 // path accepts.
@@ -707,7 +745,7 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) roi_align_kernel(const _
   const int flags = hdr[H_FLAGS];
   const long long out_row = (long long)box * a.out_ld;
   if (flags & HF_DIRECT) {  // block-uniform: what TMA cannot address or a stage cannot hold
-    direct_path(a, g, box, c_begin, c_end);
+    direct_path(a, g, box, c_begin, c_end, tid, kThreads);
     return;
   }
   if (flags & HF_EMPTY) {   // every sample out of range: the reference's sum is empty
@@ -880,40 +918,7 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) roi_align_kernel(const _
     }
     asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory");
     if (tid == 0 && chunk - chunk_begin < 8) trace_stamp(a, 4 + chunk - chunk_begin);
-    const int c0 = chunk * 32;
-    const int nvals = min(32, a.C - c0) * kP * kP;
-    const long long o0 = out_row + (long long)c0 * kP * kP;
-    if (a.out_bf16) {
-      __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(a.out) + o0;  // o0 is even: c0 % 32 == 0, out_ld is even
-      if (!(reinterpret_cast<uintptr_t>(out) & 15) && !(nvals & 7)) {
-        for (int i = tid; i < (nvals >> 3); i += kConsumers) {   // 8 values -> one 16-byte store
-          const float4 lo = *reinterpret_cast<const float4*>(ob + 8 * i);
-          const float4 hi = *reinterpret_cast<const float4*>(ob + 8 * i + 4);
-          __nv_bfloat162 b0 = __floats2bfloat162_rn(lo.x, lo.y), b1 = __floats2bfloat162_rn(lo.z, lo.w);
-          __nv_bfloat162 b2 = __floats2bfloat162_rn(hi.x, hi.y), b3 = __floats2bfloat162_rn(hi.z, hi.w);
-          uint4 pk;
-          pk.x = *reinterpret_cast<uint32_t*>(&b0);
-          pk.y = *reinterpret_cast<uint32_t*>(&b1);
-          pk.z = *reinterpret_cast<uint32_t*>(&b2);
-          pk.w = *reinterpret_cast<uint32_t*>(&b3);
-          *reinterpret_cast<uint4*>(out + 8 * i) = pk;
-        }
-      } else {
-        for (int i = tid; i < (nvals >> 1); i += kConsumers) {
-          const float2 v = *reinterpret_cast<const float2*>(ob + 2 * i);
-          *reinterpret_cast<__nv_bfloat162*>(out + 2 * i) = __floats2bfloat162_rn(v.x, v.y);
-        }
-        if ((nvals & 1) && tid == 0) out[nvals - 1] = __float2bfloat16_rn(ob[nvals - 1]);
-      }
-    } else {
-      float* out = reinterpret_cast<float*>(a.out) + o0;
-      if (!(reinterpret_cast<uintptr_t>(out) & 15) && !(nvals & 3)) {
-        for (int i = tid; i < (nvals >> 2); i += kConsumers)
-          *reinterpret_cast<float4*>(out + 4 * i) = *reinterpret_cast<const float4*>(ob + 4 * i);
-      } else {
-        for (int i = tid; i < nvals; i += kConsumers) out[i] = ob[i];
-      }
-    }
+    write_chunk(a, ob, out_row, chunk, tid);
   }
   if (tid == 0) {
     trace_stamp(a, 12);
