@@ -57,6 +57,7 @@ WORKLOAD = ("C2: OVMono3D_dinov2_SFP lift, 16 images x 100 boxes per rank-step, 
 _C2_WORKLOAD = WORKLOAD
 CONFIG = "C2"
 SEED = 1235
+LAYOUT = "nchw"     # --layout: memory format of the feature pyramid ("nchw" = what the reference's backbone emits)
 STREAM = False      # C4: the steps are consecutive batches of one stream (no L2 flush between them, one event pair)
 
 
@@ -82,7 +83,9 @@ def set_workload(name: str) -> None:
 
 def config_dict(n: int) -> Dict[str, object]:
     """`config` of the JSON line: the workload only, identical in both arms (what is arm-specific goes to `method`)."""
-    return {"workload": WORKLOAD, "name": CONFIG, "images_per_step_per_gpu": NUM_IMAGES, "boxes_per_step_per_gpu": n}
+    w = WORKLOAD if LAYOUT == "nchw" else WORKLOAD.replace("fp32 NCHW", "fp32 channels-last (torch.channels_last, NHWC)")
+    return {"workload": w, "name": CONFIG, "images_per_step_per_gpu": NUM_IMAGES, "boxes_per_step_per_gpu": n,
+            "layout": LAYOUT}
 
 
 def _peaks() -> Dict[str, float]:
@@ -248,10 +251,12 @@ def roi_align_algorithmic_bytes(boxes: np.ndarray, levels: np.ndarray, out_elt: 
 class DeviceBatch:
     """One batch with every input of the lift resident in HBM."""
 
-    def __init__(self, inp, device):
+    def __init__(self, inp, device, layout: Optional[str] = None):
         n_per = [len(b) for b in inp.boxes]
         self.n = sum(n_per)
         self.features = [f.to(device) for f in inp.features]
+        if (layout or LAYOUT) == "channels_last":
+            self.features = [f.contiguous(memory_format=torch.channels_last) for f in self.features]
         self.boxes = torch.cat(inp.boxes).to(device).contiguous()
         self.classes = torch.cat(inp.classes).to(device).contiguous()
         self.scores = torch.cat(inp.scores).to(device).contiguous()
@@ -268,7 +273,8 @@ class HostBatch:
     """One batch in pinned host memory, shaped the way the reference's caller holds it (per-image lists)."""
 
     def __init__(self, inp):
-        self.features = [f.pin_memory() for f in inp.features]
+        self.features = [(f.contiguous(memory_format=torch.channels_last) if LAYOUT == "channels_last" else f).pin_memory()
+                         for f in inp.features]
         self.boxes = [b.pin_memory() for b in inp.boxes]
         self.classes = [c.pin_memory() for c in inp.classes]
         self.scores = [s.pin_memory() for s in inp.scores]
@@ -437,6 +443,38 @@ def run_ours(args) -> Dict[str, object]:
     }
     if rank == 0:
         out.update(kernel_breakdown(eng, dbs, flush, lift, K, peaks))
+    if rank == 0 and world == 1 and LAYOUT == "nchw" and not STREAM:
+        # the same steps on a torch.channels_last copy of the same pyramids (what a channels-last backbone hands over
+        # without a copy): reported beside the headline, which stays on the reference's own NCHW layout
+        cl = [DeviceBatch(x, device, layout="channels_last") for x in inputs]
+        for i in range(W):
+            flush.zero_()
+            lift(cl[i % num_sets])
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+        for i in range(K):
+            flush.zero_()
+            ev[i][0].record()
+            got = lift(cl[i % num_sets])
+            ev[i][1].record()
+        torch.cuda.synchronize()
+        cl_ms = float(np.mean([a_.elapsed_time(b_) for a_, b_ in ev]))
+        want = lift(dbs[(K - 1) % num_sets])
+        dev_rel = float(((got - want)[:, :47].abs().max() / want[:, :47].abs().max()).item())
+        kb = kernel_breakdown(eng, cl, flush, lift, K, peaks)
+        tp = os.path.join(ROOT, "profiles", "traffic.json")
+        traffic = None
+        if os.path.exists(tp):
+            with open(tp) as f:
+                traffic = json.load(f).get("roi_align_channels_last")
+        out["channels_last_pyramid"] = {
+            "ms_per_step": cl_ms, "value": n / (cl_ms * 1e-3), "unit": UNIT,
+            "roi_align": dict(kb["kernels"]["roi_align"], traffic=traffic),
+            "stages_ms": {k: v["ms"] for k, v in kb["kernels"].items()},
+            "max_rel_diff_vs_nchw_records": dev_rel,
+            "what": "same batches with the pyramids in torch.channels_last (no copy inside the step): roi_align_kernel<.., "
+                    "channels-last> reads [row][column][64 channels] tiles; `python bench.py --layout channels_last` runs "
+                    "every arm of this file on that layout"}
+        del cl
     barrier()
     out.update(run_e2e(head, names, inputs, device, K, W, world, lift))
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -681,10 +719,14 @@ def main() -> None:
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--layout", choices=["nchw", "channels_last"], default="nchw",
+                    help="memory format of the feature pyramid (default: the reference's NCHW)")
     ap.add_argument("--config", default="C2",
                     help="BASELINE.json config to run (default C2, the one the metric is quoted on): C1, C2, C3-1x2000, "
                          "C3-8x2000, C3-8x300, C4 (the C2 batch streamed, no L2 flush), C5-sfp4, C5-dla, C5-c128, C5-c512")
     args = ap.parse_args()
+    global LAYOUT
+    LAYOUT = args.layout
     set_workload(args.config)
     # exactly one JSON line on stdout: libraries that print there (NCCL's version banner under NCCL_DEBUG) go to stderr
     sys.stdout.flush()

@@ -51,8 +51,9 @@ constexpr int kWyFloats = kP * kMaxRows;
 constexpr int kOutFloats = 32 * kP * kP;   // one chunk of results
 constexpr int kMetaInts = 72;              // 32 spare + the work item's header (kHdrInts)
 constexpr int kMaxSlots = 8;               // ring slots (a slot is as large as the box's stage, not kStageFloats)
-constexpr size_t roi_smem_bytes(int ring_floats) {
-  return 1024 + (size_t)ring_floats * 4 + (size_t)(2 * kOutFloats + kWxFloats + kWyFloats) * 4 + kMetaInts * 4 + 2 * kMaxSlots * 8;
+constexpr size_t roi_smem_bytes(int ring_floats, bool cl = false) {
+  return 1024 + (size_t)ring_floats * 4 + (size_t)(2 * kOutFloats + (cl ? 2 : 1) * kWxFloats + kWyFloats) * 4 + kMetaInts * 4 +
+         2 * kMaxSlots * 8;
 }
 constexpr int kWidths = 3;                 // tensor-map tile widths: Wt = 8, 16, 32
 constexpr int kHeights = 5;                // tensor-map tile heights: 1, 2, 4, 8, 16 footprint rows per TMA instruction
@@ -86,6 +87,8 @@ struct RoiArgs {
   int evict_first;              // feature loads carry the L2 evict_first policy (OVM_ROI_EVICT)
   int ring_floats, stage_floats;   // shared-memory ring / largest stage of the pooling kernel that will run (plan_box needs them)
   const int* box_hdr;              // [n][kHdrInts] per-box headers written by roi_plan_kernel (with `order`)
+  int cl;                          // every level is channels-last (NHWC) and TMA-addressable: roi_align_kernel<.., true>
+  int chunk_ch;                    // channels per chunk: 32 (NCHW: lane = channel) or 64 (channels-last: lane = 2 channels)
   unsigned long long* trace;    // optional [grid, 16] %globaltimer stamps (ovm_roi_set_trace), else NULL
 };
 
@@ -107,6 +110,8 @@ thread_local unsigned long long* g_roi_trace = nullptr;
 struct RoiTune {
   int split_pct;    // OVM_ROI_SPLIT   cost of a work item, in % of the average box, above which a box is cut along the channels
   int promo;        // OVM_ROI_PROMO   L2 promotion of the tensor maps: 0 none, 1 64 B, 2 128 B, 3 256 B
+  int promo_cl;     // OVM_ROI_PROMO_CL  same for channels-last maps (a pixel's chunk is one 256-byte run)
+  int cl;           // OVM_ROI_CL      0: channels-last pyramids take the direct path (no TMA kernel)
   int align8;       // OVM_ROI_ALIGN8  footprint starts on a 32-byte sector (8 floats) instead of 16 bytes
   int stages;       // OVM_ROI_STAGES  2: 48 KB ring (3 CTAs / SM), 3: 36 KB ring and 64 registers (4 CTAs / SM)
   int min_slots;    // OVM_ROI_MINSLOTS  prefer stage geometries (narrower tiles, row groups) that leave this many ring slots
@@ -119,6 +124,8 @@ const RoiTune& roi_tune() {
     RoiTune r;
     r.split_pct = env("OVM_ROI_SPLIT", 400);
     r.promo = env("OVM_ROI_PROMO", 2);
+    r.promo_cl = env("OVM_ROI_PROMO_CL", 3);
+    r.cl = env("OVM_ROI_CL", 1);
     r.align8 = env("OVM_ROI_ALIGN8", 0);
     r.stages = env("OVM_ROI_STAGES", 2);
     r.min_slots = env("OVM_ROI_MINSLOTS", 1);
@@ -365,6 +372,36 @@ __device__ __forceinline__ void consume_tile(const float* __restrict__ slab0, in
   }
 }
 
+// Channels-last tiles ([row][column][64 channels], no swizzle): lane owns channels 2 lane, 2 lane + 1 of the chunk, so
+// every FFMA2 works on the lane's channel PAIR -- one 64-bit shared-memory load per (row, column), one FFMA2 per row for
+// the vertical pass and one per bin for the horizontal one (the column weights are stored duplicated, (w, w)).
+template <int NY>
+__device__ __forceinline__ void consume_tile_cl(const float* __restrict__ slab0, int slab_floats, int ncol,
+                                                const float (&wyr)[4], const float* __restrict__ wy, int ny,
+                                                const float2* __restrict__ wx2, uint64_t (&acc)[kP]) {
+#pragma unroll 2
+  for (int x = 0; x < ncol; ++x) {
+    const float* p = slab0 + x * 64;
+    uint64_t v = 0;
+    if (NY > 0) {
+#pragma unroll
+      for (int r = 0; r < NY; ++r)
+        v = ffma2(pack2(wyr[r], wyr[r]), *reinterpret_cast<const uint64_t*>(p + r * slab_floats), v);
+    } else {
+      for (int r = 0; r < ny; ++r) v = ffma2(pack2(wy[r], wy[r]), *reinterpret_cast<const uint64_t*>(p + r * slab_floats), v);
+    }
+    const ulonglong2* w = reinterpret_cast<const ulonglong2*>(wx2 + x * 8);
+    const ulonglong2 w01 = w[0], w23 = w[1], w45 = w[2], w67 = w[3];
+    acc[0] = ffma2(w01.x, v, acc[0]);
+    acc[1] = ffma2(w01.y, v, acc[1]);
+    acc[2] = ffma2(w23.x, v, acc[2]);
+    acc[3] = ffma2(w23.y, v, acc[3]);
+    acc[4] = ffma2(w45.x, v, acc[4]);
+    acc[5] = ffma2(w45.y, v, acc[5]);
+    acc[6] = ffma2(w67.x, v, acc[6]);
+  }
+}
+
 // One warp plans one box: level, sampling geometry, the pixel range of every bin, the stage geometry (tile width, row
 // groups) of the TMA pipeline, and the footprint area the work-item planner balances by -> the 40-int header `h`
 // (warp-private).  Lanes 0..27 each take one end sample of one bin; everything else is computed redundantly.
@@ -427,7 +464,7 @@ __device__ void plan_box_warp(const RoiArgs& a, float x1, float y1, float x2, fl
       // ---- column tiling: the innermost TMA coordinate must be a multiple of 16 bytes (measured: anything else
       // faults), so the footprint starts at the 4-float boundary at or below its first column
       y_lo = yl;
-      x0 = x_lo & a.xalign_mask;
+      x0 = a.cl ? x_lo : (x_lo & a.xalign_mask);   // channels-last: the innermost TMA coordinate is the channel
       fw = x_hi - x0 + 1;
       rows_total = y_hi - y_lo + 1;
       // Row groups: a stage holds the pixel rows of G consecutive bin-rows (G = 7: the whole footprint; 4, 2, 1: tall
@@ -453,9 +490,9 @@ __device__ void plan_box_warp(const RoiArgs& a, float x1, float y1, float x2, fl
         int ws = -1, bp = INT_MAX;
 #pragma unroll
         for (int k = kWidths - 1; k >= 0; --k) {
-          const int wt = 8 << k;
+          const int wt = (a.cl ? 4 : 8) << k;   // columns per tile; channels-last tiles hold 64 channels per column
           const int pad = (fw + wt - 1) / wt * wt;
-          const int stage = rm * wt * 32;
+          const int stage = rm * (8 << k) * 32;
           if (stage <= a.stage_floats && stage * need_slots <= a.ring_floats && pad < bp) {
             bp = pad;
             ws = k;
@@ -564,7 +601,7 @@ __device__ void sort_items(const RoiArgs& a, int* __restrict__ ws, const int* hd
     if (lane == 0) mean_area = t / (float)a.n;
   }
   __syncthreads();
-  const int chunks = (a.C + 31) / 32;
+  const int chunks = (a.C + a.chunk_ch - 1) / a.chunk_ch;
   const float mean = mean_area * a.split_factor;
   // chunks per item: the largest power of two with area * cpi <= mean * chunks (never more than the launch's
   // chunks_per_split, which spreads a small batch over the SMs); pieces per box <= max(1, 2 area / mean)
@@ -641,8 +678,8 @@ __device__ void sort_items(const RoiArgs& a, int* __restrict__ ws, const int* hd
 
 // One chunk's 32 x 49 staged results -> the box's output row (contiguous run), by the kConsumers pooling threads.
 __device__ __forceinline__ void write_chunk(const RoiArgs& a, const float* ob, long long out_row, int chunk, int tid) {
-  const int c0 = chunk * 32;
-  const int nvals = min(32, a.C - c0) * kP * kP;
+  const int c0 = chunk * a.chunk_ch;
+  const int nvals = min(a.chunk_ch, a.C - c0) * kP * kP;
   const long long o0 = out_row + (long long)c0 * kP * kP;
   if (a.out_bf16) {
     __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(a.out) + o0;  // o0 is even: c0 % 32 == 0, out_ld is even
@@ -680,7 +717,11 @@ __device__ __forceinline__ void write_chunk(const RoiArgs& a, const float* ob, l
 // meta layout (ints): [0..6] x bin lo, [7..13] x bin hi, [14..20] y bin lo, [21..27] y bin hi (lo > hi: no valid sample)
 // kRingFloats: shared-memory ring of footprint stages; kStageFloats: largest stage (rows x Wt x 32 channels) the TMA
 // path accepts.
-template <int kRingFloats, int kStageFloats, int kMinBlocks>
+// kCL: the pyramid is channels-last (NHWC): tiles are [row][column][64 channels] (tensor maps {C, W, N*H}, box {64, Wt, R},
+// Wt = 4 / 8 / 16 columns, no swizzle), a chunk is 64 channels and lane owns a channel pair (consume_tile_cl).  A
+// footprint pixel is then one contiguous 256-byte run: whole L2 lines, no partially used sectors, and the column range
+// need not be rounded to 16 bytes.
+template <int kRingFloats, int kStageFloats, int kMinBlocks, bool kCL>
 __global__ void __launch_bounds__(kThreads, kMinBlocks) roi_align_kernel(const __grid_constant__ RoiMaps maps, const RoiArgs a) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
@@ -688,8 +729,10 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) roi_align_kernel(const _
   uint8_t* aligned = smem_raw + (base - raw);
   float* stages = reinterpret_cast<float*>(aligned);                 // kStages * kStageFloats
   float* outbuf = stages + kRingFloats;                   // 2 * kOutFloats
-  float* Wx = outbuf + 2 * kOutFloats;                               // [col][8]
-  float* Wy = Wx + kWxFloats;                                        // [ph][kMaxRows]
+  constexpr int kWxF = kCL ? 2 * kWxFloats : kWxFloats;
+  constexpr int kCh = kCL ? 64 : 32;                                 // channels per chunk
+  float* Wx = outbuf + 2 * kOutFloats;                               // [col][8] (channels-last: float2 (w, w) entries)
+  float* Wy = Wx + kWxF;                                             // [ph][kMaxRows]
   int* meta = reinterpret_cast<int*>(Wy + kWyFloats);
   const uint32_t bars = smem_u32(meta + kMetaInts);                  // full[kStages], empty[kStages]
 
@@ -700,7 +743,7 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) roi_align_kernel(const _
 
   pdl_trigger();
   // shared-memory set-up that depends on nothing: the tap tables are cleared, the ring's barriers initialised
-  for (int i = tid; i < (kWxFloats + kWyFloats) / 4; i += kThreads)
+  for (int i = tid; i < (kWxF + kWyFloats) / 4; i += kThreads)
     reinterpret_cast<float4*>(Wx)[i] = make_float4(0.f, 0.f, 0.f, 0.f);   // Wy follows Wx
   if (tid == 0) {
     for (int s = 0; s < kMaxSlots; ++s) {
@@ -725,7 +768,7 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) roi_align_kernel(const _
                   lane, hdr);
     if (lane == 0) {
       const int cb = (int)(blockIdx.x % a.splits) * a.chunks_per_split;
-      hdr[H_CHUNKS] = cb | ((min((a.C + 31) / 32, cb + a.chunks_per_split) - cb) << 16);
+      hdr[H_CHUNKS] = cb | ((min((a.C + kCh - 1) / kCh, cb + a.chunks_per_split) - cb) << 16);
       if (cb == 0 && a.level_out) a.level_out[bx] = hdr[H_LEVEL];
     }
   }
@@ -733,8 +776,8 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) roi_align_kernel(const _
   if (tid == 0) trace_stamp(a, 1);
   const int box = hdr[H_BOX];
   const int chunk_begin = hdr[H_CHUNKS] & 0xffff, chunk_end = chunk_begin + (hdr[H_CHUNKS] >> 16);
-  const int c_begin = chunk_begin * 32;
-  const int c_end = min(a.C, chunk_end * 32);
+  const int c_begin = chunk_begin * kCh;
+  const int c_end = min(a.C, chunk_end * kCh);
   BoxGeom g;
   g.level = hdr[H_LEVEL];
   g.b = hdr[H_IMAGE];
@@ -775,9 +818,9 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) roi_align_kernel(const _
     rows = hi - lo + 1;
   };
   const int ngroups = (kP + G - 1) / G;
-  const int Wt = 8 << wsel;
+  const int Wt = (kCL ? 4 : 8) << wsel;
   const int ntiles = ((fw + Wt - 1) / Wt * Wt) / Wt;
-  const int slab_floats = 32 * Wt;               // one footprint row of one chunk: [32 channels][Wt]
+  const int slab_floats = 32 * (8 << wsel);      // one footprint row of one chunk: [32 channels][Wt] / [Wt][64 channels]
   // The ring is cut into slots of this box's stage size: small footprints get up to kMaxSlots stages in flight.
   const int slot_floats = rmax * slab_floats;
   const int nslots = min(kMaxSlots, kRingFloats / slot_floats);
@@ -795,7 +838,7 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) roi_align_kernel(const _
       uint64_t policy = 0;
       if (a.evict_first) asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
       for (int chunk = chunk_begin; chunk < chunk_end; ++chunk) {
-        const int cc = g.b * a.C + chunk * 32;
+        const int cc = kCL ? chunk * 64 : g.b * a.C + chunk * 32;   // channels-last: first channel; NCHW: first plane
         for (int grp = 0; grp < ngroups; ++grp) {
           int gy, rows;
           group_span(G, grp, gy, rows);
@@ -811,7 +854,9 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) roi_align_kernel(const _
 #pragma unroll
             for (int k = kHeights - 1; k >= 0; --k) {
               while (rows - r >= (1 << k)) {
-                if (a.evict_first)
+                if (kCL)
+                  tma_load_3d(dst + (uint32_t)(r * slab_floats) * 4u, map + k, full, cc, xc, g.b * H + gy + r);
+                else if (a.evict_first)
                   tma_load_3d_hint(dst + (uint32_t)(r * slab_floats) * 4u, map + k, full, xc, cc, gy + r, policy);
                 else
                   tma_load_3d(dst + (uint32_t)(r * slab_floats) * 4u, map + k, full, xc, cc, gy + r);
@@ -839,7 +884,13 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) roi_align_kernel(const _
     for (int i = 0; i < grid; ++i) {
       Tap t = make_tap(start, bin, grid, lane, i, size);
       if (!t.valid) continue;
-      if (is_x) {
+      if (is_x && kCL) {
+        float2* w2 = reinterpret_cast<float2*>(Wx);
+        float2& a0 = w2[(t.lo - x0) * 8 + lane];
+        a0 = make_float2(a0.x + t.h, a0.y + t.h);
+        float2& a1 = w2[(t.hi - x0) * 8 + lane];
+        a1 = make_float2(a1.x + t.l, a1.y + t.l);
+      } else if (is_x) {
         Wx[(t.lo - x0) * 8 + lane] += t.h;
         Wx[(t.hi - x0) * 8 + lane] += t.l;
       } else {
@@ -871,7 +922,7 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) roi_align_kernel(const _
   // 16-byte unit j of lane c's row sits at unit j ^ sw (the TMA swizzle of the slab, see the header comment)
   const int sw = wsel == 2 ? (lane & 7) : (wsel == 1 ? ((lane >> 1) & 3) : ((lane >> 2) & 1));
   const int nx4_tile = Wt >> 2;
-  const int row_off = (ys - my_gy) * slab_floats + lane * Wt;
+  const int row_off = (ys - my_gy) * slab_floats + (kCL ? 2 * lane : lane * Wt);
   float wyr[4];   // row weights of a bin-row of up to 4 pixel rows (the table is zero past the bin-row's rows)
 #pragma unroll
   for (int r = 0; r < 4; ++r) wyr[r] = wy[r];
@@ -881,6 +932,7 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) roi_align_kernel(const _
   long long waited = 0;
   for (int chunk = chunk_begin; chunk < chunk_end; ++chunk) {
     PoolAcc acc{0, 0, 0, 0.f};
+    uint64_t acc2[kP] = {0, 0, 0, 0, 0, 0, 0};   // channels-last: bin pw of the lane's channel pair
     for (int grp = 0; grp < ngroups; ++grp)
     for (int tile = 0; tile < ntiles; ++tile) {
       const long long tw = a.trace ? clock64() : 0;
@@ -891,7 +943,18 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) roi_align_kernel(const _
       if (ny > 0 && grp == my_grp) {
         const float* slab0 = stages + s * slot_floats + row_off;
         const int ncol4 = min(nx4_tile, (fw - tile * Wt + 3) >> 2);   // columns past the footprint carry zero weight
-        const float* wxt = Wx + tile * Wt * 8;
+        const float* wxt = Wx + tile * Wt * (kCL ? 16 : 8);
+        if (kCL) {
+          const int ncol = min(Wt, fw - tile * Wt);
+          const float2* wx2 = reinterpret_cast<const float2*>(wxt);
+          switch (ny) {
+            case 1: consume_tile_cl<1>(slab0, slab_floats, ncol, wyr, wy, ny, wx2, acc2); break;
+            case 2: consume_tile_cl<2>(slab0, slab_floats, ncol, wyr, wy, ny, wx2, acc2); break;
+            case 3: consume_tile_cl<3>(slab0, slab_floats, ncol, wyr, wy, ny, wx2, acc2); break;
+            case 4: consume_tile_cl<4>(slab0, slab_floats, ncol, wyr, wy, ny, wx2, acc2); break;
+            default: consume_tile_cl<0>(slab0, slab_floats, ncol, wyr, wy, ny, wx2, acc2); break;
+          }
+        } else
         switch (ny) {   // warp-uniform; a bin-row is rarely taller than 2-3 pixels
           case 1: consume_tile<1>(slab0, slab_floats, sw, ncol4, wyr, wy, ny, wxt, acc); break;
           case 2: consume_tile<2>(slab0, slab_floats, sw, ncol4, wyr, wy, ny, wxt, acc); break;
@@ -908,8 +971,17 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) roi_align_kernel(const _
       }
     }
     // ---- stage the chunk's 32 x 49 results and write them as one contiguous run
-    float* ob = outbuf + ((chunk - chunk_begin) & 1) * kOutFloats;
-    {
+    // (channels-last: one buffer of 64 x 49 -- everybody must have written the previous chunk out before it is refilled)
+    float* ob = kCL ? outbuf : outbuf + ((chunk - chunk_begin) & 1) * kOutFloats;
+    if (kCL) {
+      if (chunk > chunk_begin) asm volatile("bar.sync 2, %0;" ::"n"(kConsumers) : "memory");
+      float* o = ob + 2 * lane * (kP * kP) + ph * kP;
+#pragma unroll
+      for (int p = 0; p < kP; ++p) {
+        o[p] = lo2(acc2[p]) * inv_count;
+        o[kP * kP + p] = hi2(acc2[p]) * inv_count;
+      }
+    } else {
       float* o = ob + lane * (kP * kP) + ph * kP;
       o[0] = lo2(acc.a01) * inv_count; o[1] = hi2(acc.a01) * inv_count;
       o[2] = lo2(acc.a23) * inv_count; o[3] = hi2(acc.a23) * inv_count;
@@ -947,7 +1019,10 @@ float level_threshold(int k, int canonical_level) {
 // that a box {Wt, 32, R} lands in shared memory as R consecutive [32 channels][Wt] slabs), Wt = 8 / 16 / 32 with
 // the 32 / 64 / 128-byte swizzle, R = 1, 2, 4, 8, 16.  Out-of-range elements (columns past W, rows past H, channels
 // past N*C) read as zero.
-int encode_level_maps(const float* data, int H, int W, long long NC, CUtensorMap* out) {
+// Channels-last (cl): fp32 [N, H, W, C] seen as {C, W, N*H}, box {64, Wt, R} with Wt = 4 / 8 / 16 columns, no swizzle
+// (a lane reads its channel pair, 32 lanes x 8 bytes are consecutive), 256-byte L2 promotion (a pixel's 64 channels).
+// NC is then N (images) and C is passed separately.
+int encode_level_maps(const float* data, int H, int W, long long NC, int cl_channels, CUtensorMap* out) {
   EncodeTiledFn enc = tensormap_encode_fn();
   if (!enc) {
     set_error("cuTensorMapEncodeTiled not available from the driver");
@@ -963,9 +1038,18 @@ int encode_level_maps(const float* data, int H, int W, long long NC, CUtensorMap
       cuuint64_t strides[2] = {(cuuint64_t)H * W * 4, (cuuint64_t)W * 4};
       cuuint32_t box[3] = {(cuuint32_t)(8 << k), 32, (cuuint32_t)(1 << j)};
       cuuint32_t estr[3] = {1, 1, 1};
+      CUtensorMapSwizzle sw = swz[k];
+      CUtensorMapL2promotion pr = promo[roi_tune().promo & 3];
+      if (cl_channels) {
+        const cuuint64_t C = (cuuint64_t)cl_channels;
+        dims[0] = C; dims[1] = (cuuint64_t)W; dims[2] = (cuuint64_t)NC * H;
+        strides[0] = C * 4; strides[1] = (cuuint64_t)W * C * 4;
+        box[0] = 64; box[1] = (cuuint32_t)(4 << k);
+        sw = CU_TENSOR_MAP_SWIZZLE_NONE;
+        pr = promo[roi_tune().promo_cl & 3];
+      }
       CUresult r = enc(&out[k * kHeights + j], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(data), dims,
-                       strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz[k], promo[roi_tune().promo & 3],
-                       CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                       strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw, pr, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
       if (r != CUDA_SUCCESS) {
         set_error("cuTensorMapEncodeTiled(feature map %dx%d, %lld planes, box %dx32x%d) failed with CUresult %d", H, W,
                   NC, 8 << k, 1 << j, (int)r);
@@ -981,20 +1065,21 @@ struct MapKey {
   const void* p;
   int H, W;
   long long NC;
-  bool operator<(const MapKey& o) const { return std::tie(p, H, W, NC) < std::tie(o.p, o.H, o.W, o.NC); }
+  int cl_channels;
+  bool operator<(const MapKey& o) const { return std::tie(p, H, W, NC, cl_channels) < std::tie(o.p, o.H, o.W, o.NC, o.cl_channels); }
 };
 struct MapVal {
   CUtensorMap m[kMapsPerLevel];
 };
-int level_maps(const float* data, int H, int W, long long NC, CUtensorMap* out) {
+int level_maps(const float* data, int H, int W, long long NC, int cl_channels, CUtensorMap* out) {
   static std::mutex mu;
   static std::map<MapKey, MapVal> cache;
   std::lock_guard<std::mutex> lock(mu);
-  const MapKey key{data, H, W, NC};
+  const MapKey key{data, H, W, NC, cl_channels};
   auto it = cache.find(key);
   if (it == cache.end()) {
     MapVal v;
-    int rc = encode_level_maps(data, H, W, NC, v.m);
+    int rc = encode_level_maps(data, H, W, NC, cl_channels, v.m);
     if (rc != OVM_OK) return rc;
     if (cache.size() >= 256) cache.clear();
     it = cache.emplace(key, v).first;
@@ -1032,16 +1117,25 @@ int roi_align_launch(const ovm_pooler_t* p, const float* boxes, const int32_t* b
   OVM_REQUIRE(0 <= min_level && min_level <= max_level, "[ROIPooler] bad level range %d..%d", min_level, max_level);
   RoiMaps maps;
   memset(&maps, 0, sizeof(maps));
+  const RoiTune& tune = roi_tune();
+  // channels-last fast path: every level NHWC, 16-byte aligned, C % 4 == 0 (the tensor maps' strides), P == 7
+  bool all_cl = tune.cl && p->pooler_resolution == kP && !(p->channels & 3);
+  for (int l = 0; l < a.L && all_cl; ++l)
+    all_cl = p->levels[l].layout == OVM_LAYOUT_NHWC && p->levels[l].data && !(reinterpret_cast<uintptr_t>(p->levels[l].data) & 15);
+  a.cl = all_cl;
+  a.chunk_ch = all_cl ? 64 : 32;
   for (int l = 0; l < a.L; ++l) {
     const ovm_level_t& s = p->levels[l];
     OVM_REQUIRE(s.data && s.height > 0 && s.width > 0, "ovm_roi_align: level %d is empty", l);
     OVM_REQUIRE(s.layout == OVM_LAYOUT_NCHW || s.layout == OVM_LAYOUT_NHWC, "ovm_roi_align: level %d layout", l);
     a.lv[l] = RoiLevel{s.data, s.height, s.width, (float)s.spatial_scale, s.layout};
     a.thr[l] = l == 0 ? 0.f : level_threshold(min_level + l, p->canonical_level);
-    a.tma_ok[l] = s.layout == OVM_LAYOUT_NCHW && !(reinterpret_cast<uintptr_t>(s.data) & 15) && !(s.width & 3) &&
-                  p->pooler_resolution == kP;
+    a.tma_ok[l] = all_cl || (s.layout == OVM_LAYOUT_NCHW && !(reinterpret_cast<uintptr_t>(s.data) & 15) && !(s.width & 3) &&
+                             p->pooler_resolution == kP);
     if (a.tma_ok[l]) {
-      int rc = level_maps(s.data, s.height, s.width, (long long)p->num_images * p->channels, &maps.m[l * kMapsPerLevel]);
+      int rc = all_cl ? level_maps(s.data, s.height, s.width, p->num_images, p->channels, &maps.m[l * kMapsPerLevel])
+                      : level_maps(s.data, s.height, s.width, (long long)p->num_images * p->channels, 0,
+                                   &maps.m[l * kMapsPerLevel]);
       if (rc != OVM_OK) return rc;
     }
   }
@@ -1061,13 +1155,12 @@ int roi_align_launch(const ovm_pooler_t* p, const float* boxes, const int32_t* b
   a.order = p->order_ws;
   a.trace = g_roi_trace;
   // enough CTAs for two waves of two CTAs per SM: split the channel chunks of a box over several CTAs when n is small
-  const int chunks = (a.C + 31) / 32;
+  const int chunks = (a.C + a.chunk_ch - 1) / a.chunk_ch;
   int splits = (4 * kNumSMs + n - 1) / n;
   splits = splits < 1 ? 1 : (splits > chunks ? chunks : splits);
   a.chunks_per_split = (chunks + splits - 1) / splits;
   a.splits = (chunks + a.chunks_per_split - 1) / a.chunks_per_split;
 
-  const RoiTune& tune = roi_tune();
   a.split_factor = 0.01f * (float)(tune.split_pct < 100 ? 100 : tune.split_pct);   // < 1 would break the item bound
   // with work items: a box yields at most max(splits, 2 area / (split_factor mean area)) of them
   const long long nitems = (long long)n * a.splits + (a.order ? (long long)(2.0 * n / a.split_factor) + 8 : 0);
@@ -1079,15 +1172,18 @@ int roi_align_launch(const ovm_pooler_t* p, const float* boxes, const int32_t* b
               ws_need);
   a.xalign_mask = tune.align8 ? ~7 : ~3;
   a.evict_first = tune.evict;
-  static SmemOptIn optA, optB;
-  auto kA = roi_align_kernel<12288, 6144, 0>;   // 48 KB ring, stages up to 24 KB: 69 KB of shared memory, 3 CTAs / SM
-  auto kB = roi_align_kernel<9216, 4608, 4>;    // 36 KB ring, stages up to 18 KB, 64 registers: 4 CTAs / SM -- measured 125 vs 104 us (OVM_ROI_STAGES=3, tools/roi_bench.py)
+  static SmemOptIn optA, optB, optC;
+  auto kC = roi_align_kernel<12288, 6144, 0, true>;   // channels-last pyramid
+  auto kA = roi_align_kernel<12288, 6144, 0, false>;   // 48 KB ring, stages up to 24 KB: 69 KB of shared memory, 3 CTAs / SM
+  auto kB = roi_align_kernel<9216, 4608, 4, false>;    // 36 KB ring, stages up to 18 KB, 64 registers: 4 CTAs / SM -- measured 125 vs 104 us (OVM_ROI_STAGES=3, tools/roi_bench.py)
   {
-    int rc = tune.stages == 3 ? optB.ensure(kB, roi_smem_bytes(9216)) : optA.ensure(kA, roi_smem_bytes(12288));
+    const bool small = tune.stages == 3 && !all_cl;
+    int rc = all_cl ? optC.ensure(kC, roi_smem_bytes(12288, true))
+                    : (small ? optB.ensure(kB, roi_smem_bytes(9216)) : optA.ensure(kA, roi_smem_bytes(12288)));
     if (rc != OVM_OK) return rc;
+    a.ring_floats = small ? 9216 : 12288;
+    a.stage_floats = small ? 4608 : 6144;
   }
-  a.ring_floats = tune.stages == 3 ? 9216 : 12288;
-  a.stage_floats = tune.stages == 3 ? 4608 : 6144;
   if (a.order) {
     int* box_hdr = p->order_ws + ws_items;
     a.box_hdr = box_hdr;
@@ -1099,6 +1195,11 @@ int roi_align_launch(const ovm_pooler_t* p, const float* boxes, const int32_t* b
     if (rc != OVM_OK) return rc;
   }
   const dim3 grid((unsigned)nitems);
+  if (all_cl) {
+    OVM_CUDA(launch_pdl(kC, grid, dim3(kThreads), roi_smem_bytes(12288, true), stream, maps, a));
+    OVM_LAUNCHED("roi_align_kernel");
+    return OVM_OK;
+  }
   if (tune.stages == 3)
     OVM_CUDA(launch_pdl(kB, grid, dim3(kThreads), roi_smem_bytes(9216), stream, maps, a));
   else

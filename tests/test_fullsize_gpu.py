@@ -135,8 +135,9 @@ def format_error_table(names=NAMES):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("layout", ["nchw", "channels_last"])
 @pytest.mark.parametrize("name", NAMES)
-def test_fullsize_parity(name):
+def test_fullsize_parity(name, layout):
     from ovmono3d_b200 import ops
     from ovmono3d_b200.compat import ShapeSpec
     from ovmono3d_b200.config import get_cfg
@@ -159,6 +160,8 @@ def test_fullsize_parity(name):
     assert eng.tail_fused and eng.tail_precision == "f16", "the full-size workloads run the fused fp16 tail"
 
     feats = [f.to(dev) for f in inp.features]
+    if layout == "channels_last":     # the channels-last ROIAlign kernel: same bounds, nothing copied back to NCHW
+        feats = [f.contiguous(memory_format=torch.channels_last) for f in feats]
     boxes = torch.cat(inp.boxes).to(dev)
     classes = torch.cat(inp.classes).to(dev)
     scores = torch.cat(inp.scores).to(dev)

@@ -117,8 +117,64 @@ def test_roi_align_bf16_out_and_channels_last():
     assert _field_err(pcl, out.pooled) <= FP32_TOL
 
 
+@pytest.mark.parametrize("out_dtype", [torch.float32, torch.bfloat16], ids=["f32", "bf16"])
+@pytest.mark.parametrize("case", SMALL_CASES, ids=lambda c: c.name)
+def test_roi_align_channels_last_matches_oracle(case, out_dtype):
+    """`torch.channels_last` pyramids take the channels-last TMA kernel (tiles of [row][column][64 channels], lane = a
+    channel pair): same levels bit for bit, pooled features within the fp32 tolerance of the oracle and of the golden
+    vectors, and within re-association distance of the NCHW kernel on the same values."""
+    from ovmono3d_b200 import ops
+
+    inp, weights, priors, cfg, out = helpers.run_oracle(case)
+    dev = _dev()
+    boxes, batch_idx, counts = _cat_inputs(inp, dev)
+    feats = [f.to(dev) for f in inp.features]
+    cl = [f.contiguous(memory_format=torch.channels_last) for f in feats]
+    assert all(f.is_contiguous(memory_format=torch.channels_last) for f in cl)
+    pooled, levels = ops.roi_align(cl, cfg.scales, boxes, batch_idx, cfg.pooler_resolution, cfg.sampling_ratio,
+                                   out_dtype, cfg.scale_roi_boxes)
+    assert pooled.shape == out.pooled.shape
+    if sum(counts) == 0:
+        return
+    assert torch.equal(levels.cpu().long(), out.levels), "box-to-level assignment must be bit-exact"
+    tol = FP32_TOL if out_dtype == torch.float32 else 2 ** -8
+    assert _field_err(pooled.float(), out.pooled) <= tol
+    ref = out.pooled.flatten(1)
+    got = pooled.float().flatten(1).cpu()
+    scale = ref.abs().amax(dim=1).clamp_min(1e-6)
+    assert float(((got - ref).abs().amax(dim=1) / scale).max()) <= tol
+    nchw, _ = ops.roi_align(feats, cfg.scales, boxes, batch_idx, cfg.pooler_resolution, cfg.sampling_ratio,
+                            out_dtype, cfg.scale_roi_boxes)
+    assert _field_err(pooled.float(), nchw.float()) <= (1e-5 if out_dtype == torch.float32 else 2 ** -7)
+    if out_dtype == torch.float32:
+        g = np.load(gc.golden_path(case))
+        np.testing.assert_allclose(pooled.flatten()[:: case.pooled_stride].cpu().numpy(), g["pooled"],
+                                   rtol=0, atol=FP32_TOL * float(np.abs(g["pooled"]).max()))
+
+
+@pytest.mark.parametrize("channels", [4, 60, 64, 72, 200])
+def test_roi_align_channels_last_ragged_channels(channels):
+    """Channel counts that are not a multiple of the 64-channel chunk (the last chunk is zero-filled by TMA and only its
+    real channels are written), down to a single 16-byte pixel."""
+    from oracle import thirdparty as tp
+    from ovmono3d_b200 import ops, synth
+
+    strides = (7, 14, 28)
+    inp = synth.make_inputs(5, 2, 40, strides=strides, canvas=448, channels=channels)
+    scales = [1.0 / s for s in strides]
+    want = tp.ROIPoolerOracle(7, scales, 0, "ROIAlignV2")(inp.features, inp.boxes)
+    dev = _dev()
+    boxes, batch_idx, _ = _cat_inputs(inp, dev)
+    cl = [f.to(dev).contiguous(memory_format=torch.channels_last) for f in inp.features]
+    out_ld = channels * 49
+    got, _ = ops.roi_align(cl, scales, boxes, batch_idx, 7, 0, torch.float32)
+    assert got.shape[0] == want.shape[0] and got[0].numel() == out_ld
+    assert _field_err(got, want) <= FP32_TOL
+
+
+@pytest.mark.parametrize("layout", ["nchw", "channels_last"])
 @pytest.mark.parametrize("strides,canvas", [((4, 8, 16, 32), 512), ((7, 14, 28), 448), ((4, 8, 16, 32, 64), 512)])
-def test_roi_align_tall_wide_and_huge_boxes(strides, canvas):
+def test_roi_align_tall_wide_and_huge_boxes(strides, canvas, layout):
     """Footprints that do not fit one stage: tall / wide slivers (small area -> fine level, hundreds of pixel rows),
     near-full-image boxes on every pyramid, and the row-group depth knob's geometries (G = 7, 4, 2, 1 bin-rows per
     stage, or the direct path past that) must all give the reference's numbers."""
@@ -144,7 +200,10 @@ def test_roi_align_tall_wide_and_huge_boxes(strides, canvas):
     dev = _dev()
     bd = torch.cat(boxes).to(dev)
     bi = torch.from_numpy(np.repeat(np.arange(N, dtype=np.int32), [len(b) for b in boxes])).to(dev)
-    got, lv = ops.roi_align([f.to(dev) for f in feats], scales, bd, bi, 7, 0, torch.float32)
+    fd = [f.to(dev) for f in feats]
+    if layout == "channels_last":
+        fd = [f.contiguous(memory_format=torch.channels_last) for f in fd]
+    got, lv = ops.roi_align(fd, scales, bd, bi, 7, 0, torch.float32)
     assert torch.equal(lv.cpu().long(), want_lv)
     ref = want.flatten(1)
     err = (got.flatten(1).cpu() - ref).abs().amax(dim=1) / ref.abs().amax(dim=1).clamp_min(1e-6)

@@ -22,6 +22,9 @@ def main():
     k = int(sys.argv[4]) if len(sys.argv) > 4 else 100
     inp = synth.make_inputs(1235 if len(sys.argv) == 1 else 4321, N, k, strides=strides, canvas=canvas)
     feats = [f.to(dev) for f in inp.features]
+    if os.environ.get("OVM_TRACE_LAYOUT", "nchw") == "channels_last":
+        feats = [f.contiguous(memory_format=torch.channels_last) for f in feats]
+        print("pyramid: torch.channels_last")
     counts = [len(b) for b in inp.boxes]
     boxes = torch.cat(inp.boxes).to(dev)
     bidx = torch.from_numpy(np.repeat(np.arange(N, dtype=np.int32), counts)).to(dev)
