@@ -50,6 +50,9 @@ enum {
   OVM_EUNSUPPORTED = -3 /* valid in the reference, not implemented here (message says what) */
 };
 
+/* Memory format of a pyramid level.  NCHW: [N, C, H, W] contiguous (what the reference's backbone emits).  NHWC:
+ * torch.channels_last, [N, H, W, C] in memory.  A pyramid whose levels are ALL NHWC (16-byte aligned, C % 4 == 0) runs
+ * the channels-last ROIAlign kernel; NHWC levels of a mixed pyramid are sampled by the slower direct path. */
 enum { OVM_LAYOUT_NCHW = 0, OVM_LAYOUT_NHWC = 1 };
 enum {
   OVM_F32 = 0,
