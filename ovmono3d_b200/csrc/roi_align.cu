@@ -87,8 +87,8 @@ struct RoiArgs {
   int evict_first;              // feature loads carry the L2 evict_first policy (OVM_ROI_EVICT)
   int ring_floats, stage_floats;   // shared-memory ring / largest stage of the pooling kernel that will run (plan_box needs them)
   const int* box_hdr;              // [n][kHdrInts] per-box headers written by roi_plan_kernel (with `order`)
-  int cl;                          // every level is channels-last (NHWC) and TMA-addressable: roi_align_kernel<.., true>
-  int chunk_ch;                    // channels per chunk: 32 (NCHW: lane = channel) or 64 (channels-last: lane = 2 channels)
+  int cl;                          // 0, or channels per lane (2 / 4) when every level is channels-last (NHWC) and TMA-addressable
+  int chunk_ch;                    // channels per chunk: 32 (NCHW: lane = channel) or 32 cl (channels-last)
   unsigned long long* trace;    // optional [grid, 16] %globaltimer stamps (ovm_roi_set_trace), else NULL
 };
 
@@ -109,9 +109,11 @@ thread_local unsigned long long* g_roi_trace = nullptr;
 // Development knobs (environment, read once): used by tools/roi_bench.py to compare schedules on the device.
 struct RoiTune {
   int split_pct;    // OVM_ROI_SPLIT   cost of a work item, in % of the average box, above which a box is cut along the channels
+  int split_cl;     // OVM_ROI_SPLIT_CL  the same for channels-last pyramids (cheaper prologue, at most 2-4 pieces per box: 300)
   int promo;        // OVM_ROI_PROMO   L2 promotion of the tensor maps: 0 none, 1 64 B, 2 128 B, 3 256 B
   int promo_cl;     // OVM_ROI_PROMO_CL  same for channels-last maps (a pixel's chunk is one 256-byte run)
-  int cl;           // OVM_ROI_CL      0: channels-last pyramids take the direct path (no TMA kernel)
+  int cl;           // OVM_ROI_CL      channels per lane of the channels-last kernel: 4 (128-channel chunks), 2 (64), or
+                    //                 0: channels-last pyramids take the direct path (no TMA kernel)
   int align8;       // OVM_ROI_ALIGN8  footprint starts on a 32-byte sector (8 floats) instead of 16 bytes
   int stages;       // OVM_ROI_STAGES  2: 48 KB ring (3 CTAs / SM), 3: 36 KB ring and 64 registers (4 CTAs / SM)
   int min_slots;    // OVM_ROI_MINSLOTS  prefer stage geometries (narrower tiles, row groups) that leave this many ring slots
@@ -123,9 +125,11 @@ const RoiTune& roi_tune() {
     auto env = [](const char* k, int d) { const char* v = getenv(k); return v ? atoi(v) : d; };
     RoiTune r;
     r.split_pct = env("OVM_ROI_SPLIT", 400);
+    r.split_cl = env("OVM_ROI_SPLIT_CL", env("OVM_ROI_SPLIT", 300));
     r.promo = env("OVM_ROI_PROMO", 2);
     r.promo_cl = env("OVM_ROI_PROMO_CL", 3);
-    r.cl = env("OVM_ROI_CL", 1);
+    r.cl = env("OVM_ROI_CL", 4);
+    if (r.cl != 0 && r.cl != 2 && r.cl != 4) r.cl = 4;
     r.align8 = env("OVM_ROI_ALIGN8", 0);
     r.stages = env("OVM_ROI_STAGES", 2);
     r.min_slots = env("OVM_ROI_MINSLOTS", 1);
@@ -402,6 +406,44 @@ __device__ __forceinline__ void consume_tile_cl(const float* __restrict__ slab0,
   }
 }
 
+// Four channels per lane ([row][column][128 channels] tiles): one 128-bit load per (row, column), the column weights are
+// loaded once for two channel pairs -- 3 ny + 18 instructions per column for ny x 512 bytes (2 ny + 11 for 256 above).
+template <int NY>
+__device__ __forceinline__ void consume_tile_cl4(const float* __restrict__ slab0, int slab_floats, int ncol,
+                                                 const float (&wyr)[4], const float* __restrict__ wy, int ny,
+                                                 const float2* __restrict__ wx2, uint64_t (&acc)[kP], uint64_t (&bcc)[kP]) {
+#pragma unroll 2
+  for (int x = 0; x < ncol; ++x) {
+    const float* p = slab0 + x * 128;
+    uint64_t va = 0, vb = 0;
+    if (NY > 0) {
+#pragma unroll
+      for (int r = 0; r < NY; ++r) {
+        const ulonglong2 f = *reinterpret_cast<const ulonglong2*>(p + r * slab_floats);
+        const uint64_t w2 = pack2(wyr[r], wyr[r]);
+        va = ffma2(w2, f.x, va);
+        vb = ffma2(w2, f.y, vb);
+      }
+    } else {
+      for (int r = 0; r < ny; ++r) {
+        const ulonglong2 f = *reinterpret_cast<const ulonglong2*>(p + r * slab_floats);
+        const uint64_t w2 = pack2(wy[r], wy[r]);
+        va = ffma2(w2, f.x, va);
+        vb = ffma2(w2, f.y, vb);
+      }
+    }
+    const ulonglong2* w = reinterpret_cast<const ulonglong2*>(wx2 + x * 8);
+    const ulonglong2 w01 = w[0], w23 = w[1], w45 = w[2], w67 = w[3];
+    acc[0] = ffma2(w01.x, va, acc[0]); bcc[0] = ffma2(w01.x, vb, bcc[0]);
+    acc[1] = ffma2(w01.y, va, acc[1]); bcc[1] = ffma2(w01.y, vb, bcc[1]);
+    acc[2] = ffma2(w23.x, va, acc[2]); bcc[2] = ffma2(w23.x, vb, bcc[2]);
+    acc[3] = ffma2(w23.y, va, acc[3]); bcc[3] = ffma2(w23.y, vb, bcc[3]);
+    acc[4] = ffma2(w45.x, va, acc[4]); bcc[4] = ffma2(w45.x, vb, bcc[4]);
+    acc[5] = ffma2(w45.y, va, acc[5]); bcc[5] = ffma2(w45.y, vb, bcc[5]);
+    acc[6] = ffma2(w67.x, va, acc[6]); bcc[6] = ffma2(w67.x, vb, bcc[6]);
+  }
+}
+
 // One warp plans one box: level, sampling geometry, the pixel range of every bin, the stage geometry (tile width, row
 // groups) of the TMA pipeline, and the footprint area the work-item planner balances by -> the 40-int header `h`
 // (warp-private).  Lanes 0..27 each take one end sample of one bin; everything else is computed redundantly.
@@ -490,7 +532,7 @@ __device__ void plan_box_warp(const RoiArgs& a, float x1, float y1, float x2, fl
         int ws = -1, bp = INT_MAX;
 #pragma unroll
         for (int k = kWidths - 1; k >= 0; --k) {
-          const int wt = (a.cl ? 4 : 8) << k;   // columns per tile; channels-last tiles hold 64 channels per column
+          const int wt = (a.cl == 4 ? 2 : a.cl == 2 ? 4 : 8) << k;   // columns per tile; channels-last tiles hold 64 / 128 channels per column
           const int pad = (fw + wt - 1) / wt * wt;
           const int stage = rm * (8 << k) * 32;
           if (stage <= a.stage_floats && stage * need_slots <= a.ring_floats && pad < bp) {
@@ -721,7 +763,7 @@ __device__ __forceinline__ void write_chunk(const RoiArgs& a, const float* ob, l
 // Wt = 4 / 8 / 16 columns, no swizzle), a chunk is 64 channels and lane owns a channel pair (consume_tile_cl).  A
 // footprint pixel is then one contiguous 256-byte run: whole L2 lines, no partially used sectors, and the column range
 // need not be rounded to 16 bytes.
-template <int kRingFloats, int kStageFloats, int kMinBlocks, bool kCL>
+template <int kRingFloats, int kStageFloats, int kMinBlocks, int kCL>   // kCL: 0 NCHW; 2 / 4: channels-last, channels per lane
 __global__ void __launch_bounds__(kThreads, kMinBlocks) roi_align_kernel(const __grid_constant__ RoiMaps maps, const RoiArgs a) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
@@ -730,7 +772,7 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) roi_align_kernel(const _
   float* stages = reinterpret_cast<float*>(aligned);                 // kStages * kStageFloats
   float* outbuf = stages + kRingFloats;                   // 2 * kOutFloats
   constexpr int kWxF = kCL ? 2 * kWxFloats : kWxFloats;
-  constexpr int kCh = kCL ? 64 : 32;                                 // channels per chunk
+  constexpr int kCh = kCL ? 32 * kCL : 32;                           // channels per chunk
   float* Wx = outbuf + 2 * kOutFloats;                               // [col][8] (channels-last: float2 (w, w) entries)
   float* Wy = Wx + kWxF;                                             // [ph][kMaxRows]
   int* meta = reinterpret_cast<int*>(Wy + kWyFloats);
@@ -818,7 +860,7 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) roi_align_kernel(const _
     rows = hi - lo + 1;
   };
   const int ngroups = (kP + G - 1) / G;
-  const int Wt = (kCL ? 4 : 8) << wsel;
+  const int Wt = (kCL == 4 ? 2 : kCL == 2 ? 4 : 8) << wsel;
   const int ntiles = ((fw + Wt - 1) / Wt * Wt) / Wt;
   const int slab_floats = 32 * (8 << wsel);      // one footprint row of one chunk: [32 channels][Wt] / [Wt][64 channels]
   // The ring is cut into slots of this box's stage size: small footprints get up to kMaxSlots stages in flight.
@@ -838,7 +880,7 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) roi_align_kernel(const _
       uint64_t policy = 0;
       if (a.evict_first) asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
       for (int chunk = chunk_begin; chunk < chunk_end; ++chunk) {
-        const int cc = kCL ? chunk * 64 : g.b * a.C + chunk * 32;   // channels-last: first channel; NCHW: first plane
+        const int cc = kCL ? chunk * kCh : g.b * a.C + chunk * 32;   // channels-last: first channel; NCHW: first plane
         for (int grp = 0; grp < ngroups; ++grp) {
           int gy, rows;
           group_span(G, grp, gy, rows);
@@ -922,7 +964,7 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) roi_align_kernel(const _
   // 16-byte unit j of lane c's row sits at unit j ^ sw (the TMA swizzle of the slab, see the header comment)
   const int sw = wsel == 2 ? (lane & 7) : (wsel == 1 ? ((lane >> 1) & 3) : ((lane >> 2) & 1));
   const int nx4_tile = Wt >> 2;
-  const int row_off = (ys - my_gy) * slab_floats + (kCL ? 2 * lane : lane * Wt);
+  const int row_off = (ys - my_gy) * slab_floats + (kCL ? kCL * lane : lane * Wt);
   float wyr[4];   // row weights of a bin-row of up to 4 pixel rows (the table is zero past the bin-row's rows)
 #pragma unroll
   for (int r = 0; r < 4; ++r) wyr[r] = wy[r];
@@ -932,7 +974,8 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) roi_align_kernel(const _
   long long waited = 0;
   for (int chunk = chunk_begin; chunk < chunk_end; ++chunk) {
     PoolAcc acc{0, 0, 0, 0.f};
-    uint64_t acc2[kP] = {0, 0, 0, 0, 0, 0, 0};   // channels-last: bin pw of the lane's channel pair
+    uint64_t acc2[kP] = {0, 0, 0, 0, 0, 0, 0};   // channels-last: bin pw of the lane's (first) channel pair
+    uint64_t acc3[kP] = {0, 0, 0, 0, 0, 0, 0};   // kCL == 4: ... of its second channel pair
     for (int grp = 0; grp < ngroups; ++grp)
     for (int tile = 0; tile < ntiles; ++tile) {
       const long long tw = a.trace ? clock64() : 0;
@@ -947,6 +990,15 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) roi_align_kernel(const _
         if (kCL) {
           const int ncol = min(Wt, fw - tile * Wt);
           const float2* wx2 = reinterpret_cast<const float2*>(wxt);
+          if (kCL == 4) {
+            switch (ny) {
+              case 1: consume_tile_cl4<1>(slab0, slab_floats, ncol, wyr, wy, ny, wx2, acc2, acc3); break;
+              case 2: consume_tile_cl4<2>(slab0, slab_floats, ncol, wyr, wy, ny, wx2, acc2, acc3); break;
+              case 3: consume_tile_cl4<3>(slab0, slab_floats, ncol, wyr, wy, ny, wx2, acc2, acc3); break;
+              case 4: consume_tile_cl4<4>(slab0, slab_floats, ncol, wyr, wy, ny, wx2, acc2, acc3); break;
+              default: consume_tile_cl4<0>(slab0, slab_floats, ncol, wyr, wy, ny, wx2, acc2, acc3); break;
+            }
+          } else
           switch (ny) {
             case 1: consume_tile_cl<1>(slab0, slab_floats, ncol, wyr, wy, ny, wx2, acc2); break;
             case 2: consume_tile_cl<2>(slab0, slab_floats, ncol, wyr, wy, ny, wx2, acc2); break;
@@ -973,6 +1025,50 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) roi_align_kernel(const _
     // ---- stage the chunk's 32 x 49 results and write them as one contiguous run
     // (channels-last: one buffer of 64 x 49 -- everybody must have written the previous chunk out before it is refilled)
     float* ob = kCL ? outbuf : outbuf + ((chunk - chunk_begin) & 1) * kOutFloats;
+    if (kCL == 4) {   // 128 channels per chunk: staged as bf16 (the product's output type), or in two fp32 halves
+      const int c0 = chunk * 128;
+      if (a.out_bf16) {
+        if (chunk > chunk_begin) asm volatile("bar.sync 2, %0;" ::"n"(kConsumers) : "memory");
+        __nv_bfloat16* o16 = reinterpret_cast<__nv_bfloat16*>(ob) + 4 * lane * (kP * kP) + ph * kP;
+#pragma unroll
+        for (int p = 0; p < kP; ++p) {
+          o16[p] = __float2bfloat16_rn(lo2(acc2[p]) * inv_count);
+          o16[kP * kP + p] = __float2bfloat16_rn(hi2(acc2[p]) * inv_count);
+          o16[2 * kP * kP + p] = __float2bfloat16_rn(lo2(acc3[p]) * inv_count);
+          o16[3 * kP * kP + p] = __float2bfloat16_rn(hi2(acc3[p]) * inv_count);
+        }
+        asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory");
+        const int nvals = min(128, a.C - c0) * kP * kP;
+        __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(a.out) + out_row + (long long)c0 * kP * kP;
+        const __nv_bfloat16* src = reinterpret_cast<const __nv_bfloat16*>(ob);
+        if (!(reinterpret_cast<uintptr_t>(out) & 15) && !(nvals & 7)) {
+          for (int i = tid; i < (nvals >> 3); i += kConsumers)
+            reinterpret_cast<uint4*>(out)[i] = reinterpret_cast<const uint4*>(src)[i];
+        } else {
+          for (int i = tid; i < nvals; i += kConsumers) out[i] = src[i];
+        }
+      } else {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          if (chunk > chunk_begin || h) asm volatile("bar.sync 2, %0;" ::"n"(kConsumers) : "memory");
+          float* o = ob + 2 * lane * (kP * kP) + ph * kP;
+#pragma unroll
+          for (int p = 0; p < kP; ++p) {
+            const uint64_t v = h ? acc3[p] : acc2[p];
+            o[p] = lo2(v) * inv_count;
+            o[kP * kP + p] = hi2(v) * inv_count;
+          }
+          asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory");
+          float* out = reinterpret_cast<float*>(a.out) + out_row;
+          for (int i = tid; i < 64 * kP * kP; i += kConsumers) {   // staged channel lc -> channel 4 (lc / 2) + 2 h + (lc & 1)
+            const int lc = i / (kP * kP), r = i - lc * (kP * kP);
+            const int c = c0 + (lc >> 1) * 4 + 2 * h + (lc & 1);
+            if (c < a.C) out[(long long)c * (kP * kP) + r] = ob[i];
+          }
+        }
+      }
+      continue;
+    }
     if (kCL) {
       if (chunk > chunk_begin) asm volatile("bar.sync 2, %0;" ::"n"(kConsumers) : "memory");
       float* o = ob + 2 * lane * (kP * kP) + ph * kP;
@@ -1022,7 +1118,7 @@ float level_threshold(int k, int canonical_level) {
 // Channels-last (cl): fp32 [N, H, W, C] seen as {C, W, N*H}, box {64, Wt, R} with Wt = 4 / 8 / 16 columns, no swizzle
 // (a lane reads its channel pair, 32 lanes x 8 bytes are consecutive), 256-byte L2 promotion (a pixel's 64 channels).
 // NC is then N (images) and C is passed separately.
-int encode_level_maps(const float* data, int H, int W, long long NC, int cl_channels, CUtensorMap* out) {
+int encode_level_maps(const float* data, int H, int W, long long NC, int cl_channels, int cl_vec, CUtensorMap* out) {
   EncodeTiledFn enc = tensormap_encode_fn();
   if (!enc) {
     set_error("cuTensorMapEncodeTiled not available from the driver");
@@ -1044,7 +1140,7 @@ int encode_level_maps(const float* data, int H, int W, long long NC, int cl_chan
         const cuuint64_t C = (cuuint64_t)cl_channels;
         dims[0] = C; dims[1] = (cuuint64_t)W; dims[2] = (cuuint64_t)NC * H;
         strides[0] = C * 4; strides[1] = (cuuint64_t)W * C * 4;
-        box[0] = 64; box[1] = (cuuint32_t)(4 << k);
+        box[0] = (cuuint32_t)(32 * cl_vec); box[1] = (cuuint32_t)((cl_vec == 4 ? 2 : 4) << k);
         sw = CU_TENSOR_MAP_SWIZZLE_NONE;
         pr = promo[roi_tune().promo_cl & 3];
       }
@@ -1065,21 +1161,23 @@ struct MapKey {
   const void* p;
   int H, W;
   long long NC;
-  int cl_channels;
-  bool operator<(const MapKey& o) const { return std::tie(p, H, W, NC, cl_channels) < std::tie(o.p, o.H, o.W, o.NC, o.cl_channels); }
+  int cl_channels, cl_vec;
+  bool operator<(const MapKey& o) const {
+    return std::tie(p, H, W, NC, cl_channels, cl_vec) < std::tie(o.p, o.H, o.W, o.NC, o.cl_channels, o.cl_vec);
+  }
 };
 struct MapVal {
   CUtensorMap m[kMapsPerLevel];
 };
-int level_maps(const float* data, int H, int W, long long NC, int cl_channels, CUtensorMap* out) {
+int level_maps(const float* data, int H, int W, long long NC, int cl_channels, int cl_vec, CUtensorMap* out) {
   static std::mutex mu;
   static std::map<MapKey, MapVal> cache;
   std::lock_guard<std::mutex> lock(mu);
-  const MapKey key{data, H, W, NC, cl_channels};
+  const MapKey key{data, H, W, NC, cl_channels, cl_vec};
   auto it = cache.find(key);
   if (it == cache.end()) {
     MapVal v;
-    int rc = encode_level_maps(data, H, W, NC, cl_channels, v.m);
+    int rc = encode_level_maps(data, H, W, NC, cl_channels, cl_vec, v.m);
     if (rc != OVM_OK) return rc;
     if (cache.size() >= 256) cache.clear();
     it = cache.emplace(key, v).first;
@@ -1122,8 +1220,9 @@ int roi_align_launch(const ovm_pooler_t* p, const float* boxes, const int32_t* b
   bool all_cl = tune.cl && p->pooler_resolution == kP && !(p->channels & 3);
   for (int l = 0; l < a.L && all_cl; ++l)
     all_cl = p->levels[l].layout == OVM_LAYOUT_NHWC && p->levels[l].data && !(reinterpret_cast<uintptr_t>(p->levels[l].data) & 15);
-  a.cl = all_cl;
-  a.chunk_ch = all_cl ? 64 : 32;
+  const int cl_vec = !all_cl ? 0 : (tune.cl == 4 && p->channels >= 128 ? 4 : 2);   // narrow pyramids: 64-channel chunks
+  a.cl = cl_vec;
+  a.chunk_ch = all_cl ? 32 * cl_vec : 32;
   for (int l = 0; l < a.L; ++l) {
     const ovm_level_t& s = p->levels[l];
     OVM_REQUIRE(s.data && s.height > 0 && s.width > 0, "ovm_roi_align: level %d is empty", l);
@@ -1133,8 +1232,8 @@ int roi_align_launch(const ovm_pooler_t* p, const float* boxes, const int32_t* b
     a.tma_ok[l] = all_cl || (s.layout == OVM_LAYOUT_NCHW && !(reinterpret_cast<uintptr_t>(s.data) & 15) && !(s.width & 3) &&
                              p->pooler_resolution == kP);
     if (a.tma_ok[l]) {
-      int rc = all_cl ? level_maps(s.data, s.height, s.width, p->num_images, p->channels, &maps.m[l * kMapsPerLevel])
-                      : level_maps(s.data, s.height, s.width, (long long)p->num_images * p->channels, 0,
+      int rc = all_cl ? level_maps(s.data, s.height, s.width, p->num_images, p->channels, cl_vec, &maps.m[l * kMapsPerLevel])
+                      : level_maps(s.data, s.height, s.width, (long long)p->num_images * p->channels, 0, 0,
                                    &maps.m[l * kMapsPerLevel]);
       if (rc != OVM_OK) return rc;
     }
@@ -1161,7 +1260,8 @@ int roi_align_launch(const ovm_pooler_t* p, const float* boxes, const int32_t* b
   a.chunks_per_split = (chunks + splits - 1) / splits;
   a.splits = (chunks + a.chunks_per_split - 1) / a.chunks_per_split;
 
-  a.split_factor = 0.01f * (float)(tune.split_pct < 100 ? 100 : tune.split_pct);   // < 1 would break the item bound
+  const int split_pct = all_cl ? tune.split_cl : tune.split_pct;
+  a.split_factor = 0.01f * (float)(split_pct < 100 ? 100 : split_pct);   // < 1 would break the item bound
   // with work items: a box yields at most max(splits, 2 area / (split_factor mean area)) of them
   const long long nitems = (long long)n * a.splits + (a.order ? (long long)(2.0 * n / a.split_factor) + 8 : 0);
   // workspace: [0] item count, [1..7] unused, nitems 8-byte work items, then the n per-box headers
@@ -1172,13 +1272,15 @@ int roi_align_launch(const ovm_pooler_t* p, const float* boxes, const int32_t* b
               ws_need);
   a.xalign_mask = tune.align8 ? ~7 : ~3;
   a.evict_first = tune.evict;
-  static SmemOptIn optA, optB, optC;
-  auto kC = roi_align_kernel<12288, 6144, 0, true>;   // channels-last pyramid
-  auto kA = roi_align_kernel<12288, 6144, 0, false>;   // 48 KB ring, stages up to 24 KB: 69 KB of shared memory, 3 CTAs / SM
-  auto kB = roi_align_kernel<9216, 4608, 4, false>;    // 36 KB ring, stages up to 18 KB, 64 registers: 4 CTAs / SM -- measured 125 vs 104 us (OVM_ROI_STAGES=3, tools/roi_bench.py)
+  static SmemOptIn optA, optB, optC, optD;
+  auto kC = roi_align_kernel<12288, 6144, 0, 2>;   // channels-last pyramid, 64-channel chunks
+  auto kD = roi_align_kernel<12288, 6144, 3, 4>;   // channels-last pyramid, 128-channel chunks
+  auto kA = roi_align_kernel<12288, 6144, 0, 0>;   // 48 KB ring, stages up to 24 KB: 69 KB of shared memory, 3 CTAs / SM
+  auto kB = roi_align_kernel<9216, 4608, 4, 0>;    // 36 KB ring, stages up to 18 KB, 64 registers: 4 CTAs / SM -- measured 125 vs 104 us (OVM_ROI_STAGES=3, tools/roi_bench.py)
   {
     const bool small = tune.stages == 3 && !all_cl;
-    int rc = all_cl ? optC.ensure(kC, roi_smem_bytes(12288, true))
+    int rc = cl_vec == 4 ? optD.ensure(kD, roi_smem_bytes(12288, true))
+           : all_cl ? optC.ensure(kC, roi_smem_bytes(12288, true))
                     : (small ? optB.ensure(kB, roi_smem_bytes(9216)) : optA.ensure(kA, roi_smem_bytes(12288)));
     if (rc != OVM_OK) return rc;
     a.ring_floats = small ? 9216 : 12288;
@@ -1196,7 +1298,10 @@ int roi_align_launch(const ovm_pooler_t* p, const float* boxes, const int32_t* b
   }
   const dim3 grid((unsigned)nitems);
   if (all_cl) {
-    OVM_CUDA(launch_pdl(kC, grid, dim3(kThreads), roi_smem_bytes(12288, true), stream, maps, a));
+    if (cl_vec == 4)
+      OVM_CUDA(launch_pdl(kD, grid, dim3(kThreads), roi_smem_bytes(12288, true), stream, maps, a));
+    else
+      OVM_CUDA(launch_pdl(kC, grid, dim3(kThreads), roi_smem_bytes(12288, true), stream, maps, a));
     OVM_LAUNCHED("roi_align_kernel");
     return OVM_OK;
   }

@@ -152,7 +152,7 @@ def test_roi_align_channels_last_matches_oracle(case, out_dtype):
                                    rtol=0, atol=FP32_TOL * float(np.abs(g["pooled"]).max()))
 
 
-@pytest.mark.parametrize("channels", [4, 60, 64, 72, 200])
+@pytest.mark.parametrize("channels", [4, 60, 64, 72, 128, 136, 200])
 def test_roi_align_channels_last_ragged_channels(channels):
     """Channel counts that are not a multiple of the 64-channel chunk (the last chunk is zero-filled by TMA and only its
     real channels are written), down to a single 16-byte pixel."""
