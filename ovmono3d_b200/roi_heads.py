@@ -393,7 +393,7 @@ class ROIHeads3DB200(nn.Module):
         if any(have_scores) and not all(have_scores):
             raise ops.LiftError("either every Instances or none must carry `scores`")
         with_scores = have_scores[0]
-        words = N * 12 + n + (n * 4 + n + 2 * n + 2 if on_host else 0)      # 4-byte words
+        words = N * 12 + (n * 4 + n + 2 * n + 2 if on_host else 0)          # 4-byte words
         stage, done = self._staging(words)
         done.synchronize()                                  # the copy that last used this buffer has finished
         cams_h = stage[: N * 12].view(N, 12)
@@ -410,22 +410,26 @@ class ROIHeads3DB200(nn.Module):
         cams_np[:, 10] = [d[0] for d in im_current_dims]
         cams_np[:, 11] = 0.0
         o_idx = N * 12
-        counts_key = tuple(num_boxes_per_image)
-        if self.__dict__.get("_bidx_key") != counts_key:   # the usual caller has the same box counts call after call
-            self.__dict__["_bidx_key"] = counts_key
-            self.__dict__["_bidx"] = torch.from_numpy(np.repeat(np.arange(N, dtype=np.int32), num_boxes_per_image))
-        stage[o_idx:o_idx + n].view(torch.int32).copy_(self.__dict__["_bidx"])
+        counts_key = (tuple(num_boxes_per_image), device)
+        if self.__dict__.get("_bidx_key") != counts_key:   # the usual caller has the same box counts call after call:
+            self.__dict__["_bidx_key"] = counts_key         # the box -> image index then stays on the device
+            self.__dict__["_bidx"] = torch.from_numpy(
+                np.repeat(np.arange(N, dtype=np.int32), num_boxes_per_image)).to(device)
+        batch_idx = self.__dict__["_bidx"]
         if on_host:
-            o_box, o_sc = o_idx + n, o_idx + 5 * n
+            o_box, o_sc = o_idx, o_idx + 4 * n
             o_cls = (o_sc + n + 1) // 2 * 2                                    # int64 needs an 8-byte boundary
-            def as_(ts, dt):   # the usual case (fp32 boxes / scores, int64 classes) converts nothing
-                return ts if all(t.dtype is dt for t in ts) else [t.to(dt) for t in ts]
+            def cat_into(ts, dst):   # torch.cat converts on the way when the dtypes allow it (the usual case converts
+                try:                  # nothing); anything it refuses is converted explicitly
+                    torch.cat(ts, out=dst)
+                except (RuntimeError, TypeError):
+                    torch.cat([t.to(dst.dtype) for t in ts], out=dst)
 
-            torch.cat(as_([x.pred_boxes.tensor for x in instances], torch.float32), out=stage[o_box:o_sc].view(n, 4))
+            cat_into([x.pred_boxes.tensor for x in instances], stage[o_box:o_sc].view(n, 4))
             if with_scores:
-                torch.cat(as_([x.scores for x in instances], torch.float32), out=stage[o_sc:o_sc + n])
+                cat_into([x.scores for x in instances], stage[o_sc:o_sc + n])
             cls_h = stage[o_cls:o_cls + 2 * n].view(torch.int64)
-            torch.cat(as_([x.pred_classes for x in instances], torch.int64), out=cls_h)
+            cat_into([x.pred_classes for x in instances], cls_h)
             if self.dims_priors_enabled or self.cluster_bins > 1:
                 # per-class heads / priors are indexed by the class id: the reference raises IndexError for an id outside
                 # [0, NUM_CLASSES) (e.g. a category_list longer than NUM_CLASSES); on the device such a box decodes to NaN
@@ -436,7 +440,6 @@ class ROIHeads3DB200(nn.Module):
         stage_d = stage[:words].to(device, non_blocking=True)
         done.record(self._current_stream(device))
         cams = stage_d[: N * 12].view(N, 12)
-        batch_idx = stage_d[o_idx:o_idx + n].view(torch.int32)
         if on_host:
             boxes = stage_d[o_box:o_sc].view(n, 4)
             scores = stage_d[o_sc:o_sc + n] if with_scores else None

@@ -30,6 +30,46 @@ def main():
 
     for _ in range(20):
         step()
+    if "--timeline" in sys.argv:
+        # wall-clock marks inside one call (no profiler): where the 0.30 ms of e2e_resident_features goes
+        import time
+        eng = head._get_engine()
+        marks = {}
+        real_forward = eng.forward
+
+        def forward(*a, **k):
+            marks["eng_in"] = time.perf_counter()
+            r = real_forward(*a, **k)
+            marks["eng_out"] = time.perf_counter()
+            return r
+
+        eng.forward = forward
+        rec_host = torch.empty((hb.n, 48), dtype=torch.float32).pin_memory()
+        rows = []
+        for _ in range(300):
+            inst = []
+            for i in range(len(hb.boxes)):
+                x = Instances(hb.im_dims[i])
+                x.pred_boxes = Boxes(hb.boxes[i])
+                x.pred_classes = hb.classes[i]
+                x.scores = hb.scores[i]
+                inst.append(x)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            t0 = time.perf_counter()
+            e0.record()
+            head._forward_cube(feats, inst, hb.Ks, hb.im_dims, hb.ratios)
+            t1 = time.perf_counter()
+            e1.record()
+            rec_host.copy_(head.last_records, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+            t2 = time.perf_counter()
+            rows.append(((marks["eng_in"] - t0) * 1e6, (marks["eng_out"] - marks["eng_in"]) * 1e6, (t1 - marks["eng_out"]) * 1e6,
+                         (t2 - t1) * 1e6, (t2 - t0) * 1e6, e0.elapsed_time(e1) * 1e3))
+        import numpy as np
+        m = np.median(np.array(rows[50:]), axis=0)
+        print("median us: staging + H2D enqueue %.1f | engine.forward (4 launches) %.1f | write-back %.1f | D2H + sync wait %.1f | "
+              "total %.1f | device events around the call %.1f" % tuple(m))
+        return
     pr = cProfile.Profile()
     pr.enable()
     for _ in range(200):
