@@ -518,7 +518,10 @@ def kernel_breakdown(eng, dbs, flush, lift, K: int, peaks) -> Dict[str, object]:
     fc2_flops = 2.0 * n * FC_DIM * FC_DIM
     kernels = {
         "roi_align": {"ms": ms["roi_align"], "bound": "hbm", "achieved": roi_bytes / (ms["roi_align"] * 1e-3) / 1e9,
-                      "peak": peaks["hbm"], "unit": "GB/s", "algorithmic_bytes": roi_bytes},
+                      "peak": peaks["hbm"], "unit": "GB/s", "algorithmic_bytes": roi_bytes,
+                      "note": "algorithmic bytes = the sum of every box's own footprint + its output (SURVEY 8d); boxes of an "
+                              "image overlap and the L2 serves the re-reads, so DRAM traffic (`traffic`, ncu) can be lower and "
+                              "achieved can exceed the DRAM peak when many boxes share an image"},
         "fc1": {"ms": ms["fc1"], "bound": "tensor", "achieved": fc1_flops / (ms["fc1"] * 1e-3) / 1e12,
                 "peak": peaks["tf_burst"], "unit": "TFLOP/s", "algorithmic_flops": fc1_flops,
                 "note": "split-K tcgen05 GEMM; the CTA that completes a tile applies bias/ReLU (one launch)"},
@@ -549,7 +552,8 @@ def kernel_breakdown(eng, dbs, flush, lift, K: int, peaks) -> Dict[str, object]:
     tp = os.path.join(ROOT, "profiles", "traffic.json")   # dram bytes per launch from the committed ncu capture
     if os.path.exists(tp):
         with open(tp) as f:
-            traffic = json.load(f).get(top)
+            cl_batch = not dbs[0].features[0].is_contiguous()
+            traffic = json.load(f).get("roi_align_channels_last" if top == "roi_align" and cl_batch else top)
     t = kernels[top]
     roofline = {"kernel": top, "bound": t["bound"], "achieved": t["achieved"], "peak": t["peak"], "unit": t["unit"],
                 "frac": t["frac"], "traffic": traffic, "peak_source": peaks["source"] + " (burst: kernel timed alone "
