@@ -104,6 +104,21 @@ typedef struct {
 int ovm_roi_align(const ovm_pooler_t* pooler, const float* boxes, const int32_t* batch_idx, int32_t n,
                   void* out, int32_t out_dtype, int64_t out_ld, int32_t* level_out, void* stream);
 
+/* ovm_roi_align without caller-provided scratch, for callers that cannot allocate device memory (code under CUDA graph
+ * capture, serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * Same arguments, results and errors as ovm_roi_align; pooler->order_ws / order_ws_len are ignored:
+ * the planner's scratch (work items, per-box headers) is a file-scope `static __device__` array of the library,
+ * OVM_ROI_STATIC_WS_BYTES (3.0 MiB) that every GPU which loads the library holds until the process exits.  Limits and
+ * rules: n <= OVM_ROI_STATIC_MAX_BOXES, larger batches are refused with OVM_EINVAL (use ovm_roi_align); the call
+ * allocates nothing on the device (no cudaMalloc / cudaFree, no allocating library routine); every call on a device shares the one
+ * array, which keeps the previous call's contents (the words that must start at zero are cleared on `stream` by the
+ * call itself); therefore two calls that overlap on the GPU (different streams, or graph branches that may run
+ * concurrently) RACE -- order them on one stream.                                                                */
+#define OVM_ROI_STATIC_MAX_BOXES 16384
+#define OVM_ROI_STATIC_WS_BYTES (4 * OVM_ORDER_WS_LEN(OVM_ROI_STATIC_MAX_BOXES))
+int ovm_roi_align_static(const ovm_pooler_t* pooler, const float* boxes, const int32_t* batch_idx, int32_t n,
+                         void* out, int32_t out_dtype, int64_t out_ld, int32_t* level_out, void* stream);
+
 /* D[M,N] = act(A[M,K] . B[N,K]^T + bias), A and B bf16 row-major with leading dimensions lda, ldb
  * (elements, multiples of 8; base pointers 16-byte aligned), fp32 accumulation in TMEM.
  * mode DIRECT: one CTA per 128 x BN tile, epilogue applies bias (may be NULL) and ReLU (relu != 0)

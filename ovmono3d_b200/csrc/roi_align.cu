@@ -1314,3 +1314,61 @@ int roi_align_launch(const ovm_pooler_t* p, const float* boxes, const int32_t* b
 }
 
 }  // namespace ovm
+
+// ===== ovm_roi_align_static: the same launch with the planner's scratch in a file-scope device array =====================
+// For callers that cannot allocate device memory (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc):
+// no counterpart in the reference.  The array is part of the library's
+// image: every GPU that loads the library holds OVM_ROI_STATIC_WS_BYTES of it until the process exits.
+namespace ovm {
+namespace {
+
+constexpr long long kStaticWsInts = OVM_ORDER_WS_LEN(OVM_ROI_STATIC_MAX_BOXES);
+static_assert(kStaticWsInts * 4 == OVM_ROI_STATIC_WS_BYTES, "OVM_ROI_STATIC_WS_BYTES must match OVM_ORDER_WS_LEN(max boxes)");
+static __device__ __align__(256) int g_roi_static_ws[kStaticWsInts];
+
+// In host code `g_roi_static_ws` is a host-side stand-in for the symbol, not a device address: the address a kernel can
+// use comes from cudaGetSymbolAddress, asked once per device with that device current.
+int roi_static_ws(int** out) {
+  constexpr int kMaxDevices = 64;
+  static std::mutex mu;
+  static int* ptrs[kMaxDevices] = {};
+  int dev = -1;
+  OVM_CUDA(cudaGetDevice(&dev));
+  OVM_REQUIRE(dev >= 0 && dev < kMaxDevices, "ovm_roi_align_static: device index %d not in [0,%d)", dev, kMaxDevices);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptrs[dev]) {
+    void* p = nullptr;
+    OVM_CUDA(cudaGetSymbolAddress(&p, g_roi_static_ws));
+    OVM_REQUIRE(p != nullptr && !(reinterpret_cast<uintptr_t>(p) & 255), "ovm_roi_align_static: bad scratch address %p", p);
+    ptrs[dev] = static_cast<int*>(p);
+  }
+  *out = ptrs[dev];
+  return OVM_OK;
+}
+
+}  // namespace
+}  // namespace ovm
+
+#pragma GCC visibility push(default)
+extern "C" int ovm_roi_align_static(const ovm_pooler_t* pooler, const float* boxes, const int32_t* batch_idx, int32_t n,
+                                    void* out, int32_t out_dtype, int64_t out_ld, int32_t* level_out, void* stream) {
+  using namespace ovm;
+  OVM_REQUIRE(pooler != nullptr, "ovm_roi_align_static: pooler is NULL");
+  OVM_REQUIRE(n >= 0 && n <= OVM_ROI_STATIC_MAX_BOXES,
+              "ovm_roi_align_static: n = %d boxes, the built-in scratch holds at most %d (OVM_ROI_STATIC_MAX_BOXES); "
+              "use ovm_roi_align with a caller-allocated order_ws for larger batches", n, OVM_ROI_STATIC_MAX_BOXES);
+  if (n == 0) return OVM_OK;
+  int* ws = nullptr;
+  int rc = roi_static_ws(&ws);
+  if (rc != OVM_OK) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  // The array keeps the previous call's contents.  Words 0..7 (item count, ticket counter) must start at zero: a call
+  // hands the ticket back cleared, but one that was aborted would not have.  Items and headers are rewritten by the
+  // planner before the pooling kernel reads them.
+  OVM_CUDA(cudaMemsetAsync(ws, 0, 8 * sizeof(int), st));
+  ovm_pooler_t p = *pooler;      // the caller's order_ws (if any) is ignored
+  p.order_ws = ws;
+  p.order_ws_len = (int32_t)kStaticWsInts;
+  return roi_align_launch(&p, boxes, batch_idx, n, out, out_dtype, out_ld, level_out, st, nullptr);
+}
+#pragma GCC visibility pop

@@ -35,7 +35,8 @@ EXPORTS = ("ovm_abi_version", "ovm_last_error", "ovm_launch_count", "ovm_struct_
            "ovm_bias_act", "ovm_cast_bf16", "ovm_head_decode", "ovm_lift_forward", "ovm_set_stage_events", "ovm_gemm_set_trace",
            "ovm_roi_set_trace", "ovm_head_set_trace", "ovm_nms", "ovm_gdino_post", "ovm_box_inference", "ovm_post_set_trace",
            "ovm_fc_tail", "ovm_round_tf32", "ovm_iou_box3d", "ovm_lift_forward_peers",
-           "ovm_records_postprocess", "ovm_peer_store_f32", "ovm_cast_f16")
+           "ovm_records_postprocess", "ovm_peer_store_f32", "ovm_cast_f16", "ovm_roi_align_static")
+ROI_STATIC_MAX_BOXES = 16384               # OVM_ROI_STATIC_MAX_BOXES of the header
 NMS_MAX_SEGMENT = 4096
 SPLITK_SLOTS_LEN = 74 * 2 * 128 * 256      # OVM_SPLITK_SLOTS_LEN / OVM_SPLITK_FLAGS_LEN of the header
 SPLITK_FLAGS_LEN = 74 * 2 * 8
@@ -130,6 +131,7 @@ def load_library() -> C.CDLL:
         raise LiftError("ABI version mismatch: library %d, binding %d" % (lib.ovm_abi_version(), OVM_ABI_VERSION))
     vp, i32, i64 = C.c_void_p, C.c_int32, C.c_int64
     lib.ovm_roi_align.argtypes = [C.POINTER(ovm_pooler_t), vp, vp, i32, vp, i32, i64, vp, vp]
+    lib.ovm_roi_align_static.argtypes = [C.POINTER(ovm_pooler_t), vp, vp, i32, vp, i32, i64, vp, vp]
     lib.ovm_gemm_bf16.argtypes = [vp, i64, vp, i64, i32, i32, i32, vp, i32, vp, i32, i64, i32, C.POINTER(i32), vp]
     lib.ovm_bias_act.argtypes = [vp, i64, vp, i32, i32, i32, vp, i32, i64, vp]
     lib.ovm_cast_bf16.argtypes = [vp, i64, i32, i32, vp, i64, vp]
@@ -302,6 +304,27 @@ def roi_align(features: Sequence[torch.Tensor], scales: Sequence[float], boxes: 
                                  dtype_code(out_dtype), Cc * P * P, levels.data_ptr(), _stream()), "ovm_roi_align")
     del keep
     return out, levels
+
+
+def roi_align_static(pooler: ovm_pooler_t, boxes: torch.Tensor, batch_idx: torch.Tensor, out: torch.Tensor,
+                     levels: Optional[torch.Tensor] = None) -> None:
+    """`ovm_roi_align_static`: the same ROIAlign with the planner's scratch inside the library (a file-scope device array),
+    for callers that may not allocate.  Everything is supplied by the caller -- `pooler` from `make_pooler` (keep its
+    tensors alive), `out` [n, C, P, P] fp32 / bf16 contiguous, `levels` [n] int32 -- and nothing is allocated here, by
+    torch or by the library.  n <= ROI_STATIC_MAX_BOXES; calls that overlap on the GPU race (one shared array)."""
+    lib = load_library()
+    n = boxes.shape[0]
+    _need_cuda(boxes, "boxes", torch.float32)
+    _need_cuda(batch_idx, "batch_idx", torch.int32)
+    if not (boxes.is_contiguous() and batch_idx.is_contiguous() and out.is_contiguous()):
+        raise LiftError("roi_align_static takes contiguous tensors (it copies nothing)")
+    cpp = pooler.channels * pooler.pooler_resolution ** 2
+    if out.device != boxes.device or out.numel() != n * cpp:
+        raise LiftError("out must hold [n, C, P, P] on %s" % boxes.device)
+    if levels is not None:
+        _need_cuda(levels, "levels", torch.int32)
+    _check(lib.ovm_roi_align_static(C.byref(pooler), boxes.data_ptr(), batch_idx.data_ptr(), n, out.data_ptr(),
+                                    dtype_code(out.dtype), cpp, _ptr(levels), _stream()), "ovm_roi_align_static")
 
 
 def gemm_bf16(A: torch.Tensor, B: torch.Tensor, bias: Optional[torch.Tensor] = None, relu: bool = False,
