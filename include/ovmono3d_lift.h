@@ -296,6 +296,19 @@ int ovm_lift_forward_peers(const ovm_pooler_t* pooler, const ovm_fc_stack_t* fc,
  * announces its record count to every rank of the fused exchange (shard.RecordExchange, "peer" transport). */
 int ovm_peer_store_f32(float* const* ptrs, int32_t n, float value, void* stream);
 
+/* ovm_lift_forward_peers in two calls, so that a host-driven caller can start the GPU before it has finished staging
+ * its inputs (the reference stages everything first, roi_heads.py:378-400, then launches): OVM_PHASE_POOL plans and
+ * pools (needs pooler, boxes, batch_idx, n, ws; classes / scores / cams / records may be NULL), OVM_PHASE_HEAD runs the
+ * FC stack and the decode on what the pooling phase of the SAME n, ws left in ws->pooled (needs everything).  Both
+ * bits = ovm_lift_forward_peers.  The two calls go to the same stream, pooling first.                               */
+#define OVM_PHASE_POOL 1
+#define OVM_PHASE_HEAD 2
+int ovm_lift_forward_phase(const ovm_pooler_t* pooler, const ovm_fc_stack_t* fc, const ovm_decode_cfg_t* cfg,
+                           const ovm_head_weights_t* heads, const float* boxes, const int64_t* classes,
+                           const float* scores, const int32_t* batch_idx, const float* cams, int32_t n,
+                           const ovm_workspace_t* ws, float* records, float* raw, const ovm_peer_records_t* peers,
+                           int32_t phases, void* stream);
+
 /* Measurement hook (bench.py): while set, ovm_lift_forward records events[0] before its first launch and the
  * next event after each stage -- ROIAlign, every FC layer in issue order (memset + split-K GEMM + bias/ReLU
  * count as one layer), heads+decode -- on the stream it was given, up to `count` events.  Events are

@@ -225,7 +225,17 @@ int ovm_lift_forward_peers(const ovm_pooler_t* pooler, const ovm_fc_stack_t* fc,
                            const float* scores, const int32_t* batch_idx, const float* cams, int32_t n,
                            const ovm_workspace_t* ws, float* records, float* raw, const ovm_peer_records_t* peers,
                            void* stream_) {
+  return ovm_lift_forward_phase(pooler, fc, cfg, heads, boxes, classes, scores, batch_idx, cams, n, ws, records, raw, peers,
+                                OVM_PHASE_POOL | OVM_PHASE_HEAD, stream_);
+}
+
+int ovm_lift_forward_phase(const ovm_pooler_t* pooler, const ovm_fc_stack_t* fc, const ovm_decode_cfg_t* cfg,
+                           const ovm_head_weights_t* heads, const float* boxes, const int64_t* classes,
+                           const float* scores, const int32_t* batch_idx, const float* cams, int32_t n,
+                           const ovm_workspace_t* ws, float* records, float* raw, const ovm_peer_records_t* peers,
+                           int32_t phases, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  OVM_REQUIRE(phases >= 1 && phases <= 3, "ovm_lift_forward_phase: phases = %d (OVM_PHASE_POOL | OVM_PHASE_HEAD)", phases);
   if (peers && peers->num_peers == 0) peers = nullptr;
   OVM_REQUIRE(pooler && fc && cfg && heads && ws, "ovm_lift_forward: NULL descriptor");
   OVM_REQUIRE(fc->num_groups >= 1 && fc->num_groups <= 5 && fc->num_fc >= 1 && fc->layers,
@@ -238,12 +248,19 @@ int ovm_lift_forward_peers(const ovm_pooler_t* pooler, const ovm_fc_stack_t* fc,
               "ovm_lift_forward: workspace.pooled must be [n, ld_pooled >= C*P*P], ld_pooled %% 8 == 0");
   OVM_REQUIRE(fc->num_fc == 1 || (ws->act_a && ws->act_b), "ovm_lift_forward: workspace.act_a/act_b missing");
   int stage = 0;
-  int rc = stage_mark(stage, stream);
-  if (rc != OVM_OK) return rc;
-  rc = roi_align_launch(pooler, boxes, batch_idx, n, ws->pooled, OVM_BF16, ws->ld_pooled, ws->levels, stream, &stage);
-  if (rc != OVM_OK) return rc;
-  rc = stage_mark(stage, stream);
-  if (rc != OVM_OK) return rc;
+  int rc = OVM_OK;
+  if (phases & OVM_PHASE_POOL) {
+    rc = stage_mark(stage, stream);
+    if (rc != OVM_OK) return rc;
+    rc = roi_align_launch(pooler, boxes, batch_idx, n, ws->pooled, OVM_BF16, ws->ld_pooled, ws->levels, stream, &stage);
+    if (rc != OVM_OK) return rc;
+    rc = stage_mark(stage, stream);
+    if (rc != OVM_OK) return rc;
+  } else {
+    stage = 3;     // the three events of the pooling phase belong to the earlier call
+  }
+  if (!(phases & OVM_PHASE_HEAD)) return OVM_OK;
+  OVM_REQUIRE(classes && cams && records, "ovm_lift_forward: classes, cams and records are needed by the head phase");
   // fc1 reads only the first C*P*P columns of each pooled row (its TMA map is K wide), so the pad is never touched
   const int64_t ld_feats = (int64_t)fc->num_groups * cfg->fc_dim;
   const ovm_fc_layer_t& tail = fc->layers[fc->num_fc - 1];

@@ -227,27 +227,7 @@ class LiftEngine:
         raw = torch.empty((n, 16), device=device, dtype=torch.float32) if want_raw else None
         if n == 0:
             return records, raw
-        # the pyramid descriptor depends only on the maps' addresses, shapes and layouts: a steady-state caller (the same
-        # backbone output buffers call after call) re-describes nothing
-        pkey = tuple((f.data_ptr(), f.shape, f.stride()) for f in features)
-        cached = self._pooler_cache.get(pkey)
-        if cached is None:
-            cached = ops.make_pooler(features, self.scales, self.P, self.sampling_ratio, self.canonical_box_size,
-                                     self.canonical_level, self.settings.scale_roi_boxes)
-            if cached[0].channels * self.P * self.P != self.in_dim:
-                raise ops.LiftError("fc1 expects %d inputs but the pyramid gives C*P*P = %d"
-                                    % (self.in_dim, cached[0].channels * self.P * self.P))
-            if any(k is not f for k, f in zip(cached[1], features)):
-                cached = (cached[0], cached[1], False)     # a level was copied to make it contiguous: do not cache the copy
-            else:
-                cached = (cached[0], None, True)           # (do not keep the caller's tensors alive)
-                if len(self._pooler_cache) >= 8:
-                    self._pooler_cache.clear()
-                self._pooler_cache[pkey] = cached
-        pooler, keep = cached[0], cached[1]
-        ws = self._workspace(n, device)
-        pooler.order_ws = self._ws_tensors["order"].data_ptr()
-        pooler.order_ws_len = self._ws_tensors["order"].numel()
+        pooler, keep, ws = self._describe(features, n, device)
         ops._need_cuda(boxes, "boxes", torch.float32)
         ops._need_cuda(classes, "classes", torch.int64)
         ops._need_cuda(batch_idx, "batch_idx", torch.int32)
@@ -269,6 +249,66 @@ class LiftEngine:
         ops._check(rc, "ovm_lift_forward")
         del keep
         return records, raw
+
+    def begin(self, features: Sequence[torch.Tensor], boxes: torch.Tensor, batch_idx: torch.Tensor):
+        """First half of `forward` for a host-driven caller (`ovm_lift_forward_phase`, OVM_PHASE_POOL): plan and pool as
+        soon as the boxes are on the device, so that the GPU works while the host is still staging classes, scores and
+        cameras.  Returns the state `finish` needs; n must be > 0."""
+        lib = ops.load_library()
+        n, device = boxes.shape[0], boxes.device
+        pooler, keep, ws = self._describe(features, n, device)
+        ops._need_cuda(boxes, "boxes", torch.float32)
+        ops._need_cuda(batch_idx, "batch_idx", torch.int32)
+        rc = lib.ovm_lift_forward_phase(C.byref(pooler), C.byref(self._fc_stack), C.byref(self._cfg), C.byref(self._heads),
+                                        boxes.data_ptr(), None, None, batch_idx.data_ptr(), None, n, C.byref(ws), None, None,
+                                        None, ops.PHASE_POOL, ops._stream())
+        ops._check(rc, "ovm_lift_forward_phase(pool)")
+        return (pooler, keep, ws, boxes, batch_idx)
+
+    def finish(self, state, classes: torch.Tensor, scores: Optional[torch.Tensor], cams: torch.Tensor,
+               want_raw: bool = False) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+        """Second half (OVM_PHASE_HEAD): FC stack + decode on what `begin` pooled.  Same stream as `begin`."""
+        lib = ops.load_library()
+        pooler, keep, ws, boxes, batch_idx = state
+        n, device = boxes.shape[0], boxes.device
+        records = torch.empty((n, ops.RECORD_WIDTH), device=device, dtype=torch.float32)
+        raw = torch.empty((n, 16), device=device, dtype=torch.float32) if want_raw else None
+        ops._need_cuda(classes, "classes", torch.int64)
+        ops._need_cuda(cams, "cams", torch.float32)
+        if scores is not None:
+            ops._need_cuda(scores, "scores", torch.float32)
+        rc = lib.ovm_lift_forward_phase(C.byref(pooler), C.byref(self._fc_stack), C.byref(self._cfg), C.byref(self._heads),
+                                        boxes.data_ptr(), classes.data_ptr(), ops._ptr(scores), batch_idx.data_ptr(),
+                                        cams.data_ptr(), n, C.byref(ws), records.data_ptr(), ops._ptr(raw), None,
+                                        ops.PHASE_HEAD, ops._stream())
+        ops._check(rc, "ovm_lift_forward_phase(head)")
+        del keep
+        return records, raw
+
+    def _describe(self, features: Sequence[torch.Tensor], n: int, device: torch.device):
+        """-> (pooler descriptor, tensors it needs kept alive or None, workspace) for n boxes on `device`."""
+        # the pyramid descriptor depends only on the maps' addresses, shapes and layouts: a steady-state caller (the same
+        # backbone output buffers call after call) re-describes nothing
+        pkey = tuple((f.data_ptr(), f.shape, f.stride()) for f in features)
+        cached = self._pooler_cache.get(pkey)
+        if cached is None:
+            cached = ops.make_pooler(features, self.scales, self.P, self.sampling_ratio, self.canonical_box_size,
+                                     self.canonical_level, self.settings.scale_roi_boxes)
+            if cached[0].channels * self.P * self.P != self.in_dim:
+                raise ops.LiftError("fc1 expects %d inputs but the pyramid gives C*P*P = %d"
+                                    % (self.in_dim, cached[0].channels * self.P * self.P))
+            if any(k is not f for k, f in zip(cached[1], features)):
+                cached = (cached[0], cached[1], False)     # a level was copied to make it contiguous: do not cache the copy
+            else:
+                cached = (cached[0], None, True)           # (do not keep the caller's tensors alive)
+                if len(self._pooler_cache) >= 8:
+                    self._pooler_cache.clear()
+                self._pooler_cache[pkey] = cached
+        pooler, keep = cached[0], cached[1]
+        ws = self._workspace(n, device)
+        pooler.order_ws = self._ws_tensors["order"].data_ptr()
+        pooler.order_ws_len = self._ws_tensors["order"].numel()
+        return pooler, keep, ws
 
     @property
     def last_levels(self) -> Optional[torch.Tensor]:

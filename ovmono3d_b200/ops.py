@@ -35,7 +35,9 @@ EXPORTS = ("ovm_abi_version", "ovm_last_error", "ovm_launch_count", "ovm_struct_
            "ovm_bias_act", "ovm_cast_bf16", "ovm_head_decode", "ovm_lift_forward", "ovm_set_stage_events", "ovm_gemm_set_trace",
            "ovm_roi_set_trace", "ovm_head_set_trace", "ovm_nms", "ovm_gdino_post", "ovm_box_inference", "ovm_post_set_trace",
            "ovm_fc_tail", "ovm_round_tf32", "ovm_iou_box3d", "ovm_lift_forward_peers",
-           "ovm_records_postprocess", "ovm_peer_store_f32", "ovm_cast_f16", "ovm_roi_align_static")
+           "ovm_records_postprocess", "ovm_peer_store_f32", "ovm_cast_f16", "ovm_roi_align_static",
+           "ovm_lift_forward_phase")
+PHASE_POOL, PHASE_HEAD = 1, 2
 ROI_STATIC_MAX_BOXES = 16384               # OVM_ROI_STATIC_MAX_BOXES of the header
 NMS_MAX_SEGMENT = 4096
 SPLITK_SLOTS_LEN = 74 * 2 * 128 * 256      # OVM_SPLITK_SLOTS_LEN / OVM_SPLITK_FLAGS_LEN of the header
@@ -143,6 +145,9 @@ def load_library() -> C.CDLL:
     lib.ovm_lift_forward_peers.argtypes = [C.POINTER(ovm_pooler_t), C.POINTER(ovm_fc_stack_t), C.POINTER(ovm_decode_cfg_t),
                                            C.POINTER(ovm_head_weights_t), vp, vp, vp, vp, vp, i32,
                                            C.POINTER(ovm_workspace_t), vp, vp, C.POINTER(ovm_peer_records_t), vp]
+    lib.ovm_lift_forward_phase.argtypes = [C.POINTER(ovm_pooler_t), C.POINTER(ovm_fc_stack_t), C.POINTER(ovm_decode_cfg_t),
+                                           C.POINTER(ovm_head_weights_t), vp, vp, vp, vp, vp, i32,
+                                           C.POINTER(ovm_workspace_t), vp, vp, C.POINTER(ovm_peer_records_t), i32, vp]
     lib.ovm_fc_tail.argtypes = [vp, i64, i32, vp, i64, vp, i32, i32, C.POINTER(ovm_decode_cfg_t),
                                 C.POINTER(ovm_head_weights_t), vp, vp, vp, vp, vp, i32, i32, vp, vp, vp]
     lib.ovm_round_tf32.argtypes = [vp, i64, i32, i32, vp, i64, vp]

@@ -35,15 +35,20 @@ def main():
         import time
         eng = head._get_engine()
         marks = {}
-        real_forward = eng.forward
 
-        def forward(*a, **k):
-            marks["eng_in"] = time.perf_counter()
-            r = real_forward(*a, **k)
-            marks["eng_out"] = time.perf_counter()
-            return r
+        def wrap(name):
+            real = getattr(eng, name)
 
-        eng.forward = forward
+            def f(*a, **k):
+                marks[name + "_in"] = time.perf_counter()
+                r = real(*a, **k)
+                marks[name + "_out"] = time.perf_counter()
+                return r
+
+            setattr(eng, name, f)
+
+        wrap("begin")
+        wrap("finish")
         rec_host = torch.empty((hb.n, 48), dtype=torch.float32).pin_memory()
         rows = []
         for _ in range(300):
@@ -63,12 +68,14 @@ def main():
             rec_host.copy_(head.last_records, non_blocking=True)
             torch.cuda.current_stream().synchronize()
             t2 = time.perf_counter()
-            rows.append(((marks["eng_in"] - t0) * 1e6, (marks["eng_out"] - marks["eng_in"]) * 1e6, (t1 - marks["eng_out"]) * 1e6,
-                         (t2 - t1) * 1e6, (t2 - t0) * 1e6, e0.elapsed_time(e1) * 1e3))
+            rows.append(((marks["begin_in"] - t0) * 1e6, (marks["begin_out"] - marks["begin_in"]) * 1e6,
+                         (marks["finish_in"] - marks["begin_out"]) * 1e6, (marks["finish_out"] - marks["finish_in"]) * 1e6,
+                         (t1 - marks["finish_out"]) * 1e6, (t2 - t1) * 1e6, (t2 - t0) * 1e6, e0.elapsed_time(e1) * 1e3))
         import numpy as np
         m = np.median(np.array(rows[50:]), axis=0)
-        print("median us: staging + H2D enqueue %.1f | engine.forward (4 launches) %.1f | write-back %.1f | D2H + sync wait %.1f | "
-              "total %.1f | device events around the call %.1f" % tuple(m))
+        print("median us: box staging + H2D %.1f | engine.begin (plan + pool launches) %.1f | camera / score / class staging + "
+              "H2D %.1f | engine.finish (FC + decode launches) %.1f | write-back %.1f | D2H + sync wait %.1f | total %.1f | "
+              "device events around the call %.1f" % tuple(m))
         return
     pr = cProfile.Profile()
     pr.enable()
