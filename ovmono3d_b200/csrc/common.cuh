@@ -3,6 +3,7 @@
 
 #include <cuda.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -106,6 +107,35 @@ int roi_align_launch(const ovm_pooler_t* pooler, const float* boxes, const int32
                      int* stage_idx = nullptr);
 // Split-K with a fused finish (lift_api.cu): `out` of gemm_bf16_launch is the zeroed fp32 accumulator, the CTA that
 // completes a tile writes act(acc + bias) to `out` here and zeroes accumulator and counter again.
+#ifdef __CUDACC__
+// round-to-nearest (ties away) to TF32's 10 mantissa bits; the value stays an fp32 bit pattern
+__device__ __forceinline__ float round_tf32(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
+__device__ __forceinline__ float4 round_tf32(float4 v) {
+  return make_float4(round_tf32(v.x), round_tf32(v.y), round_tf32(v.z), round_tf32(v.w));
+}
+// four fp32 -> four 16-bit values: bf16 (round to nearest even) or fp16 (the same, saturated to +-65504 so that no
+// infinity is made; NaN stays NaN).  fp16 carries TF32's 10 mantissa bits in bf16's 2 bytes: the format of the
+// activations handed to a kind::f16 tail layer (fc_tail.cu).
+__device__ __forceinline__ float sat_f16(float x) { return x > 65504.f ? 65504.f : (x < -65504.f ? -65504.f : x); }
+__device__ __forceinline__ uint2 pack16(float4 v, int f16) {
+  uint2 pk;
+  if (f16) {
+    __half2 lo = __floats2half2_rn(sat_f16(v.x), sat_f16(v.y)), hi = __floats2half2_rn(sat_f16(v.z), sat_f16(v.w));
+    pk.x = *reinterpret_cast<uint32_t*>(&lo);
+    pk.y = *reinterpret_cast<uint32_t*>(&hi);
+  } else {
+    __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+    pk.x = *reinterpret_cast<uint32_t*>(&lo);
+    pk.y = *reinterpret_cast<uint32_t*>(&hi);
+  }
+  return pk;
+}
+#endif
+
 struct GemmFinish {
   int32_t* tile_counters;   // device, zero on entry, >= num_counters entries
   int32_t num_counters;
@@ -119,6 +149,7 @@ struct GemmFinish {
   int64_t slots_len = 0;
   int32_t* slot_flags = nullptr;
   int32_t flags_len = 0;
+  int32_t defer = 0;        // accumulate only: no counters, no finish -- the consumer applies bias / ReLU (TailPending)
 };
 int gemm_bf16_launch(const void* A, int64_t lda, const void* B, int64_t ldb, int32_t M, int32_t N, int32_t K,
                      const float* bias, int32_t relu, void* out, int32_t out_dtype, int64_t ldo, int32_t mode,
@@ -137,12 +168,21 @@ int head_decode_launch(const ovm_decode_cfg_t* cfg, const ovm_head_weights_t* w,
                        const int32_t* batch_idx, const float* cams, int32_t num_images, int32_t n,
                        float* records, float* raw, cudaStream_t stream, const ovm_peer_records_t* peers = nullptr);
 // fc_tail.cu: last FC layer + heads + decode in one launch (class-agnostic heads, shared FC stack)
+// `pending`: the layer before was a split-K GEMM that only ACCUMULATED (GemmFinish.defer): its raw fp32 sums sit in
+// acc [n, ld] (a workspace that is zero between calls) and A has not been written yet.  The tail then finishes that
+// layer on the way in: every CTA reads the rows it is about to load, adds the bias, applies ReLU, rounds to A's format,
+// writes A, and hands acc back zeroed.
+struct TailPending {
+  float* acc;
+  int64_t ld;
+  const float* bias;   // [K of the tail] = [N of the layer before]
+};
 bool fc_tail_supported(const ovm_decode_cfg_t* cfg, int32_t N, int32_t K);
 int fc_tail_launch(const void* A, int64_t lda, int32_t a_dtype, const void* W, int64_t ldw, const float* bias, int32_t N,
                    int32_t K, const ovm_decode_cfg_t* cfg, const ovm_head_weights_t* w, const float* boxes,
                    const int64_t* classes, const float* scores, const int32_t* batch_idx, const float* cams,
                    int32_t num_images, int32_t n, float* records, float* raw, cudaStream_t stream,
-                   const ovm_peer_records_t* peers = nullptr);
+                   const ovm_peer_records_t* peers = nullptr, const struct TailPending* pending = nullptr);
 int cast_f16_launch(const float* in, int64_t ld_in, int32_t rows, int32_t cols, void* out, int64_t ld_out, cudaStream_t stream);
 int round_tf32_launch(const float* in, int64_t ld_in, int32_t rows, int32_t cols, float* out, int64_t ld_out,
                       cudaStream_t stream);

@@ -44,6 +44,7 @@ constexpr int kTailEpiWarps = 8;       // two per TMEM lane quadrant, each takes
 constexpr int kTailThreads = (2 + kTailEpiWarps) * 32;
 constexpr int kHwStride = 16;          // head rows per column in shared memory (13 used)
 constexpr int kMaxCS = 8;
+constexpr int kConvGroups = 4;         // column groups of the deferred finish of the layer before (TailPending)
 constexpr int kPartFloats = 2 * kMaxCS * kMaxHeadRows * (kTM / kMaxCS);   // [2 CS contributors][13][128 / CS rows]
 constexpr int kXchStride = 20;         // floats one box's two decoding threads exchange (M 9, has_m, X Y z u v score, 3 raw)
 constexpr size_t kTailSmemBytes = 1024 + (size_t)kTailStages * kTailStageBytes + 128 /* barriers, tmem slot */ +
@@ -57,6 +58,13 @@ struct TailArgs {
   int kblocks;           // ceil(K * sizeof(element) / 128)
   int elems_per_row;     // K elements per 128-byte row: 32 (tf32) or 64 (bf16)
   const float* bias;     // [N]
+  // the layer before only accumulated (TailPending): raw sums in acc [n, acc_ld]; this kernel writes a_out (the tensor
+  // tmA describes, pitch a_ld elements) = round(relu(acc + bias_prev)) for the rows it loads and zeroes acc
+  float* acc;
+  long long acc_ld;
+  const float* bias_prev;
+  void* a_out;
+  long long a_ld;
 };
 
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
@@ -64,6 +72,9 @@ __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
 }
 __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   uint32_t done;
@@ -186,6 +197,75 @@ __device__ __forceinline__ void tail_stamp(const TailArgs& g, int slot) {
   }
 }
 
+// The finish of the layer before (TailPending) by the eight epilogue warps of one CTA; see the call site.  Kept out of line:
+// inlined, its sixteen float4 in flight changed the register allocation of the whole kernel (109 -> 128) and cost the
+// main loop and the decode 1.5 us.
+template <int FMT>
+__device__ __noinline__ void finish_prev_layer(float* acc, long long acc_ld, const float* bias_prev, void* a_out, long long a_ld,
+                                               int K, int n, int cs, int rank, int m_tile, bool conv_grouped,
+                                               uint32_t tfull_bar) {   // (scalars: a reference to the kernel's
+                                                                       // parameter struct would copy it to local memory)
+  auto conv_bar = [&](int c) { return c == 0 ? tfull_bar + 8 : tfull_bar + 16 + 8 * (uint32_t)c; };
+    const int slice = kTM / cs;
+    const int row0 = m_tile * kTM + rank * slice;
+    auto finish4 = [&](float4 w, long long row, int c) {
+      __stcg(reinterpret_cast<float4*>(acc + row * acc_ld + c), make_float4(0.f, 0.f, 0.f, 0.f));
+      const float4 bv = __ldg(reinterpret_cast<const float4*>(bias_prev + c));
+      w.x += bv.x; w.y += bv.y; w.z += bv.z; w.w += bv.w;
+      w.x = w.x < 0.f ? 0.f : w.x; w.y = w.y < 0.f ? 0.f : w.y;     // torch.relu keeps NaN
+      w.z = w.z < 0.f ? 0.f : w.z; w.w = w.w < 0.f ? 0.f : w.w;
+      if (FMT == kFmtTF32)
+        *reinterpret_cast<float4*>(reinterpret_cast<float*>(a_out) + row * a_ld + c) = round_tf32(w);
+      else
+        *reinterpret_cast<uint2*>(reinterpret_cast<uint16_t*>(a_out) + row * a_ld + c) = pack16(w, FMT == kFmtF16);
+    };
+    const int et = threadIdx.x - 64;
+    if (conv_grouped) {
+      // slice * K = 16384 floats = 4096 float4 = 16 per thread, 4 per thread and group; k4g float4 per row and group
+      const int k4g = K / (4 * kConvGroups), sh = __ffs(k4g) - 1;
+      float4 x[16];
+#pragma unroll
+      for (int u = 0; u < 16; ++u) {
+        const int grp = u >> 2, rem = (u & 3) * 256 + et;
+        const int r = rem >> sh, c = (grp * k4g + (rem & (k4g - 1))) * 4;
+        x[u] = row0 + r < n ? __ldcg(reinterpret_cast<const float4*>(acc + (long long)(row0 + r) * acc_ld + c))
+                                : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+#pragma unroll
+      for (int grp = 0; grp < kConvGroups; ++grp) {
+#pragma unroll
+        for (int v = 0; v < 4; ++v) {
+          const int rem = v * 256 + et;
+          const int r = rem >> sh, c = (grp * k4g + (rem & (k4g - 1))) * 4;
+          if (row0 + r < n) finish4(x[grp * 4 + v], row0 + r, c);
+        }
+        asm volatile("fence.proxy.async.global;" ::: "memory");
+        mbar_arrive(conv_bar(grp));
+      }
+    } else {
+      const int k4 = K >> 2;
+      const int total = slice * k4;
+      constexpr int kBatch = 8;
+      for (int i0 = et; i0 < total; i0 += kTailEpiWarps * 32 * kBatch) {
+        float4 x[kBatch];
+#pragma unroll
+        for (int u = 0; u < kBatch; ++u) {
+          const int i = i0 + u * kTailEpiWarps * 32;
+          const int r = i / k4, c = (i - r * k4) * 4;
+          if (i < total && row0 + r < n) x[u] = __ldcg(reinterpret_cast<const float4*>(acc + (long long)(row0 + r) * acc_ld + c));
+        }
+#pragma unroll
+        for (int u = 0; u < kBatch; ++u) {
+          const int i = i0 + u * kTailEpiWarps * 32;
+          const int r = i / k4, c = (i - r * k4) * 4;
+          if (i < total && row0 + r < n) finish4(x[u], row0 + r, c);
+        }
+      }
+      asm volatile("fence.proxy.async.global;" ::: "memory");
+      mbar_arrive(conv_bar(0));
+    }
+}
+
 template <int FMT>
 __global__ void __launch_bounds__(kTailThreads, 1)
 fc_tail_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TailArgs g) {
@@ -200,6 +280,9 @@ fc_tail_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const uint32_t empty_bar = bars + 8 * kTailStages;       // kTailStages
   const uint32_t tfull_bar = bars + 16 * kTailStages;      // 1
   const uint32_t tmem_slot = tfull_bar + 16;
+  // conversion barriers (TailPending) in the free words of the 128-byte barrier block: +88, +104, +112, +120
+  auto conv_bar = [&](int c) { return c == 0 ? tfull_bar + 8 : tfull_bar + 16 + 8 * (uint32_t)c; };
+  static_assert(16 * kTailStages + 16 + 8 * kConvGroups <= 128, "barrier block is 128 bytes");
   uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(aligned + kTailStages * kTailStageBytes + 16 * kTailStages + 16);
   float* hw_t = reinterpret_cast<float*>(aligned + kTailStages * kTailStageBytes + 128);   // [128 columns][16 rows]
   float* b2s = hw_t + kTN * kHwStride;                                                     // [128]
@@ -228,6 +311,7 @@ fc_tail_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       mbar_init(empty_bar + 8 * s, cs);      // a slot is free when every CTA of the cluster has consumed it (A is multicast)
     }
     mbar_init(tfull_bar, 1);
+    for (int c = 0; c < kConvGroups; ++c) mbar_init(conv_bar(c), kTailEpiWarps * 32);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) {
@@ -272,8 +356,17 @@ fc_tail_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const uint32_t tmem_base = *tmem_slot_ptr;
   if (threadIdx.x == 0) tail_stamp(g, 1);
   pdl_trigger();
-  pdl_wait();                // h1 comes from the FC layer before
+  pdl_wait();                // h1 (or its raw sums) comes from the FC layer before
   if (threadIdx.x == 0) tail_stamp(g, 2);
+
+  // ===== finish of the layer before (TailPending), for exactly the rows this CTA's TMA loads (and multicasts): rows
+  // [rank * slice, +slice) of the tile, all K columns.  Generic-proxy global stores -> fence.proxy.async -> mbarrier ->
+  // TMA (async proxy) reads of the same addresses by the same CTA: no cluster-wide synchronisation is needed.  The
+  // columns go in kConvGroups groups of whole K blocks, each with its own barrier, so that the producer starts on the
+  // first group while the others are still being converted; every load is issued before the first result is used.
+  const bool conv_grouped = g.acc && (kTM / cs) * g.K == 16 * 1024 && g.kblocks % kConvGroups == 0;
+  if (g.acc && warp >= 2)
+    finish_prev_layer<FMT>(g.acc, g.acc_ld, g.bias_prev, g.a_out, g.a_ld, g.K, g.d.n, cs, rank, m_tile, conv_grouped, tfull_bar);
 
   if (warp == 0) {
     if (lane == 0) {
@@ -284,7 +377,13 @@ fc_tail_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       uint32_t phase = 0;
       const uint16_t mask = (uint16_t)((1u << cs) - 1u);
       const int slice_rows = kTM / cs;
+      const int conv_every = conv_grouped ? g.kblocks / kConvGroups : g.kblocks;
+      int conv_next = g.acc ? 0 : g.kblocks, conv_grp = 0;
       for (int kb = 0; kb < g.kblocks; ++kb) {
+        if (kb == conv_next) {     // this CTA's rows of the next group of K blocks are written
+          mbar_wait(conv_bar(conv_grp++), 0);
+          conv_next += conv_every;
+        }
         mbar_wait(empty_bar + 8 * stage, phase ^ 1);
         mbar_expect_tx(full_bar + 8 * stage, kTailStageBytes);
         const uint32_t a_dst = smem_a + stage * kTailABytes + rank * slice_rows * kRowBytes;
@@ -494,7 +593,7 @@ int fc_tail_launch(const void* A, int64_t lda, int32_t a_dtype, const void* W, i
                    int32_t K, const ovm_decode_cfg_t* cfg, const ovm_head_weights_t* w, const float* boxes,
                    const int64_t* classes, const float* scores, const int32_t* batch_idx, const float* cams,
                    int32_t num_images, int32_t n, float* records, float* raw, cudaStream_t stream,
-                   const ovm_peer_records_t* peers) {
+                   const ovm_peer_records_t* peers, const TailPending* pending) {
   OVM_REQUIRE(cfg && w, "ovm_fc_tail: cfg / weights are NULL");
   OVM_REQUIRE(a_dtype == OVM_BF16 || a_dtype == OVM_TF32 || a_dtype == OVM_F16,
               "ovm_fc_tail: operand dtype %d (OVM_BF16, OVM_F16 or OVM_TF32)", a_dtype);
@@ -547,6 +646,16 @@ int fc_tail_launch(const void* A, int64_t lda, int32_t a_dtype, const void* W, i
   g.elems_per_row = kRowBytes / esz;
   g.kblocks = (K + g.elems_per_row - 1) / g.elems_per_row;
   g.bias = bias;
+  if (pending) {
+    OVM_REQUIRE(pending->acc && pending->bias && pending->ld >= K && pending->ld % 4 == 0 && K % 4 == 0 &&
+                    !(reinterpret_cast<uintptr_t>(pending->acc) & 15) && !(reinterpret_cast<uintptr_t>(pending->bias) & 15),
+                "ovm_fc_tail: pending accumulator must be [n, ld >= K] fp32, 16-byte aligned, K %% 4 == 0");
+    g.acc = pending->acc;
+    g.acc_ld = pending->ld;
+    g.bias_prev = pending->bias;
+    g.a_out = const_cast<void*>(A);
+    g.a_ld = lda;
+  }
   CUtensorMap tmA, tmB;
   int rc = make_tail_map(&tmA, A, n, K, lda, a_dtype, kTM / g.cs);   // each CTA multicasts its slice of the rows
   if (rc != OVM_OK) return rc;

@@ -153,32 +153,7 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* v) {
       : "memory");
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
-// round-to-nearest (ties away) to TF32's 10 mantissa bits; the value stays an fp32 bit pattern
-__device__ __forceinline__ float round_tf32(float x) {
-  uint32_t r;
-  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
-  return __uint_as_float(r);
-}
-__device__ __forceinline__ float4 round_tf32(float4 v) {
-  return make_float4(round_tf32(v.x), round_tf32(v.y), round_tf32(v.z), round_tf32(v.w));
-}
-// four fp32 -> four 16-bit values: bf16 (round to nearest even) or fp16 (the same, saturated to +-65504 so that no
-// infinity is made; NaN stays NaN).  fp16 carries TF32's 10 mantissa bits in bf16's 2 bytes: the format of the
-// activations handed to a kind::f16 tail layer (fc_tail.cu).
-__device__ __forceinline__ float sat_f16(float x) { return x > 65504.f ? 65504.f : (x < -65504.f ? -65504.f : x); }
-__device__ __forceinline__ uint2 pack16(float4 v, int f16) {
-  uint2 pk;
-  if (f16) {
-    __half2 lo = __floats2half2_rn(sat_f16(v.x), sat_f16(v.y)), hi = __floats2half2_rn(sat_f16(v.z), sat_f16(v.w));
-    pk.x = *reinterpret_cast<uint32_t*>(&lo);
-    pk.y = *reinterpret_cast<uint32_t*>(&hi);
-  } else {
-    __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
-    pk.x = *reinterpret_cast<uint32_t*>(&lo);
-    pk.y = *reinterpret_cast<uint32_t*>(&hi);
-  }
-  return pk;
-}
+// (round_tf32, sat_f16, pack16: common.cuh -- shared with fc_tail.cu)
 __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
@@ -1185,7 +1160,7 @@ int gemm_bf16_launch(const void* A, int64_t lda, const void* B, int64_t ldb, int
     OVM_REQUIRE(g.streamk && fin->tile_counters && fin->out && fin->num_counters >= g.num_tiles && N % 4 == 0 &&
                     fin->ldo >= N && fin->ldo % 4 == 0 && !(reinterpret_cast<uintptr_t>(fin->out) & 15),
                 "ovm_gemm_bf16: fused split-K finish needs STREAMK, %d tile counters and an aligned output", g.num_tiles);
-    g.tile_counters = fin->tile_counters;
+    g.tile_counters = fin->defer ? nullptr : fin->tile_counters;
     g.bias = fin->bias;
     g.relu = fin->relu;
     g.fin_out = fin->out;
@@ -1212,14 +1187,14 @@ int gemm_bf16_launch(const void* A, int64_t lda, const void* B, int64_t ldb, int
     // needs registers the epilogue does not have (spills: 69 us).  What it buys is a bit-reproducible layer.
     static const bool slots_ok = [] { const char* v = getenv("OVM_GEMM_SLOTS"); return v && atoi(v) != 0; }();
     const long long starts_per_tile = ((long long)g.kb_per_tile * clusters + total - 1) / total;   // cluster ranges starting in one tile, at most
-    const bool use_slots = slots_ok && fin->slots && fin->slot_flags && starts_per_tile <= kMaxPartials &&
+    const bool use_slots = !fin->defer && slots_ok && fin->slots && fin->slot_flags && starts_per_tile <= kMaxPartials &&
                            fin->slots_len >= (long long)clusters * 2 * BM * kPairBN && fin->flags_len >= clusters * 2 * kEpiWarps &&
                            !(reinterpret_cast<uintptr_t>(fin->slots) & 15);
     // Opt-in (OVM_GEMM_GRIDFIN=1).  Measured at C2: the fc1 stage alone 53.4 -> 51.7 us, but the step 0.168 -> 0.172 ms:
     // with every fc1 CTA held to the end, the next kernel's CTAs (resident 13 us early on the SMs of fc1 CTAs that finish
     // first, staging their head weights) lose their head start.
     static const bool gridfin = [] { const char* v = getenv("OVM_GEMM_GRIDFIN"); return v && atoi(v) != 0; }();
-    g.grid_finish = gridfin && !use_slots && fin->num_counters >= 2 && 2 * clusters <= kNumSMs;
+    g.grid_finish = !fin->defer && gridfin && !use_slots && fin->num_counters >= 2 && 2 * clusters <= kNumSMs;
     if (use_slots) {
       g.slots = fin->slots;
       g.slot_flags = fin->slot_flags;

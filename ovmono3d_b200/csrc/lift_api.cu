@@ -55,7 +55,7 @@ namespace {
 // and *out_last / *ld_last describe the activations handed to the tail.
 int run_fc_group(const ovm_fc_layer_t* layers, int num_fc, bool ends_stack, int last_mid_dtype, const void* x, int64_t ldx,
                  int32_t n, const ovm_workspace_t* ws, float* feats, int64_t ld_feats, cudaStream_t stream, int& stage,
-                 const void** out_last = nullptr, int64_t* ld_last = nullptr) {
+                 const void** out_last = nullptr, int64_t* ld_last = nullptr, TailPending* defer_last = nullptr) {
   const void* in = x;
   int64_t ld_in = ldx;
   for (int k = 0; k < num_fc; ++k) {
@@ -80,8 +80,13 @@ int run_fc_group(const ovm_fc_layer_t* layers, int num_fc, bool ends_stack, int 
       // ws->acc (and the tile counters) are zero on entry (workspace contract) and handed back zeroed
       if (ws->tile_counters && ws->num_tile_counters >= ((n + 127) / 128) * ((L.N + 255) / 256)) {
         // one launch: the CTA that completes a tile applies bias + ReLU and writes the layer's output
-        const GemmFinish fin{ws->tile_counters, ws->num_tile_counters, L.bias, 1, out, out_dtype, ldo,
-                             ws->splitk_slots, ws->splitk_slots_len, ws->splitk_flags, ws->splitk_flags_len};
+        GemmFinish fin{ws->tile_counters, ws->num_tile_counters, L.bias, 1, out, out_dtype, ldo,
+                       ws->splitk_slots, ws->splitk_slots_len, ws->splitk_flags, ws->splitk_flags_len};
+        if (defer_last && k == num_fc - 1 && !ends_stack) {
+          // the fused tail finishes this layer on its way in (TailPending): the GEMM only accumulates into ws->acc
+          fin.defer = 1;
+          *defer_last = TailPending{ws->acc, L.N, L.bias};
+        }
         int rc = gemm_bf16_launch(in, ld_in, L.weight, L.ldw, n, L.N, L.K, nullptr, 0, ws->acc, OVM_F32, L.N,
                                   OVM_GEMM_STREAMK, nullptr, stream, &fin);
         if (rc != OVM_OK) return rc;
@@ -274,12 +279,15 @@ int ovm_lift_forward_phase(const ovm_pooler_t* pooler, const ovm_fc_stack_t* fc,
     const int fmt = alt ? tail.alt_dtype : OVM_BF16;
     const void* h = nullptr;
     int64_t ldh = 0;
+    // OVM_TAIL_DEFER=0: the split-K layer before the tail finishes itself (per-tile counters, round 2's first version)
+    static const bool defer_ok = [] { const char* v = getenv("OVM_TAIL_DEFER"); return !v || atoi(v) != 0; }();
+    TailPending pending{nullptr, 0, nullptr};
     rc = run_fc_group(fc->layers, fc->num_fc - 1, /*ends_stack=*/false, fmt, ws->pooled, ws->ld_pooled, n, ws, nullptr, 0,
-                      stream, stage, &h, &ldh);
+                      stream, stage, &h, &ldh, defer_ok ? &pending : nullptr);
     if (rc != OVM_OK) return rc;
     rc = fc_tail_launch(h, ldh, fmt, alt ? tail.weight_alt : tail.weight, alt ? tail.ldw_alt : tail.ldw, tail.bias, tail.N,
                         tail.K, cfg, heads, boxes, classes, scores, batch_idx, cams, pooler->num_images, n, records, raw,
-                        stream, peers);
+                        stream, peers, pending.acc ? &pending : nullptr);
     if (rc != OVM_OK) return rc;
     return stage_mark(stage, stream);
   }
