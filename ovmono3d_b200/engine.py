@@ -87,6 +87,11 @@ class LiftEngine:
         ts = self._params + [p for p in priors if p is not None]
         return tuple((t.data_ptr(), t._version) for t in ts)
 
+    @property
+    def ready(self) -> bool:
+        """`prepare` has built the descriptors at least once (they may be stale: `prepare` checks)."""
+        return self._weights_key is not None
+
     def invalidate(self) -> None:
         """Forget the bf16 / TF32 copies of the FC weights: the next `prepare` rebuilds them.  `prepare` notices
         re-assigned parameters and in-place updates that bump the tensor version (`load_state_dict`, `copy_`, optimiser

@@ -50,6 +50,12 @@ def _head_fc(fan_in: int, fan_out: int, bias: float = 0.0) -> nn.Linear:
     return fc
 
 
+# column widths of a detection record (ops.REC_*): corners 24 | centre 3 | projected centre 2 | dimensions 3 | pose 9 |
+# 2-D box 4 | score 1 | class + pad 2
+_REC_WIDTHS = [24, 3, 2, 3, 9, 4, 1, 2]
+assert sum(_REC_WIDTHS) == ops.RECORD_WIDTH and ops.REC_SCORE == 45 and ops.REC_POSE == slice(32, 41)
+
+
 @ROI_CUBE_HEAD_REGISTRY.register()
 class CubeHead(nn.Module):
     """Parameter container with the reference CubeHead's module tree and state-dict keys
@@ -406,7 +412,11 @@ class ROIHeads3DB200(nn.Module):
         stage, done = self._staging(words)
         done.synchronize()                                  # the copies that last used this buffer have finished
         eng = self._get_engine()
-        eng.prepare(device, self.priors_dims_per_cat, self.priors_z_scales, getattr(self, "priors_z_stats", None))
+        # the weight check (a version / address scan of ~35 parameters, 11 us) is only needed before the FC stack: in the
+        # steady state it runs after the pooling launches (the pooling phase reads no weights)
+        prepared = not (on_host and eng.ready)
+        if prepared:
+            eng.prepare(device, self.priors_dims_per_cat, self.priors_z_scales, getattr(self, "priors_z_stats", None))
         counts_key = (tuple(num_boxes_per_image), device)
         if self.__dict__.get("_bidx_key") != counts_key:   # the usual caller has the same box counts call after call:
             self.__dict__["_bidx_key"] = counts_key         # the box -> image index then stays on the device
@@ -425,21 +435,24 @@ class ROIHeads3DB200(nn.Module):
             cat_into(box_ts, stage[:o_cam].view(n, 4))
             boxes = stage[:o_cam].to(device, non_blocking=True).view(n, 4)
             state = eng.begin(feats, boxes, batch_idx)      # the GPU starts here
+        if not prepared:
+            eng.prepare(device, self.priors_dims_per_cat, self.priors_z_scales, getattr(self, "priors_z_stats", None))
 
         cams_np = stage[o_cam:o_sc].view(N, 12).numpy()
         # the reference accepts Ks as a list of [3,3] tensors on any device or as nested lists (rcnn3d.py:95)
-        if all(type(k) is torch.Tensor and k.dtype is torch.float32 and k.device.type == "cpu" for k in Ks):
-            kbuf = self.__dict__.get("_kbuf")              # the usual caller: host fp32 [3,3] tensors -> one stack into
-            if kbuf is None or kbuf[0].shape[0] != N:       # a kept buffer, one strided numpy assignment
-                t = torch.empty(N, 3, 3)
-                kbuf = self.__dict__["_kbuf"] = (t, t.numpy().reshape(N, 9))
+        kbuf = self.__dict__.get("_kbuf")
+        if kbuf is None or kbuf[0].shape[0] != N:
+            t = torch.empty(N, 3, 3)
+            kbuf = self.__dict__["_kbuf"] = (t, t.numpy().reshape(N, 9))
+        try:      # the usual caller: host [3,3] tensors -> one stack into a kept buffer, one strided numpy assignment
             torch.stack(Ks if isinstance(Ks, (list, tuple)) else list(Ks), out=kbuf[0])
             cams_np[:, :9] = kbuf[1]
-        elif all(isinstance(k, torch.Tensor) for k in Ks):
-            k_all = (torch.stack(list(Ks)) if N > 1 else Ks[0].unsqueeze(0)).to("cpu", torch.float32)
-            cams_np[:, :9] = k_all.reshape(N, 9).numpy()
-        else:
-            cams_np[:, :9] = np.asarray([np.asarray(k, dtype=np.float32) for k in Ks]).reshape(N, 9)
+        except (RuntimeError, TypeError):    # tensors on another device, or nested lists
+            if all(isinstance(k, torch.Tensor) for k in Ks):
+                k_all = (torch.stack(list(Ks)) if N > 1 else Ks[0].unsqueeze(0)).to("cpu", torch.float32)
+                cams_np[:, :9] = k_all.reshape(N, 9).numpy()
+            else:
+                cams_np[:, :9] = np.asarray([np.asarray(k, dtype=np.float32) for k in Ks]).reshape(N, 9)
         cams_np[:, 9] = im_scales_ratio
         cams_np[:, 10] = [d[0] for d in im_current_dims]
         cams_np[:, 11] = 0.0
@@ -472,21 +485,29 @@ class ROIHeads3DB200(nn.Module):
             scores = gather([f["scores"] for f in fdicts], torch.float32) if with_scores else None
             records, raw = eng.forward(feats, boxes, classes, scores, batch_idx, cams, want_raw=return_raw)
 
-        # write-back (roi_heads.py:811-843): the Instances fields are views into the [n,48] records
-        fields = (("scores", records[:, ops.REC_SCORE]), ("pred_bbox3D", records[:, ops.REC_BBOX3D].view(n, 8, 3)),
-                  ("pred_center_cam", records[:, ops.REC_CENTER_CAM]), ("pred_center_2D", records[:, ops.REC_CENTER_2D]),
-                  ("pred_dimensions", records[:, ops.REC_DIMENSIONS]), ("pred_pose", records[:, ops.REC_POSE].view(n, 3, 3)))
+        # write-back (roi_heads.py:811-843): the Instances fields are views into the [n,48] records.  One split along the
+        # columns, then per field one unbind over the images when the box counts are equal (the usual fixed top-k
+        # detector) or one split otherwise: every tensor object costs ~0.7 us of host time and there are 6 N of them.
+        # Lengths match by construction, so Instances.set()'s per-field len() assertion (96 per batch) is skipped.
         k0 = num_boxes_per_image[0]
-        equal = all(k == k0 for k in num_boxes_per_image)
-        for name, t in fields:
-            # lengths match by construction: skip Instances.set()'s per-field len() assertion (96 of them per batch)
-            if N == 1:
-                fdicts[0][name] = t
-                continue
-            # equal box counts (the usual fixed top-k detector): one unbind instead of a split with N sizes
-            parts = t.unflatten(0, (N, k0)).unbind(0) if equal else t.split(num_boxes_per_image)
-            for f, part in zip(fdicts, parts):
-                f[name] = part
+        equal = N > 1 and all(k == k0 for k in num_boxes_per_image)
+        rec3 = records.view(N, k0, ops.RECORD_WIDTH) if equal else records
+        bbox, ccam, c2d, dims, pose, _box2d, score, _rest = rec3.split(_REC_WIDTHS, dim=-1)
+        if equal:
+            fields = (("scores", score.squeeze(-1)), ("pred_bbox3D", bbox.view(N, k0, 8, 3)), ("pred_center_cam", ccam),
+                      ("pred_center_2D", c2d), ("pred_dimensions", dims), ("pred_pose", pose.view(N, k0, 3, 3)))
+            for name, t in fields:
+                for f, part in zip(fdicts, t.unbind(0)):
+                    f[name] = part
+        else:
+            fields = (("scores", score.squeeze(-1)), ("pred_bbox3D", bbox.view(n, 8, 3)), ("pred_center_cam", ccam),
+                      ("pred_center_2D", c2d), ("pred_dimensions", dims), ("pred_pose", pose.view(n, 3, 3)))
+            for name, t in fields:
+                if N == 1:
+                    fdicts[0][name] = t
+                    continue
+                for f, part in zip(fdicts, t.split(num_boxes_per_image)):
+                    f[name] = part
         self.last_records, self.last_raw = records, raw
         return instances
 
