@@ -414,7 +414,7 @@ class ROIHeads3DB200(nn.Module):
         eng = self._get_engine()
         # the weight check (a version / address scan of ~35 parameters, 11 us) is only needed before the FC stack: in the
         # steady state it runs after the pooling launches (the pooling phase reads no weights)
-        prepared = not (on_host and eng.ready)
+        prepared = not eng.ready
         if prepared:
             eng.prepare(device, self.priors_dims_per_cat, self.priors_z_scales, getattr(self, "priors_z_stats", None))
         counts_key = (tuple(num_boxes_per_image), device)
@@ -430,11 +430,16 @@ class ROIHeads3DB200(nn.Module):
             except (RuntimeError, TypeError):
                 torch.cat([t.to(dst.dtype) for t in ts], out=dst)
 
-        state = None
+        def gather(ts, dt):   # one Instances (the GDINO flow) with the right dtype on the device: no copy at all
+            t = ts[0] if len(ts) == 1 else torch.cat(ts)
+            return t.to(device=device, dtype=dt).contiguous()
+
         if on_host:
             cat_into(box_ts, stage[:o_cam].view(n, 4))
             boxes = stage[:o_cam].to(device, non_blocking=True).view(n, 4)
-            state = eng.begin(feats, boxes, batch_idx)      # the GPU starts here
+        else:
+            boxes = gather(box_ts, torch.float32)
+        state = eng.begin(feats, boxes, batch_idx)          # the GPU starts here
         if not prepared:
             eng.prepare(device, self.priors_dims_per_cat, self.priors_z_scales, getattr(self, "priors_z_stats", None))
 
@@ -474,16 +479,10 @@ class ROIHeads3DB200(nn.Module):
         if on_host:
             scores = rest_d[o_sc - o_cam:o_sc - o_cam + n] if with_scores else None
             classes = rest_d[o_cls - o_cam:o_cls - o_cam + 2 * n].view(torch.int64)
-            records, raw = eng.finish(state, classes, scores, cams, want_raw=return_raw)
         else:
-            def gather(ts, dt):   # one Instances (the GDINO flow) with the right dtype on the device: no copy at all
-                t = ts[0] if len(ts) == 1 else torch.cat(ts)
-                return t.to(device=device, dtype=dt).contiguous()
-
-            boxes = gather(box_ts, torch.float32)
             classes = gather([f["pred_classes"] for f in fdicts], torch.int64)
             scores = gather([f["scores"] for f in fdicts], torch.float32) if with_scores else None
-            records, raw = eng.forward(feats, boxes, classes, scores, batch_idx, cams, want_raw=return_raw)
+        records, raw = eng.finish(state, classes, scores, cams, want_raw=return_raw)
 
         # write-back (roi_heads.py:811-843): the Instances fields are views into the [n,48] records.  One split along the
         # columns, then per field one unbind over the images when the box counts are equal (the usual fixed top-k

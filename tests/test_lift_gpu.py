@@ -456,24 +456,31 @@ def test_plugin_host_instances_repeated_calls(name):
 
 @pytest.mark.parametrize("name", ["c1_full", "priors_exp_zsigmoid", "ragged_with_empty"])
 def test_two_phase_call_equals_single_call(name):
-    """Host-resident Instances go through `ovm_lift_forward_phase` twice (pool as soon as the boxes are over, head once
-    cameras / scores / classes are), device-resident ones through one `ovm_lift_forward`: same records (fc1's split-K
+    """The plugin goes through `ovm_lift_forward_phase` twice (pool as soon as the boxes are on the device, head once
+    cameras / scores / classes are), `LiftEngine.forward` through one `ovm_lift_forward`: same records (fc1's split-K
     partial sums meet in L2 atomics, so to 1e-4 rather than bit for bit) and the same levels."""
     case = gc.CASE_BY_NAME[name]
-    _, _, head_h, res_h = _run_plugin(case, host_instances=True, return_raw=True)
-    rec_h, raw_h, lv_h = head_h.last_records.clone(), head_h.last_raw.clone(), head_h._engine.last_levels.clone()
-    _, _, head_d, res_d = _run_plugin(case, host_instances=False, return_raw=True)
-    rec_d, raw_d = head_d.last_records, head_d.last_raw
-    n = rec_d.shape[0]
+    inp, _, head, res = _run_plugin(case, host_instances=True, return_raw=True)
+    rec_h, raw_h = head.last_records.clone(), head.last_raw.clone()
+    n = rec_h.shape[0]
+    eng, dev = head._engine, _dev()
+    lv_h = eng.last_levels[:n].clone()
+    boxes, bidx, counts = _cat_inputs(inp, dev)
+    cams = torch.zeros(len(counts), 12)
+    for i in range(len(counts)):
+        cams[i, :9] = inp.Ks[i].reshape(9)
+        cams[i, 9] = inp.im_scales_ratio[i]
+        cams[i, 10] = inp.im_dims[i][0]
+    scores = torch.cat(inp.scores).to(dev) if case.with_scores else None
+    feats = [t.to(dev) for t in inp.features]
+    rec_d, raw_d = eng.forward(feats, boxes, torch.cat(inp.classes).to(dev), scores, bidx, cams.to(dev), want_raw=True)
     assert rec_h.shape == rec_d.shape and n > 0
-    assert torch.equal(lv_h[:n], head_d._engine.last_levels[:n])
+    assert torch.equal(lv_h, eng.last_levels[:n])
     fin = torch.isfinite(rec_d)
     assert torch.equal(torch.isfinite(rec_h), fin)
     scale = rec_d[fin].abs().max().clamp_min(1e-30)
     assert float((rec_h - rec_d)[fin].abs().max() / scale) <= 1e-4
     assert float((raw_h - raw_d)[:, :13].abs().max() / raw_d[:, :13].abs().max().clamp_min(1e-30)) <= 1e-4
-    for a, b in zip(res_h, res_d):
-        assert a.pred_bbox3D.shape == b.pred_bbox3D.shape and a.pred_pose.shape == b.pred_pose.shape
 
 
 def test_plugin_n0_returns_input_untouched():
