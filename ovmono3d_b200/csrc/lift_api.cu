@@ -280,10 +280,17 @@ int ovm_lift_forward_phase(const ovm_pooler_t* pooler, const ovm_fc_stack_t* fc,
     const void* h = nullptr;
     int64_t ldh = 0;
     // OVM_TAIL_DEFER=0: the split-K layer before the tail finishes itself (per-tile counters, round 2's first version)
-    static const bool defer_ok = [] { const char* v = getenv("OVM_TAIL_DEFER"); return !v || atoi(v) != 0; }();
+    // (and OVM_GEMM_SLOTS=1, the bit-reproducible split-K exchange, keeps the finish inside the GEMM: its owners sum the
+    // partials in a fixed order; the deferred finish reads sums that met in L2 atomics)
+    static const bool defer_ok = [] {
+      const char* v = getenv("OVM_TAIL_DEFER");
+      const char* sl = getenv("OVM_GEMM_SLOTS");
+      return (!v || atoi(v) != 0) && !(sl && atoi(sl) != 0);
+    }();
     TailPending pending{nullptr, 0, nullptr};
     rc = run_fc_group(fc->layers, fc->num_fc - 1, /*ends_stack=*/false, fmt, ws->pooled, ws->ld_pooled, n, ws, nullptr, 0,
-                      stream, stage, &h, &ldh, defer_ok ? &pending : nullptr);
+                      stream, stage, &h, &ldh, defer_ok && n >= 256 ? &pending : nullptr);   // (80 boxes: the finish is
+                      // cheap and the tail's conversion is not hidden -- measured 69.4 vs 71.1 us per step at C1)
     if (rc != OVM_OK) return rc;
     rc = fc_tail_launch(h, ldh, fmt, alt ? tail.weight_alt : tail.weight, alt ? tail.ldw_alt : tail.ldw, tail.bias, tail.N,
                         tail.K, cfg, heads, boxes, classes, scores, batch_idx, cams, pooler->num_images, n, records, raw,

@@ -157,7 +157,9 @@ def test_fullsize_parity(name, layout):
     head = head.to(dev).eval()
     eng = head._get_engine()
     eng.prepare(dev, head.priors_dims_per_cat, head.priors_z_scales, getattr(head, "priors_z_stats", None))
-    assert eng.tail_fused and eng.tail_precision == "f16", "the full-size workloads run the fused fp16 tail"
+    if eng.tail_precision != "f16":
+        pytest.skip("OVM_TAIL_PRECISION=%s: this test emulates the default fp16 tail operands" % eng.tail_precision)
+    assert eng.tail_fused, "the full-size workloads run the fused tail"
 
     feats = [f.to(dev) for f in inp.features]
     if layout == "channels_last":     # the channels-last ROIAlign kernel: same bounds, nothing copied back to NCHW
