@@ -87,6 +87,7 @@ struct RoiArgs {
   int evict_first;              // feature loads carry the L2 evict_first policy (OVM_ROI_EVICT)
   int ring_floats, stage_floats;   // shared-memory ring / largest stage of the pooling kernel that will run (plan_box needs them)
   const int* box_hdr;              // [n][kHdrInts] per-box headers written by roi_plan_kernel (with `order`)
+  int plan_boxes;                  // boxes (= planning warps) per CTA of roi_plan_kernel, <= kPlanBoxes
   int cl;                          // 0, or channels per lane (2 / 4) when every level is channels-last (NHWC) and TMA-addressable
   int chunk_ch;                    // channels per chunk: 32 (NCHW: lane = channel) or 32 cl (channels-last)
   unsigned long long* trace;    // optional [grid, 16] %globaltimer stamps (ovm_roi_set_trace), else NULL
@@ -568,9 +569,22 @@ __device__ void plan_box_warp(const RoiArgs& a, float x1, float y1, float x2, fl
 }
 
 __device__ void sort_items(const RoiArgs& a, int* __restrict__ ws, const int* hdr);
+// planner timeline (tools/roi_trace.py --plan): trace rows 65000 + CTA, slots 0 entry, 1 after the wait, 2 boxes planned,
+// 3 last CTA elected, 4 mean known, 5 histogram, 6 scan, 7 items written
+__device__ __forceinline__ void plan_stamp(const RoiArgs& a, int slot) {
+  if (a.trace && threadIdx.x == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    a.trace[(size_t)(65000 + blockIdx.x) * 16 + slot] = t;
+  }
+}
 
-constexpr int kPlanBoxes = 32;  // boxes (= planning warps) per CTA.  8 per CTA (200 CTAs of 1024 threads, 24 warps of each idle until
-                                // the sort) measured slower: planner stage 14.9 -> 17.0 us
+constexpr int kPlanBoxes = 32;  // most boxes (= planning warps) per CTA; the launch uses kPlanBoxesDefault (OVM_ROI_PLANBOXES)
+// Measured at C2 (tools/roi_trace.py --plan: boxes planned / items written, us after entry): 32 per CTA (50 CTAs) 4.6 / 10.2,
+// 16 (100 CTAs) 3.6 / 9.7, 11 (146 CTAs, one per SM) 3.3 / 9.5, 8 (200 CTAs: a second wave of 1024-thread CTAs) 2.8-6.7 / 12.3.
+// Planning one box is a ~1000-instruction dependent chain (3 us even with 11 warps per SM); after it the last CTA needs
+// ~6 us alone: election 1.3, costs + mean 1.8, histogram 1.1, scan 0.4, items 1.4.
+constexpr int kPlanBoxesDefault = 16;
 // First kernel of the lift: one warp per box, kPlanBoxes boxes per CTA, spread over the SMs.  Writes the per-box headers
 // (hdr [n][kHdrInts]) and the level of every box; the last CTA to finish then sorts the work items (sort_items).
 __global__ void __launch_bounds__(1024) roi_plan_kernel(const RoiArgs a, int* __restrict__ hdr, int* __restrict__ ws) {
@@ -579,11 +593,13 @@ __global__ void __launch_bounds__(1024) roi_plan_kernel(const RoiArgs a, int* __
   // comes after it -- so no later kernel of the chain can start before that point, and they may read the call's inputs
   // (boxes, classes, cameras, weights) ahead of their own wait.  It also covers the workspace, which the ROIAlign
   // kernel of the previous call may still be reading.
+  plan_stamp(a, 0);
   pdl_wait();
   pdl_trigger();
+  plan_stamp(a, 1);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int box = blockIdx.x * kPlanBoxes + warp;
-  if (warp < kPlanBoxes && box < a.n) {
+  const int box = blockIdx.x * a.plan_boxes + warp;
+  if (warp < a.plan_boxes && box < a.n) {
     const float x1 = a.boxes[4 * box + 0], y1 = a.boxes[4 * box + 1], x2 = a.boxes[4 * box + 2], y2 = a.boxes[4 * box + 3];
     const int image = a.batch_idx[box];
     plan_box_warp(a, x1, y1, x2, y2, image, box, lane, h[warp]);
@@ -597,11 +613,14 @@ __global__ void __launch_bounds__(1024) roi_plan_kernel(const RoiArgs a, int* __
   __shared__ int last;
   __threadfence();
   __syncthreads();
+  plan_stamp(a, 2);
   if (threadIdx.x == 0) last = atomicAdd(ws + 1, 1) == (int)gridDim.x - 1;
   __syncthreads();
   if (!last) return;
   __threadfence();
+  plan_stamp(a, 3);
   sort_items(a, ws, hdr);
+  plan_stamp(a, 7);
 }
 
 // Work items for a grid of CTAs with very different run times.  One CTA turns the planned boxes into items
@@ -643,6 +662,7 @@ __device__ void sort_items(const RoiArgs& a, int* __restrict__ ws, const int* hd
     if (lane == 0) mean_area = t / (float)a.n;
   }
   __syncthreads();
+  plan_stamp(a, 4);
   const int chunks = (a.C + a.chunk_ch - 1) / a.chunk_ch;
   const float mean = mean_area * a.split_factor;
   // chunks per item: the largest power of two with area * cpi <= mean * chunks (never more than the launch's
@@ -671,6 +691,7 @@ __device__ void sort_items(const RoiArgs& a, int* __restrict__ ws, const int* hd
     atomicAdd(&hist[slot_of(ar, cpi)], (chunks + cpi - 1) / cpi);
   }
   __syncthreads();
+  plan_stamp(a, 5);
   {   // exclusive scan of the 64 x 32 counters in (bucket, warp) order: two per thread
     const int e0 = 2 * tid, e1 = 2 * tid + 1;
     const int i0 = (e0 >> 5) * 33 + (e0 & 31), i1 = (e1 >> 5) * 33 + (e1 & 31);
@@ -703,6 +724,7 @@ __device__ void sort_items(const RoiArgs& a, int* __restrict__ ws, const int* hd
     hist[i1] = before + h0;
   }
   __syncthreads();
+  plan_stamp(a, 6);
   // an item = (box, first chunk | chunks << 16): the pooling CTA reads it, then the box's header (roi_plan_kernel).
   // (Copying the 160-byte header into every item made this one CTA move 0.6 MB: 28 us instead of 13 for the stage.)
   auto emit = [&](int box, float ar) {
@@ -1272,6 +1294,10 @@ int roi_align_launch(const ovm_pooler_t* p, const float* boxes, const int32_t* b
               ws_need);
   a.xalign_mask = tune.align8 ? ~7 : ~3;
   a.evict_first = tune.evict;
+  {
+    static const int pb = [] { const char* v = getenv("OVM_ROI_PLANBOXES"); int x = v ? atoi(v) : 0; return x >= 1 && x <= kPlanBoxes ? x : 0; }();
+    a.plan_boxes = pb ? pb : kPlanBoxesDefault;
+  }
   static SmemOptIn optA, optB, optC, optD;
   auto kC = roi_align_kernel<12288, 6144, 0, 2>;   // channels-last pyramid, 64-channel chunks
   auto kD = roi_align_kernel<12288, 6144, 3, 4>;   // channels-last pyramid, 128-channel chunks
@@ -1289,7 +1315,7 @@ int roi_align_launch(const ovm_pooler_t* p, const float* boxes, const int32_t* b
   if (a.order) {
     int* box_hdr = p->order_ws + ws_items;
     a.box_hdr = box_hdr;
-    OVM_CUDA(launch_pdl(roi_plan_kernel, dim3((unsigned)((n + kPlanBoxes - 1) / kPlanBoxes)), dim3(1024), 0, stream, a, box_hdr, p->order_ws));
+    OVM_CUDA(launch_pdl(roi_plan_kernel, dim3((unsigned)((n + a.plan_boxes - 1) / a.plan_boxes)), dim3(1024), 0, stream, a, box_hdr, p->order_ws));
     OVM_LAUNCHED("roi_plan_kernel");
   }
   if (stage_idx) {

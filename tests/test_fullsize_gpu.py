@@ -250,6 +250,66 @@ def test_fullsize_parity(name, layout):
         "pose geodesic median %.3f p99 %.3f deg" % (float(ang.median()), float(ang.quantile(0.99)))
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("fc_dim", [128, 256, 512])
+def test_fused_tail_finishes_fc1_at_every_fc_dim(fc_dim):
+    """FC_DIM 128 / 256 / 512 (clusters of 1 / 2 / 4 CTAs, 128 / 64 / 32 rows converted per CTA, the ungrouped and the
+    grouped conversion): fc1 runs split-K and only accumulates, the fused tail applies its bias / ReLU / fp16 rounding on
+    the way in and hands the accumulator back zeroed.  Kernel correctness against the oracle with the product's operand
+    rounding, three calls in a row (a dirty accumulator would show in the second)."""
+    from ovmono3d_b200.compat import ShapeSpec
+    from ovmono3d_b200.config import get_cfg
+    from ovmono3d_b200.roi_heads import build_roi_heads
+
+    w = workloads.Workload("X-fc%d" % fc_dim, "fused tail at FC_DIM %d" % fc_dim, canvas=448, channels=64, num_images=2,
+                           boxes_per_image=160, seed=77 + fc_dim, fc_dim=fc_dim)
+    dev = torch.device("cuda:0")
+    inp, weights = w.make_inputs(), w.make_weights()
+    counts = [len(b) for b in inp.boxes]
+    n = sum(counts)
+    assert n >= 256, "the deferred finish is used from 256 boxes"
+    c = get_cfg()
+    c.MODEL.ROI_HEADS.NAME = "ROIHeads3DB200"
+    c.MODEL.ROI_HEADS.IN_FEATURES = list(w.in_features)
+    c.MODEL.ROI_CUBE_HEAD.DIMS_PRIORS_ENABLED = False
+    c.MODEL.ROI_CUBE_HEAD.FC_DIM = fc_dim
+    head = build_roi_heads(c, {f: ShapeSpec(channels=w.channels, stride=s) for f, s in zip(w.in_features, w.strides)})
+    head.cube_head.load_state_dict(weights)
+    head = head.to(dev).eval()
+    eng = head._get_engine()
+    eng.prepare(dev, head.priors_dims_per_cat, head.priors_z_scales, getattr(head, "priors_z_stats", None))
+    if eng.tail_precision != "f16":
+        pytest.skip("emulates the default fp16 tail operands")
+    assert eng.tail_fused
+    feats = [f.to(dev) for f in inp.features]
+    boxes = torch.cat(inp.boxes).to(dev)
+    classes = torch.cat(inp.classes).to(dev)
+    scores = torch.cat(inp.scores).to(dev)
+    bidx = torch.from_numpy(np.repeat(np.arange(len(counts), dtype=np.int32), counts)).to(dev)
+    cams = torch.zeros(len(counts), 12)
+    for i in range(len(counts)):
+        cams[i, :9] = inp.Ks[i].reshape(9)
+        cams[i, 9] = inp.im_scales_ratio[i]
+        cams[i, 10] = inp.im_dims[i][0]
+    cams = cams.to(dev)
+    recs = [eng.forward(feats, boxes, classes, scores, bidx, cams, want_raw=True) for _ in range(3)]
+    torch.cuda.synchronize()
+    rec, raw = recs[0][0].cpu(), recs[0][1].cpu()
+    for r2, _ in recs[1:]:
+        assert float((rec - r2.cpu()).abs().max()) <= 1e-4 * float(rec.abs().max()), "a repeated call must reproduce the records"
+    emu, emu_raw6 = _oracle(w, inp, weights, True)
+    mine = _split_records(rec, counts)
+    for f in DIRECT_FIELDS:
+        mx, _ = _per_image_err(mine[f], getattr(emu, f))
+        assert mx <= KERNEL_TOL, "%s vs product-operand oracle: %.3g" % (f, mx)
+    emu_raw = torch.cat([_raw_heads(emu), emu_raw6], dim=1)
+    kraw_err = (raw[:, :13] - emu_raw).abs()
+    assert float((kraw_err.amax(0) / emu_raw.abs().amax(0).clamp_min(1e-30)).max()) <= KERNEL_TOL, "raw head outputs"
+    k_allowed = COND_SAFETY * kraw_err[:, 7:13].double().norm(dim=1) * _conditioning(emu_raw6) + KERNEL_TOL
+    k_pose = (torch.cat(mine["pred_pose"]).double() - torch.cat(emu.pred_pose).double()).abs().amax(dim=(1, 2))
+    assert bool((k_pose <= k_allowed).all()), "pose vs product-operand oracle"
+
+
 if __name__ == "__main__":
     if "--format-error" in sys.argv:
         torch.set_num_threads(torch.get_num_threads())

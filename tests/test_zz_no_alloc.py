@@ -11,6 +11,7 @@ same plan, so the results are compared exactly; the oracle tolerance of tests/te
 top against torchvision's ROIAlign rules through the oracle.
 """
 import ctypes as C
+import gc
 
 import numpy as np
 import pytest
@@ -50,12 +51,16 @@ def test_static_scratch_matches_allocating_entry_point_twice(layout):
         pooler, keep = ops.make_pooler(feats, scales, 7, 0)
         out = torch.full((n, 128, 7, 7), float("nan"), device=dev)
         lv = torch.full((n,), -7, dtype=torch.int32, device=dev)
+        gc.collect()                      # (tensors of earlier tests may be freed at any moment: count allocations, not bytes)
         torch.cuda.synchronize()
-        mem0 = torch.cuda.memory_allocated(dev)
+        allocs0 = torch.cuda.memory_stats(dev)["allocation.all.allocated"]
+        segs0 = torch.cuda.memory_stats(dev)["segment.all.allocated"]
         free0, _ = torch.cuda.mem_get_info(dev)
         ops.roi_align_static(pooler, boxes, bidx, out, lv)
         torch.cuda.synchronize()
-        assert torch.cuda.memory_allocated(dev) == mem0, "torch allocated during the call"
+        st = torch.cuda.memory_stats(dev)
+        assert st["allocation.all.allocated"] == allocs0 and st["segment.all.allocated"] == segs0, \
+            "torch allocated device memory during the call"
         if call == 1:     # (the first call may load kernel images lazily; by the second one everything is resident)
             assert torch.cuda.mem_get_info(dev)[0] >= free0, "device memory was allocated during the call"
         assert torch.equal(lv, want_lv), "call %d: levels differ" % call

@@ -16,11 +16,12 @@ def main():
     lib = ops.load_library()
     dev = torch.device("cuda:0")
     # optional: strides (comma list), canvas, images, boxes per image   e.g.  4,8,16,32 1024 16 100
-    strides = tuple(int(v) for v in sys.argv[1].split(",")) if len(sys.argv) > 1 else (7, 14, 28)
-    canvas = int(sys.argv[2]) if len(sys.argv) > 2 else 896
-    N = int(sys.argv[3]) if len(sys.argv) > 3 else 16
-    k = int(sys.argv[4]) if len(sys.argv) > 4 else 100
-    inp = synth.make_inputs(1235 if len(sys.argv) == 1 else 4321, N, k, strides=strides, canvas=canvas)
+    argv = [a for a in sys.argv if not a.startswith("--")]
+    strides = tuple(int(v) for v in argv[1].split(",")) if len(argv) > 1 else (7, 14, 28)
+    canvas = int(argv[2]) if len(argv) > 2 else 896
+    N = int(argv[3]) if len(argv) > 3 else 16
+    k = int(argv[4]) if len(argv) > 4 else 100
+    inp = synth.make_inputs(1235 if len(argv) == 1 else 4321, N, k, strides=strides, canvas=canvas)
     feats = [f.to(dev) for f in inp.features]
     if os.environ.get("OVM_TRACE_LAYOUT", "nchw") == "channels_last":
         feats = [f.contiguous(memory_format=torch.channels_last) for f in feats]
@@ -39,6 +40,18 @@ def main():
     lib.ovm_roi_set_trace(None)
     torch.cuda.synchronize()
     t = trace.cpu().numpy().reshape(-1, 16)
+    if "--plan" in sys.argv:
+        pl = t[65000:65000 + 512].astype(np.float64)
+        pl = pl[pl[:, 0] > 0]
+        p0 = pl[:, 0].min()
+        names = ["entry", "after the wait", "boxes planned", "last CTA elected", "mean known", "histogram", "scan", "items written"]
+        print("roi_plan_kernel: %d CTAs; first ROIAlign CTA enters %.2f us after the planner's first" % (
+            len(pl), (t[:60000][t[:60000, 0] > 0][:, 0].min() - p0) / 1e3))
+        for j, nm in enumerate(names):
+            v = pl[:, j][pl[:, j] > 0]
+            print("  %-18s min %6.2f  median %6.2f  max %6.2f us  (%d CTAs)" % (nm, (v.min() - p0) / 1e3, (np.median(v) - p0) / 1e3,
+                                                                            (v.max() - p0) / 1e3, len(v)))
+    t = t[:60000]
     t = t[t[:, 0] > 0]
     t0 = t[:, 0].min()
     tma = t[:, 12] > 0
