@@ -339,10 +339,13 @@ fc_tail_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   // Two threads per box: role 0 takes the pose / dims chain and writes the record, role 1 the centre chain (projected
   // centre, allocentric rotation, depth, back-projection, score).  On one thread the decode is a ~1100-instruction
   // dependent chain at ~10 cycles per instruction (5.9 us); the two chains are independent until the last matrix product.
+  // The two roles of a box sit in DIFFERENT warps (role 1 starts at a warp boundary): with 16 boxes per CTA both used to
+  // share one warp, whose divergent halves ran the two chains one after the other.
   const int e = threadIdx.x - 64;
-  const int role = e >= rpc ? 1 : 0, t = e - role * rpc;
+  const int rs = rpc < 32 ? 32 : rpc;
+  const int role = e >= rs ? 1 : 0, t = e - role * rs;
   const int my_row = m_tile * kTM + rank * rpc + t;
-  const bool decoder = e >= 0 && e < 2 * rpc && my_row < g.d.n;
+  const bool decoder = e >= 0 && t < rpc && e < rs + rpc && my_row < g.d.n;
   BoxIn in{};
   BoxCam cam{};
   if (decoder) {
