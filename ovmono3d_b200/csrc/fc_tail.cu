@@ -177,13 +177,16 @@ __device__ __forceinline__ void cluster_sync_all() {
 
 // Row r of the class-agnostic head stack in decode order (deltas 0-1, dims 2-4, z 5, uncertainty 6 if any, pose after)
 __device__ __forceinline__ const float* agnostic_head_row(const ovm_head_weights_t& w, int r, int conf_rows, int K,
-                                                          float* bias) {
-  if (r < 2) { *bias = w.b_deltas[r]; return w.w_deltas + (long long)r * K; }
-  if (r < 5) { *bias = w.b_dims[r - 2]; return w.w_dims + (long long)(r - 2) * K; }
-  if (r == 5) { *bias = w.b_z[0]; return w.w_z; }
-  if (r == 6 && conf_rows) { *bias = w.b_uncert[0]; return w.w_uncert; }
-  *bias = w.b_pose[r - 6 - conf_rows];
-  return w.w_pose + (long long)(r - 6 - conf_rows) * K;
+                                                          float* bias) {   // bias: NULL = not wanted (no load)
+  const float* b;
+  const float* row;
+  if (r < 2) { b = w.b_deltas + r; row = w.w_deltas + (long long)r * K; }
+  else if (r < 5) { b = w.b_dims + (r - 2); row = w.w_dims + (long long)(r - 2) * K; }
+  else if (r == 5) { b = w.b_z; row = w.w_z; }
+  else if (r == 6 && conf_rows) { b = w.b_uncert; row = w.w_uncert; }
+  else { b = w.b_pose + (r - 6 - conf_rows); row = w.w_pose + (long long)(r - 6 - conf_rows) * K; }
+  if (bias) *bias = *b;
+  return row;
 }
 
 // ovm_head_set_trace: [grid, 8] %globaltimer stamps per CTA -- 0 entry, 1 set-up + staging done (cluster barrier passed),
@@ -318,23 +321,6 @@ fc_tail_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"((uint32_t)kTN) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
-  // parameters of the model (not results of the kernels before): staged while fc1 is still running
-  if (warp >= 2) {
-    const int e = threadIdx.x - 64;             // 0 .. 255
-    const int col0 = rank * kTN;
-    for (int i = e; i < kTN * kHwStride; i += kTailEpiWarps * 32) {
-      const int r = i / kTN, j = i - r * kTN;   // consecutive threads read consecutive columns of one head row
-      float v = 0.f;
-      if (r < nrows) {
-        float b;
-        const float* row = agnostic_head_row(g.d.w, r, conf_rows, g.N, &b);
-        v = __ldg(row + col0 + j);
-        if (j == 0) hbias[r] = b;
-      }
-      hw_t[j * kHwStride + r] = v;
-    }
-    if (e < kTN) b2s[e] = __ldg(g.bias + col0 + e);
-  }
   // the boxes this CTA decodes are inputs of the call (complete before the chain's first kernel): loaded ahead of the wait
   // Two threads per box: role 0 takes the pose / dims chain and writes the record, role 1 the centre chain (projected
   // centre, allocentric rotation, depth, back-projection, score).  On one thread the decode is a ~1100-instruction
@@ -348,10 +334,36 @@ fc_tail_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const bool decoder = e >= 0 && t < rpc && e < rs + rpc && my_row < g.d.n;
   BoxIn in{};
   BoxCam cam{};
-  if (decoder) {
-    in = load_box_in(g.d, my_row);
-    cam = box_camera(cfg, in);
+  if (decoder) in = load_box_in(g.d, my_row);   // two dependent global loads (image index -> camera row): issued first, in
+                                                // flight under the staging loads below; consumed by box_camera after them
+  // parameters of the model (not results of the kernels before): staged while fc1 is still running
+  if (warp >= 2) {
+    const int e = threadIdx.x - 64;             // 0 .. 255
+    const int col0 = rank * kTN;
+    // thread -> column j of head rows r0, r0 + 2, .. (consecutive threads read consecutive columns of one row).  All
+    // eight loads are issued before the first store: as a load / store loop this was eight serial round trips (5 us of
+    // the 6 us set-up, measured with a stamp ahead of the cluster barrier).
+    static_assert(kTN * kHwStride == 8 * kTailEpiWarps * 32 && kTailEpiWarps * 32 == 2 * kTN, "8 head rows per thread");
+    const int j = e & (kTN - 1), r0 = e >> 7;
+    float v[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int r = r0 + 2 * k;
+      const int rr = r < nrows ? r : 0;
+      const float* row = agnostic_head_row(g.d.w, rr, conf_rows, g.N, nullptr);
+      v[k] = __ldg(row + col0 + j);
+      if (r >= nrows) v[k] = 0.f;
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) hw_t[j * kHwStride + r0 + 2 * k] = v[k];
+    if (e < kMaxHeadRows && e < nrows) {
+      float b = 0.f;
+      agnostic_head_row(g.d.w, e, conf_rows, g.N, &b);
+      hbias[e] = b;
+    }
+    if (e < kTN) b2s[e] = __ldg(g.bias + col0 + e);
   }
+  if (decoder) cam = box_camera(cfg, in);
 
   tcgen05_fence_before();
   cluster_sync_all();        // barriers initialised, TMEM allocated, staging visible; every CTA of the cluster has started
