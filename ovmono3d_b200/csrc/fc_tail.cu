@@ -211,9 +211,8 @@ __device__ __noinline__ void finish_prev_layer(float* acc, long long acc_ld, con
   auto conv_bar = [&](int c) { return c == 0 ? tfull_bar + 8 : tfull_bar + 16 + 8 * (uint32_t)c; };
     const int slice = kTM / cs;
     const int row0 = m_tile * kTM + rank * slice;
-    auto finish4 = [&](float4 w, long long row, int c) {
+    auto finish4 = [&](float4 w, float4 bv, long long row, int c) {
       __stcg(reinterpret_cast<float4*>(acc + row * acc_ld + c), make_float4(0.f, 0.f, 0.f, 0.f));
-      const float4 bv = __ldg(reinterpret_cast<const float4*>(bias_prev + c));
       w.x += bv.x; w.y += bv.y; w.z += bv.z; w.w += bv.w;
       w.x = w.x < 0.f ? 0.f : w.x; w.y = w.y < 0.f ? 0.f : w.y;     // torch.relu keeps NaN
       w.z = w.z < 0.f ? 0.f : w.z; w.w = w.w < 0.f ? 0.f : w.w;
@@ -226,6 +225,12 @@ __device__ __noinline__ void finish_prev_layer(float* acc, long long acc_ld, con
     if (conv_grouped) {
       // slice * K = 16384 floats = 4096 float4 = 16 per thread, 4 per thread and group; k4g float4 per row and group
       const int k4g = K / (4 * kConvGroups), sh = __ffs(k4g) - 1;
+      // the thread's column within a group is the same for its four rows (256 is a multiple of k4g): one bias float4 per
+      // group, loaded ahead of everything (inside the loop it was one more round trip per group, behind the fence)
+      float4 bvg[kConvGroups];
+#pragma unroll
+      for (int grp = 0; grp < kConvGroups; ++grp)
+        bvg[grp] = __ldg(reinterpret_cast<const float4*>(bias_prev + (grp * k4g + (et & (k4g - 1))) * 4));
       float4 x[16];
 #pragma unroll
       for (int u = 0; u < 16; ++u) {
@@ -240,7 +245,7 @@ __device__ __noinline__ void finish_prev_layer(float* acc, long long acc_ld, con
         for (int v = 0; v < 4; ++v) {
           const int rem = v * 256 + et;
           const int r = rem >> sh, c = (grp * k4g + (rem & (k4g - 1))) * 4;
-          if (row0 + r < n) finish4(x[grp * 4 + v], row0 + r, c);
+          if (row0 + r < n) finish4(x[grp * 4 + v], bvg[grp], row0 + r, c);
         }
         asm volatile("fence.proxy.async.global;" ::: "memory");
         mbar_arrive(conv_bar(grp));
@@ -261,7 +266,7 @@ __device__ __noinline__ void finish_prev_layer(float* acc, long long acc_ld, con
         for (int u = 0; u < kBatch; ++u) {
           const int i = i0 + u * kTailEpiWarps * 32;
           const int r = i / k4, c = (i - r * k4) * 4;
-          if (i < total && row0 + r < n) finish4(x[u], row0 + r, c);
+          if (i < total && row0 + r < n) finish4(x[u], __ldg(reinterpret_cast<const float4*>(bias_prev + c)), row0 + r, c);
         }
       }
       asm volatile("fence.proxy.async.global;" ::: "memory");
